@@ -1,0 +1,192 @@
+/*
+ * spray_gpu.h — C ABI of libspraygpu: the B200 (sm_100a) replacement for the Embree calls on SpRay's
+ * per-domain ray-tracing hot path.  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the SpRay tree).
+ * All functions return SPRAYGPU_OK (0) or a negative error code; spraygpu_last_error() gives the text.
+ * The reference never propagates errors (CHECK/LOG(FATAL) abort, trimesh_buffer.cc:68-113); the C++
+ * shim in host/ aborts on non-zero to mirror that.
+ *
+ * Pointer arguments marked [h|d] may be host or device pointers (detected with
+ * cudaPointerGetAttributes).  Host pointers are staged through device memory inside the call and the
+ * call returns after the results are back on the host; device pointers are used in place, the work is
+ * enqueued on the device's stream and the call returns without synchronising.
+ *
+ * Threading: intersect/occluded/trace calls on committed scenes may be issued from any host thread
+ * but are serialised per spraygpu_device (one stream).  set_mesh/commit/destroy must be externally
+ * serialised per scene — the same contract as the reference (load/commit inside `omp single`,
+ * src/ooc/ooc_pcontext.h:145-154).
+ */
+#ifndef SPRAY_GPU_H
+#define SPRAY_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SPRAYGPU_API __attribute__((visibility("default")))
+#else
+#define SPRAYGPU_API
+#endif
+
+#define SPRAYGPU_OK 0
+#define SPRAYGPU_ERR_CUDA (-1)
+#define SPRAYGPU_ERR_ARG (-2)
+#define SPRAYGPU_ERR_STATE (-3)
+#define SPRAYGPU_ERR_LIMIT (-4)
+
+#define SPRAYGPU_MAX_DOMAINS 512      /* 9 key bits */
+#define SPRAYGPU_MAX_PRIMS (1u << 23) /* 23 key bits */
+#define SPRAYGPU_MAX_LIGHTS 8
+#define SPRAYGPU_KEY_MISS 0xFFFFFFFFFFFFFFFFull
+
+typedef struct spraygpu_device_s* spraygpu_device;
+typedef struct spraygpu_scene_s* spraygpu_scene;
+
+/* Ray record, 32 B.  Replaces the org/dir/tnear/tfar head of RTCRay / RTCRayIntersection
+ * (src/render/rays.h:117-170,246-274).  tmin is honoured; tmax is IGNORED (= inf) exactly like every
+ * reference call site (rays.h:345-363,389-423 set tfar = SPRAY_FLOAT_INF for radiance AND shadow). */
+typedef struct { float ox, oy, oz, tmin, dx, dy, dz, tmax; } spraygpu_ray;
+
+/* Hit key: (float_bits(t) << 32) | (domain << 23) | primID ; SPRAYGPU_KEY_MISS when nothing was hit.
+ * Monotone in t because t > tnear = 0.001 > 0 (src/render/spray.h:46).  Replaces the
+ * tfar/geomID/primID output fields of RTCRay and the per-sample t-buffer entry of ooc::VBuf /
+ * insitu::VBuf (src/ooc/ooc_vbuf.cc:54-112, src/insitu/insitu_vbuf.h:74-152). */
+typedef uint64_t spraygpu_key;
+
+enum { SPRAYGPU_MTL_DIFFUSE = 0, SPRAYGPU_MTL_MIRROR = 1, SPRAYGPU_MTL_GLASS = 2, SPRAYGPU_MTL_TRANSMISSION = 3 };
+/* Domain material: src/render/domain.h:34 (Bsdf*), src/io/scene_loader.cc:89-141.
+ * params: diffuse albedo rgb | mirror reflectance rgb | glass/transmission eta_exterior, eta_interior. */
+typedef struct { int32_t type; float params[3]; } spraygpu_material;
+
+enum { SPRAYGPU_LIGHT_POINT = 0, SPRAYGPU_LIGHT_DIFFUSE = 1 };
+/* src/render/light.h:41-89 ; src/io/scene_loader.cc:199-228 */
+typedef struct { int32_t type; float position[3]; float radiance[3]; } spraygpu_light;
+
+/* Pinhole camera frame as src/render/camera.h:128-160 stores it (computed on the host). */
+typedef struct {
+  float pos[3], lowerleft[3], wvec[3], hvec[3];
+  int32_t image_w, image_h;
+} spraygpu_camera;
+
+/* A blocking tile (src/render/tile.h Tile; produced by ImageScheduleTileList, tile.cc:317-391).
+ * samid of sample s of pixel (x,y) = spp * ((y - tile.y) * tile.w + (x - tile.x)) + s
+ * (src/ooc/ooc_tracer.inl:84-172). */
+typedef struct { int32_t x, y, w, h; } spraygpu_tile;
+
+enum { SPRAYGPU_SHADER_PT = 0, SPRAYGPU_SHADER_AO = 1 };
+/* Shader configuration: ShaderPt::init / ShaderAo::init (src/ooc/ooc_shader_pt.h:45-52,
+ * ooc_shader_ao.h) + Config fields (src/render/config.cc:33-73). */
+typedef struct {
+  int32_t shader;         /* SPRAYGPU_SHADER_* */
+  int32_t bounces;        /* cfg.bounces (>= 1) */
+  int32_t pixel_samples;  /* cfg.pixel_samples */
+  int32_t ao_samples;     /* cfg.ao_samples (area-light / AO sample count) */
+  float ks[3];            /* cfg.ks   (--blinn) */
+  float shininess;        /* cfg.shininess */
+  int32_t nlights;
+  spraygpu_light lights[SPRAYGPU_MAX_LIGHTS];
+} spraygpu_shade;
+
+typedef struct {
+  uint64_t eye_rays;        /* primary rays generated */
+  uint64_t radiance_rays;   /* closest-hit rays resolved (primary + bounce) */
+  uint64_t shadow_rays;     /* any-hit rays resolved */
+  uint64_t domain_tests;    /* (ray, domain) traversals started */
+  uint64_t nodes_visited;   /* BVH8 nodes fetched  (counters build only, else 0) */
+  uint64_t tris_tested;     /* triangles fetched   (counters build only, else 0) */
+  uint64_t hits;            /* radiance rays that hit */
+} spraygpu_stats;
+
+typedef struct {
+  uint64_t num_vertices, num_faces, num_nodes;
+  uint64_t node_bytes, tri_bytes, attr_bytes;
+  float bounds[6];
+  double build_ms;  /* device time of the last commit (CUDA events) */
+} spraygpu_scene_info;
+
+SPRAYGPU_API const char* spraygpu_last_error(void);
+SPRAYGPU_API const char* spraygpu_version(void);
+
+/* ---- device: replaces rtcNewDevice / rtcDeleteDevice (src/render/trimesh_buffer.cc:104,178;
+ *      wbvh_embree.cc:60) ---- */
+SPRAYGPU_API int spraygpu_device_create(int cuda_device, spraygpu_device* out);
+SPRAYGPU_API int spraygpu_device_destroy(spraygpu_device dev);
+/* Launch on an existing cudaStream_t (e.g. torch's current stream) instead of the default stream. */
+SPRAYGPU_API int spraygpu_device_set_stream(spraygpu_device dev, void* cuda_stream);
+SPRAYGPU_API int spraygpu_device_synchronize(spraygpu_device dev);
+/* kernels launched by this library since device_create (bench.py's gpu_launches) */
+SPRAYGPU_API uint64_t spraygpu_device_launch_count(spraygpu_device dev);
+
+/* ---- per-domain scene: replaces rtcDeviceNewScene / rtcDeleteScene / rtcNewTriangleMesh /
+ *      rtcSetBuffer2 / rtcUpdate / rtcEnable / rtcCommit (src/render/trimesh_buffer.cc:112,174,189-225) ---- */
+SPRAYGPU_API int spraygpu_scene_create(spraygpu_device dev, spraygpu_scene* out);
+SPRAYGPU_API int spraygpu_scene_destroy(spraygpu_scene scene);
+/* COPIES the mesh to the device (Embree borrows host arrays via rtcSetBuffer2; a GPU cannot).
+ * xyz: nv*3 floats (object space), idx: nf*3 uint32, rgb: nv packed 0x00RRGGBB (src/io/ply_loader.cc:247)
+ * or NULL.  [h|d] */
+SPRAYGPU_API int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, const uint32_t* idx, size_t nf,
+                            const uint32_t* rgb);
+/* Column-major 4x4 applied to every vertex at commit with glm's mat4*vec4 operation order
+ * (TriMeshBuffer::load, src/render/trimesh_buffer.cc:141-157).  NULL = identity (no transform pass). */
+SPRAYGPU_API int spraygpu_scene_set_transform(spraygpu_scene scene, const float* mat4_colmajor);
+/* transform -> per-vertex normals (TriMeshBuffer::computeNormals, trimesh_buffer.cc:267-326, bit-exact:
+ * same per-vertex summation order) -> LBVH -> 8-wide compressed BVH -> attribute pack.  = rtcCommit. */
+SPRAYGPU_API int spraygpu_scene_commit(spraygpu_scene scene);
+SPRAYGPU_API int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_info* out);
+SPRAYGPU_API int spraygpu_scene_get_normals(spraygpu_scene scene, float* out_nv3);      /* [h|d] */
+SPRAYGPU_API int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out_nv3);     /* world space, [h|d] */
+
+/* Scene::intersect on ONE domain = rtcIntersect + TriMeshBuffer::updateIntersection, batched
+ * (src/render/scene.inl:190-199).  keys[i] carries domain_id in its domain field; uv may be NULL. [h|d] */
+SPRAYGPU_API int spraygpu_intersect(spraygpu_scene scene, int domain_id, const spraygpu_ray* rays, size_t n, spraygpu_key* keys,
+                       float* uv);
+/* Scene::occluded = rtcOccluded, batched (src/render/scene.inl:202-209).  occ[i] = 1 if occluded. [h|d] */
+SPRAYGPU_API int spraygpu_occluded(spraygpu_scene scene, const spraygpu_ray* rays, size_t n, uint8_t* occ);
+
+/* ---- domain table: replaces WbvhEmbree::init/build (src/render/wbvh_embree.cc:31-111) and
+ *      Scene::getBsdf (domain.h:34) ---- */
+SPRAYGPU_API int spraygpu_domains_set(spraygpu_device dev, int ndomains, const float* world_aabb6, const spraygpu_material* mtl);
+/* Bind a committed scene as the resident data of a domain (Scene::load cache hit, scene.inl:135-187);
+ * scene == NULL marks the domain non-resident on this GPU (in-situ partition / cache eviction). */
+SPRAYGPU_API int spraygpu_domain_bind(spraygpu_device dev, int domain_id, spraygpu_scene scene);
+
+/* Ray -> list of ALL entered domains sorted by (tmin, id): WbvhEmbree::intersect + cbIntersect1 +
+ * DomainList::sort (wbvh_embree.cc:126-140, rays.h:71-79, aabb.h:139-169).  cap entries per ray. [h|d] */
+SPRAYGPU_API int spraygpu_domain_lists(spraygpu_device dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts,
+                          int32_t* ids, float* tmins);
+/* Closest hit over all RESIDENT entered domains (what the speculative queues + VBuf converge to).
+ * merge = 0: keys[i] is overwritten; merge = 1: keys[i] = min(keys[i], local result) with a 64-bit
+ * atomicMin (multi-GPU / out-of-core accumulation).  uv may be NULL. [h|d] */
+SPRAYGPU_API int spraygpu_intersect_domains(spraygpu_device dev, const spraygpu_ray* rays, size_t n, spraygpu_key* keys,
+                               float* uv, int merge);
+/* Any hit over all RESIDENT entered domains.  merge = 1: occ[i] |= local. [h|d] */
+SPRAYGPU_API int spraygpu_occluded_domains(spraygpu_device dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge);
+/* TriMeshBuffer::updateIntersection for resolved keys (trimesh_buffer.cc:328-360): packed colour and
+ * unnormalised shading normal; u,v are recomputed from (ray, primID).  [h|d] */
+SPRAYGPU_API int spraygpu_hit_attributes(spraygpu_device dev, const spraygpu_ray* rays, const spraygpu_key* keys, size_t n,
+                            uint32_t* color, float* ns3);
+/* Eye rays of a blocking tile (ooc::Tracer::genSingleEyes/genMultiEyes, ooc_tracer.inl:84-172).  [h|d] */
+SPRAYGPU_API int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
+                          spraygpu_ray* rays);
+
+/* ---- the fused path: one blocking tile from eye rays to radiance in the frame buffer.
+ * Replaces ooc::Tracer::trace's per-tile body (ooc_tracer.inl:184-234): genSingleEyes/genMultiEyes,
+ * Isector (domain culling), PContext::isectPrims (rtcIntersect/rtcOccluded loops, VBuf, shaders) and
+ * TContext::retire -> HdrImage::add (ooc_tcontext.inl:123-135, display/image.h:99-109).
+ * fb: image_w*image_h float4, ACCUMULATED into (caller clears, as SprayRenderer::renderFilm does). [h|d]
+ * stats may be NULL. */
+SPRAYGPU_API int spraygpu_trace_tile(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                        spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
+/* Same, with BVH node / triangle fetch counters (slower; used for the roofline's N_node, N_tri). */
+SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

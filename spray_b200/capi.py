@@ -1,0 +1,318 @@
+"""ctypes binding of libspraygpu.so (include/spray_gpu.h) — the reference-facing C ABI.
+
+Loading the library never needs a GPU (so `-m "not gpu"` tests can check the exported symbols); every
+compute entry point needs one and raises SprayGpuError otherwise.  There is no CPU fallback.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libspraygpu.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "spray_gpu.h")
+
+KEY_MISS = 0xFFFFFFFFFFFFFFFF
+MAX_LIGHTS = 8
+
+
+class SprayGpuError(RuntimeError):
+    pass
+
+
+def build(force=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a ... (spray_b200/csrc/Makefile).  Cross-compiles
+    without a GPU."""
+    csrc = os.path.join(_HERE, "csrc")
+    srcs = [os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith((".cu", ".cuh", "Makefile"))] + [HEADER_PATH]
+    if (not force and os.path.exists(LIB_PATH)
+            and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(s) for s in srcs)):
+        return LIB_PATH
+    r = subprocess.run(["make", "-C", csrc], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise SprayGpuError("building libspraygpu.so failed:\n" + r.stdout[-4000:])
+    return LIB_PATH
+
+
+class Ray(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("ox", "oy", "oz", "tmin", "dx", "dy", "dz", "tmax")]
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_int32), ("params", C.c_float * 3)]
+
+
+class Light(C.Structure):
+    _fields_ = [("type", C.c_int32), ("position", C.c_float * 3), ("radiance", C.c_float * 3)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("pos", C.c_float * 3), ("lowerleft", C.c_float * 3), ("wvec", C.c_float * 3),
+                ("hvec", C.c_float * 3), ("image_w", C.c_int32), ("image_h", C.c_int32)]
+
+
+class Tile(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32), ("w", C.c_int32), ("h", C.c_int32)]
+
+
+class Shade(C.Structure):
+    _fields_ = [("shader", C.c_int32), ("bounces", C.c_int32), ("pixel_samples", C.c_int32),
+                ("ao_samples", C.c_int32), ("ks", C.c_float * 3), ("shininess", C.c_float), ("nlights", C.c_int32),
+                ("lights", Light * MAX_LIGHTS)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("eye_rays", "radiance_rays", "shadow_rays", "domain_tests",
+                                           "nodes_visited", "tris_tested", "hits")]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("num_vertices", C.c_uint64), ("num_faces", C.c_uint64), ("num_nodes", C.c_uint64),
+                ("node_bytes", C.c_uint64), ("tri_bytes", C.c_uint64), ("attr_bytes", C.c_uint64),
+                ("bounds", C.c_float * 6), ("build_ms", C.c_double)]
+
+
+_vp = C.c_void_p
+_PROTOS = {
+    "spraygpu_last_error": (C.c_char_p, []),
+    "spraygpu_version": (C.c_char_p, []),
+    "spraygpu_device_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "spraygpu_device_destroy": (C.c_int, [_vp]),
+    "spraygpu_device_set_stream": (C.c_int, [_vp, _vp]),
+    "spraygpu_device_synchronize": (C.c_int, [_vp]),
+    "spraygpu_device_launch_count": (C.c_uint64, [_vp]),
+    "spraygpu_scene_create": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "spraygpu_scene_destroy": (C.c_int, [_vp]),
+    "spraygpu_scene_set_mesh": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp]),
+    "spraygpu_scene_set_transform": (C.c_int, [_vp, _vp]),
+    "spraygpu_scene_commit": (C.c_int, [_vp]),
+    "spraygpu_scene_get_info": (C.c_int, [_vp, C.POINTER(SceneInfo)]),
+    "spraygpu_scene_get_normals": (C.c_int, [_vp, _vp]),
+    "spraygpu_scene_get_vertices": (C.c_int, [_vp, _vp]),
+    "spraygpu_intersect": (C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp]),
+    "spraygpu_occluded": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "spraygpu_domains_set": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "spraygpu_domain_bind": (C.c_int, [_vp, C.c_int, _vp]),
+    "spraygpu_domain_lists": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp, _vp]),
+    "spraygpu_intersect_domains": (C.c_int, [_vp, _vp, C.c_size_t, _vp, _vp, C.c_int]),
+    "spraygpu_occluded_domains": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_int]),
+    "spraygpu_hit_attributes": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
+    "spraygpu_gen_eye_rays": (C.c_int, [_vp, C.POINTER(Camera), Tile, C.c_int, _vp]),
+    "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
+    "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libspraygpu.so.  Raises (loudly) if the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SprayGpuError("libspraygpu.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'` "
+                            "or `make -C spray_b200/csrc`); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    for name, (res, args) in _PROTOS.items():
+        fn = getattr(L, name)  # AttributeError if a declared symbol is missing
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def declared_symbols():
+    """Entry points declared in include/spray_gpu.h."""
+    import re
+    with open(HEADER_PATH) as f:
+        return sorted(set(re.findall(r"SPRAYGPU_API\s+[\w\s\*]+?\b(spraygpu_\w+)\s*\(", f.read())))
+
+
+def _check(rc):
+    if rc != 0:
+        raise SprayGpuError("libspraygpu error %d: %s" % (rc, lib().spraygpu_last_error().decode()))
+
+
+def _ptr(a):
+    """numpy array -> host pointer; torch tensor -> its data_ptr (device or host); None -> NULL."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):
+        assert a.is_contiguous()
+        return a.data_ptr()
+    return a
+
+
+def make_camera(desc):
+    cam = Camera()
+    for k in ("pos", "lowerleft", "wvec", "hvec"):
+        for i in range(3):
+            getattr(cam, k)[i] = float(np.float32(desc[k][i]))
+    cam.image_w, cam.image_h = int(desc["image_w"]), int(desc["image_h"])
+    return cam
+
+
+def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4, 0.4), shininess=10.0, lights=()):
+    sh = Shade()
+    sh.shader, sh.bounces, sh.pixel_samples, sh.ao_samples = shader, bounces, pixel_samples, ao_samples
+    for k in range(3):
+        sh.ks[k] = float(ks[k])
+    sh.shininess = float(shininess)
+    sh.nlights = len(lights)
+    for i, (ty, pos, rad) in enumerate(lights):
+        sh.lights[i].type = ty
+        for k in range(3):
+            sh.lights[i].position[k] = float(pos[k]); sh.lights[i].radiance[k] = float(rad[k])
+    return sh
+
+
+class Device:
+    def __init__(self, cuda_device=0, stream=None):
+        self.h = _vp()
+        _check(lib().spraygpu_device_create(int(cuda_device), C.byref(self.h)))
+        self.scenes = []
+        if stream is not None:
+            self.set_stream(stream)
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(lib().spraygpu_device_set_stream(self.h, _vp(cuda_stream_ptr)))
+
+    def synchronize(self):
+        _check(lib().spraygpu_device_synchronize(self.h))
+
+    def launch_count(self):
+        return int(lib().spraygpu_device_launch_count(self.h))
+
+    def close(self):
+        if self.h:
+            for s in self.scenes:
+                s.close()
+            self.scenes = []
+            lib().spraygpu_device_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- domains
+    def set_domains(self, bounds6, materials=None):
+        b = np.ascontiguousarray(bounds6, np.float32).reshape(-1, 6)
+        n = b.shape[0]
+        m = None
+        if materials is not None:
+            m = (Material * n)()
+            for i, (ty, params) in enumerate(materials):
+                m[i].type = int(ty)
+                for k in range(3):
+                    m[i].params[k] = float(params[k])
+        _check(lib().spraygpu_domains_set(self.h, n, b.ctypes.data, C.cast(m, _vp) if m is not None else None))
+        self.ndomains = n
+
+    def bind(self, domain_id, scene):
+        _check(lib().spraygpu_domain_bind(self.h, int(domain_id), scene.h if scene is not None else None))
+
+    def new_scene(self):
+        s = Scene(self)
+        self.scenes.append(s)
+        return s
+
+    def load_scene(self, scene_desc, owned=None):
+        """Upload + commit every domain of a spray_b200.scenes description and bind it.  `owned`: iterable of
+        domain ids resident on this GPU (default all) — the in-situ partition."""
+        doms = scene_desc["domains"]
+        self.set_domains(np.stack([d["bounds"] for d in doms]), [d.get("mtl", (0, (1, 1, 1))) for d in doms])
+        owned = set(range(len(doms))) if owned is None else set(int(i) for i in owned)
+        out = {}
+        for i, d in enumerate(doms):
+            if i not in owned:
+                continue
+            s = self.new_scene()
+            s.set_mesh(d["verts"], d["faces"], d.get("rgb"))
+            s.set_transform(d.get("transform"))
+            s.commit()
+            self.bind(i, s)
+            out[i] = s
+        return out
+
+    # ---- batched queries (numpy host arrays or torch device tensors)
+    def domain_lists(self, rays, n, cap, counts, ids, tmins):
+        _check(lib().spraygpu_domain_lists(self.h, _ptr(rays), n, cap, _ptr(counts), _ptr(ids), _ptr(tmins)))
+
+    def intersect_domains(self, rays, n, keys, uv=None, merge=False):
+        _check(lib().spraygpu_intersect_domains(self.h, _ptr(rays), n, _ptr(keys), _ptr(uv), int(merge)))
+
+    def occluded_domains(self, rays, n, occ, merge=False):
+        _check(lib().spraygpu_occluded_domains(self.h, _ptr(rays), n, _ptr(occ), int(merge)))
+
+    def hit_attributes(self, rays, keys, n, color, ns3):
+        _check(lib().spraygpu_hit_attributes(self.h, _ptr(rays), _ptr(keys), n, _ptr(color), _ptr(ns3)))
+
+    def gen_eye_rays(self, cam, tile, spp, rays):
+        _check(lib().spraygpu_gen_eye_rays(self.h, C.byref(cam), Tile(*tile), spp, _ptr(rays)))
+
+    def trace_tile(self, cam, shade, tile, fb, stats=False, counted=False):
+        st = Stats() if stats else None
+        fn = lib().spraygpu_trace_tile_counted if counted else lib().spraygpu_trace_tile
+        _check(fn(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb), C.byref(st) if st is not None else None))
+        return st
+
+
+class Scene:
+    def __init__(self, dev):
+        self.dev = dev
+        self.h = _vp()
+        _check(lib().spraygpu_scene_create(dev.h, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().spraygpu_scene_destroy(self.h)
+            self.h = _vp()
+
+    def set_mesh(self, verts, faces, rgb=None):
+        v = np.ascontiguousarray(verts, np.float32).reshape(-1, 3)
+        f = np.ascontiguousarray(faces, np.uint32).reshape(-1, 3)
+        c = None if rgb is None else np.ascontiguousarray(rgb, np.uint32)
+        _check(lib().spraygpu_scene_set_mesh(self.h, v.ctypes.data, v.shape[0], f.ctypes.data, f.shape[0],
+                                             None if c is None else c.ctypes.data))
+        self.nv, self.nf = v.shape[0], f.shape[0]
+
+    def set_transform(self, m):
+        if m is None:
+            _check(lib().spraygpu_scene_set_transform(self.h, None))
+        else:
+            m = np.ascontiguousarray(m, np.float32).reshape(16)
+            _check(lib().spraygpu_scene_set_transform(self.h, m.ctypes.data))
+
+    def commit(self):
+        _check(lib().spraygpu_scene_commit(self.h))
+
+    def info(self):
+        inf = SceneInfo()
+        _check(lib().spraygpu_scene_get_info(self.h, C.byref(inf)))
+        return inf
+
+    def normals(self):
+        out = np.zeros((self.nv, 3), np.float32)
+        _check(lib().spraygpu_scene_get_normals(self.h, out.ctypes.data))
+        return out
+
+    def vertices(self):
+        out = np.zeros((self.nv, 3), np.float32)
+        _check(lib().spraygpu_scene_get_vertices(self.h, out.ctypes.data))
+        return out
+
+    def intersect(self, domain_id, rays, n, keys, uv=None):
+        _check(lib().spraygpu_intersect(self.h, int(domain_id), _ptr(rays), n, _ptr(keys), _ptr(uv)))
+
+    def occluded(self, rays, n, occ):
+        _check(lib().spraygpu_occluded(self.h, _ptr(rays), n, _ptr(occ)))

@@ -1,0 +1,508 @@
+// capi.cu — the C ABI of libspraygpu (include/spray_gpu.h).  Thin: argument checks, host/device pointer
+// staging, and launches.  There is NO CPU fallback anywhere: every entry point that computes needs a
+// CUDA device and fails with SPRAYGPU_ERR_CUDA otherwise.
+#include <stdarg.h>
+
+#include <mutex>
+
+#include "internal.cuh"
+
+namespace spraygpu {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static bool is_device_ptr(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Per-call staging of host buffers.  Inputs are copied H2D up front; outputs are copied D2H by finish().
+struct Stager {
+  Device* dev;
+  struct Out { void* host; void* devp; size_t bytes; };
+  std::vector<Out> outs;
+  size_t in_off = 0, out_off = 0;
+  bool any_host = false;
+  int rc = SPRAYGPU_OK;
+
+  explicit Stager(Device* d) : dev(d) {}
+
+  // must be called before in()/out(): total bytes of host-side inputs / outputs (upper bounds)
+  int reserve(size_t in_bytes, size_t out_bytes) {
+    int r = ensure_scratch(dev->stage_in, in_bytes + 4096);
+    if (r) return r;
+    return ensure_scratch(dev->stage_out, out_bytes + 4096);
+  }
+  template <typename T> const T* in(const T* p, size_t count) {
+    if (!p || !count || is_device_ptr(p)) return p;
+    any_host = true;
+    in_off = (in_off + 255) & ~(size_t)255;
+    char* d = (char*)dev->stage_in.ptr + in_off;
+    size_t bytes = count * sizeof(T);
+    if (in_off + bytes > dev->stage_in.bytes) { set_error("staging overflow (in)"); rc = SPRAYGPU_ERR_STATE; return nullptr; }
+    in_off += bytes;
+    cudaError_t e = cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, dev->stream);
+    if (e != cudaSuccess) { set_error("H2D copy failed: %s", cudaGetErrorString(e)); rc = SPRAYGPU_ERR_CUDA; return nullptr; }
+    return (const T*)d;
+  }
+  // copy_in: the kernel reads-modifies the buffer (merge modes)
+  template <typename T> T* out(T* p, size_t count, bool copy_in = false) {
+    if (!p || !count || is_device_ptr(p)) return p;
+    any_host = true;
+    out_off = (out_off + 255) & ~(size_t)255;
+    char* d = (char*)dev->stage_out.ptr + out_off;
+    size_t bytes = count * sizeof(T);
+    if (out_off + bytes > dev->stage_out.bytes) { set_error("staging overflow (out)"); rc = SPRAYGPU_ERR_STATE; return nullptr; }
+    out_off += bytes;
+    if (copy_in) {
+      cudaError_t e = cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, dev->stream);
+      if (e != cudaSuccess) { set_error("H2D copy failed: %s", cudaGetErrorString(e)); rc = SPRAYGPU_ERR_CUDA; return nullptr; }
+    }
+    outs.push_back({(void*)p, (void*)d, bytes});
+    return (T*)d;
+  }
+  int finish() {
+    if (rc) return rc;
+    for (auto& o : outs) SG_CUDA(cudaMemcpyAsync(o.host, o.devp, o.bytes, cudaMemcpyDeviceToHost, dev->stream));
+    if (any_host) SG_CUDA(cudaStreamSynchronize(dev->stream));
+    return SPRAYGPU_OK;
+  }
+};
+
+int upload_domain_table(Device* dev) {
+  if (!dev->table_dirty) return SPRAYGPU_OK;
+  SG_CHECK(dev->ndomains > 0, SPRAYGPU_ERR_STATE, "no domain table: call spraygpu_domains_set first");
+  SG_CUDA(cudaMemcpyAsync(dev->d_domains, dev->h_domains.data(), sizeof(DomainEntry) * dev->ndomains,
+                          cudaMemcpyHostToDevice, dev->stream));
+  // h_domains is pageable: the runtime stages it before returning, so later host edits are safe
+  dev->table_dirty = false;
+  return SPRAYGPU_OK;
+}
+
+}  // namespace spraygpu
+
+using namespace spraygpu;
+
+#define DEV(d) ((Device*)(d))
+#define SCN(s) ((Scene*)(s))
+
+extern "C" {
+
+const char* spraygpu_last_error(void) { return g_err; }
+const char* spraygpu_version(void) { return "spraygpu 0.1 (sm_100a)"; }
+
+int spraygpu_device_create(int cuda_device, spraygpu_device* out) {
+  SG_CHECK(out, SPRAYGPU_ERR_ARG, "device_create: out is NULL");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    set_error("no CUDA device available (%s); libspraygpu has no CPU fallback",
+              e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    cudaGetLastError();
+    return SPRAYGPU_ERR_CUDA;
+  }
+  SG_CHECK(cuda_device >= 0 && cuda_device < count, SPRAYGPU_ERR_ARG, "device_create: bad device %d", cuda_device);
+  SG_CUDA(cudaSetDevice(cuda_device));
+  Device* d = new Device();
+  d->cuda_device = cuda_device;
+  cudaDeviceProp prop;
+  SG_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
+  d->sm_count = prop.multiProcessorCount;
+  SG_CUDA(cudaMalloc(&d->d_domains, sizeof(DomainEntry) * SPRAYGPU_MAX_DOMAINS));
+  SG_CUDA(cudaMalloc(&d->d_counters, sizeof(unsigned long long) * 8));
+  SG_CUDA(cudaMemset(d->d_counters, 0, sizeof(unsigned long long) * 8));
+  SG_CUDA(cudaMallocHost(&d->pinned, 4096));
+  d->pinned_bytes = 4096;
+  *out = (spraygpu_device)d;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_device_destroy(spraygpu_device dev) {
+  if (!dev) return SPRAYGPU_OK;
+  Device* d = DEV(dev);
+  cudaSetDevice(d->cuda_device);
+  cudaStreamSynchronize(d->stream);
+  if (d->scratch.ptr) cudaFree(d->scratch.ptr);
+  if (d->stage_in.ptr) cudaFree(d->stage_in.ptr);
+  if (d->stage_out.ptr) cudaFree(d->stage_out.ptr);
+  if (d->pinned) cudaFreeHost(d->pinned);
+  cudaFree(d->d_domains);
+  cudaFree(d->d_counters);
+  delete d;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_device_set_stream(spraygpu_device dev, void* cuda_stream) {
+  SG_CHECK(dev, SPRAYGPU_ERR_ARG, "set_stream: dev is NULL");
+  DEV(dev)->stream = (cudaStream_t)cuda_stream;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_device_synchronize(spraygpu_device dev) {
+  SG_CHECK(dev, SPRAYGPU_ERR_ARG, "synchronize: dev is NULL");
+  SG_CUDA(cudaStreamSynchronize(DEV(dev)->stream));
+  return SPRAYGPU_OK;
+}
+
+uint64_t spraygpu_device_launch_count(spraygpu_device dev) { return dev ? DEV(dev)->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+int spraygpu_scene_create(spraygpu_device dev, spraygpu_scene* out) {
+  SG_CHECK(dev && out, SPRAYGPU_ERR_ARG, "scene_create: NULL argument");
+  Scene* s = new Scene();
+  s->dev = DEV(dev);
+  *out = (spraygpu_scene)s;
+  return SPRAYGPU_OK;
+}
+
+static void scene_free_mesh(Scene* s) {
+  if (s->d_verts && s->d_verts != s->d_verts_obj) cudaFree(s->d_verts);
+  if (s->d_verts_obj) cudaFree(s->d_verts_obj);
+  if (s->d_faces) cudaFree(s->d_faces);
+  if (s->d_rgb) cudaFree(s->d_rgb);
+  if (s->d_normals) cudaFree(s->d_normals);
+  if (s->d_nodes) cudaFree(s->d_nodes);
+  if (s->d_tris) cudaFree(s->d_tris);
+  if (s->d_attr) cudaFree(s->d_attr);
+  s->d_verts = s->d_verts_obj = nullptr; s->d_faces = s->d_rgb = nullptr; s->d_normals = nullptr;
+  s->d_nodes = nullptr; s->d_tris = s->d_attr = nullptr;
+  s->committed = false; s->n_nodes = 0;
+}
+
+int spraygpu_scene_destroy(spraygpu_scene scene) {
+  if (!scene) return SPRAYGPU_OK;
+  Scene* s = SCN(scene);
+  Device* d = s->dev;
+  cudaSetDevice(d->cuda_device);
+  cudaStreamSynchronize(d->stream);
+  for (int i = 0; i < d->ndomains; ++i)
+    if (d->bound[i] == s) {
+      d->bound[i] = nullptr;
+      d->h_domains[i].resident = 0;
+      d->h_domains[i].nodes = nullptr; d->h_domains[i].tris = nullptr; d->h_domains[i].attr = nullptr;
+      d->h_domains[i].verts = nullptr; d->h_domains[i].faces = nullptr;
+      d->table_dirty = true;
+    }
+  scene_free_mesh(s);
+  delete s;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, const uint32_t* idx, size_t nf,
+                            const uint32_t* rgb) {
+  SG_CHECK(scene && xyz && idx, SPRAYGPU_ERR_ARG, "set_mesh: NULL argument");
+  SG_CHECK(nv > 0 && nf > 0, SPRAYGPU_ERR_ARG, "set_mesh: empty mesh (nv=%zu, nf=%zu)", nv, nf);
+  SG_CHECK(nf <= SPRAYGPU_MAX_PRIMS, SPRAYGPU_ERR_LIMIT, "set_mesh: %zu faces exceed the 23-bit primID field", nf);
+  SG_CHECK(nv <= 0xFFFFFFFFull, SPRAYGPU_ERR_LIMIT, "set_mesh: too many vertices");
+  Scene* s = SCN(scene);
+  Device* d = s->dev;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  SG_CUDA(cudaStreamSynchronize(d->stream));
+  scene_free_mesh(s);
+  s->nv = nv; s->nf = nf;
+  SG_CUDA(cudaMalloc(&s->d_verts_obj, sizeof(float) * 3 * nv));
+  SG_CUDA(cudaMalloc(&s->d_faces, sizeof(uint32_t) * 3 * nf));
+  SG_CUDA(cudaMemcpyAsync(s->d_verts_obj, xyz, sizeof(float) * 3 * nv, cudaMemcpyDefault, d->stream));
+  SG_CUDA(cudaMemcpyAsync(s->d_faces, idx, sizeof(uint32_t) * 3 * nf, cudaMemcpyDefault, d->stream));
+  if (rgb) {
+    SG_CUDA(cudaMalloc(&s->d_rgb, sizeof(uint32_t) * nv));
+    SG_CUDA(cudaMemcpyAsync(s->d_rgb, rgb, sizeof(uint32_t) * nv, cudaMemcpyDefault, d->stream));
+  }
+  SG_CUDA(cudaStreamSynchronize(d->stream));  // host arrays may be freed after return
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_scene_set_transform(spraygpu_scene scene, const float* m) {
+  SG_CHECK(scene, SPRAYGPU_ERR_ARG, "set_transform: scene is NULL");
+  Scene* s = SCN(scene);
+  s->has_xf = m != nullptr;
+  if (m) memcpy(s->xf, m, sizeof(float) * 16);
+  s->committed = false;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_scene_commit(spraygpu_scene scene) {
+  SG_CHECK(scene, SPRAYGPU_ERR_ARG, "commit: scene is NULL");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->d_verts_obj && s->d_faces, SPRAYGPU_ERR_STATE, "commit: no mesh set");
+  SG_CUDA(cudaSetDevice(s->dev->cuda_device));
+  int rc = build_scene(s);
+  if (rc) return rc;
+  // refresh table entries that point at this scene
+  Device* d = s->dev;
+  for (int i = 0; i < d->ndomains; ++i)
+    if (d->bound[i] == s) spraygpu_domain_bind((spraygpu_device)d, i, scene);
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_info* out) {
+  SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_info: NULL argument");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_info: scene not committed");
+  out->num_vertices = s->nv; out->num_faces = s->nf; out->num_nodes = s->n_nodes;
+  out->node_bytes = (uint64_t)s->n_nodes * 80; out->tri_bytes = (uint64_t)s->nf * 48; out->attr_bytes = (uint64_t)s->nf * 48;
+  memcpy(out->bounds, s->bounds, sizeof(out->bounds));
+  out->build_ms = s->build_ms;
+  return SPRAYGPU_OK;
+}
+
+static int copy_out(Device* d, void* dst, const void* src, size_t bytes) {
+  SG_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, d->stream));
+  if (!is_device_ptr(dst)) SG_CUDA(cudaStreamSynchronize(d->stream));
+  return SPRAYGPU_OK;
+}
+int spraygpu_scene_get_normals(spraygpu_scene scene, float* out) {
+  SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_normals: NULL argument");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_normals: scene not committed");
+  return copy_out(s->dev, out, s->d_normals, sizeof(float) * 3 * s->nv);
+}
+int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out) {
+  SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_vertices: NULL argument");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_vertices: scene not committed");
+  return copy_out(s->dev, out, s->d_verts, sizeof(float) * 3 * s->nv);
+}
+
+int spraygpu_intersect(spraygpu_scene scene, int domain_id, const spraygpu_ray* rays, size_t n, spraygpu_key* keys,
+                       float* uv) {
+  SG_CHECK(scene && (n == 0 || (rays && keys)), SPRAYGPU_ERR_ARG, "intersect: NULL argument");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "intersect: scene not committed");
+  SG_CHECK(domain_id >= 0 && domain_id < SPRAYGPU_MAX_DOMAINS, SPRAYGPU_ERR_ARG, "intersect: bad domain id %d", domain_id);
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(s->dev->cuda_device));
+  Stager st(s->dev);
+  int rc = st.reserve(n * sizeof(spraygpu_ray), n * 16 + 512);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  uint64_t* dk = st.out(keys, n);
+  float* duv = st.out(uv, 2 * n);
+  if (st.rc) return st.rc;
+  rc = launch_intersect_scene(s, domain_id, dr, n, dk, duv);
+  if (rc) return rc;
+  return st.finish();
+}
+
+int spraygpu_occluded(spraygpu_scene scene, const spraygpu_ray* rays, size_t n, uint8_t* occ) {
+  SG_CHECK(scene && (n == 0 || (rays && occ)), SPRAYGPU_ERR_ARG, "occluded: NULL argument");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "occluded: scene not committed");
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(s->dev->cuda_device));
+  Stager st(s->dev);
+  int rc = st.reserve(n * sizeof(spraygpu_ray), n + 512);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  uint8_t* docc = st.out(occ, n);
+  if (st.rc) return st.rc;
+  rc = launch_occluded_scene(s, dr, n, docc);
+  if (rc) return rc;
+  return st.finish();
+}
+
+// ---------------------------------------------------------------------------------------------
+int spraygpu_domains_set(spraygpu_device dev, int nd, const float* aabb6, const spraygpu_material* mtl) {
+  SG_CHECK(dev && aabb6, SPRAYGPU_ERR_ARG, "domains_set: NULL argument");
+  SG_CHECK(nd > 0 && nd <= SPRAYGPU_MAX_DOMAINS, SPRAYGPU_ERR_LIMIT, "domains_set: %d domains (limit %d: 9 key bits)", nd,
+           SPRAYGPU_MAX_DOMAINS);
+  Device* d = DEV(dev);
+  d->ndomains = nd;
+  d->h_domains.assign(nd, DomainEntry());
+  d->bound.assign(nd, nullptr);
+  for (int i = 0; i < nd; ++i) {
+    DomainEntry& e = d->h_domains[i];
+    memset(&e, 0, sizeof(e));
+    memcpy(e.box, aabb6 + 6 * i, sizeof(float) * 6);
+    e.mtl_type = mtl ? mtl[i].type : SPRAYGPU_MTL_DIFFUSE;
+    for (int k = 0; k < 3; ++k) e.mtl[k] = mtl ? mtl[i].params[k] : 1.0f;
+  }
+  d->table_dirty = true;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_domain_bind(spraygpu_device dev, int id, spraygpu_scene scene) {
+  SG_CHECK(dev, SPRAYGPU_ERR_ARG, "domain_bind: dev is NULL");
+  Device* d = DEV(dev);
+  SG_CHECK(id >= 0 && id < d->ndomains, SPRAYGPU_ERR_ARG, "domain_bind: bad domain id %d (table has %d)", id, d->ndomains);
+  DomainEntry& e = d->h_domains[id];
+  Scene* s = SCN(scene);
+  if (s) {
+    SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "domain_bind: scene not committed");
+    SG_CHECK(s->dev == d, SPRAYGPU_ERR_ARG, "domain_bind: scene belongs to another device");
+    e.resident = 1; e.nprims = (uint32_t)s->nf;
+    e.nodes = s->d_nodes; e.tris = s->d_tris; e.attr = s->d_attr; e.verts = s->d_verts; e.faces = s->d_faces;
+  } else {
+    e.resident = 0; e.nprims = 0;
+    e.nodes = nullptr; e.tris = nullptr; e.attr = nullptr; e.verts = nullptr; e.faces = nullptr;
+  }
+  d->bound[id] = s;
+  d->table_dirty = true;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_domain_lists(spraygpu_device dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts,
+                          int32_t* ids, float* tmins) {
+  SG_CHECK(dev && (n == 0 || (rays && counts && ids && tmins)) && cap > 0, SPRAYGPU_ERR_ARG, "domain_lists: bad argument");
+  Device* d = DEV(dev);
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  Stager st(d);
+  rc = st.reserve(n * sizeof(spraygpu_ray), n * (4 + 8 * (size_t)cap) + 1024);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  int32_t* dc = st.out(counts, n);
+  int32_t* di = st.out(ids, n * cap);
+  float* dt = st.out(tmins, n * cap);
+  if (st.rc) return st.rc;
+  rc = launch_domain_lists(d, dr, n, cap, dc, di, dt);
+  if (rc) return rc;
+  return st.finish();
+}
+
+int spraygpu_intersect_domains(spraygpu_device dev, const spraygpu_ray* rays, size_t n, spraygpu_key* keys, float* uv,
+                               int merge) {
+  SG_CHECK(dev && (n == 0 || (rays && keys)), SPRAYGPU_ERR_ARG, "intersect_domains: NULL argument");
+  Device* d = DEV(dev);
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  Stager st(d);
+  rc = st.reserve(n * sizeof(spraygpu_ray), n * 16 + 1024);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  uint64_t* dk = st.out(keys, n, merge != 0);
+  float* duv = st.out(uv, 2 * n, merge != 0);
+  if (st.rc) return st.rc;
+  rc = launch_intersect_domains(d, dr, n, dk, duv, merge);
+  if (rc) return rc;
+  return st.finish();
+}
+
+int spraygpu_occluded_domains(spraygpu_device dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge) {
+  SG_CHECK(dev && (n == 0 || (rays && occ)), SPRAYGPU_ERR_ARG, "occluded_domains: NULL argument");
+  Device* d = DEV(dev);
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  Stager st(d);
+  rc = st.reserve(n * sizeof(spraygpu_ray), n + 1024);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  uint8_t* docc = st.out(occ, n, merge != 0);
+  if (st.rc) return st.rc;
+  rc = launch_occluded_domains(d, dr, n, docc, merge);
+  if (rc) return rc;
+  return st.finish();
+}
+
+int spraygpu_hit_attributes(spraygpu_device dev, const spraygpu_ray* rays, const spraygpu_key* keys, size_t n,
+                            uint32_t* color, float* ns3) {
+  SG_CHECK(dev && (n == 0 || (rays && keys && color && ns3)), SPRAYGPU_ERR_ARG, "hit_attributes: NULL argument");
+  Device* d = DEV(dev);
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  Stager st(d);
+  rc = st.reserve(n * (sizeof(spraygpu_ray) + 8) + 1024, n * 16 + 1024);
+  if (rc) return rc;
+  const spraygpu_ray* dr = st.in(rays, n);
+  const uint64_t* dk = st.in(keys, n);
+  uint32_t* dc = st.out(color, n);
+  float* dn = st.out(ns3, 3 * n);
+  if (st.rc) return st.rc;
+  rc = launch_hit_attributes(d, dr, dk, n, dc, dn);
+  if (rc) return rc;
+  return st.finish();
+}
+
+int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
+                          spraygpu_ray* rays) {
+  SG_CHECK(dev && cam && rays && spp > 0, SPRAYGPU_ERR_ARG, "gen_eye_rays: bad argument");
+  Device* d = DEV(dev);
+  const size_t n = (size_t)tile.w * tile.h * spp;
+  if (!n) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  Stager st(d);
+  int rc = st.reserve(0, n * sizeof(spraygpu_ray) + 512);
+  if (rc) return rc;
+  spraygpu_ray* dr = st.out(rays, n);
+  if (st.rc) return st.rc;
+  rc = launch_eye_rays(d, cam, tile, spp, dr);
+  if (rc) return rc;
+  return st.finish();
+}
+
+static int trace_tile_impl(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                           spraygpu_tile tile, float* fb, spraygpu_stats* stats, bool counted) {
+  SG_CHECK(dev && cam && shade && fb, SPRAYGPU_ERR_ARG, "trace_tile: NULL argument");
+  SG_CHECK(shade->pixel_samples >= 1 && shade->bounces >= 1, SPRAYGPU_ERR_ARG, "trace_tile: pixel_samples and bounces must be >= 1");
+  SG_CHECK(shade->nlights >= 0 && shade->nlights <= SPRAYGPU_MAX_LIGHTS, SPRAYGPU_ERR_LIMIT, "trace_tile: %d lights (limit %d)",
+           shade->nlights, SPRAYGPU_MAX_LIGHTS);
+  SG_CHECK(shade->shader == SPRAYGPU_SHADER_AO || shade->nlights > 0, SPRAYGPU_ERR_ARG,
+           "trace_tile: the PT shader needs at least one light (ooc_tracer.inl:68)");
+  SG_CHECK(shade->shader == SPRAYGPU_SHADER_PT || shade->ao_samples > 0, SPRAYGPU_ERR_ARG, "trace_tile: ao_samples must be > 0");
+  SG_CHECK(tile.x >= 0 && tile.y >= 0 && tile.w >= 0 && tile.h >= 0 && tile.x + tile.w <= cam->image_w &&
+               tile.y + tile.h <= cam->image_h,
+           SPRAYGPU_ERR_ARG, "trace_tile: tile (%d,%d,%d,%d) outside the %dx%d image", tile.x, tile.y, tile.w, tile.h,
+           cam->image_w, cam->image_h);
+  Device* d = DEV(dev);
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  const bool host_fb = !is_device_ptr(fb);
+  float* dfb = fb;
+  const size_t img_bytes = sizeof(float) * 4 * (size_t)cam->image_w * cam->image_h;
+  const size_t row_bytes = sizeof(float) * 4 * (size_t)cam->image_w;
+  if (host_fb) {
+    // Host frame buffer: render into a zeroed device image, then copy the tile's rows back.  (The
+    // reference clears the image each frame and tiles are disjoint, src/render/spray_renderer.inl:363.)
+    rc = ensure_scratch(d->stage_out, img_bytes + 4096);
+    if (rc) return rc;
+    dfb = (float*)d->stage_out.ptr;
+    SG_CUDA(cudaMemsetAsync((char*)dfb + row_bytes * tile.y, 0, row_bytes * tile.h, d->stream));
+  }
+  rc = launch_render_tile(d, cam, shade, tile, dfb, counted);
+  if (rc) return rc;
+  if (host_fb && tile.w > 0 && tile.h > 0) {
+    const size_t off = (size_t)tile.y * cam->image_w + tile.x;
+    SG_CUDA(cudaMemcpy2DAsync(fb + 4 * off, row_bytes, dfb + 4 * off, row_bytes, sizeof(float) * 4 * tile.w, tile.h,
+                              cudaMemcpyDeviceToHost, d->stream));
+  }
+  if (stats) {
+    unsigned long long* h = (unsigned long long*)d->pinned;
+    SG_CUDA(cudaMemcpyAsync(h, d->d_counters, sizeof(unsigned long long) * 8, cudaMemcpyDeviceToHost, d->stream));
+    SG_CUDA(cudaStreamSynchronize(d->stream));
+    stats->eye_rays = h[1]; stats->radiance_rays = h[2]; stats->shadow_rays = h[3]; stats->domain_tests = h[4];
+    stats->nodes_visited = h[5]; stats->tris_tested = h[6]; stats->hits = h[7];
+  } else if (host_fb) {
+    SG_CUDA(cudaStreamSynchronize(d->stream));
+  }
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_trace_tile(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
+                        float* fb, spraygpu_stats* stats) {
+  return trace_tile_impl(dev, cam, shade, tile, fb, stats, false);
+}
+int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                spraygpu_tile tile, float* fb, spraygpu_stats* stats) {
+  return trace_tile_impl(dev, cam, shade, tile, fb, stats, true);
+}
+
+}  // extern "C"

@@ -1,0 +1,674 @@
+// core.cuh — building blocks of the B200 ray-tracing path, written as __host__ __device__ functions so
+// that the exact same logic can be exercised by the host-emulation harness (tests/hostemu) in the
+// GPU-less build container.  The product only ever runs them inside CUDA kernels (trace.cu, build.cu).
+//
+// FP32 contract (DESIGN.md "FP32 contract"):
+//   * R-ops (mul_rn/add_rn/sub_rn/div_rn/sqrt_rn) round once and are never contracted: they restate the
+//     reference's glm/C++ arithmetic (glm 0.9.9.3 dot = (x*x'+y*y')+z*z', normalize = v*(1/sqrt(dot))).
+//   * The ray/triangle test (S1) uses explicit fused multiply-adds in a fixed order.
+//   * Box tests (BVH8 nodes) are free-form FP32: only conservativeness matters there.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#ifdef __CUDACC__
+#define SPRAY_HD __host__ __device__ __forceinline__
+#else
+#define SPRAY_HD inline
+#endif
+
+namespace spraygpu {
+
+// ---------------------------------------------------------------------------------------------
+// exactly-rounded scalar ops
+// ---------------------------------------------------------------------------------------------
+#if defined(__CUDA_ARCH__)
+SPRAY_HD float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+SPRAY_HD float add_rn(float a, float b) { return __fadd_rn(a, b); }
+SPRAY_HD float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+SPRAY_HD float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+SPRAY_HD float sqrt_rn(float a) { return __fsqrt_rn(a); }
+SPRAY_HD float fma_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+SPRAY_HD uint32_t f2u(float f) { return __float_as_uint(f); }
+SPRAY_HD float u2f(uint32_t u) { return __uint_as_float(u); }
+SPRAY_HD int clz32(uint32_t x) { return __clz((int)x); }
+SPRAY_HD int popc32(uint32_t x) { return __popc(x); }
+SPRAY_HD int ffs32(uint32_t x) { return __ffs((int)x); }
+#else
+// host emulation: compiled with -ffp-contract=off, so plain operators round once
+SPRAY_HD float mul_rn(float a, float b) { return a * b; }
+SPRAY_HD float add_rn(float a, float b) { return a + b; }
+SPRAY_HD float sub_rn(float a, float b) { return a - b; }
+SPRAY_HD float div_rn(float a, float b) { return a / b; }
+SPRAY_HD float sqrt_rn(float a) { return sqrtf(a); }
+SPRAY_HD float fma_rn(float a, float b, float c) { return fmaf(a, b, c); }
+SPRAY_HD uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+SPRAY_HD float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+SPRAY_HD int clz32(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+SPRAY_HD int popc32(uint32_t x) { return __builtin_popcount(x); }
+SPRAY_HD int ffs32(uint32_t x) { return __builtin_ffs((int)x); }
+#endif
+
+struct vec3 { float x, y, z; };
+SPRAY_HD vec3 mk3(float x, float y, float z) { vec3 r; r.x = x; r.y = y; r.z = z; return r; }
+// reference-order (glm) helpers
+SPRAY_HD vec3 gadd(vec3 a, vec3 b) { return mk3(add_rn(a.x, b.x), add_rn(a.y, b.y), add_rn(a.z, b.z)); }
+SPRAY_HD vec3 gsub(vec3 a, vec3 b) { return mk3(sub_rn(a.x, b.x), sub_rn(a.y, b.y), sub_rn(a.z, b.z)); }
+SPRAY_HD vec3 gmul(vec3 a, vec3 b) { return mk3(mul_rn(a.x, b.x), mul_rn(a.y, b.y), mul_rn(a.z, b.z)); }
+SPRAY_HD vec3 gscale(vec3 a, float s) { return mk3(mul_rn(a.x, s), mul_rn(a.y, s), mul_rn(a.z, s)); }
+SPRAY_HD vec3 gneg(vec3 a) { return mk3(-a.x, -a.y, -a.z); }
+SPRAY_HD float gdot(vec3 a, vec3 b) { return add_rn(add_rn(mul_rn(a.x, b.x), mul_rn(a.y, b.y)), mul_rn(a.z, b.z)); }
+SPRAY_HD vec3 gcross(vec3 x, vec3 y) {
+  return mk3(sub_rn(mul_rn(x.y, y.z), mul_rn(y.y, x.z)), sub_rn(mul_rn(x.z, y.x), mul_rn(y.z, x.x)),
+             sub_rn(mul_rn(x.x, y.y), mul_rn(y.x, x.y)));
+}
+SPRAY_HD vec3 gnormalize(vec3 v) { return gscale(v, div_rn(1.0f, sqrt_rn(gdot(v, v)))); }
+SPRAY_HD float gclamp(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// fused helpers of the triangle test (contract S1)
+SPRAY_HD float edot(vec3 a, vec3 b) { return fma_rn(a.x, b.x, fma_rn(a.y, b.y, mul_rn(a.z, b.z))); }
+SPRAY_HD vec3 ecross(vec3 a, vec3 b) {
+  return mk3(fma_rn(a.y, b.z, -mul_rn(a.z, b.y)), fma_rn(a.z, b.x, -mul_rn(a.x, b.z)),
+             fma_rn(a.x, b.y, -mul_rn(a.y, b.x)));
+}
+
+#define SPRAY_RAY_EPS 0.001f              /* SPRAY_RAY_EPSILON, reference src/render/spray.h:46 */
+#define SPRAY_ONE_OVER_PI 0.3183098861837907f /* src/render/spray.h:50 */
+#define SPRAY_KEY_MISS 0xFFFFFFFFFFFFFFFFull
+#define SPRAY_DOMAIN_BITS 9
+#define SPRAY_PRIM_BITS 23
+
+SPRAY_HD uint64_t make_key(float t, uint32_t dom, uint32_t prim) {
+  return ((uint64_t)f2u(t) << 32) | ((uint64_t)dom << SPRAY_PRIM_BITS) | (uint64_t)prim;
+}
+SPRAY_HD float key_t(uint64_t k) { return u2f((uint32_t)(k >> 32)); }
+SPRAY_HD uint32_t key_domain(uint64_t k) { return (uint32_t)((k >> SPRAY_PRIM_BITS) & 0x1ff); }
+SPRAY_HD uint32_t key_prim(uint64_t k) { return (uint32_t)(k & 0x7fffff); }
+
+// ---------------------------------------------------------------------------------------------
+// RNG — reference deps/embree/random_sampler.h:34-108 (MurmurHash3 seed + LCG; integer exact)
+// ---------------------------------------------------------------------------------------------
+SPRAY_HD uint32_t murmur_mix(uint32_t hash, uint32_t k) {
+  k *= 0xcc9e2d51u;
+  k = (k << 15) | (k >> 17);
+  k *= 0x1b873593u;
+  hash ^= k;
+  return ((hash << 13) | (hash >> 19)) * 5u + 0xe6546b64u;
+}
+SPRAY_HD uint32_t murmur_fin(uint32_t h) {
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+SPRAY_HD uint32_t rng_init1(uint32_t id) { return murmur_fin(murmur_mix(0u, id)); }
+SPRAY_HD uint32_t rng_init2(uint32_t a, uint32_t b) { return murmur_fin(murmur_mix(murmur_mix(0u, a), b)); }
+SPRAY_HD float rng_float(uint32_t& s) {
+  s = s * 1664525u + 1013904223u;
+  return mul_rn((float)(int)(s >> 1), 4.656612873077392578125e-10f);
+}
+
+// Morton — reference src/render/morton.h:33-52 (10 bits / axis)
+SPRAY_HD uint32_t expand_bits10(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+SPRAY_HD uint32_t morton30(float x, float y, float z) {
+  x = fminf(fmaxf(mul_rn(x, 1024.0f), 0.0f), 1023.0f);
+  y = fminf(fmaxf(mul_rn(y, 1024.0f), 0.0f), 1023.0f);
+  z = fminf(fmaxf(mul_rn(z, 1024.0f), 0.0f), 1023.0f);
+  return expand_bits10((uint32_t)x) * 4 + expand_bits10((uint32_t)y) * 2 + expand_bits10((uint32_t)z);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Domain slab test — reference src/render/aabb.h:139-169, behaviour-identical (early-out order, NaN
+// handling through the comparison directions, tmin not clamped).  b = {lo.xyz, hi.xyz}.
+// ---------------------------------------------------------------------------------------------
+SPRAY_HD bool domain_slab(const float* b, vec3 o, vec3 d, float t0, float t1, float* tmin_o) {
+  float ix = div_rn(1.0f, d.x), iy = div_rn(1.0f, d.y), iz = div_rn(1.0f, d.z);
+  int sx = ix < 0.0f, sy = iy < 0.0f, sz = iz < 0.0f;
+  float tmin = mul_rn(sub_rn(b[sx * 3 + 0], o.x), ix);
+  float tmax = mul_rn(sub_rn(b[(1 - sx) * 3 + 0], o.x), ix);
+  float tymin = mul_rn(sub_rn(b[sy * 3 + 1], o.y), iy);
+  float tymax = mul_rn(sub_rn(b[(1 - sy) * 3 + 1], o.y), iy);
+  if ((tmin > tymax) || (tymin > tmax)) return false;
+  if (tymin > tmin) tmin = tymin;
+  if (tymax < tmax) tmax = tymax;
+  float tzmin = mul_rn(sub_rn(b[sz * 3 + 2], o.z), iz);
+  float tzmax = mul_rn(sub_rn(b[(1 - sz) * 3 + 2], o.z), iz);
+  if ((tmin > tzmax) || (tzmin > tmax)) return false;
+  if (tzmin > tmin) tmin = tzmin;
+  if (tzmax < tmax) tmax = tzmax;
+  *tmin_o = tmin;
+  return (tmin < t1) && (tmax > t0);
+}
+
+// order-preserving float -> uint (handles negative entry distances: origin inside the box)
+SPRAY_HD uint32_t float_sortable(float f) {
+  uint32_t u = f2u(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+SPRAY_HD float sortable_float(uint32_t s) {
+  uint32_t u = (s & 0x80000000u) ? (s & 0x7fffffffu) : ~s;
+  return u2f(u);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Triangle record: 3 x float4 (48 B): (v0.xyz, primID bits) (e1.xyz, -) (e2.xyz, -),
+// e1 = v0 - v1, e2 = v2 - v0 computed once with sub_rn (same values the per-ray subtraction gives).
+// Contract S1: Moeller-Trumbore in the form used by Embree's triangle-v intersector [unverified, the
+// dependency is not in the container]: no culling, inclusive edges, u,v relative to v1,v2, t > tnear.
+// ---------------------------------------------------------------------------------------------
+struct TriHit { float t, u, v; };
+SPRAY_HD bool tri_test(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear, TriHit* h) {
+  vec3 Ng = ecross(e2, e1);
+  vec3 C = gsub(v0, O);
+  vec3 R = ecross(C, D);
+  float den = edot(Ng, D);
+  float absDen = fabsf(den);
+  uint32_t sgn = f2u(den) & 0x80000000u;
+  float U = u2f(f2u(edot(R, e2)) ^ sgn);
+  float V = u2f(f2u(edot(R, e1)) ^ sgn);
+  if (!(den != 0.0f) || !(U >= 0.0f) || !(V >= 0.0f) || !(add_rn(U, V) <= absDen)) return false;
+  float T = u2f(f2u(edot(Ng, C)) ^ sgn);
+  if (!(T > mul_rn(absDen, tnear))) return false;
+  h->t = div_rn(T, absDen);
+  h->u = div_rn(U, absDen);
+  h->v = div_rn(V, absDen);
+  return true;
+}
+// any-hit variant: no divisions
+SPRAY_HD bool tri_test_any(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear) {
+  vec3 Ng = ecross(e2, e1);
+  vec3 C = gsub(v0, O);
+  vec3 R = ecross(C, D);
+  float den = edot(Ng, D);
+  float absDen = fabsf(den);
+  uint32_t sgn = f2u(den) & 0x80000000u;
+  float U = u2f(f2u(edot(R, e2)) ^ sgn);
+  float V = u2f(f2u(edot(R, e1)) ^ sgn);
+  if (!(den != 0.0f) || !(U >= 0.0f) || !(V >= 0.0f) || !(add_rn(U, V) <= absDen)) return false;
+  float T = u2f(f2u(edot(Ng, C)) ^ sgn);
+  return T > mul_rn(absDen, tnear);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Compressed 8-wide BVH node, 80 B = 5 x 16 B (layout after Ylitie, Karras, Laine 2017):
+//   q0: p.x p.y p.z | ex ey ez imask
+//   q1: child_base | tri_base | meta[0..3] | meta[4..7]
+//   q2: qlox[0..3] qlox[4..7] qloy[0..3] qloy[4..7]
+//   q3: qloz[0..3] qloz[4..7] qhix[0..3] qhix[4..7]
+//   q4: qhiy[0..3] qhiy[4..7] qhiz[0..3] qhiz[4..7]
+// meta: 0 = empty; internal = 0b001_xxxxx with xxxxx = 24 + slot; leaf = unary tri count (001,011,111)
+// in the top 3 bits, low 5 bits = first triangle offset from tri_base (0..23).
+// ---------------------------------------------------------------------------------------------
+struct u4 { uint32_t x, y, z, w; };
+
+struct RayCtx {
+  vec3 o, d;       // exact origin/direction (triangle test)
+  vec3 idir;       // 1/d with |d| clamped away from 0 (box tests only)
+  vec3 far_bias;   // 2^100 on axes where d == 0: the slab then passes iff lo <= o (inclusive far face)
+  uint32_t octinv; // 7 - octant, octant bit k set <=> d[k] < 0
+  float tnear;
+};
+
+SPRAY_HD RayCtx make_ray_ctx(vec3 o, vec3 d, float tnear) {
+  RayCtx r;
+  r.o = o; r.d = d; r.tnear = tnear;
+  const float eps = 8.271806125530277e-25f; // 2^-80
+  float dx = fabsf(d.x) > eps ? d.x : copysignf(eps, d.x);
+  float dy = fabsf(d.y) > eps ? d.y : copysignf(eps, d.y);
+  float dz = fabsf(d.z) > eps ? d.z : copysignf(eps, d.z);
+  r.idir = mk3(1.0f / dx, 1.0f / dy, 1.0f / dz);
+  // A ray lying exactly in a box face (d[k] == 0, o[k] == hi[k]) would see t_far == 0 < tnear and skip
+  // the box; pushing the far plane of parallel axes to +2^100 keeps such boxes (conservative).
+  const float huge = 1.2676506e30f;
+  r.far_bias = mk3(d.x == 0.0f ? huge : 0.0f, d.y == 0.0f ? huge : 0.0f, d.z == 0.0f ? huge : 0.0f);
+  uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+  r.octinv = 7u - oct;
+  return r;
+}
+
+SPRAY_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
+
+// returns the 32-bit hit mask of one node: bits 31..24 internal children in traversal priority order,
+// bits 23..0 one bit per leaf triangle.
+SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4, const RayCtx& r,
+                             float tmax) {
+  const float px = u2f(q0.x), py = u2f(q0.y), pz = u2f(q0.z);
+  const uint32_t e = q0.w;
+  const float aix = u2f((e & 0xffu) << 23) * r.idir.x;
+  const float aiy = u2f(((e >> 8) & 0xffu) << 23) * r.idir.y;
+  const float aiz = u2f(((e >> 16) & 0xffu) << 23) * r.idir.z;
+  const float ox = (px - r.o.x) * r.idir.x;
+  const float oy = (py - r.o.y) * r.idir.y;
+  const float oz = (pz - r.o.z) * r.idir.z;
+  const float fx = ox + r.far_bias.x, fy = oy + r.far_bias.y, fz = oz + r.far_bias.z;
+  const uint32_t octinv4 = r.octinv * 0x01010101u;
+  const bool nx = r.idir.x < 0.0f, ny = r.idir.y < 0.0f, nz = r.idir.z < 0.0f;
+  uint32_t hitmask = 0;
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const uint32_t meta4 = half ? q1.w : q1.z;
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+    const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+    const uint32_t lox = half ? q2.y : q2.x, loy = half ? q2.w : q2.z, loz = half ? q3.y : q3.x;
+    const uint32_t hix = half ? q3.w : q3.z, hiy = half ? q4.y : q4.x, hiz = half ? q4.w : q4.z;
+    const uint32_t nearx = nx ? hix : lox, farx = nx ? lox : hix;
+    const uint32_t neary = ny ? hiy : loy, fary = ny ? loy : hiy;
+    const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float t0x = fmaf((float)byte_of(nearx, j), aix, ox);
+      const float t0y = fmaf((float)byte_of(neary, j), aiy, oy);
+      const float t0z = fmaf((float)byte_of(nearz, j), aiz, oz);
+      const float t1x = fmaf((float)byte_of(farx, j), aix, fx);
+      const float t1y = fmaf((float)byte_of(fary, j), aiy, fy);
+      const float t1z = fmaf((float)byte_of(farz, j), aiz, fz);
+      const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
+      // 1 + 2^-21: the quantised box is conservative for the geometry, this covers FP32 rounding of
+      // the six plane distances relative to the triangle test's t
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.00000048f;
+      if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+    }
+  }
+  return hitmask;
+}
+
+#define SPRAY_STACK_SIZE 48
+
+struct Closest {
+  float t, u, v;
+  uint32_t prim; // valid iff t < inf
+};
+
+// Closest hit in ONE domain's BVH8: lexicographic min of (t, primID) over every triangle passing S1.
+// nodes: 5 x u4 per node; tris: 3 x float4-equivalent (12 floats) per triangle.  LOADN / LOADT abstract
+// the memory access (global loads on the device, plain reads in host emulation).
+template <typename NodeLoader, typename TriLoader>
+SPRAY_HD void bvh8_closest(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, Closest& best,
+                           uint32_t* stack_x, uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
+  uint32_t ngx = 0, ngy = 0x80000000u;
+  int sp = 0;
+  for (;;) {
+    uint32_t tgx = 0, tgy = 0;
+    if (ngy > 0x00FFFFFFu) {
+      const uint32_t imask = ngy & 0xffu;
+      const int bit = 31 - clz32(ngy);
+      ngy &= ~(1u << bit);
+      if (ngy > 0x00FFFFFFu) {
+        if (sp < SPRAY_STACK_SIZE) { stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp; }
+      }
+      const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
+      const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+      const uint32_t idx = ngx + rel;
+      u4 q0, q1, q2, q3, q4;
+      loadn(idx, q0, q1, q2, q3, q4);
+      if (n_nodes) ++*n_nodes;
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, best.t);
+      ngx = q1.x; tgx = q1.y;
+      ngy = (hm & 0xFF000000u) | (q0.w >> 24);
+      tgy = hm & 0x00FFFFFFu;
+    }
+    while (tgy) {
+      const int ti = ffs32(tgy) - 1;
+      tgy &= tgy - 1;
+      vec3 v0, e1, e2; uint32_t prim;
+      loadt(tgx + (uint32_t)ti, v0, e1, e2, prim);
+      if (n_tris) ++*n_tris;
+      TriHit h;
+      if (tri_test(r.o, r.d, v0, e1, e2, r.tnear, &h)) {
+        if (h.t < best.t || (h.t == best.t && prim < best.prim)) {
+          best.t = h.t; best.u = h.u; best.v = h.v; best.prim = prim;
+        }
+      }
+    }
+    if (ngy <= 0x00FFFFFFu) {
+      if (sp == 0) break;
+      --sp; ngx = stack_x[sp]; ngy = stack_y[sp];
+    }
+  }
+}
+
+template <typename NodeLoader, typename TriLoader>
+SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, uint32_t* stack_x,
+                       uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
+  uint32_t ngx = 0, ngy = 0x80000000u;
+  int sp = 0;
+  for (;;) {
+    uint32_t tgx = 0, tgy = 0;
+    if (ngy > 0x00FFFFFFu) {
+      const uint32_t imask = ngy & 0xffu;
+      const int bit = 31 - clz32(ngy);
+      ngy &= ~(1u << bit);
+      if (ngy > 0x00FFFFFFu) {
+        if (sp < SPRAY_STACK_SIZE) { stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp; }
+      }
+      const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
+      const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+      u4 q0, q1, q2, q3, q4;
+      loadn(ngx + rel, q0, q1, q2, q3, q4);
+      if (n_nodes) ++*n_nodes;
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, INFINITY);
+      ngx = q1.x; tgx = q1.y;
+      ngy = (hm & 0xFF000000u) | (q0.w >> 24);
+      tgy = hm & 0x00FFFFFFu;
+    }
+    while (tgy) {
+      const int ti = ffs32(tgy) - 1;
+      tgy &= tgy - 1;
+      vec3 v0, e1, e2; uint32_t prim;
+      loadt(tgx + (uint32_t)ti, v0, e1, e2, prim);
+      if (n_tris) ++*n_tris;
+      if (tri_test_any(r.o, r.d, v0, e1, e2, r.tnear)) return true;
+    }
+    if (ngy <= 0x00FFFFFFu) {
+      if (sp == 0) break;
+      --sp; ngx = stack_x[sp]; ngy = stack_y[sp];
+    }
+  }
+  return false;
+}
+
+// ---------------------------------------------------------------------------------------------
+// LBVH (Karras 2012) over sorted 32-bit Morton keys; ties broken by index.
+// ---------------------------------------------------------------------------------------------
+SPRAY_HD int lbvh_delta(const uint32_t* keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  uint32_t a = keys[i], b = keys[j];
+  if (a == b) return 32 + clz32((uint32_t)i ^ (uint32_t)j);
+  return clz32(a ^ b);
+}
+
+// internal node i of n-1: outputs child refs (>=0 internal index, <0: ~leaf_position) and its key range
+SPRAY_HD void lbvh_node(const uint32_t* keys, int n, int i, int* left, int* right, int* first, int* last) {
+  int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+  int dmin = lbvh_delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  int j = i + l * d;
+  int dnode = lbvh_delta(keys, n, i, j);
+  int s = 0;
+  int t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  int gamma = i + s * d + (d < 0 ? -1 : 0);
+  int lo = i < j ? i : j, hi = i < j ? j : i;
+  *left = (lo == gamma) ? ~gamma : gamma;
+  *right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+  *first = lo; *last = hi;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Collapse one binary subtree root into one compressed 8-wide node.
+// Inputs (binary LBVH, n leaves, n-1 internal nodes):
+//   bl/br child refs, bfirst/blast ranges, blo/bhi internal boxes (3 floats each, stride 3),
+//   llo/lhi leaf boxes by sorted position.
+// Outputs: the 80-byte node, the list of internal children (binary refs, in slot order) and the leaf
+//   triangle ranges (sorted positions) in slot order.
+// ---------------------------------------------------------------------------------------------
+#define SPRAY_LEAF_MAX 3
+
+struct CollapseOut {
+  int n_inner;          // number of internal children
+  int inner_ref[8];     // binary internal-node index of each, in increasing slot order
+  int n_tris;           // total leaf triangles (<= 24)
+  int tri_first[8];     // per leaf child (slot order): first sorted position
+  int tri_count[8];     // per leaf child: 1..3
+  int n_leaf;
+  uint8_t meta[8];
+  uint8_t imask;
+  float lo[8][3], hi[8][3]; // child boxes by slot (valid where meta != 0)
+};
+
+SPRAY_HD float box_half_area(const float* lo, const float* hi) {
+  float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+  return dx * dy + dy * dz + dz * dx;
+}
+
+SPRAY_HD void collapse_select(int b, const int* bl, const int* br, const int* bfirst, const int* blast,
+                              const float* blo, const float* bhi, const float* llo, const float* lhi,
+                              CollapseOut* out) {
+  int ref[8]; float area[8]; int cnt[8];
+  int nc = 0;
+  {
+    int c0 = bl[b], c1 = br[b];
+    int cs[2] = {c0, c1};
+    for (int k = 0; k < 2; ++k) {
+      int c = cs[k];
+      ref[nc] = c;
+      if (c < 0) { cnt[nc] = 1; area[nc] = 0.f; }
+      else { cnt[nc] = blast[c] - bfirst[c] + 1; area[nc] = box_half_area(blo + 3 * c, bhi + 3 * c); }
+      ++nc;
+    }
+  }
+  while (nc < 8) {
+    int best = -1; float ba = -1.f;
+    for (int k = 0; k < nc; ++k)
+      if (ref[k] >= 0 && cnt[k] > SPRAY_LEAF_MAX && area[k] > ba) { ba = area[k]; best = k; }
+    if (best < 0) break;
+    int c = ref[best];
+    int cs[2] = {bl[c], br[c]};
+    for (int k = 0; k < 2; ++k) {
+      int cc = cs[k];
+      int dst = (k == 0) ? best : nc;
+      ref[dst] = cc;
+      if (cc < 0) { cnt[dst] = 1; area[dst] = 0.f; }
+      else { cnt[dst] = blast[cc] - bfirst[cc] + 1; area[dst] = box_half_area(blo + 3 * cc, bhi + 3 * cc); }
+    }
+    ++nc;
+  }
+  // child boxes + centroids
+  float clo[8][3], chi[8][3];
+  float nlo[3] = {INFINITY, INFINITY, INFINITY}, nhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int k = 0; k < nc; ++k) {
+    const float* lo; const float* hi;
+    if (ref[k] < 0) { lo = llo + 3 * (~ref[k]); hi = lhi + 3 * (~ref[k]); }
+    else { lo = blo + 3 * ref[k]; hi = bhi + 3 * ref[k]; }
+    for (int a = 0; a < 3; ++a) {
+      clo[k][a] = lo[a]; chi[k][a] = hi[a];
+      nlo[a] = fminf(nlo[a], lo[a]); nhi[a] = fmaxf(nhi[a], hi[a]);
+    }
+  }
+  // greedy octant slot assignment: maximise sum of dot(child centre - node centre, dir(slot))
+  float cost[8][8];
+  for (int k = 0; k < nc; ++k) {
+    float cx = 0.5f * (clo[k][0] + chi[k][0]) - 0.5f * (nlo[0] + nhi[0]);
+    float cy = 0.5f * (clo[k][1] + chi[k][1]) - 0.5f * (nlo[1] + nhi[1]);
+    float cz = 0.5f * (clo[k][2] + chi[k][2]) - 0.5f * (nlo[2] + nhi[2]);
+    for (int s = 0; s < 8; ++s)
+      cost[k][s] = ((s & 1) ? cx : -cx) + ((s & 2) ? cy : -cy) + ((s & 4) ? cz : -cz);
+  }
+  int slot_of[8]; int child_at[8];
+  for (int s = 0; s < 8; ++s) child_at[s] = -1;
+  for (int k = 0; k < 8; ++k) slot_of[k] = -1;
+  for (int it = 0; it < nc; ++it) {
+    int bk = -1, bs = -1; float bc = -INFINITY;
+    for (int k = 0; k < nc; ++k) {
+      if (slot_of[k] >= 0) continue;
+      for (int s = 0; s < 8; ++s) {
+        if (child_at[s] >= 0) continue;
+        if (cost[k][s] > bc) { bc = cost[k][s]; bk = k; bs = s; }
+      }
+    }
+    slot_of[bk] = bs; child_at[bs] = bk;
+  }
+  out->n_inner = 0; out->n_tris = 0; out->n_leaf = 0; out->imask = 0;
+  for (int s = 0; s < 8; ++s) {
+    out->meta[s] = 0;
+    int k = child_at[s];
+    if (k < 0) continue;
+    for (int a = 0; a < 3; ++a) { out->lo[s][a] = clo[k][a]; out->hi[s][a] = chi[k][a]; }
+    if (ref[k] >= 0 && cnt[k] > SPRAY_LEAF_MAX) {
+      out->meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+      out->imask |= (uint8_t)(1u << s);
+      out->inner_ref[out->n_inner++] = ref[k];
+    } else {
+      int first = ref[k] < 0 ? ~ref[k] : bfirst[ref[k]];
+      int c = cnt[k];
+      uint32_t unary = c == 1 ? 1u : (c == 2 ? 3u : 7u);
+      out->meta[s] = (uint8_t)((unary << 5) | (uint32_t)out->n_tris);
+      out->tri_first[out->n_leaf] = first;
+      out->tri_count[out->n_leaf] = c;
+      out->n_leaf++;
+      out->n_tris += c;
+    }
+  }
+}
+
+// quantise child boxes against the node box [nlo, nhi] and emit the 5 x u4 words
+SPRAY_HD void encode_node8(const float* nlo, const float* nhi, const CollapseOut& c, uint32_t child_base,
+                           uint32_t tri_base, u4* q) {
+  uint32_t ebits[3]; float scale[3];
+  for (int a = 0; a < 3; ++a) {
+    float ext = nhi[a] - nlo[a];
+    // smallest e with ext <= 255 * 2^e (with margin for the conservative rounding below)
+    int e;
+    if (!(ext > 0.0f)) e = -126;
+    else {
+      float f = frexpf(ext / 255.0f, &e); // ext/255 = f * 2^e, f in [0.5,1)  =>  2^e > ext/255
+      if (f == 0.5f) --e;                 // exact power of two: 2^(e-1) == ext/255 suffices
+    }
+    if (e < -126) e = -126;
+    if (e > 127) e = 127;
+    // verify 255 * 2^e reaches the far side after FP32 rounding; bump otherwise
+    while (e < 127 && nlo[a] + 255.0f * u2f((uint32_t)(e + 127) << 23) < nhi[a]) ++e;
+    ebits[a] = (uint32_t)(e + 127);
+    scale[a] = u2f(ebits[a] << 23);
+  }
+  uint32_t qlo[3][8], qhi[3][8];
+  for (int s = 0; s < 8; ++s) {
+    for (int a = 0; a < 3; ++a) {
+      if (c.meta[s] == 0) { qlo[a][s] = 255; qhi[a][s] = 0; continue; }
+      float l = floorf((c.lo[s][a] - nlo[a]) / scale[a]);
+      float h = ceilf((c.hi[s][a] - nlo[a]) / scale[a]);
+      int li = (int)fminf(fmaxf(l, 0.f), 255.f), hi = (int)fminf(fmaxf(h, 0.f), 255.f);
+      // enforce conservativeness under the decode expression p + q * 2^e (exact product, one rounding)
+      while (li > 0 && nlo[a] + (float)li * scale[a] > c.lo[s][a]) --li;
+      while (hi < 255 && nlo[a] + (float)hi * scale[a] < c.hi[s][a]) ++hi;
+      qlo[a][s] = (uint32_t)li; qhi[a][s] = (uint32_t)hi;
+    }
+  }
+  auto pack4 = [](const uint32_t* v) -> uint32_t { return v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24); };
+  uint32_t m[8];
+  for (int s = 0; s < 8; ++s) m[s] = c.meta[s];
+  q[0].x = f2u(nlo[0]); q[0].y = f2u(nlo[1]); q[0].z = f2u(nlo[2]);
+  q[0].w = ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | ((uint32_t)c.imask << 24);
+  q[1].x = child_base; q[1].y = tri_base; q[1].z = pack4(m); q[1].w = pack4(m + 4);
+  q[2].x = pack4(qlo[0]); q[2].y = pack4(qlo[0] + 4); q[2].z = pack4(qlo[1]); q[2].w = pack4(qlo[1] + 4);
+  q[3].x = pack4(qlo[2]); q[3].y = pack4(qlo[2] + 4); q[3].z = pack4(qhi[0]); q[3].w = pack4(qhi[0] + 4);
+  q[4].x = pack4(qhi[1]); q[4].y = pack4(qhi[1] + 4); q[4].z = pack4(qhi[2]); q[4].w = pack4(qhi[2] + 4);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Hit attributes — reference src/render/trimesh_buffer.cc:328-360 (colour: float interpolation then
+// truncation to integer; shading normal: unnormalised barycentric mix) and utils/util.h:69-73 (unpack).
+// ---------------------------------------------------------------------------------------------
+SPRAY_HD uint32_t interp_color(uint32_t c0, uint32_t c1, uint32_t c2, float u, float v, float w) {
+  uint32_t out = 0;
+#pragma unroll
+  for (int sh = 16; sh >= 0; sh -= 8) {
+    float a = (float)((c0 >> sh) & 0xffu), b = (float)((c1 >> sh) & 0xffu), c = (float)((c2 >> sh) & 0xffu);
+    float s = add_rn(add_rn(mul_rn(a, w), mul_rn(b, u)), mul_rn(c, v));
+    out |= ((uint32_t)s) << sh;
+  }
+  return out;
+}
+SPRAY_HD float unpack_channel(uint32_t c8) { return (float)((double)c8 * 0.00392156862745098); }
+SPRAY_HD vec3 unpack_color(uint32_t c) {
+  return mk3(unpack_channel((c >> 16) & 0xffu), unpack_channel((c >> 8) & 0xffu), unpack_channel(c & 0xffu));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sampling / BSDF pieces — reference src/render/sampler.h:49-128, sampler.cc:54-60,
+// reflection.h:126-214, light.h:41-89.
+// ---------------------------------------------------------------------------------------------
+SPRAY_HD void concentric_disk(float u1, float u2, float* dx, float* dy) {
+  float r, theta;
+  float sx = sub_rn(mul_rn(2.0f, u1), 1.0f);
+  float sy = sub_rn(mul_rn(2.0f, u2), 1.0f);
+  if (sx == 0.0f && sy == 0.0f) { *dx = 0.0f; *dy = 0.0f; return; }
+  if (sx >= -sy) {
+    if (sx > sy) { r = sx; theta = (sy > 0.0f) ? div_rn(sy, r) : add_rn(8.0f, div_rn(sy, r)); }
+    else { r = sy; theta = sub_rn(2.0f, div_rn(sx, r)); }
+  } else {
+    if (sx <= sy) { r = -sx; theta = sub_rn(4.0f, div_rn(sy, r)); }
+    else { r = -sy; theta = add_rn(6.0f, div_rn(sx, r)); }
+  }
+  theta = (float)((double)theta * (3.14159265358979323846 / 4.0)); // theta *= SPRAY_PI / 4.f (double)
+  *dx = mul_rn(r, cosf(theta));
+  *dy = mul_rn(r, sinf(theta));
+}
+SPRAY_HD vec3 local_to_world(vec3 N, vec3 v) {
+  vec3 dx0 = mk3(0.f, N.z, -N.y);
+  vec3 dx1 = mk3(-N.z, 0.f, N.x);
+  vec3 dx = gnormalize(gdot(dx0, dx0) > gdot(dx1, dx1) ? dx0 : dx1);
+  vec3 dy = gnormalize(gcross(N, dx));
+  return mk3(add_rn(add_rn(mul_rn(dx.x, v.x), mul_rn(dy.x, v.y)), mul_rn(N.x, v.z)),
+             add_rn(add_rn(mul_rn(dx.y, v.x), mul_rn(dy.y, v.y)), mul_rn(N.y, v.z)),
+             add_rn(add_rn(mul_rn(dx.z, v.x), mul_rn(dy.z, v.y)), mul_rn(N.z, v.z)));
+}
+SPRAY_HD void cosine_hemisphere(float u1, float u2, vec3 N, vec3* wi, float* pdf) {
+  vec3 v;
+  concentric_disk(u1, u2, &v.x, &v.y);
+  v.z = sqrt_rn(fmaxf(0.f, sub_rn(sub_rn(1.f, mul_rn(v.x, v.x)), mul_rn(v.y, v.y))));
+  v = gnormalize(v);
+  *wi = gnormalize(local_to_world(N, v));
+  *pdf = mul_rn(v.z, SPRAY_ONE_OVER_PI);
+}
+SPRAY_HD vec3 blinn_phong(float costheta, vec3 kd, vec3 ks, float shininess, vec3 li, vec3 wi, vec3 n, vec3 wo) {
+  vec3 half_hat = gnormalize(gadd(wi, wo));
+  float n_dot_h = gclamp(gdot(n, half_hat), 0.0f, 1.0f);
+  vec3 cs = gscale(ks, powf(n_dot_h, shininess));
+  vec3 cd = gscale(kd, costheta);
+  return gmul(li, gadd(cd, cs));
+}
+SPRAY_HD bool has_positive(vec3 v) { return v.x > 0.0f || v.y > 0.0f || v.z > 0.0f; }
+
+SPRAY_HD float fr_dielectric(float cosI, float etaI, float etaT, vec3 wo, vec3 n, vec3* wt) {
+  float sin2I = fmaxf(0.0f, sub_rn(1.0f, mul_rn(cosI, cosI)));
+  float eta = div_rn(etaI, etaT);
+  float sin2T = mul_rn(mul_rn(eta, eta), sin2I);
+  if (sin2T >= 1.0f) return 1.0f;
+  float cosT = sqrt_rn(sub_rn(1.0f, sin2T));
+  float Rparl = div_rn(sub_rn(mul_rn(etaT, cosI), mul_rn(etaI, cosT)), add_rn(mul_rn(etaT, cosI), mul_rn(etaI, cosT)));
+  float Rperp = div_rn(sub_rn(mul_rn(etaI, cosI), mul_rn(etaT, cosT)), add_rn(mul_rn(etaI, cosI), mul_rn(etaT, cosT)));
+  float fr = div_rn(add_rn(mul_rn(Rparl, Rparl), mul_rn(Rperp, Rperp)), 2.0f);
+  *wt = gadd(gscale(gneg(wo), eta), gscale(n, sub_rn(mul_rn(eta, cosI), cosT)));
+  return fr;
+}
+SPRAY_HD bool refract_dir(float cosI, float etaI, float etaT, vec3 wo, vec3 n, vec3* wt) {
+  float sin2I = fmaxf(0.0f, sub_rn(1.0f, mul_rn(cosI, cosI)));
+  float eta = div_rn(etaI, etaT);
+  float sin2T = mul_rn(mul_rn(eta, eta), sin2I);
+  if (sin2T >= 1.0f) return false;
+  float cosT = sqrt_rn(sub_rn(1.0f, sin2T));
+  *wt = gadd(gscale(gneg(wo), eta), gscale(n, sub_rn(mul_rn(eta, cosI), cosT)));
+  return true;
+}
+
+// Eye ray direction — reference src/render/camera.h:171-209
+struct CameraDev {
+  float pos[3], lowerleft[3], wvec[3], hvec[3];
+  int image_w, image_h;
+};
+SPRAY_HD vec3 camera_dir(const CameraDev& c, float x, float y) {
+  float u = div_rn(x, (float)c.image_w);
+  float v = div_rn(y, (float)c.image_h);
+  vec3 ll = mk3(c.lowerleft[0], c.lowerleft[1], c.lowerleft[2]);
+  vec3 wv = mk3(c.wvec[0], c.wvec[1], c.wvec[2]);
+  vec3 hv = mk3(c.hvec[0], c.hvec[1], c.hvec[2]);
+  vec3 pos = mk3(c.pos[0], c.pos[1], c.pos[2]);
+  return gnormalize(gsub(gadd(gadd(ll, gscale(wv, u)), gscale(hv, v)), pos));
+}
+
+} // namespace spraygpu

@@ -1,0 +1,113 @@
+// internal.cuh — host-side state of libspraygpu (device context, per-domain scene, domain table).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/spray_gpu.h"
+#include "core.cuh"
+
+namespace spraygpu {
+
+void set_error(const char* fmt, ...);
+
+#define SG_CUDA(call)                                                                          \
+  do {                                                                                         \
+    cudaError_t e__ = (call);                                                                  \
+    if (e__ != cudaSuccess) {                                                                  \
+      set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));   \
+      return SPRAYGPU_ERR_CUDA;                                                                \
+    }                                                                                          \
+  } while (0)
+
+#define SG_CHECK(cond, code, ...)            \
+  do {                                       \
+    if (!(cond)) {                           \
+      set_error(__VA_ARGS__);                \
+      return code;                           \
+    }                                        \
+  } while (0)
+
+// device-visible per-domain record (96 B)
+struct DomainEntry {
+  float box[6];           // world AABB as given by the scene description
+  int32_t resident;       // 1 if a committed scene is bound on THIS GPU
+  int32_t mtl_type;       // SPRAYGPU_MTL_*
+  float mtl[3];
+  uint32_t nprims;
+  const uint4* nodes;     // BVH8 nodes (5 x uint4 each)
+  const float4* tris;     // 3 x float4 per triangle, BVH leaf order
+  const float4* attr;     // 3 x float4 per triangle, primID order: (n_k.xyz, rgb_k bits)
+  const float* verts;     // world-space vertices (key -> (u,v) re-derivation)
+  const uint32_t* faces;  // index triples, primID order
+  uint64_t pad;
+};
+static_assert(sizeof(DomainEntry) == 96, "DomainEntry layout");
+
+struct Scratch {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+};
+
+struct Scene;
+
+struct Device {
+  int cuda_device = 0;
+  cudaStream_t stream = nullptr;   // stream every launch goes to (default: legacy default stream)
+  bool own_stream = false;
+  int sm_count = 148;
+  Scratch scratch;                 // build scratch (grown on demand)
+  Scratch stage_in, stage_out;     // device staging for host-pointer calls
+  void* pinned = nullptr;          // pinned bounce buffer for small D2H reads
+  size_t pinned_bytes = 0;
+  // domain table
+  int ndomains = 0;
+  std::vector<DomainEntry> h_domains;
+  std::vector<Scene*> bound;
+  DomainEntry* d_domains = nullptr;
+  bool table_dirty = true;
+  unsigned long long* d_counters = nullptr;  // [0] work counter, [1..] stats
+  uint64_t launches = 0;           // kernels launched by this library (bench "gpu_launches")
+};
+
+struct Scene {
+  Device* dev = nullptr;
+  size_t nv = 0, nf = 0;
+  float* d_verts_obj = nullptr;  // as given by set_mesh
+  uint32_t* d_faces = nullptr;
+  uint32_t* d_rgb = nullptr;
+  bool has_xf = false;
+  float xf[16];
+  // committed
+  bool committed = false;
+  float* d_verts = nullptr;    // world space (aliases d_verts_obj when no transform)
+  float* d_normals = nullptr;  // nv*3
+  uint4* d_nodes = nullptr;
+  uint32_t n_nodes = 0;
+  float4* d_tris = nullptr;
+  float4* d_attr = nullptr;
+  float bounds[6];
+  double build_ms = 0.0;
+};
+
+int ensure_scratch(Scratch& s, size_t bytes);
+int build_scene(Scene* sc);   // build.cu
+int upload_domain_table(Device* dev);
+
+// trace.cu launchers
+int launch_domain_lists(Device* dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts, int32_t* ids,
+                        float* tmins);
+int launch_intersect_scene(Scene* sc, int domain_id, const spraygpu_ray* rays, size_t n, uint64_t* keys, float* uv);
+int launch_occluded_scene(Scene* sc, const spraygpu_ray* rays, size_t n, uint8_t* occ);
+int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint64_t* keys, float* uv, int merge);
+int launch_occluded_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge);
+int launch_hit_attributes(Device* dev, const spraygpu_ray* rays, const uint64_t* keys, size_t n, uint32_t* color,
+                          float* ns3);
+int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, spraygpu_ray* rays);
+int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
+                       float* fb, bool counted);
+
+}  // namespace spraygpu

@@ -1,0 +1,207 @@
+// hostemu.cpp — DEVELOPMENT/TEST harness: runs the __host__ __device__ building blocks of
+// spray_b200/csrc/core.cuh serially on the CPU (LBVH -> 8-wide collapse -> traversal) so the logic can
+// be checked against the oracle in the GPU-less build container.  It is NOT a product path and is
+// never loaded by spray_b200/; tests/test_hostemu.py is its only user.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <numeric>
+#include <vector>
+
+#include "../../spray_b200/csrc/core.cuh"
+
+using namespace spraygpu;
+
+struct EmuScene {
+  std::vector<u4> nodes;        // 5 per node
+  std::vector<float> tris;      // 12 floats per tri (leaf order)
+  std::vector<float> verts;
+  std::vector<uint32_t> faces;
+  int max_sp = 0;
+};
+
+struct NodeLoaderH {
+  const u4* nodes;
+  void operator()(uint32_t idx, u4& q0, u4& q1, u4& q2, u4& q3, u4& q4) const {
+    const u4* p = nodes + 5 * (size_t)idx; q0 = p[0]; q1 = p[1]; q2 = p[2]; q3 = p[3]; q4 = p[4];
+  }
+};
+struct TriLoaderH {
+  const float* tris;
+  void operator()(uint32_t idx, vec3& v0, vec3& e1, vec3& e2, uint32_t& prim) const {
+    const float* p = tris + 12 * (size_t)idx;
+    v0 = mk3(p[0], p[1], p[2]); memcpy(&prim, p + 3, 4);
+    e1 = mk3(p[4], p[5], p[6]); e2 = mk3(p[8], p[9], p[10]);
+  }
+};
+
+static void write_tri(const EmuScene& s, uint32_t prim, float* out) {
+  const uint32_t* f = &s.faces[3 * (size_t)prim];
+  vec3 v0 = mk3(s.verts[3 * f[0]], s.verts[3 * f[0] + 1], s.verts[3 * f[0] + 2]);
+  vec3 v1 = mk3(s.verts[3 * f[1]], s.verts[3 * f[1] + 1], s.verts[3 * f[1] + 2]);
+  vec3 v2 = mk3(s.verts[3 * f[2]], s.verts[3 * f[2] + 1], s.verts[3 * f[2] + 2]);
+  vec3 e1 = gsub(v0, v1), e2 = gsub(v2, v0);
+  out[0] = v0.x; out[1] = v0.y; out[2] = v0.z; memcpy(out + 3, &prim, 4);
+  out[4] = e1.x; out[5] = e1.y; out[6] = e1.z; out[7] = 0;
+  out[8] = e2.x; out[9] = e2.y; out[10] = e2.z; out[11] = 0;
+}
+
+extern "C" {
+
+EmuScene* emu_build(const float* verts, size_t nv, const uint32_t* faces, size_t nf) {
+  EmuScene* s = new EmuScene();
+  s->verts.assign(verts, verts + 3 * nv);
+  s->faces.assign(faces, faces + 3 * nf);
+  const int n = (int)nf;
+  std::vector<float> tlo(3 * nf), thi(3 * nf);
+  float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (size_t i = 0; i < nf; ++i) {
+    for (int a = 0; a < 3; ++a) { tlo[3 * i + a] = INFINITY; thi[3 * i + a] = -INFINITY; }
+    for (int k = 0; k < 3; ++k)
+      for (int a = 0; a < 3; ++a) {
+        float x = verts[3 * (size_t)faces[3 * i + k] + a];
+        tlo[3 * i + a] = fminf(tlo[3 * i + a], x); thi[3 * i + a] = fmaxf(thi[3 * i + a], x);
+      }
+    for (int a = 0; a < 3; ++a) {
+      float c = 0.5f * (tlo[3 * i + a] + thi[3 * i + a]);
+      clo[a] = fminf(clo[a], c); chi[a] = fmaxf(chi[a], c);
+    }
+  }
+  s->tris.resize(12 * nf);
+  if (n == 1) {
+    CollapseOut co; co.n_inner = 0; co.n_tris = 1; co.n_leaf = 1; co.imask = 0;
+    for (int k = 0; k < 8; ++k) co.meta[k] = 0;
+    co.meta[0] = 1u << 5; co.tri_first[0] = 0; co.tri_count[0] = 1;
+    for (int a = 0; a < 3; ++a) { co.lo[0][a] = tlo[a]; co.hi[0][a] = thi[a]; }
+    s->nodes.resize(5);
+    encode_node8(tlo.data(), thi.data(), co, 0, 0, s->nodes.data());
+    write_tri(*s, 0, s->tris.data());
+    return s;
+  }
+  std::vector<uint32_t> keys(nf), order(nf);
+  for (size_t i = 0; i < nf; ++i) {
+    float p[3];
+    for (int a = 0; a < 3; ++a) {
+      float c = 0.5f * (tlo[3 * i + a] + thi[3 * i + a]);
+      float ext = chi[a] - clo[a];
+      p[a] = ext > 0.f ? (c - clo[a]) / ext : 0.f;
+    }
+    keys[i] = morton30(p[0], p[1], p[2]);
+  }
+  std::iota(order.begin(), order.end(), 0u);
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+  std::vector<uint32_t> skeys(nf);
+  std::vector<float> llo(3 * nf), lhi(3 * nf);
+  for (size_t i = 0; i < nf; ++i) {
+    skeys[i] = keys[order[i]];
+    for (int a = 0; a < 3; ++a) { llo[3 * i + a] = tlo[3 * (size_t)order[i] + a]; lhi[3 * i + a] = thi[3 * (size_t)order[i] + a]; }
+  }
+  std::vector<int> bl(n), br(n), bfirst(n), blast(n), parent(2 * n, -1);
+  for (int i = 0; i < n - 1; ++i) {
+    lbvh_node(skeys.data(), n, i, &bl[i], &br[i], &bfirst[i], &blast[i]);
+    parent[bl[i] < 0 ? (n - 1 + ~bl[i]) : bl[i]] = i;
+    parent[br[i] < 0 ? (n - 1 + ~br[i]) : br[i]] = i;
+  }
+  parent[0] = -1;
+  // structural check: every node except the root has exactly one parent
+  std::vector<float> blo(3 * nf, INFINITY), bhi(3 * nf, -INFINITY);
+  std::vector<int> flags(n, 0);
+  for (int i = 0; i < n; ++i) {
+    int p = parent[n - 1 + i];
+    while (p >= 0) {
+      if (flags[p]++ == 0) break;
+      int cs[2] = {bl[p], br[p]};
+      for (int k = 0; k < 2; ++k) {
+        int c = cs[k];
+        const float* lo = c < 0 ? &llo[3 * (size_t)(~c)] : &blo[3 * (size_t)c];
+        const float* hi = c < 0 ? &lhi[3 * (size_t)(~c)] : &bhi[3 * (size_t)c];
+        for (int a = 0; a < 3; ++a) { blo[3 * p + a] = fminf(blo[3 * p + a], lo[a]); bhi[3 * p + a] = fmaxf(bhi[3 * p + a], hi[a]); }
+      }
+      p = parent[p];
+    }
+  }
+  std::vector<int> queue(n);
+  s->nodes.resize(5 * (size_t)n);
+  queue[0] = 0;
+  unsigned node_count = 1, tri_count = 0;
+  int begin = 0, end = 1;
+  while (begin < end) {
+    for (int j = begin; j < end; ++j) {
+      int b = queue[j];
+      CollapseOut co;
+      collapse_select(b, bl.data(), br.data(), bfirst.data(), blast.data(), blo.data(), bhi.data(), llo.data(), lhi.data(), &co);
+      uint32_t child_base = node_count; node_count += co.n_inner;
+      uint32_t tri_base = tri_count; tri_count += co.n_tris;
+      for (int r = 0; r < co.n_inner; ++r) queue[child_base + r] = co.inner_ref[r];
+      encode_node8(&blo[3 * (size_t)b], &bhi[3 * (size_t)b], co, child_base, tri_base, &s->nodes[5 * (size_t)j]);
+      uint32_t off = 0;
+      for (int l = 0; l < co.n_leaf; ++l)
+        for (int k = 0; k < co.tri_count[l]; ++k, ++off)
+          write_tri(*s, order[co.tri_first[l] + k], &s->tris[12 * (size_t)(tri_base + off)]);
+    }
+    begin = end; end = (int)node_count;
+  }
+  s->nodes.resize(5 * (size_t)node_count);
+  if (tri_count != (unsigned)n) { delete s; return nullptr; }
+  return s;
+}
+
+void emu_destroy(EmuScene* s) { delete s; }
+size_t emu_num_nodes(const EmuScene* s) { return s->nodes.size() / 5; }
+
+// rays: 8 floats each (ox,oy,oz,tmin,dx,dy,dz,tmax)
+void emu_intersect(EmuScene* s, uint32_t domain, const float* rays, size_t n, uint64_t* keys, float* uv,
+                   uint64_t* n_nodes, uint64_t* n_tris) {
+  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  uint64_t tn = 0, tt = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const float* r = rays + 8 * i;
+    RayCtx rc = make_ray_ctx(mk3(r[0], r[1], r[2]), mk3(r[4], r[5], r[6]), r[3]);
+    Closest c; c.t = INFINITY; c.u = c.v = 0; c.prim = 0xFFFFFFFFu;
+    uint32_t nn = 0, nt = 0;
+    bvh8_closest(NodeLoaderH{s->nodes.data()}, TriLoaderH{s->tris.data()}, rc, c, sx, sy, &nn, &nt);
+    tn += nn; tt += nt;
+    bool hit = c.prim != 0xFFFFFFFFu;
+    keys[i] = hit ? make_key(c.t, domain, c.prim) : SPRAY_KEY_MISS;
+    if (uv) { uv[2 * i] = hit ? c.u : 0.f; uv[2 * i + 1] = hit ? c.v : 0.f; }
+  }
+  if (n_nodes) *n_nodes = tn;
+  if (n_tris) *n_tris = tt;
+}
+
+void emu_occluded(EmuScene* s, const float* rays, size_t n, uint8_t* occ) {
+  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  for (size_t i = 0; i < n; ++i) {
+    const float* r = rays + 8 * i;
+    RayCtx rc = make_ray_ctx(mk3(r[0], r[1], r[2]), mk3(r[4], r[5], r[6]), r[3]);
+    occ[i] = bvh8_any(NodeLoaderH{s->nodes.data()}, TriLoaderH{s->tris.data()}, rc, sx, sy, nullptr, nullptr) ? 1 : 0;
+  }
+}
+
+// closed-form pieces, for cross-checking core.cuh against the oracle
+uint32_t emu_rng_init1(uint32_t id) { return rng_init1(id); }
+float emu_rng_float(uint32_t* s) { return rng_float(*s); }
+uint32_t emu_morton(float x, float y, float z) { return morton30(x, y, z); }
+int emu_domain_slab(const float* b, const float* o, const float* d, float* tmin) {
+  return domain_slab(b, mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), SPRAY_RAY_EPS, INFINITY, tmin) ? 1 : 0;
+}
+uint32_t emu_interp_color(uint32_t c0, uint32_t c1, uint32_t c2, float u, float v) {
+  return interp_color(c0, c1, c2, u, v, sub_rn(sub_rn(1.f, u), v));
+}
+void emu_cosine_hemisphere(float u1, float u2, const float* n, float* wi, float* pdf) {
+  vec3 w; cosine_hemisphere(u1, u2, mk3(n[0], n[1], n[2]), &w, pdf); wi[0] = w.x; wi[1] = w.y; wi[2] = w.z;
+}
+void emu_blinn_phong(float costheta, const float* kd, const float* ks, float sh, const float* li, const float* wi,
+                     const float* n, const float* wo, float* out) {
+  vec3 r = blinn_phong(costheta, mk3(kd[0], kd[1], kd[2]), mk3(ks[0], ks[1], ks[2]), sh, mk3(li[0], li[1], li[2]),
+                       mk3(wi[0], wi[1], wi[2]), mk3(n[0], n[1], n[2]), mk3(wo[0], wo[1], wo[2]));
+  out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+void emu_camera_dir(const float* cam13, int w, int h, float x, float y, float* dir) {
+  CameraDev c;
+  for (int k = 0; k < 3; ++k) { c.pos[k] = cam13[k]; c.lowerleft[k] = cam13[3 + k]; c.wvec[k] = cam13[6 + k]; c.hvec[k] = cam13[9 + k]; }
+  c.image_w = w; c.image_h = h;
+  vec3 d = camera_dir(c, x, y); dir[0] = d.x; dir[1] = d.y; dir[2] = d.z;
+}
+}
