@@ -270,9 +270,10 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
       const float t1y = fmaf((float)byte_of(fary, j), aiy, fy);
       const float t1z = fmaf((float)byte_of(farz, j), aiz, fz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
-      // 1 + 2^-21: the quantised box is conservative for the geometry, this covers FP32 rounding of
-      // the six plane distances relative to the triangle test's t
-      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.00000048f;
+      // The quantised box is conservative for the exact geometry; the 1e-5 relative slack (cmin > 0, so
+      // one multiply widens the interval on both sides) covers FP32 rounding of the six plane distances
+      // AND rays the FP32 triangle test accepts although they graze just outside the exact triangle.
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.00001f;
       if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
     }
   }

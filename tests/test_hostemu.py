@@ -1,0 +1,144 @@
+"""core.cuh (the product's __host__ __device__ building blocks) executed on the CPU by the development
+harness tests/hostemu and compared with the oracle: LBVH -> 8-wide collapse -> traversal, and every
+closed-form piece that has a reference-order contract.  Runs in the GPU-less container."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import make_rays, random_rays
+from spray_b200 import scenes
+
+f32 = np.float32
+
+
+def _emu_intersect(E, h, rays, dom=0):
+    n = len(rays)
+    keys = np.zeros(n, np.uint64); uv = np.zeros((n, 2), np.float32)
+    nn, nt = C.c_uint64(), C.c_uint64()
+    E.emu_intersect(h, dom, rays.ctypes.data, n, keys.ctypes.data, uv.ctypes.data, C.byref(nn), C.byref(nt))
+    return keys, uv, nn.value / max(n, 1), nt.value / max(n, 1)
+
+
+def test_bvh8_wavelet_equals_oracle(oracle, hostemu):
+    sc = scenes.wavelet_single()
+    d = sc["domains"][0]
+    osc = oracle.Scene(sc["domains"])
+    h = hostemu.emu_build(d["verts"].ctypes.data, len(d["verts"]), d["faces"].ctypes.data, len(d["faces"]))
+    assert h
+    assert hostemu.emu_num_nodes(h) < len(d["faces"]) // 3
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cam = oracle.camera_from_desc(scenes.camera_frame(pos, lookat, up, 90.0, 160, 160))
+    rays = np.concatenate([oracle.gen_eye_rays(cam, (0, 0, 160, 160)), random_rays(30000, [-10] * 3, [10] * 3, seed=2)])
+    k, uv, nn, nt = _emu_intersect(hostemu, h, rays)
+    ko, uvo = osc.intersect_domain(0, rays)
+    assert np.array_equal(k, ko) and np.array_equal(uv, uvo)
+    assert nn < 20 and nt < 12
+    occ = np.zeros(len(rays), np.uint8)
+    hostemu.emu_occluded(h, rays.ctypes.data, len(rays), occ.ctypes.data)
+    assert np.array_equal(occ, osc.occluded_domain(0, rays))
+    # axis-parallel rays from lattice points: zero direction components, origins exactly on vertex planes
+    rng = np.random.default_rng(7)
+    n = 20000
+    o = np.round(rng.uniform(-14, 14, (n, 3))).astype(np.float32)
+    dd = np.zeros((n, 3), np.float32)
+    dd[np.arange(n), rng.integers(0, 3, n)] = np.where(rng.random(n) < 0.5, 1, -1)
+    r2 = make_rays(o, dd)
+    k, uv, _, _ = _emu_intersect(hostemu, h, r2)
+    ko, uvo = osc.intersect_domain(0, r2)
+    assert np.array_equal(k, ko) and np.array_equal(uv, uvo)
+    hostemu.emu_destroy(h)
+
+
+@pytest.mark.parametrize("ntris", [1, 2, 3, 4, 9, 100, 5000])
+def test_bvh8_soup_and_tiny_meshes(oracle, hostemu, ntris):
+    v, f, rgb = scenes.soup_domain(3, ntris, (0, 0, 0), (20, 20, 20))
+    dom = dict(verts=v, faces=f, rgb=rgb, transform=None, bounds=np.array([0, 0, 0, 20, 20, 20], np.float32))
+    osc = oracle.Scene([dom])
+    h = hostemu.emu_build(v.ctypes.data, len(v), f.ctypes.data, len(f))
+    assert h
+    rays = random_rays(8000, [0] * 3, [20] * 3, seed=ntris)
+    if ntris <= 4:   # aim at the few triangles so that something is hit
+        tgt = v[np.random.default_rng(1).integers(0, len(v), len(rays))]
+        dd = tgt - rays[:, 0:3]; dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+        rays[:, 4:7] = dd
+    k, uv, _, _ = _emu_intersect(hostemu, h, rays)
+    ko, uvo = osc.intersect_domain(0, rays)
+    assert (ko != oracle.KEY_MISS).any()
+    assert np.array_equal(k, ko) and np.array_equal(uv, uvo)
+    hostemu.emu_destroy(h)
+
+
+def test_degenerate_and_duplicate_triangles(oracle, hostemu):
+    """Zero-area triangles, exact duplicates (Morton-key ties) and coplanar overlaps: ties resolve to the
+    lowest primID in both implementations."""
+    base, f0, _ = scenes.soup_domain(9, 300, (0, 0, 0), (10, 10, 10))
+    v = np.concatenate([base, base[:300], np.zeros((3, 3), np.float32) + 5.0]).astype(np.float32)
+    f = np.concatenate([f0, f0[:100] + 0, (np.arange(300, dtype=np.uint32).reshape(100, 3) + np.uint32(len(base))),
+                        np.array([[len(v) - 3, len(v) - 2, len(v) - 1]], np.uint32)]).astype(np.uint32)
+    dom = dict(verts=v, faces=f, rgb=None, transform=None, bounds=np.array([0, 0, 0, 10, 10, 10], np.float32))
+    osc = oracle.Scene([dom])
+    h = hostemu.emu_build(v.ctypes.data, len(v), f.ctypes.data, len(f))
+    assert h
+    rays = random_rays(20000, [0] * 3, [10] * 3, seed=5)
+    k, uv, _, _ = _emu_intersect(hostemu, h, rays)
+    ko, uvo = osc.intersect_domain(0, rays)
+    assert np.array_equal(k, ko) and np.array_equal(uv, uvo)
+    _, _, prim = oracle.key_fields(ko[ko != oracle.KEY_MISS])
+    assert prim.max() < 300 + 100 + 100 + 1
+    hostemu.emu_destroy(h)
+
+
+def test_closed_forms_equal_oracle(oracle, hostemu):
+    L, E = oracle.lib(), hostemu
+    fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+    rng = np.random.default_rng(0)
+    for seed in [0, 1, 99, 2 ** 31 - 1, 0xFFFFFFFF, 123456789]:
+        a = L.orc_rng_init1(C.c_int(seed if seed < 2 ** 31 else seed - 2 ** 32)); b = E.emu_rng_init1(seed)
+        assert a == b
+        sa, sb = C.c_uint32(a), C.c_uint32(b)
+        for _ in range(8):
+            assert L.orc_rng_get_float(C.byref(sa)) == E.emu_rng_float(C.byref(sb)) and sa.value == sb.value
+    for x, y, z in rng.uniform(-0.2, 1.2, (200, 3)).astype(np.float32):
+        assert L.orc_morton(x, y, z) == E.emu_morton(x, y, z)
+    box = np.array([-10, -10, -10, 10, 9.324713, 10], np.float32)
+    for _ in range(500):
+        o = rng.uniform(-30, 30, 3).astype(np.float32); d = rng.normal(size=3).astype(np.float32)
+        if rng.random() < 0.3:
+            d[rng.integers(0, 3)] = 0.0
+        if rng.random() < 0.3:
+            o = np.round(o / 10) * 10
+            o = o.astype(np.float32)
+        t1, t2, tm = C.c_float(), C.c_float(), C.c_float()
+        a = L.orc_intersect_aabb(fp(box), fp(o), fp(d), f32(1e-3), f32(np.inf), C.byref(t1), C.byref(t2))
+        b = E.emu_domain_slab(box.ctypes.data, o.ctypes.data, d.ctypes.data, C.byref(tm))
+        assert bool(a) == bool(b)
+        if a:
+            assert t1.value == tm.value
+    for _ in range(300):
+        cs = [int(x) for x in rng.integers(0, 1 << 24, 3)]
+        u = f32(rng.uniform(0, 1)); v = f32(rng.uniform(0, 1 - u))
+        assert L.orc_interp_color(cs[0], cs[1], cs[2], u, v) == E.emu_interp_color(cs[0], cs[1], cs[2], u, v)
+    for _ in range(300):
+        n = rng.normal(size=3); n = (n / np.linalg.norm(n)).astype(np.float32)
+        u1, u2 = f32(rng.random()), f32(rng.random())
+        wa, wb = np.zeros(3, np.float32), np.zeros(3, np.float32); pa, pb = C.c_float(), C.c_float()
+        L.orc_cosine_hemisphere(u1, u2, fp(n), fp(wa), C.byref(pa))
+        E.emu_cosine_hemisphere(u1, u2, n.ctypes.data, wb.ctypes.data, C.byref(pb))
+        assert np.array_equal(wa, wb) and pa.value == pb.value
+        kd = rng.random(3).astype(np.float32); ks = np.full(3, 0.4, np.float32); li = np.ones(3, np.float32)
+        wo = rng.normal(size=3); wo = (wo / np.linalg.norm(wo)).astype(np.float32)
+        oa, ob = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        L.orc_blinn_phong(f32(0.7), fp(kd), fp(ks), f32(10.0), fp(li), fp(wa), fp(n), fp(wo), fp(oa))
+        E.emu_blinn_phong(f32(0.7), kd.ctypes.data, ks.ctypes.data, f32(10.0), li.ctypes.data, wb.ctypes.data, n.ctypes.data, wo.ctypes.data, ob.ctypes.data)
+        assert np.array_equal(oa, ob)
+    p = scenes.WAVELETS64_CAMERA
+    cd = scenes.camera_frame(p["pos"], p["lookat"], p["up"], 90.0, 2048, 2048)
+    cam = oracle.camera_from_desc(cd)
+    c13 = np.concatenate([cd["pos"], cd["lowerleft"], cd["wvec"], cd["hvec"]]).astype(np.float32)
+    for _ in range(300):
+        x, y = f32(rng.uniform(0, 2048)), f32(rng.uniform(0, 2048))
+        org = np.zeros(3, np.float32); da = np.zeros(3, np.float32); db = np.zeros(3, np.float32)
+        L.orc_camera_ray(C.byref(cam), x, y, fp(org), fp(da))
+        E.emu_camera_dir(c13.ctypes.data, 2048, 2048, x, y, db.ctypes.data)
+        assert np.array_equal(da, db)
