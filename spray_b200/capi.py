@@ -10,7 +10,8 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libspraygpu.so")
+# SPRAYGPU_LIB selects an experimental build variant of the SAME sources (tools/variants.sh)
+LIB_PATH = os.environ.get("SPRAYGPU_LIB") or os.path.join(_HERE, "libspraygpu.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "spray_gpu.h")
 
 KEY_MISS = 0xFFFFFFFFFFFFFFFF

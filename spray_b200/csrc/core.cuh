@@ -233,6 +233,16 @@ SPRAY_HD RayCtx make_ray_ctx(vec3 o, vec3 d, float tnear) {
 
 SPRAY_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
 
+// byte j of w as a float, WITHOUT the XU-pipe I2F: PRMT builds 0x4B0000qq (= 2^23 + q), one FADD removes
+// the 2^23 (exact).  ncu on the first build showed the quarter-rate XU pipe saturated by 48 I2F per node.
+SPRAY_HD float byte_to_float(uint32_t w, int j) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u | (uint32_t)j)) - 8388608.0f;
+#else
+  return (float)byte_of(w, j);
+#endif
+}
+
 // returns the 32-bit hit mask of one node: bits 31..24 internal children in traversal priority order,
 // bits 23..0 one bit per leaf triangle.
 SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4, const RayCtx& r,
@@ -263,12 +273,12 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const float t0x = fmaf((float)byte_of(nearx, j), aix, ox);
-      const float t0y = fmaf((float)byte_of(neary, j), aiy, oy);
-      const float t0z = fmaf((float)byte_of(nearz, j), aiz, oz);
-      const float t1x = fmaf((float)byte_of(farx, j), aix, fx);
-      const float t1y = fmaf((float)byte_of(fary, j), aiy, fy);
-      const float t1z = fmaf((float)byte_of(farz, j), aiz, fz);
+      const float t0x = fmaf(byte_to_float(nearx, j), aix, ox);
+      const float t0y = fmaf(byte_to_float(neary, j), aiy, oy);
+      const float t0z = fmaf(byte_to_float(nearz, j), aiz, oz);
+      const float t1x = fmaf(byte_to_float(farx, j), aix, fx);
+      const float t1y = fmaf(byte_to_float(fary, j), aiy, fy);
+      const float t1z = fmaf(byte_to_float(farz, j), aiz, fz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
       // The quantised box is conservative for the exact geometry; the 1e-5 relative slack (cmin > 0, so
       // one multiply widens the interval on both sides) covers FP32 rounding of the six plane distances

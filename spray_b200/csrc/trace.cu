@@ -38,28 +38,124 @@ struct TriLoaderG {
   }
 };
 
-// ---- ray -> sorted list of entered domains (a6).  Keeps the MAXLIST nearest entries with key > after;
-//      returns the count, *more = true if entries beyond the kept ones exist.
-__device__ __forceinline__ int domain_list(const float* __restrict__ boxes, const uint8_t* __restrict__ resident,
-                                           int nd, vec3 o, vec3 d, bool have_after, uint64_t after,
+// ------------------------------------------------------------------------------------------------
+// Domain culling (a6), two stages:
+//  1. warp_cull: the warp's active rays are bounded by an origin box and a direction box; every lane tests
+//     nd/32 domain boxes against that BEAM (decoupled per-axis interval test, conservative) and a ballot
+//     publishes the candidate bit mask.  For coherent rays (8x4 pixel blocks, shadow rays to one light)
+//     this leaves ~10 of 64 boxes; for incoherent rays it degrades gracefully to "all boxes".
+//  2. each lane runs the reference's exact slab test (aabb.h:139-169) on the candidates only and keeps
+//     its own (tmin, id)-sorted list.
+// ------------------------------------------------------------------------------------------------
+#define CAND_WORDS (SPRAYGPU_MAX_DOMAINS / 32)
+
+struct DomSmem {
+  const float* boxes;       // nd x 6
+  const uint8_t* resident;  // nd
+  uint32_t* cand;           // this warp's CAND_WORDS candidate words
+  int nd;
+};
+
+__host__ __device__ inline size_t dom_smem_bytes(int nd, int nwarps) {
+  return (size_t)nd * 6 * sizeof(float) + (((size_t)nd + 15) & ~(size_t)15) + (size_t)nwarps * CAND_WORDS * 4;
+}
+
+__device__ __forceinline__ DomSmem load_domain_smem(const DomainEntry* __restrict__ table, int nd, float* smem) {
+  float* boxes = smem;
+  uint8_t* resident = (uint8_t*)(boxes + 6 * nd);
+  uint32_t* cand = (uint32_t*)(resident + ((nd + 15) & ~15));
+  for (int i = threadIdx.x; i < nd; i += blockDim.x) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) boxes[6 * i + k] = table[i].box[k];
+    resident[i] = (uint8_t)table[i].resident;
+  }
+  __syncthreads();
+  DomSmem d;
+  d.boxes = boxes; d.resident = resident; d.cand = cand + (threadIdx.x >> 5) * CAND_WORDS; d.nd = nd;
+  return d;
+}
+
+__device__ __forceinline__ float warp_min_f(float v) { return sortable_float(__reduce_min_sync(0xffffffffu, float_sortable(v))); }
+__device__ __forceinline__ float warp_max_f(float v) { return sortable_float(__reduce_max_sync(0xffffffffu, float_sortable(v))); }
+
+// one axis of the beam/box test: the beam's coordinate range at parameter t >= 0 is
+// [o0 + t*d0, o1 + t*d1]; it must overlap [lo, hi]:  o0 + t*d0 <= hi  and  o1 + t*d1 >= lo.
+__device__ __forceinline__ void beam_axis(float lo, float hi, float o0, float o1, float d0, float d1, float r0, float r1,
+                                          float& tl, float& th) {
+  const float a = (hi - o0) * r0;  // o0 + t*d0 <= hi
+  if (d0 > 0.0f) th = fminf(th, a);
+  else if (d0 < 0.0f) tl = fmaxf(tl, a);
+  else if (o0 > hi) th = -INFINITY;
+  const float b = (lo - o1) * r1;  // o1 + t*d1 >= lo
+  if (d1 > 0.0f) tl = fmaxf(tl, b);
+  else if (d1 < 0.0f) th = fminf(th, b);
+  else if (o1 < lo) th = -INFINITY;
+}
+
+// `only_resident`: skip domains that are not resident on this GPU (traversal); the parity surface
+// spraygpu_domain_lists reports all entered domains.
+__device__ __forceinline__ void warp_cull(const DomSmem& D, bool active, vec3 o, vec3 d, bool only_resident) {
+  const int lane = threadIdx.x & 31;
+  const int nwords = (D.nd + 31) >> 5;
+  const float o0x = warp_min_f(active ? o.x : INFINITY), o1x = warp_max_f(active ? o.x : -INFINITY);
+  const float o0y = warp_min_f(active ? o.y : INFINITY), o1y = warp_max_f(active ? o.y : -INFINITY);
+  const float o0z = warp_min_f(active ? o.z : INFINITY), o1z = warp_max_f(active ? o.z : -INFINITY);
+  const float d0x = warp_min_f(active ? d.x : INFINITY), d1x = warp_max_f(active ? d.x : -INFINITY);
+  const float d0y = warp_min_f(active ? d.y : INFINITY), d1y = warp_max_f(active ? d.y : -INFINITY);
+  const float d0z = warp_min_f(active ? d.z : INFINITY), d1z = warp_max_f(active ? d.z : -INFINITY);
+  const bool any = o0x <= o1x;  // false when no lane is active (or NaN origins: then pass everything below)
+  const bool finite = (o1x - o0x) < INFINITY && (o1y - o0y) < INFINITY && (o1z - o0z) < INFINITY &&
+                      (d1x - d0x) < INFINITY && (d1y - d0y) < INFINITY && (d1z - d0z) < INFINITY;
+  // scene-scale pad: absorbs the FP32 rounding differences between this test and the exact slab test
+  const float pad = 1e-4f * (fabsf(o0x) + fabsf(o1x) + fabsf(o0y) + fabsf(o1y) + fabsf(o0z) + fabsf(o1z) + 1.0f);
+  const float r0x = __frcp_rn(d0x), r1x = __frcp_rn(d1x), r0y = __frcp_rn(d0y), r1y = __frcp_rn(d1y),
+              r0z = __frcp_rn(d0z), r1z = __frcp_rn(d1z);
+  for (int w = 0; w < nwords; ++w) {
+    const int i = (w << 5) + lane;
+    bool pass = false;
+    if (i < D.nd && (!only_resident || D.resident[i])) {
+      if (!finite) pass = any;
+      else if (any) {
+        const float* b = D.boxes + 6 * i;
+        const float bp = pad + 1e-4f * (fabsf(b[0]) + fabsf(b[1]) + fabsf(b[2]) + fabsf(b[3]) + fabsf(b[4]) + fabsf(b[5]));
+        float tl = 0.0f, th = INFINITY;
+        beam_axis(b[0] - bp, b[3] + bp, o0x, o1x, d0x, d1x, r0x, r1x, tl, th);
+        beam_axis(b[1] - bp, b[4] + bp, o0y, o1y, d0y, d1y, r0y, r1y, tl, th);
+        beam_axis(b[2] - bp, b[5] + bp, o0z, o1z, d0z, d1z, r0z, r1z, tl, th);
+        pass = !(tl * 0.9999f > th * 1.0001f + 1e-6f);  // NaN -> pass (conservative)
+      }
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, pass);
+    if (lane == 0) D.cand[w] = m;
+  }
+  __syncwarp();
+}
+
+// per-lane exact test on the candidates: keeps the MAXLIST nearest entries with key > after.
+__device__ __forceinline__ int domain_list(const DomSmem& D, vec3 o, vec3 d, bool have_after, uint64_t after,
                                            uint64_t* list, bool* more) {
   int cnt = 0;
   bool overflow = false;
-  for (int i = 0; i < nd; ++i) {
-    if (resident && !resident[i]) continue;
-    float tmin;
-    if (!domain_slab(boxes + 6 * i, o, d, SPRAY_RAY_EPS, INFINITY, &tmin)) continue;
-    const uint64_t key = ((uint64_t)float_sortable(tmin) << 32) | (uint32_t)i;
-    if (have_after && key <= after) continue;
-    if (cnt == MAXLIST) {
-      overflow = true;
-      if (key >= list[MAXLIST - 1]) continue;
-      cnt = MAXLIST - 1;
+  const int nwords = (D.nd + 31) >> 5;
+  for (int w = 0; w < nwords; ++w) {
+    uint32_t m = D.cand[w];
+    while (m) {
+      const int i = (w << 5) + __ffs((int)m) - 1;
+      m &= m - 1;
+      float tmin;
+      if (!domain_slab(D.boxes + 6 * i, o, d, SPRAY_RAY_EPS, INFINITY, &tmin)) continue;
+      const uint64_t key = ((uint64_t)float_sortable(tmin) << 32) | (uint32_t)i;
+      if (have_after && key <= after) continue;
+      if (cnt == MAXLIST) {
+        overflow = true;
+        if (key >= list[MAXLIST - 1]) continue;
+        cnt = MAXLIST - 1;
+      }
+      int k = cnt;
+      while (k > 0 && list[k - 1] > key) { list[k] = list[k - 1]; --k; }
+      list[k] = key;
+      ++cnt;
     }
-    int k = cnt;
-    while (k > 0 && list[k - 1] > key) { list[k] = list[k - 1]; --k; }
-    list[k] = key;
-    ++cnt;
   }
   *more = overflow;
   return cnt;
@@ -70,10 +166,10 @@ struct SceneHit {
   uint32_t prim, dom;
 };
 
+// closest hit over the warp-culled candidate domains; call warp_cull(..., true) first (all lanes).
 template <bool COUNT>
-__device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const float* boxes,
-                                              const uint8_t* resident, int nd, vec3 o, vec3 d, SceneHit& out,
-                                              uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+__device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
+                                              SceneHit& out, uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
   uint64_t list[MAXLIST];
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
   out.t = INFINITY; out.prim = 0; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
@@ -81,9 +177,10 @@ __device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ ta
   bool have_after = false, more = false, done = false;
   uint64_t after = 0;
   do {
-    const int n = domain_list(boxes, resident, nd, o, d, have_after, after, list, &more);
+    const int n = domain_list(D, o, d, have_after, after, list, &more);
     for (int k = 0; k < n && !done; ++k) {
       const float tdom = sortable_float((uint32_t)(list[k] >> 32));
+      // front-to-back early out (an optimisation only; slack keeps it conservative)
       if (out.t < INFINITY && tdom > out.t * 1.0001f + 1e-4f) { done = true; break; }
       const uint32_t id = (uint32_t)list[k];
       const DomainEntry* e = table + id;
@@ -102,21 +199,21 @@ __device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ ta
 }
 
 template <bool COUNT>
-__device__ __forceinline__ bool scene_occluded(const DomainEntry* __restrict__ table, const float* boxes,
-                                               const uint8_t* resident, int nd, vec3 o, vec3 d, uint32_t* cnt) {
+__device__ __forceinline__ bool scene_occluded(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
+                                               uint32_t* cnt) {
   uint64_t list[MAXLIST];
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
   const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
   bool have_after = false, more = false;
   uint64_t after = 0;
   do {
-    const int n = domain_list(boxes, resident, nd, o, d, have_after, after, list, &more);
+    const int n = domain_list(D, o, d, have_after, after, list, &more);
     for (int k = 0; k < n; ++k) {
       const DomainEntry* e = table + (uint32_t)list[k];
-      NodeLoaderG ln{e->nodes};
-      TriLoaderG lt{e->tris};
       if (COUNT) cnt[0]++;
-      if (bvh8_any(ln, lt, r, sx, sy, COUNT ? cnt + 1 : nullptr, COUNT ? cnt + 2 : nullptr)) return true;
+      if (bvh8_any(NodeLoaderG{e->nodes}, TriLoaderG{e->tris}, r, sx, sy, COUNT ? cnt + 1 : nullptr,
+                   COUNT ? cnt + 2 : nullptr))
+        return true;
     }
     if (n > 0) { after = list[n - 1]; have_after = true; }
   } while (more);
@@ -135,36 +232,28 @@ __device__ __forceinline__ void fetch_attributes(const DomainEntry* e, uint32_t 
   Ns->z = add_rn(add_rn(mul_rn(a.z, w), mul_rn(b.z, u)), mul_rn(c.z, v));
 }
 
-__device__ __forceinline__ void load_domain_smem(const DomainEntry* __restrict__ table, int nd, float* boxes,
-                                                 uint8_t* resident) {
-  for (int i = threadIdx.x; i < nd; i += blockDim.x) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) boxes[6 * i + k] = table[i].box[k];
-    resident[i] = (uint8_t)table[i].resident;
-  }
-  __syncthreads();
-}
-
 // ------------------------------------------------------------------------------------------------
-// batched kernels
+// batched kernels.  No thread leaves before the warp-cooperative culling: out-of-range lanes stay as
+// inactive participants.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
     domain_lists_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays, size_t n,
                         int cap, int32_t* __restrict__ counts, int32_t* __restrict__ ids, float* __restrict__ tmins) {
   extern __shared__ float smem[];
-  float* boxes = smem;
-  uint8_t* resident = (uint8_t*)(boxes + 6 * nd);
-  load_domain_smem(table, nd, boxes, resident);
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const spraygpu_ray ry = rays[i];
+  const DomSmem D = load_domain_smem(table, nd, smem);
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const bool valid = i < n;
+  spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
+  if (valid) ry = rays[i];
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
+  warp_cull(D, valid, o, d, false);
+  if (!valid) return;
   uint64_t list[MAXLIST];
   bool have_after = false, more = false;
   uint64_t after = 0;
   int total = 0;
   do {
-    const int c = domain_list(boxes, nullptr, nd, o, d, have_after, after, list, &more);
+    const int c = domain_list(D, o, d, have_after, after, list, &more);
     for (int k = 0; k < c; ++k, ++total) {
       if (total < cap) {
         ids[i * cap + total] = (int32_t)(uint32_t)list[k];
@@ -207,14 +296,16 @@ __global__ void __launch_bounds__(128)
     intersect_domains_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays,
                              size_t n, uint64_t* __restrict__ keys, float* __restrict__ uv, int merge) {
   extern __shared__ float smem[];
-  float* boxes = smem;
-  uint8_t* resident = (uint8_t*)(boxes + 6 * nd);
-  load_domain_smem(table, nd, boxes, resident);
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const spraygpu_ray ry = rays[i];
+  const DomSmem D = load_domain_smem(table, nd, smem);
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const bool valid = i < n;
+  spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
+  if (valid) ry = rays[i];
+  const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
+  warp_cull(D, valid, o, d, true);
+  if (!valid) return;
   SceneHit h;
-  scene_closest<false>(table, boxes, resident, nd, mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), h, nullptr);
+  scene_closest<false>(table, D, o, d, h, nullptr);
   const bool hit = h.t < INFINITY;
   const uint64_t key = hit ? make_key(h.t, h.dom, h.prim) : SPRAY_KEY_MISS;
   if (merge) {
@@ -231,17 +322,18 @@ __global__ void __launch_bounds__(128)
     occluded_domains_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays,
                             size_t n, uint8_t* __restrict__ occ, int merge) {
   extern __shared__ float smem[];
-  float* boxes = smem;
-  uint8_t* resident = (uint8_t*)(boxes + 6 * nd);
-  load_domain_smem(table, nd, boxes, resident);
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (merge && occ[i]) return;  // already occluded elsewhere
-  const spraygpu_ray ry = rays[i];
-  const bool o = scene_occluded<false>(table, boxes, resident, nd, mk3(ry.ox, ry.oy, ry.oz),
-                                       mk3(ry.dx, ry.dy, ry.dz), nullptr);
-  if (merge) { if (o) occ[i] = 1; }
-  else occ[i] = o ? 1 : 0;
+  const DomSmem D = load_domain_smem(table, nd, smem);
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  // merge: rays already occluded elsewhere (or flagged 1 by the caller as "not a ray") are skipped
+  const bool valid = i < n && !(merge && occ[i]);
+  spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
+  if (valid) ry = rays[i];
+  const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
+  warp_cull(D, valid, o, d, true);
+  if (!valid) return;
+  const bool oc = scene_occluded<false>(table, D, o, d, nullptr);
+  if (merge) { if (oc) occ[i] = 1; }
+  else occ[i] = oc ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(128)
@@ -303,7 +395,15 @@ __global__ void __launch_bounds__(256)
 }
 
 // ------------------------------------------------------------------------------------------------
-// the fused persistent render kernel
+// The fused persistent render kernel.
+//
+// Persistent CTAs (SM count x resident CTAs/SM); each WARP pulls 32 sample slots (one 8x4 pixel block) at a
+// time from a global counter and carries them through the whole ray stream in warp-synchronous
+// generations:   closest-hit rays -> shade -> shadow rays (one light sample per pass) -> bounce rays.
+// Every stage starts with the warp-cooperative domain culling above, so the lanes of a warp stay in
+// the same stage (their traversals still diverge in length, as in any per-lane BVH walk).
+// Reference: ooc::Tracer::trace tile body (ooc_tracer.inl:184-234), TContext::procRads/procShads/retire
+// (ooc_tcontext.inl:29-135), ShaderPt / ShaderAo (ooc_shader_pt.h:94-227, ooc_shader_ao.h:92-197).
 // ------------------------------------------------------------------------------------------------
 struct RenderParams {
   const DomainEntry* table;
@@ -319,31 +419,20 @@ struct RenderParams {
 
 struct Pending { vec3 o, d, w; int depth; };
 
+#ifndef SPRAY_RENDER_MINBLOCKS
+#define SPRAY_RENDER_MINBLOCKS 3
+#endif
 template <bool COUNT>
-__device__ __forceinline__ void shadow_and_add(const RenderParams& P, const float* boxes, const uint8_t* resident,
-                                               vec3 pos, vec3 wi, vec3 Lr, uint32_t pixid, float scale,
-                                               uint32_t* cnt, uint32_t* n_shadow) {
-  ++*n_shadow;
-  if (!scene_occluded<COUNT>(P.table, boxes, resident, P.nd, pos, wi, cnt)) {
-    // TContext::retire -> HdrImage::add (ooc_tcontext.inl:123-135, image.h:99-109)
-    float* px = P.fb + 4 * (size_t)pixid;
-    atomicAdd(px + 0, mul_rn(scale, Lr.x));
-    atomicAdd(px + 1, mul_rn(scale, Lr.y));
-    atomicAdd(px + 2, mul_rn(scale, Lr.z));
-  }
-}
-
-template <bool COUNT>
-__global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
+__global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
   extern __shared__ float smem[];
-  float* boxes = smem;
-  uint8_t* resident = (uint8_t*)(boxes + 6 * P.nd);
-  load_domain_smem(P.table, P.nd, boxes, resident);
+  const DomSmem D = load_domain_smem(P.table, P.nd, smem);
 
   const int lane = threadIdx.x & 31;
   const int spp = P.shade.pixel_samples;
   const float scale = (float)(1.0 / (double)spp);
   const vec3 ks = mk3(P.shade.ks[0], P.shade.ks[1], P.shade.ks[2]);
+  const bool pt = P.shade.shader == SPRAYGPU_SHADER_PT;
+  const int nl = pt ? P.shade.nlights : 1;
   uint32_t cnt[3] = {0, 0, 0};
   uint32_t n_eye = 0, n_rad = 0, n_shadow = 0, n_hit = 0;
 
@@ -358,55 +447,57 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
     const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
     const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
     const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
-    if (slot >= P.total_slots || x0 >= (uint32_t)P.tile.w || y0 >= (uint32_t)P.tile.h) continue;
+    bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
 
-    uint32_t samid, pixid; vec3 dir;
-    eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &samid, &pixid, &dir);
-    ++n_eye;
+    uint32_t samid = 0, pixid = 0;
+    Pending cur;
+    cur.o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+    cur.d = mk3(0.f, 0.f, 1.f); cur.w = mk3(1.f, 1.f, 1.f); cur.depth = 0;
+    if (has_ray) {
+      eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &samid, &pixid, &cur.d);
+      ++n_eye;
+    }
+    Pending stack[MAX_PENDING];  // second rays of glass hits (reflection + transmission); rarely used
+    int nstack = 0;
 
-    Pending stack[MAX_PENDING];
-    int nstack = 1;
-    stack[0].o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-    stack[0].d = dir; stack[0].w = mk3(1.f, 1.f, 1.f); stack[0].depth = 0;
-
-    while (nstack) {
-      const Pending c = stack[--nstack];
-      SceneHit h;
-      scene_closest<COUNT>(P.table, boxes, resident, P.nd, c.o, c.d, h, cnt);
-      ++n_rad;
-      if (!(h.t < INFINITY)) continue;
-      ++n_hit;
-      const DomainEntry* e = P.table + h.dom;
-      uint32_t color; vec3 normal;
-      fetch_attributes(e, h.prim, h.u, h.v, &color, &normal);
-      // ShaderPt / ShaderAo :: operator()  (ooc_shader_pt.h:94-227, ooc_shader_ao.h:92-197)
-      const vec3 pos = mk3(add_rn(mul_rn(c.d.x, h.t), c.o.x), add_rn(mul_rn(c.d.y, h.t), c.o.y),
-                           add_rn(mul_rn(c.d.z, h.t), c.o.z));
-      const vec3 kd = unpack_color(color);
-      vec3 wo = gneg(c.d);
-      const vec3 Lin = c.w;
-      float cos_theta_i = gdot(wo, normal);
-      const bool entering = cos_theta_i > 0.0f;
-      const vec3 nff = gnormalize(entering ? normal : gneg(normal));
-      const int mtl = e->mtl_type;
+    while (__any_sync(0xffffffffu, has_ray)) {
+      // ---------------- closest hit ----------------
+      warp_cull(D, has_ray, cur.o, cur.d, true);
+      SceneHit h; h.t = INFINITY; h.dom = 0; h.prim = 0; h.u = h.v = 0.f;
+      if (has_ray) { scene_closest<COUNT>(P.table, D, cur.o, cur.d, h, cnt); ++n_rad; }
+      const bool hit = has_ray && h.t < INFINITY;
+      // ---------------- shading context ----------------
+      vec3 pos = cur.o, kd = mk3(0, 0, 0), nff = mk3(0, 0, 1), wo = gneg(cur.d);
+      float cos_theta_i = 0.f; bool entering = false; int mtl = SPRAYGPU_MTL_DIFFUSE; float eta0 = 1.f, eta1 = 1.f;
+      if (hit) {
+        ++n_hit;
+        const DomainEntry* e = P.table + h.dom;
+        uint32_t color; vec3 normal;
+        fetch_attributes(e, h.prim, h.u, h.v, &color, &normal);
+        pos = mk3(add_rn(mul_rn(cur.d.x, h.t), cur.o.x), add_rn(mul_rn(cur.d.y, h.t), cur.o.y),
+                  add_rn(mul_rn(cur.d.z, h.t), cur.o.z));
+        kd = unpack_color(color);
+        cos_theta_i = gdot(wo, normal);
+        entering = cos_theta_i > 0.0f;
+        nff = gnormalize(entering ? normal : gneg(normal));
+        mtl = e->mtl_type; eta0 = e->mtl[0]; eta1 = e->mtl[1];
+      }
       const bool delta = mtl != SPRAYGPU_MTL_DIFFUSE;
-      const int next_depth = c.depth + 1;
-      vec3 wi, Lr; float pdf, costheta;
-
-      // shadow rays: one per point light, ao_samples per area light (PT) / ao_samples (AO).  A single
-      // trace call site keeps the kernel small.
-      if (!delta) {
-        const bool pt = P.shade.shader == SPRAYGPU_SHADER_PT;
-        uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler seed
+      const int next_depth = cur.depth + 1;
+      const vec3 Lin = cur.w;
+      // ---------------- shadow rays: one light sample per warp pass ----------------
+      {
+        uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
         const float ao_weight = div_rn(1.0f, (float)P.shade.ao_samples);
-        const int nl = pt ? P.shade.nlights : 1;
-        for (int l = 0; l < nl; ++l) {
-          const spraygpu_light& L = P.shade.lights[pt ? l : 0];
-          const bool area = pt ? (L.type == SPRAYGPU_LIGHT_DIFFUSE) : true;
-          const vec3 rad = mk3(L.radiance[0], L.radiance[1], L.radiance[2]);
-          const int ns = area ? P.shade.ao_samples : 1;
-          for (int k = 0; k < ns; ++k) {
-            bool emit = false;
+        int l = 0, k = 0;
+        bool more_lights = hit && !delta && nl > 0;
+        while (__any_sync(0xffffffffu, more_lights)) {
+          bool emit = false; vec3 wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
+          if (more_lights) {
+            const spraygpu_light& L = P.shade.lights[pt ? l : 0];
+            const bool area = pt ? (L.type == SPRAYGPU_LIGHT_DIFFUSE) : true;
+            const vec3 rad = mk3(L.radiance[0], L.radiance[1], L.radiance[2]);
+            float pdf, costheta;
             if (pt) {
               if (area) {
                 const float u1 = rng_float(ls), u2 = rng_float(ls);
@@ -431,14 +522,30 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
               Lr = gscale(gmul(Lin, kd), div_rn(mul_rn(mul_rn(SPRAY_ONE_OVER_PI, costheta), ao_weight), pdf));
               emit = true;
             }
-            if (emit && has_positive(Lr))
-              shadow_and_add<COUNT>(P, boxes, resident, pos, wi, Lr, pixid, scale, cnt, &n_shadow);
+            emit = emit && has_positive(Lr);
+            // advance (l, k)
+            ++k;
+            if (k >= (area ? P.shade.ao_samples : 1)) { k = 0; ++l; }
+            more_lights = l < nl;
+          }
+          warp_cull(D, emit, pos, wi, true);
+          if (emit) {
+            ++n_shadow;
+            if (!scene_occluded<COUNT>(P.table, D, pos, wi, cnt)) {
+              // TContext::retire -> HdrImage::add (ooc_tcontext.inl:123-135, image.h:99-109)
+              float* px = P.fb + 4 * (size_t)pixid;
+              atomicAdd(px + 0, mul_rn(scale, Lr.x));
+              atomicAdd(px + 1, mul_rn(scale, Lr.y));
+              atomicAdd(px + 2, mul_rn(scale, Lr.z));
+            }
           }
         }
       }
-
-      if (next_depth < P.shade.bounces) {
+      // ---------------- next ray of this lane: bounce, or a pending second ray ----------------
+      bool next = false;
+      if (hit && next_depth < P.shade.bounces) {
         wo = gnormalize(wo);
+        vec3 wi, Lr; float pdf, costheta;
         if (delta) {
           if (cos_theta_i != 0.0f) {
             cos_theta_i = gclamp(cos_theta_i, -1.0f, 1.0f);
@@ -447,7 +554,7 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
             bool has_reflect = false, has_trans = false; float fr = 0.f; vec3 wt = mk3(0, 0, 0);
             if (mtl == SPRAYGPU_MTL_MIRROR) { fr = 1.0f; has_reflect = true; }
             else {
-              const float etaI = entering ? e->mtl[0] : e->mtl[1], etaT = entering ? e->mtl[1] : e->mtl[0];
+              const float etaI = entering ? eta0 : eta1, etaT = entering ? eta1 : eta0;
               if (mtl == SPRAYGPU_MTL_GLASS) {
                 fr = fr_dielectric(cos_theta_i, etaI, etaT, wo, nff, &wt);
                 if (fr == 1.0f) has_reflect = true;
@@ -458,17 +565,22 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
                 else { has_reflect = true; fr = 1.0f; }
               }
             }
-            if (has_trans && nstack < MAX_PENDING) {
+            // the reference CHECK-fails when glass yields both (ooc_shader_pt.h:199-201); we trace both:
+            // reflection first, transmission parked on the lane's pending stack
+            Pending refl, trans; bool ok_r = false, ok_t = false;
+            if (has_trans) {
               wi = gnormalize(wt);
               Lr = gscale(Lin, div_rn(sub_rn(1.0f, fr), abs_cos));
-              if (has_positive(Lr)) { stack[nstack].o = pos; stack[nstack].d = wi; stack[nstack].w = Lr; stack[nstack].depth = next_depth; ++nstack; }
+              if (has_positive(Lr)) { trans.o = pos; trans.d = wi; trans.w = Lr; trans.depth = next_depth; ok_t = true; }
             }
-            if (has_reflect && nstack < MAX_PENDING) {
+            if (has_reflect) {
               const vec3 wr = gadd(gneg(wo), gscale(nff, mul_rn(2.0f, gdot(wo, nff))));
               wi = gnormalize(wr);
               Lr = gscale(Lin, div_rn(fr, abs_cos));
-              if (has_positive(Lr)) { stack[nstack].o = pos; stack[nstack].d = wi; stack[nstack].w = Lr; stack[nstack].depth = next_depth; ++nstack; }
+              if (has_positive(Lr)) { refl.o = pos; refl.d = wi; refl.w = Lr; refl.depth = next_depth; ok_r = true; }
             }
+            if (ok_r) { cur = refl; next = true; if (ok_t && nstack < MAX_PENDING) stack[nstack++] = trans; }
+            else if (ok_t) { cur = trans; next = true; }
           }
         } else {
           uint32_t rs = rng_init1(samid * (uint32_t)next_depth);
@@ -477,11 +589,11 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
           costheta = gclamp(gdot(nff, wi), 0.0f, 1.0f);
           Lr = gscale(gscale(gmul(Lin, kd), SPRAY_ONE_OVER_PI), costheta);
           Lr = mk3(div_rn(Lr.x, pdf), div_rn(Lr.y, pdf), div_rn(Lr.z, pdf));
-          if (has_positive(Lr) && nstack < MAX_PENDING) {
-            stack[nstack].o = pos; stack[nstack].d = wi; stack[nstack].w = Lr; stack[nstack].depth = next_depth; ++nstack;
-          }
+          if (has_positive(Lr)) { cur.o = pos; cur.d = wi; cur.w = Lr; cur.depth = next_depth; next = true; }
         }
       }
+      if (!next && has_ray && nstack > 0) { cur = stack[--nstack]; next = true; }
+      has_ray = next;
     }
   }
 
@@ -499,7 +611,6 @@ __global__ void __launch_bounds__(256) render_tile_kernel(RenderParams P) {
 // ------------------------------------------------------------------------------------------------
 // host-side launchers (called from capi.cu)
 // ------------------------------------------------------------------------------------------------
-static inline size_t domain_smem_bytes(int nd) { return (size_t)nd * 6 * sizeof(float) + (((size_t)nd + 15) & ~(size_t)15); }
 static inline int grid_for(size_t n, int t) { return (int)((n + t - 1) / t); }
 
 static CameraDev to_camdev(const spraygpu_camera* c) {
@@ -512,7 +623,7 @@ static CameraDev to_camdev(const spraygpu_camera* c) {
 int launch_domain_lists(Device* dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts, int32_t* ids,
                         float* tmins) {
   if (!n) return SPRAYGPU_OK;
-  domain_lists_kernel<<<grid_for(n, 128), 128, domain_smem_bytes(dev->ndomains), dev->stream>>>(
+  domain_lists_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
       dev->d_domains, dev->ndomains, rays, n, cap, counts, ids, tmins);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
@@ -535,7 +646,7 @@ int launch_occluded_scene(Scene* sc, const spraygpu_ray* rays, size_t n, uint8_t
 }
 int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint64_t* keys, float* uv, int merge) {
   if (!n) return SPRAYGPU_OK;
-  intersect_domains_kernel<<<grid_for(n, 128), 128, domain_smem_bytes(dev->ndomains), dev->stream>>>(
+  intersect_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
       dev->d_domains, dev->ndomains, rays, n, keys, uv, merge);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
@@ -543,7 +654,7 @@ int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, ui
 }
 int launch_occluded_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge) {
   if (!n) return SPRAYGPU_OK;
-  occluded_domains_kernel<<<grid_for(n, 128), 128, domain_smem_bytes(dev->ndomains), dev->stream>>>(
+  occluded_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
       dev->d_domains, dev->ndomains, rays, n, occ, merge);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
@@ -578,7 +689,7 @@ int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_s
   P.total_slots = (uint32_t)slots;
   if (!slots) return SPRAYGPU_OK;
   SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long) * 8, dev->stream));
-  const size_t smem = domain_smem_bytes(dev->ndomains);
+  const size_t smem = dom_smem_bytes(dev->ndomains, 8);
   int per_sm = 0;
   if (counted) {
     SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tile_kernel<true>, 256, smem));
