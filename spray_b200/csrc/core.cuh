@@ -162,36 +162,30 @@ SPRAY_HD float sortable_float(uint32_t s) {
 // dependency is not in the container]: no culling, inclusive edges, u,v relative to v1,v2, t > tnear.
 // ---------------------------------------------------------------------------------------------
 struct TriHit { float t, u, v; };
-SPRAY_HD bool tri_test(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear, TriHit* h) {
+// pass/fail part (no divisions): scaled T, U, V and |den|
+SPRAY_HD bool tri_test_raw(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear, float* T, float* U, float* V,
+                           float* absDen) {
   vec3 Ng = ecross(e2, e1);
   vec3 C = gsub(v0, O);
   vec3 R = ecross(C, D);
   float den = edot(Ng, D);
-  float absDen = fabsf(den);
+  float ad = fabsf(den);
   uint32_t sgn = f2u(den) & 0x80000000u;
-  float U = u2f(f2u(edot(R, e2)) ^ sgn);
-  float V = u2f(f2u(edot(R, e1)) ^ sgn);
-  if (!(den != 0.0f) || !(U >= 0.0f) || !(V >= 0.0f) || !(add_rn(U, V) <= absDen)) return false;
-  float T = u2f(f2u(edot(Ng, C)) ^ sgn);
-  if (!(T > mul_rn(absDen, tnear))) return false;
-  h->t = div_rn(T, absDen);
-  h->u = div_rn(U, absDen);
-  h->v = div_rn(V, absDen);
+  float u = u2f(f2u(edot(R, e2)) ^ sgn);
+  float v = u2f(f2u(edot(R, e1)) ^ sgn);
+  if (!(den != 0.0f) || !(u >= 0.0f) || !(v >= 0.0f) || !(add_rn(u, v) <= ad)) return false;
+  float t = u2f(f2u(edot(Ng, C)) ^ sgn);
+  if (!(t > mul_rn(ad, tnear))) return false;
+  *T = t; *U = u; *V = v; *absDen = ad;
   return true;
 }
-// any-hit variant: no divisions
-SPRAY_HD bool tri_test_any(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear) {
-  vec3 Ng = ecross(e2, e1);
-  vec3 C = gsub(v0, O);
-  vec3 R = ecross(C, D);
-  float den = edot(Ng, D);
-  float absDen = fabsf(den);
-  uint32_t sgn = f2u(den) & 0x80000000u;
-  float U = u2f(f2u(edot(R, e2)) ^ sgn);
-  float V = u2f(f2u(edot(R, e1)) ^ sgn);
-  if (!(den != 0.0f) || !(U >= 0.0f) || !(V >= 0.0f) || !(add_rn(U, V) <= absDen)) return false;
-  float T = u2f(f2u(edot(Ng, C)) ^ sgn);
-  return T > mul_rn(absDen, tnear);
+SPRAY_HD bool tri_test(vec3 O, vec3 D, vec3 v0, vec3 e1, vec3 e2, float tnear, TriHit* h) {
+  float T, U, V, ad;
+  if (!tri_test_raw(O, D, v0, e1, e2, tnear, &T, &U, &V, &ad)) return false;
+  h->t = div_rn(T, ad);
+  h->u = div_rn(U, ad);
+  h->v = div_rn(V, ad);
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -233,33 +227,62 @@ SPRAY_HD RayCtx make_ray_ctx(vec3 o, vec3 d, float tnear) {
 
 SPRAY_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
 
-// byte j of w as a float, WITHOUT the XU-pipe I2F: PRMT builds 0x4B0000qq (= 2^23 + q), one FADD removes
-// the 2^23 (exact).  ncu on the first build showed the quarter-rate XU pipe saturated by 48 I2F per node.
-SPRAY_HD float byte_to_float(uint32_t w, int j) {
+// Quantised plane byte j of w as the float 32768 + q, built by ONE byte permute: 0x4700qq00 has exponent
+// 2^15 and q in mantissa bits 8..15 (weight 2^0).  The 32768 is folded into the FMA offset of the slab
+// test (node8_hits), so a plane distance costs PRMT + FFMA and never touches the quarter-rate XU pipe
+// (ncu on the first build: 48 I2F per node saturated it).
+#define SPRAY_QBIAS 32768.0f
+// k47 = 0x47000000 held in a REGISTER (opaque_k47) so that the selector can be the instruction's immediate:
+// with both constant, ptxas makes 0x47000000 the immediate and re-materialises the selector per PRMT.
+#if defined(__CUDACC__)
+static __constant__ uint32_t spray_k47_const = 0x47000000u;  // constant bank: ptxas cannot fold it
+#endif
+SPRAY_HD uint32_t opaque_k47() {
 #if defined(__CUDA_ARCH__)
-  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u | (uint32_t)j)) - 8388608.0f;
+  return spray_k47_const;
 #else
-  return (float)byte_of(w, j);
+  return 0x47000000u;
+#endif
+}
+SPRAY_HD float byte_to_biased_float(uint32_t w, int j, uint32_t k47) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(__byte_perm(w, k47, 0x7404u | ((uint32_t)j << 4)));
+#else
+  return u2f(k47 | (byte_of(w, j) << 8));
 #endif
 }
 
 // returns the 32-bit hit mask of one node: bits 31..24 internal children in traversal priority order,
 // bits 23..0 one bit per leaf triangle.
+//
+// Slab distances: plane = p + q * 2^e  =>  t = (plane - o) * idir = q * a + b with a = 2^e * idir and
+// b = (p - o) * idir.  With f = 32768 + q:  t = fma(f, a, b - 32768 * a).  The extra rounding of the
+// folded offset is <= 2^-9 quantisation steps; encode_node8 keeps every child plane >= 2^-7 step inside
+// its quantised plane, so the test stays conservative.  The far side carries the 1e-5 relative slack
+// (FP32 rounding of the plane distances, and rays the FP32 triangle test accepts although they graze
+// just outside the exact triangle) pre-multiplied into its coefficients.
+// The two halves (children 0..3 / 4..7) run as a real loop: the traversal loop must stay small enough
+// for the 6 KB L0 instruction cache (ncu: a fully unrolled node test stalled ~40 % on instruction fetch).
 SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4, const RayCtx& r,
                              float tmax) {
-  const float px = u2f(q0.x), py = u2f(q0.y), pz = u2f(q0.z);
   const uint32_t e = q0.w;
+  const float slack = 1.00001f;
   const float aix = u2f((e & 0xffu) << 23) * r.idir.x;
   const float aiy = u2f(((e >> 8) & 0xffu) << 23) * r.idir.y;
   const float aiz = u2f(((e >> 16) & 0xffu) << 23) * r.idir.z;
-  const float ox = (px - r.o.x) * r.idir.x;
-  const float oy = (py - r.o.y) * r.idir.y;
-  const float oz = (pz - r.o.z) * r.idir.z;
-  const float fx = ox + r.far_bias.x, fy = oy + r.far_bias.y, fz = oz + r.far_bias.z;
+  const float ox = fmaf(-SPRAY_QBIAS, aix, (u2f(q0.x) - r.o.x) * r.idir.x);
+  const float oy = fmaf(-SPRAY_QBIAS, aiy, (u2f(q0.y) - r.o.y) * r.idir.y);
+  const float oz = fmaf(-SPRAY_QBIAS, aiz, (u2f(q0.z) - r.o.z) * r.idir.z);
+  const float afx = aix * slack, afy = aiy * slack, afz = aiz * slack;
+  const float fx = fmaf(ox, slack, r.far_bias.x), fy = fmaf(oy, slack, r.far_bias.y), fz = fmaf(oz, slack, r.far_bias.z);
+  const float tfar = tmax * slack;
   const uint32_t octinv4 = r.octinv * 0x01010101u;
   const bool nx = r.idir.x < 0.0f, ny = r.idir.y < 0.0f, nz = r.idir.z < 0.0f;
   uint32_t hitmask = 0;
-#pragma unroll
+  const uint32_t k47 = opaque_k47();
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
   for (int half = 0; half < 2; ++half) {
     const uint32_t meta4 = half ? q1.w : q1.z;
     const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
@@ -273,18 +296,17 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
     const uint32_t nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const float t0x = fmaf(byte_to_float(nearx, j), aix, ox);
-      const float t0y = fmaf(byte_to_float(neary, j), aiy, oy);
-      const float t0z = fmaf(byte_to_float(nearz, j), aiz, oz);
-      const float t1x = fmaf(byte_to_float(farx, j), aix, fx);
-      const float t1y = fmaf(byte_to_float(fary, j), aiy, fy);
-      const float t1z = fmaf(byte_to_float(farz, j), aiz, fz);
+      const float t0x = fmaf(byte_to_biased_float(nearx, j, k47), aix, ox);
+      const float t0y = fmaf(byte_to_biased_float(neary, j, k47), aiy, oy);
+      const float t0z = fmaf(byte_to_biased_float(nearz, j, k47), aiz, oz);
+      const float t1x = fmaf(byte_to_biased_float(farx, j, k47), afx, fx);
+      const float t1y = fmaf(byte_to_biased_float(fary, j, k47), afy, fy);
+      const float t1z = fmaf(byte_to_biased_float(farz, j, k47), afz, fz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
-      // The quantised box is conservative for the exact geometry; the 1e-5 relative slack (cmin > 0, so
-      // one multiply widens the interval on both sides) covers FP32 rounding of the six plane distances
-      // AND rays the FP32 triangle test accepts although they graze just outside the exact triangle.
-      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.00001f;
-      if (cmin <= cmax) hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tfar));
+      // branch-free: a per-child branch costs a fetch redirect and a reconvergence barrier
+      const uint32_t sh = byte_of(child_bits4, j) << byte_of(bit_index4, j);
+      hitmask |= (cmin <= cmax) ? sh : 0u;
     }
   }
   return hitmask;
@@ -297,57 +319,17 @@ struct Closest {
   uint32_t prim; // valid iff t < inf
 };
 
-// Closest hit in ONE domain's BVH8: lexicographic min of (t, primID) over every triangle passing S1.
+// ONE traversal routine for both query kinds (a single code instance keeps the persistent kernel's hot
+// loop inside the instruction cache):
+//   any == false: closest hit in ONE domain's BVH8 = lexicographic min of (t, primID) over every triangle
+//                 passing S1; `best` is updated in place (seed best.t with the best t so far).
+//   any == true : returns true at the first triangle passing S1 (best is untouched).
 // nodes: 5 x u4 per node; tris: 3 x float4-equivalent (12 floats) per triangle.  LOADN / LOADT abstract
 // the memory access (global loads on the device, plain reads in host emulation).
 template <typename NodeLoader, typename TriLoader>
-SPRAY_HD void bvh8_closest(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, Closest& best,
-                           uint32_t* stack_x, uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
-  uint32_t ngx = 0, ngy = 0x80000000u;
-  int sp = 0;
-  for (;;) {
-    uint32_t tgx = 0, tgy = 0;
-    if (ngy > 0x00FFFFFFu) {
-      const uint32_t imask = ngy & 0xffu;
-      const int bit = 31 - clz32(ngy);
-      ngy &= ~(1u << bit);
-      if (ngy > 0x00FFFFFFu) {
-        if (sp < SPRAY_STACK_SIZE) { stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp; }
-      }
-      const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
-      const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
-      const uint32_t idx = ngx + rel;
-      u4 q0, q1, q2, q3, q4;
-      loadn(idx, q0, q1, q2, q3, q4);
-      if (n_nodes) ++*n_nodes;
-      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, best.t);
-      ngx = q1.x; tgx = q1.y;
-      ngy = (hm & 0xFF000000u) | (q0.w >> 24);
-      tgy = hm & 0x00FFFFFFu;
-    }
-    while (tgy) {
-      const int ti = ffs32(tgy) - 1;
-      tgy &= tgy - 1;
-      vec3 v0, e1, e2; uint32_t prim;
-      loadt(tgx + (uint32_t)ti, v0, e1, e2, prim);
-      if (n_tris) ++*n_tris;
-      TriHit h;
-      if (tri_test(r.o, r.d, v0, e1, e2, r.tnear, &h)) {
-        if (h.t < best.t || (h.t == best.t && prim < best.prim)) {
-          best.t = h.t; best.u = h.u; best.v = h.v; best.prim = prim;
-        }
-      }
-    }
-    if (ngy <= 0x00FFFFFFu) {
-      if (sp == 0) break;
-      --sp; ngx = stack_x[sp]; ngy = stack_y[sp];
-    }
-  }
-}
-
-template <typename NodeLoader, typename TriLoader>
-SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, uint32_t* stack_x,
-                       uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
+SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, const bool any,
+                         Closest& best, uint32_t* stack_x, uint32_t* stack_y, uint32_t* n_nodes,
+                         uint32_t* n_tris) {
   uint32_t ngx = 0, ngy = 0x80000000u;
   int sp = 0;
   for (;;) {
@@ -364,7 +346,7 @@ SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const Ra
       u4 q0, q1, q2, q3, q4;
       loadn(ngx + rel, q0, q1, q2, q3, q4);
       if (n_nodes) ++*n_nodes;
-      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, INFINITY);
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, best.t);
       ngx = q1.x; tgx = q1.y;
       ngy = (hm & 0xFF000000u) | (q0.w >> 24);
       tgy = hm & 0x00FFFFFFu;
@@ -375,7 +357,14 @@ SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const Ra
       vec3 v0, e1, e2; uint32_t prim;
       loadt(tgx + (uint32_t)ti, v0, e1, e2, prim);
       if (n_tris) ++*n_tris;
-      if (tri_test_any(r.o, r.d, v0, e1, e2, r.tnear)) return true;
+      float T, U, V, ad;
+      if (tri_test_raw(r.o, r.d, v0, e1, e2, r.tnear, &T, &U, &V, &ad)) {
+        if (any) return true;
+        const float t = div_rn(T, ad);
+        if (t < best.t || (t == best.t && prim < best.prim)) {
+          best.t = t; best.u = div_rn(U, ad); best.v = div_rn(V, ad); best.prim = prim;
+        }
+      }
     }
     if (ngy <= 0x00FFFFFFu) {
       if (sp == 0) break;
@@ -383,6 +372,19 @@ SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const Ra
     }
   }
   return false;
+}
+
+template <typename NodeLoader, typename TriLoader>
+SPRAY_HD void bvh8_closest(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, Closest& best,
+                           uint32_t* stack_x, uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
+  bvh8_trace(loadn, loadt, r, false, best, stack_x, stack_y, n_nodes, n_tris);
+}
+
+template <typename NodeLoader, typename TriLoader>
+SPRAY_HD bool bvh8_any(const NodeLoader& loadn, const TriLoader& loadt, const RayCtx& r, uint32_t* stack_x,
+                       uint32_t* stack_y, uint32_t* n_nodes, uint32_t* n_tris) {
+  Closest none; none.t = INFINITY; none.u = none.v = 0.f; none.prim = 0xFFFFFFFFu;
+  return bvh8_trace(loadn, loadt, r, true, none, stack_x, stack_y, n_nodes, n_tris);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -536,43 +538,53 @@ SPRAY_HD void collapse_select(int b, const int* bl, const int* br, const int* bf
   }
 }
 
-// quantise child boxes against the node box [nlo, nhi] and emit the 5 x u4 words
+// Quantise child boxes and emit the 5 x u4 words.  Per axis the frame is  plane(q) = p + q * 2^e  with
+// p = nlo - 2^e (one step below the node box) and 253 * 2^e >= extent, so every child plane lies in
+// [plane(1), plane(254)] and can be widened.  Guarantee kept here and relied on by node8_hits:
+//   plane(qlo) + 2^e/128 <= child.lo   and   plane(qhi) - 2^e/128 >= child.hi   (FP32-evaluated)
+// which absorbs the <= 2^-9-step rounding of the folded slab offset and the ulp of (p - o) * idir.
 SPRAY_HD void encode_node8(const float* nlo, const float* nhi, const CollapseOut& c, uint32_t child_base,
                            uint32_t tri_base, u4* q) {
-  uint32_t ebits[3]; float scale[3];
+  uint32_t ebits[3]; float porg[3];
+  uint32_t qlo[3][8], qhi[3][8];
+  const float margin = 0.0078125f;  // 2^-7 step
   for (int a = 0; a < 3; ++a) {
-    float ext = nhi[a] - nlo[a];
-    // smallest e with ext <= 255 * 2^e (with margin for the conservative rounding below)
+    const float ext = nhi[a] - nlo[a];
     int e;
     if (!(ext > 0.0f)) e = -126;
     else {
-      float f = frexpf(ext / 255.0f, &e); // ext/255 = f * 2^e, f in [0.5,1)  =>  2^e > ext/255
-      if (f == 0.5f) --e;                 // exact power of two: 2^(e-1) == ext/255 suffices
+      float f = frexpf(ext / 253.0f, &e);  // ext/253 = f * 2^e, f in [0.5,1)  =>  2^e > ext/253
+      (void)f;
     }
-    if (e < -126) e = -126;
-    if (e > 127) e = 127;
-    // verify 255 * 2^e reaches the far side after FP32 rounding; bump otherwise
-    while (e < 127 && nlo[a] + 255.0f * u2f((uint32_t)(e + 127) << 23) < nhi[a]) ++e;
-    ebits[a] = (uint32_t)(e + 127);
-    scale[a] = u2f(ebits[a] << 23);
-  }
-  uint32_t qlo[3][8], qhi[3][8];
-  for (int s = 0; s < 8; ++s) {
-    for (int a = 0; a < 3; ++a) {
-      if (c.meta[s] == 0) { qlo[a][s] = 255; qhi[a][s] = 0; continue; }
-      float l = floorf((c.lo[s][a] - nlo[a]) / scale[a]);
-      float h = ceilf((c.hi[s][a] - nlo[a]) / scale[a]);
-      int li = (int)fminf(fmaxf(l, 0.f), 255.f), hi = (int)fminf(fmaxf(h, 0.f), 255.f);
-      // enforce conservativeness under the decode expression p + q * 2^e (exact product, one rounding)
-      while (li > 0 && nlo[a] + (float)li * scale[a] > c.lo[s][a]) --li;
-      while (hi < 255 && nlo[a] + (float)hi * scale[a] < c.hi[s][a]) ++hi;
-      qlo[a][s] = (uint32_t)li; qhi[a][s] = (uint32_t)hi;
+    // the step must stay well above the ulp of the coordinates, or p = nlo - step would round away
+    {
+      const float m = fmaxf(fabsf(nlo[a]), fabsf(nhi[a]));
+      int em = -126;
+      if (m > 0.0f) { (void)frexpf(m, &em); em -= 22; }  // 2^em >= 2 ulp(m)
+      if (e < em) e = em;
+    }
+    if (e < -100) e = -100;
+    if (e > 100) e = 100;
+    for (;; ++e) {
+      const float scale = u2f((uint32_t)(e + 127) << 23);
+      const float p = nlo[a] - scale;
+      bool ok = true;
+      for (int s = 0; s < 8 && ok; ++s) {
+        if (c.meta[s] == 0) { qlo[a][s] = 255; qhi[a][s] = 0; continue; }
+        int li = (int)fminf(fmaxf(floorf((c.lo[s][a] - p) / scale), 0.f), 255.f);
+        int hi = (int)fminf(fmaxf(ceilf((c.hi[s][a] - p) / scale), 0.f), 255.f);
+        while (li > 0 && p + ((float)li + margin) * scale > c.lo[s][a]) --li;
+        while (hi < 255 && p + ((float)hi - margin) * scale < c.hi[s][a]) ++hi;
+        if (p + ((float)li + margin) * scale > c.lo[s][a] || p + ((float)hi - margin) * scale < c.hi[s][a]) ok = false;
+        qlo[a][s] = (uint32_t)li; qhi[a][s] = (uint32_t)hi;
+      }
+      if (ok || e >= 120) { ebits[a] = (uint32_t)(e + 127); porg[a] = p; break; }
     }
   }
   auto pack4 = [](const uint32_t* v) -> uint32_t { return v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24); };
   uint32_t m[8];
   for (int s = 0; s < 8; ++s) m[s] = c.meta[s];
-  q[0].x = f2u(nlo[0]); q[0].y = f2u(nlo[1]); q[0].z = f2u(nlo[2]);
+  q[0].x = f2u(porg[0]); q[0].y = f2u(porg[1]); q[0].z = f2u(porg[2]);
   q[0].w = ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | ((uint32_t)c.imask << 24);
   q[1].x = child_base; q[1].y = tri_base; q[1].z = pack4(m); q[1].w = pack4(m + 4);
   q[2].x = pack4(qlo[0]); q[2].y = pack4(qlo[0] + 4); q[2].z = pack4(qlo[1]); q[2].w = pack4(qlo[1] + 4);

@@ -131,14 +131,25 @@ __device__ __forceinline__ void warp_cull(const DomSmem& D, bool active, vec3 o,
   __syncwarp();
 }
 
+// candidate-word sources for the per-lane exact test
+struct WarpCand {      // the warp's beam-culled candidate words (warp_cull)
+  const uint32_t* cand;
+  __device__ __forceinline__ uint32_t operator()(int w) const { return cand[w]; }
+};
+struct StridedCand {   // one ray's own exact domain mask, word w at base[w * stride] (ray queue, SoA)
+  const uint32_t* base; int stride;
+  __device__ __forceinline__ uint32_t operator()(int w) const { return base[w * stride]; }
+};
+
 // per-lane exact test on the candidates: keeps the MAXLIST nearest entries with key > after.
-__device__ __forceinline__ int domain_list(const DomSmem& D, vec3 o, vec3 d, bool have_after, uint64_t after,
-                                           uint64_t* list, bool* more) {
+template <typename CandF>
+__device__ __forceinline__ int domain_list(const DomSmem& D, const CandF& cand, vec3 o, vec3 d, bool have_after,
+                                           uint64_t after, uint64_t* list, bool* more) {
   int cnt = 0;
   bool overflow = false;
   const int nwords = (D.nd + 31) >> 5;
   for (int w = 0; w < nwords; ++w) {
-    uint32_t m = D.cand[w];
+    uint32_t m = cand(w);
     while (m) {
       const int i = (w << 5) + __ffs((int)m) - 1;
       m &= m - 1;
@@ -161,15 +172,31 @@ __device__ __forceinline__ int domain_list(const DomSmem& D, vec3 o, vec3 d, boo
   return cnt;
 }
 
+// exact per-lane domain mask of candidate word w (reference slab test, aabb.h:139-169)
+__device__ __forceinline__ uint32_t exact_mask_word(const DomSmem& D, int w, uint32_t m, vec3 o, vec3 d) {
+  uint32_t out = 0;
+  while (m) {
+    const int b = __ffs((int)m) - 1;
+    m &= m - 1;
+    float tmin;
+    if (domain_slab(D.boxes + 6 * ((w << 5) + b), o, d, SPRAY_RAY_EPS, INFINITY, &tmin)) out |= 1u << b;
+  }
+  return out;
+}
+
 struct SceneHit {
   float t, u, v;
   uint32_t prim, dom;
 };
 
-// closest hit over the warp-culled candidate domains; call warp_cull(..., true) first (all lanes).
-template <bool COUNT>
-__device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
-                                              SceneHit& out, uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+// ONE routine for both query kinds over the warp-culled candidate domains (call warp_cull(..., true) first,
+// all lanes).  A single instance keeps the persistent kernel's code small (instruction cache).
+//   any == false: closest hit = lexicographic min of (t, domain, prim); returns out.t < inf.
+//   any == true : returns true as soon as any resident entered domain occludes the ray.
+template <bool COUNT, typename CandF>
+__device__ __forceinline__ bool scene_trace(const DomainEntry* __restrict__ table, const DomSmem& D, const CandF& cand,
+                                            vec3 o, vec3 d, const bool any, SceneHit& out,
+                                            uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
   uint64_t list[MAXLIST];
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
   out.t = INFINITY; out.prim = 0; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
@@ -177,7 +204,7 @@ __device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ ta
   bool have_after = false, more = false, done = false;
   uint64_t after = 0;
   do {
-    const int n = domain_list(D, o, d, have_after, after, list, &more);
+    const int n = domain_list(D, cand, o, d, have_after, after, list, &more);
     for (int k = 0; k < n && !done; ++k) {
       const float tdom = sortable_float((uint32_t)(list[k] >> 32));
       // front-to-back early out (an optimisation only; slack keeps it conservative)
@@ -187,37 +214,29 @@ __device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ ta
       // Seed with the best t so far (prim = max): the traversal then admits hits with t < best, or
       // t == best (exact tie, resolved below to the lowest (domain, prim)).
       Closest cc; cc.t = out.t; cc.u = cc.v = 0.f; cc.prim = 0xFFFFFFFFu;
-      bvh8_closest(NodeLoaderG{e->nodes}, TriLoaderG{e->tris}, r, cc, sx, sy, COUNT ? cnt + 1 : nullptr,
-                   COUNT ? cnt + 2 : nullptr);
       if (COUNT) cnt[0]++;
+      const bool occ = bvh8_trace(NodeLoaderG{e->nodes}, TriLoaderG{e->tris}, r, any, cc, sx, sy,
+                                  COUNT ? cnt + 1 : nullptr, COUNT ? cnt + 2 : nullptr);
+      if (occ) return true;
       if (cc.prim != 0xFFFFFFFFu && (cc.t < out.t || (cc.t == out.t && id < out.dom))) {
         out.t = cc.t; out.u = cc.u; out.v = cc.v; out.prim = cc.prim; out.dom = id;
       }
     }
     if (n > 0) { after = list[n - 1]; have_after = true; }
   } while (more && !done);
+  return !any && out.t < INFINITY;
 }
 
 template <bool COUNT>
+__device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
+                                              SceneHit& out, uint32_t* cnt) {
+  scene_trace<COUNT>(table, D, WarpCand{D.cand}, o, d, false, out, cnt);
+}
+template <bool COUNT>
 __device__ __forceinline__ bool scene_occluded(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
                                                uint32_t* cnt) {
-  uint64_t list[MAXLIST];
-  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
-  const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
-  bool have_after = false, more = false;
-  uint64_t after = 0;
-  do {
-    const int n = domain_list(D, o, d, have_after, after, list, &more);
-    for (int k = 0; k < n; ++k) {
-      const DomainEntry* e = table + (uint32_t)list[k];
-      if (COUNT) cnt[0]++;
-      if (bvh8_any(NodeLoaderG{e->nodes}, TriLoaderG{e->tris}, r, sx, sy, COUNT ? cnt + 1 : nullptr,
-                   COUNT ? cnt + 2 : nullptr))
-        return true;
-    }
-    if (n > 0) { after = list[n - 1]; have_after = true; }
-  } while (more);
-  return false;
+  SceneHit h;
+  return scene_trace<COUNT>(table, D, WarpCand{D.cand}, o, d, true, h, cnt);
 }
 
 // TriMeshBuffer::updateIntersection (trimesh_buffer.cc:328-360) from the 48-byte attribute record
@@ -253,7 +272,7 @@ __global__ void __launch_bounds__(128)
   uint64_t after = 0;
   int total = 0;
   do {
-    const int c = domain_list(D, o, d, have_after, after, list, &more);
+    const int c = domain_list(D, WarpCand{D.cand}, o, d, have_after, after, list, &more);
     for (int k = 0; k < c; ++k, ++total) {
       if (total < cap) {
         ids[i * cap + total] = (int32_t)(uint32_t)list[k];
@@ -420,101 +439,252 @@ struct RenderParams {
 struct Pending { vec3 o, d, w; int depth; };
 
 #ifndef SPRAY_RENDER_MINBLOCKS
-#define SPRAY_RENDER_MINBLOCKS 3
+#define SPRAY_RENDER_MINBLOCKS 2
 #endif
-template <bool COUNT>
+
+// ------------------------------------------------------------------------------------------------
+// Per-warp ray queue (shared memory, SoA, LIFO).  Every ray that enters at least one resident domain
+// — eye, bounce or shadow — is pushed with its exact domain mask; the warp pops 32 at a time, so all
+// lanes traverse (ballot / prefix-sum compaction of the speculative ray stream).  Rays that enter no
+// domain never occupy a lane.
+// fields (QCAP entries each): 0-2 origin, 3-5 direction, 6-8 throughput (radiance) or radiance to add
+// (shadow), 9 pixid, 10 samid, 11 depth << 1 | kind (0 radiance, 1 shadow), 12.. exact domain mask words
+// ------------------------------------------------------------------------------------------------
+#define QF_O 0
+#define QF_D 3
+#define QF_W 6
+#define QF_PIX 9
+#define QF_SAM 10
+#define QF_DK 11
+#define QF_MASK 12
+
+struct RayQueue {
+  uint32_t* q;        // this warp's fields, field f entry s at q[f * cap + s]
+  uint32_t* scratch;  // this warp's provisional mask words, word w of lane l at scratch[w * 32 + l]
+  int cap, nwords;
+};
+
+__host__ __device__ inline size_t queue_words_per_warp(int nd, int cap) {
+  const int nw = (nd + 31) >> 5;
+  return (size_t)(QF_MASK + nw) * cap + (size_t)nw * 32;
+}
+
+// Warp-cooperative push.  Returns true for lanes whose ray is live (emit) but enters NO resident domain:
+// such a ray is resolved on the spot (radiance: miss, shadow: unoccluded).  `count` is warp-uniform.
+__device__ __forceinline__ bool queue_push(const RayQueue& Q, const DomSmem& D, int& count, bool emit, vec3 o, vec3 d,
+                                           vec3 w, uint32_t pixid, uint32_t samid, uint32_t depthkind) {
+  const int lane = threadIdx.x & 31;
+  warp_cull(D, emit, o, d, true);
+  bool nonempty = false;
+  if (emit) {
+    for (int k = 0; k < Q.nwords; ++k) {
+      const uint32_t m = exact_mask_word(D, k, D.cand[k], o, d);
+      Q.scratch[k * 32 + lane] = m;
+      nonempty = nonempty || (m != 0u);
+    }
+  }
+  const bool go = emit && nonempty;
+  const uint32_t b = __ballot_sync(0xffffffffu, go);
+  if (go) {
+    const int s = count + __popc(b & ((1u << lane) - 1u));
+    uint32_t* q = Q.q + s;
+    const int c = Q.cap;
+    q[(QF_O + 0) * c] = __float_as_uint(o.x); q[(QF_O + 1) * c] = __float_as_uint(o.y); q[(QF_O + 2) * c] = __float_as_uint(o.z);
+    q[(QF_D + 0) * c] = __float_as_uint(d.x); q[(QF_D + 1) * c] = __float_as_uint(d.y); q[(QF_D + 2) * c] = __float_as_uint(d.z);
+    q[(QF_W + 0) * c] = __float_as_uint(w.x); q[(QF_W + 1) * c] = __float_as_uint(w.y); q[(QF_W + 2) * c] = __float_as_uint(w.z);
+    q[QF_PIX * c] = pixid; q[QF_SAM * c] = samid; q[QF_DK * c] = depthkind;
+    for (int k = 0; k < Q.nwords; ++k) q[(QF_MASK + k) * c] = Q.scratch[k * 32 + lane];
+  }
+  count += __popc(b);
+  __syncwarp();
+  return emit && !nonempty;
+}
+
+__device__ __forceinline__ void fb_add(float* fb, uint32_t pixid, float scale, vec3 Lr) {
+  // TContext::retire -> HdrImage::add (ooc_tcontext.inl:123-135, image.h:99-109)
+  float* px = fb + 4 * (size_t)pixid;
+  atomicAdd(px + 0, mul_rn(scale, Lr.x));
+  atomicAdd(px + 1, mul_rn(scale, Lr.y));
+  atomicAdd(px + 2, mul_rn(scale, Lr.z));
+}
+
+// GENERAL == false is the lean variant for the common configuration (PT shader, ONE point light, every
+// domain diffuse): area-light / AO sampling, delta materials and the inline shadow fallback are compiled
+// out, which keeps the code the instruction cache has to hold small.  The launcher picks the variant.
+template <bool GENERAL> struct QueueCap { static constexpr int value = GENERAL ? 128 : 96; };
+
+template <bool COUNT, bool GENERAL>
 __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
   extern __shared__ float smem[];
   const DomSmem D = load_domain_smem(P.table, P.nd, smem);
-
+  constexpr int QCAP = QueueCap<GENERAL>::value;
   const int lane = threadIdx.x & 31;
+  RayQueue Q;
+  Q.cap = QCAP; Q.nwords = (P.nd + 31) >> 5;
+  {
+    uint32_t* qbase = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, 8) + 15) & ~(size_t)15));
+    Q.q = qbase + (size_t)(threadIdx.x >> 5) * queue_words_per_warp(P.nd, QCAP);
+    Q.scratch = Q.q + (size_t)(QF_MASK + Q.nwords) * QCAP;
+  }
   const int spp = P.shade.pixel_samples;
   const float scale = (float)(1.0 / (double)spp);
   const vec3 ks = mk3(P.shade.ks[0], P.shade.ks[1], P.shade.ks[2]);
-  const bool pt = P.shade.shader == SPRAYGPU_SHADER_PT;
+  const bool pt = GENERAL ? (P.shade.shader == SPRAYGPU_SHADER_PT) : true;
   const int nl = pt ? P.shade.nlights : 1;
   uint32_t cnt[3] = {0, 0, 0};
   uint32_t n_eye = 0, n_rad = 0, n_shadow = 0, n_hit = 0;
+  int count = 0;      // rays in this warp's queue (warp-uniform)
+  bool more = true;   // the tile still has unclaimed sample slots
 
   for (;;) {
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(P.counters, 32ull);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= P.total_slots) break;
-    const uint32_t slot = (uint32_t)base + lane;
-    // slot -> (pixel block, lane in block, sample)
-    const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
-    const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-    const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
-    const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
-    bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
-
-    uint32_t samid = 0, pixid = 0;
-    Pending cur;
-    cur.o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-    cur.d = mk3(0.f, 0.f, 1.f); cur.w = mk3(1.f, 1.f, 1.f); cur.depth = 0;
-    if (has_ray) {
-      eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &samid, &pixid, &cur.d);
-      ++n_eye;
-    }
-    Pending stack[MAX_PENDING];  // second rays of glass hits (reflection + transmission); rarely used
-    int nstack = 0;
-
-    while (__any_sync(0xffffffffu, has_ray)) {
-      // ---------------- closest hit ----------------
-      warp_cull(D, has_ray, cur.o, cur.d, true);
-      SceneHit h; h.t = INFINITY; h.dom = 0; h.prim = 0; h.u = h.v = 0.f;
-      if (has_ray) { scene_closest<COUNT>(P.table, D, cur.o, cur.d, h, cnt); ++n_rad; }
-      const bool hit = has_ray && h.t < INFINITY;
-      // ---------------- shading context ----------------
-      vec3 pos = cur.o, kd = mk3(0, 0, 0), nff = mk3(0, 0, 1), wo = gneg(cur.d);
-      float cos_theta_i = 0.f; bool entering = false; int mtl = SPRAYGPU_MTL_DIFFUSE; float eta0 = 1.f, eta1 = 1.f;
-      if (hit) {
-        ++n_hit;
-        const DomainEntry* e = P.table + h.dom;
-        uint32_t color; vec3 normal;
-        fetch_attributes(e, h.prim, h.u, h.v, &color, &normal);
-        pos = mk3(add_rn(mul_rn(cur.d.x, h.t), cur.o.x), add_rn(mul_rn(cur.d.y, h.t), cur.o.y),
-                  add_rn(mul_rn(cur.d.z, h.t), cur.o.z));
-        kd = unpack_color(color);
-        cos_theta_i = gdot(wo, normal);
-        entering = cos_theta_i > 0.0f;
-        nff = gnormalize(entering ? normal : gneg(normal));
-        mtl = e->mtl_type; eta0 = e->mtl[0]; eta1 = e->mtl[1];
+    if (count < 32 && more) {
+      // ---------------- refill: one 8x4 pixel block of eye rays (ooc_tracer.inl:84-172) ----------------
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd(P.counters, 32ull);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (base >= P.total_slots) { more = false; continue; }
+      const uint32_t slot = (uint32_t)base + lane;
+      const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
+      const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
+      const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
+      const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
+      const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
+      uint32_t samid = 0, pixid = 0;
+      vec3 dir = mk3(0.f, 0.f, 1.f);
+      if (has_ray) {
+        eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &samid, &pixid, &dir);
+        ++n_eye; ++n_rad;
       }
-      const bool delta = mtl != SPRAYGPU_MTL_DIFFUSE;
-      const int next_depth = cur.depth + 1;
-      const vec3 Lin = cur.w;
-      // ---------------- shadow rays: one light sample per warp pass ----------------
-      {
-        uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
-        const float ao_weight = div_rn(1.0f, (float)P.shade.ao_samples);
-        int l = 0, k = 0;
-        bool more_lights = hit && !delta && nl > 0;
-        while (__any_sync(0xffffffffu, more_lights)) {
-          bool emit = false; vec3 wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
-          if (more_lights) {
-            const spraygpu_light& L = P.shade.lights[pt ? l : 0];
-            const bool area = pt ? (L.type == SPRAYGPU_LIGHT_DIFFUSE) : true;
-            const vec3 rad = mk3(L.radiance[0], L.radiance[1], L.radiance[2]);
-            float pdf, costheta;
-            if (pt) {
-              if (area) {
-                const float u1 = rng_float(ls), u2 = rng_float(ls);
-                cosine_hemisphere(u1, u2, nff, &wi, &pdf);
-                if (pdf > 0.0f) {
-                  costheta = gclamp(gdot(nff, wi), 0.0f, 1.0f);
-                  Lr = gscale(gmul(Lin, blinn_phong(costheta, kd, ks, P.shade.shininess, rad, wi, nff, wo)),
-                              div_rn(1.0f, mul_rn(pdf, (float)P.shade.ao_samples)));
-                  emit = true;
-                }
+      queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), pixid,
+                 samid, 0u);
+      continue;
+    }
+    if (count == 0) break;
+
+    // ---------------- pop up to 32 rays; every popped lane traverses ----------------
+    const int n = count < 32 ? count : 32;
+    count -= n;
+    const bool act = lane < n;
+    const uint32_t* qe = Q.q + count + (act ? lane : 0);
+    const vec3 ro = mk3(__uint_as_float(qe[(QF_O + 0) * QCAP]), __uint_as_float(qe[(QF_O + 1) * QCAP]),
+                        __uint_as_float(qe[(QF_O + 2) * QCAP]));
+    const vec3 rd = mk3(__uint_as_float(qe[(QF_D + 0) * QCAP]), __uint_as_float(qe[(QF_D + 1) * QCAP]),
+                        __uint_as_float(qe[(QF_D + 2) * QCAP]));
+    const uint32_t dk = qe[QF_DK * QCAP];
+    const bool shadow = (dk & 1u) != 0u;
+    SceneHit h; h.t = INFINITY; h.dom = 0; h.prim = 0; h.u = h.v = 0.f;
+    bool found = false;
+    if (act) found = scene_trace<COUNT>(P.table, D, StridedCand{qe + QF_MASK * QCAP, QCAP}, ro, rd, shadow, h, cnt);
+    // payload (read before any push overwrites the popped entries)
+    const vec3 Lin = mk3(__uint_as_float(qe[(QF_W + 0) * QCAP]), __uint_as_float(qe[(QF_W + 1) * QCAP]),
+                         __uint_as_float(qe[(QF_W + 2) * QCAP]));
+    const uint32_t pixid = qe[QF_PIX * QCAP], samid = qe[QF_SAM * QCAP];
+    __syncwarp();
+
+    if (act && shadow && !found) fb_add(P.fb, pixid, scale, Lin);
+
+    // ---------------- shade radiance hits (ooc_shader_pt.h:94-227, ooc_shader_ao.h:92-197) ----------------
+    const bool hit = act && !shadow && found;
+    const int next_depth = (int)(dk >> 1) + 1;
+    vec3 pos = ro, kd = mk3(0, 0, 0), nff = mk3(0, 0, 1), wo = gneg(rd);
+    float cos_theta_i = 0.f; bool entering = false; int mtl = SPRAYGPU_MTL_DIFFUSE; float eta0 = 1.f, eta1 = 1.f;
+    if (hit) {
+      ++n_hit;
+      const DomainEntry* e = P.table + h.dom;
+      uint32_t color; vec3 normal;
+      fetch_attributes(e, h.prim, h.u, h.v, &color, &normal);
+      pos = mk3(add_rn(mul_rn(rd.x, h.t), ro.x), add_rn(mul_rn(rd.y, h.t), ro.y), add_rn(mul_rn(rd.z, h.t), ro.z));
+      kd = unpack_color(color);
+      cos_theta_i = gdot(wo, normal);
+      entering = cos_theta_i > 0.0f;
+      nff = gnormalize(entering ? normal : gneg(normal));
+      if (GENERAL) { mtl = e->mtl_type; eta0 = e->mtl[0]; eta1 = e->mtl[1]; }
+    }
+    const bool delta = mtl != SPRAYGPU_MTL_DIFFUSE;
+
+    // ---------------- secondary rays: pushed first (the queue has room for them by construction) ----------------
+    {
+      bool em1 = false, em2 = false;
+      vec3 d1 = mk3(0, 0, 1), w1 = mk3(0, 0, 0), d2 = mk3(0, 0, 1), w2 = mk3(0, 0, 0);
+      if (hit && next_depth < P.shade.bounces) {
+        const vec3 won = gnormalize(wo);
+        if (GENERAL && delta) {
+          if (cos_theta_i != 0.0f) {
+            float ci = gclamp(cos_theta_i, -1.0f, 1.0f);
+            const float abs_cos = fabsf(ci);
+            if (!entering) ci = abs_cos;
+            bool has_reflect = false, has_trans = false; float fr = 0.f; vec3 wt = mk3(0, 0, 0);
+            if (mtl == SPRAYGPU_MTL_MIRROR) { fr = 1.0f; has_reflect = true; }
+            else {
+              const float etaI = entering ? eta0 : eta1, etaT = entering ? eta1 : eta0;
+              if (mtl == SPRAYGPU_MTL_GLASS) {
+                fr = fr_dielectric(ci, etaI, etaT, won, nff, &wt);
+                if (fr == 1.0f) has_reflect = true;
+                else if (fr == 0.0f) has_trans = true;
+                else { has_reflect = true; has_trans = true; }
               } else {
-                wi = gnormalize(gsub(mk3(L.position[0], L.position[1], L.position[2]), pos));
+                if (refract_dir(ci, etaI, etaT, won, nff, &wt)) { has_trans = true; fr = 0.0f; }
+                else { has_reflect = true; fr = 1.0f; }
+              }
+            }
+            // the reference CHECK-fails when glass yields both (ooc_shader_pt.h:199-201); we trace both
+            if (has_reflect) {
+              const vec3 wr = gadd(gneg(won), gscale(nff, mul_rn(2.0f, gdot(won, nff))));
+              d1 = gnormalize(wr);
+              w1 = gscale(Lin, div_rn(fr, abs_cos));
+              em1 = has_positive(w1);
+            }
+            if (has_trans) {
+              d2 = gnormalize(wt);
+              w2 = gscale(Lin, div_rn(sub_rn(1.0f, fr), abs_cos));
+              em2 = has_positive(w2);
+            }
+          }
+        } else {
+          uint32_t rs = rng_init1(samid * (uint32_t)next_depth);
+          const float u1 = rng_float(rs), u2 = rng_float(rs);
+          float pdf;
+          cosine_hemisphere(u1, u2, nff, &d1, &pdf);
+          const float costheta = gclamp(gdot(nff, d1), 0.0f, 1.0f);
+          vec3 Lr = gscale(gscale(gmul(Lin, kd), SPRAY_ONE_OVER_PI), costheta);
+          w1 = mk3(div_rn(Lr.x, pdf), div_rn(Lr.y, pdf), div_rn(Lr.z, pdf));
+          em1 = has_positive(w1);
+        }
+      }
+      if (em1) ++n_rad;
+      if (__any_sync(0xffffffffu, em1))
+        queue_push(Q, D, count, em1, pos, d1, w1, pixid, samid, (uint32_t)next_depth << 1);
+      if (GENERAL) {
+        if (em2) ++n_rad;
+        if (__any_sync(0xffffffffu, em2))
+          queue_push(Q, D, count, em2, pos, d2, w2, pixid, samid, (uint32_t)next_depth << 1);
+      }
+    }
+    // ---------------- shadow rays: one light sample per lane per pass ----------------
+    {
+      uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
+      int l = 0, k = 0;
+      bool more_lights = hit && !delta && nl > 0;
+      while (__any_sync(0xffffffffu, more_lights)) {
+        bool emit = false; vec3 wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
+        if (more_lights) {
+          const spraygpu_light& L = P.shade.lights[pt ? l : 0];
+          const bool area = GENERAL ? (pt ? (L.type == SPRAYGPU_LIGHT_DIFFUSE) : true) : false;
+          const vec3 rad = mk3(L.radiance[0], L.radiance[1], L.radiance[2]);
+          float costheta;
+          if (GENERAL && area) {
+            float pdf;
+            if (pt) {
+              const float u1 = rng_float(ls), u2 = rng_float(ls);
+              cosine_hemisphere(u1, u2, nff, &wi, &pdf);
+              if (pdf > 0.0f) {
                 costheta = gclamp(gdot(nff, wi), 0.0f, 1.0f);
-                Lr = gscale(gmul(Lin, blinn_phong(costheta, kd, ks, P.shade.shininess, rad, wi, nff, wo)), 1.0f);
+                Lr = gscale(gmul(Lin, blinn_phong(costheta, kd, ks, P.shade.shininess, rad, wi, nff, wo)),
+                            div_rn(1.0f, mul_rn(pdf, (float)P.shade.ao_samples)));
                 emit = true;
               }
             } else {
+              const float ao_weight = div_rn(1.0f, (float)P.shade.ao_samples);
               uint32_t as = rng_init1(pixid * (uint32_t)(k + 1));  // ooc_shader_ao.h:131
               const float u1 = rng_float(as), u2 = rng_float(as);
               cosine_hemisphere(u1, u2, nff, &wi, &pdf);
@@ -522,78 +692,30 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
               Lr = gscale(gmul(Lin, kd), div_rn(mul_rn(mul_rn(SPRAY_ONE_OVER_PI, costheta), ao_weight), pdf));
               emit = true;
             }
-            emit = emit && has_positive(Lr);
-            // advance (l, k)
-            ++k;
-            if (k >= (area ? P.shade.ao_samples : 1)) { k = 0; ++l; }
-            more_lights = l < nl;
+          } else {
+            wi = gnormalize(gsub(mk3(L.position[0], L.position[1], L.position[2]), pos));
+            costheta = gclamp(gdot(nff, wi), 0.0f, 1.0f);
+            Lr = gscale(gmul(Lin, blinn_phong(costheta, kd, ks, P.shade.shininess, rad, wi, nff, wo)), 1.0f);
+            emit = true;
           }
+          emit = emit && has_positive(Lr);
+          ++k;
+          if (k >= (area ? P.shade.ao_samples : 1)) { k = 0; ++l; }
+          more_lights = l < nl;
+        }
+        if (emit) ++n_shadow;
+        if (!GENERAL || count + 32 <= QCAP) {
+          // a shadow ray that enters no resident domain is unoccluded
+          if (queue_push(Q, D, count, emit, pos, wi, Lr, pixid, samid, 1u)) fb_add(P.fb, pixid, scale, Lr);
+        } else {
+          // queue full (many light samples per hit): trace this pass in place
           warp_cull(D, emit, pos, wi, true);
           if (emit) {
-            ++n_shadow;
-            if (!scene_occluded<COUNT>(P.table, D, pos, wi, cnt)) {
-              // TContext::retire -> HdrImage::add (ooc_tcontext.inl:123-135, image.h:99-109)
-              float* px = P.fb + 4 * (size_t)pixid;
-              atomicAdd(px + 0, mul_rn(scale, Lr.x));
-              atomicAdd(px + 1, mul_rn(scale, Lr.y));
-              atomicAdd(px + 2, mul_rn(scale, Lr.z));
-            }
+            SceneHit hs;
+            if (!scene_trace<COUNT>(P.table, D, WarpCand{D.cand}, pos, wi, true, hs, cnt)) fb_add(P.fb, pixid, scale, Lr);
           }
         }
       }
-      // ---------------- next ray of this lane: bounce, or a pending second ray ----------------
-      bool next = false;
-      if (hit && next_depth < P.shade.bounces) {
-        wo = gnormalize(wo);
-        vec3 wi, Lr; float pdf, costheta;
-        if (delta) {
-          if (cos_theta_i != 0.0f) {
-            cos_theta_i = gclamp(cos_theta_i, -1.0f, 1.0f);
-            const float abs_cos = fabsf(cos_theta_i);
-            if (!entering) cos_theta_i = abs_cos;
-            bool has_reflect = false, has_trans = false; float fr = 0.f; vec3 wt = mk3(0, 0, 0);
-            if (mtl == SPRAYGPU_MTL_MIRROR) { fr = 1.0f; has_reflect = true; }
-            else {
-              const float etaI = entering ? eta0 : eta1, etaT = entering ? eta1 : eta0;
-              if (mtl == SPRAYGPU_MTL_GLASS) {
-                fr = fr_dielectric(cos_theta_i, etaI, etaT, wo, nff, &wt);
-                if (fr == 1.0f) has_reflect = true;
-                else if (fr == 0.0f) has_trans = true;
-                else { has_reflect = true; has_trans = true; }
-              } else {
-                if (refract_dir(cos_theta_i, etaI, etaT, wo, nff, &wt)) { has_trans = true; fr = 0.0f; }
-                else { has_reflect = true; fr = 1.0f; }
-              }
-            }
-            // the reference CHECK-fails when glass yields both (ooc_shader_pt.h:199-201); we trace both:
-            // reflection first, transmission parked on the lane's pending stack
-            Pending refl, trans; bool ok_r = false, ok_t = false;
-            if (has_trans) {
-              wi = gnormalize(wt);
-              Lr = gscale(Lin, div_rn(sub_rn(1.0f, fr), abs_cos));
-              if (has_positive(Lr)) { trans.o = pos; trans.d = wi; trans.w = Lr; trans.depth = next_depth; ok_t = true; }
-            }
-            if (has_reflect) {
-              const vec3 wr = gadd(gneg(wo), gscale(nff, mul_rn(2.0f, gdot(wo, nff))));
-              wi = gnormalize(wr);
-              Lr = gscale(Lin, div_rn(fr, abs_cos));
-              if (has_positive(Lr)) { refl.o = pos; refl.d = wi; refl.w = Lr; refl.depth = next_depth; ok_r = true; }
-            }
-            if (ok_r) { cur = refl; next = true; if (ok_t && nstack < MAX_PENDING) stack[nstack++] = trans; }
-            else if (ok_t) { cur = trans; next = true; }
-          }
-        } else {
-          uint32_t rs = rng_init1(samid * (uint32_t)next_depth);
-          const float u1 = rng_float(rs), u2 = rng_float(rs);
-          cosine_hemisphere(u1, u2, nff, &wi, &pdf);
-          costheta = gclamp(gdot(nff, wi), 0.0f, 1.0f);
-          Lr = gscale(gscale(gmul(Lin, kd), SPRAY_ONE_OVER_PI), costheta);
-          Lr = mk3(div_rn(Lr.x, pdf), div_rn(Lr.y, pdf), div_rn(Lr.z, pdf));
-          if (has_positive(Lr)) { cur.o = pos; cur.d = wi; cur.w = Lr; cur.depth = next_depth; next = true; }
-        }
-      }
-      if (!next && has_ray && nstack > 0) { cur = stack[--nstack]; next = true; }
-      has_ray = next;
     }
   }
 
@@ -689,20 +811,25 @@ int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_s
   P.total_slots = (uint32_t)slots;
   if (!slots) return SPRAYGPU_OK;
   SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long) * 8, dev->stream));
-  const size_t smem = dom_smem_bytes(dev->ndomains, 8);
+  // lean variant: PT shader, ONE point light, all domains diffuse
+  bool general = shade->shader != SPRAYGPU_SHADER_PT || shade->nlights != 1;
+  for (int i = 0; i < shade->nlights; ++i) general = general || shade->lights[i].type != SPRAYGPU_LIGHT_POINT;
+  for (int i = 0; i < dev->ndomains; ++i) general = general || dev->h_domains[i].mtl_type != SPRAYGPU_MTL_DIFFUSE;
+  void (*kern)(RenderParams) =
+      counted ? (general ? render_tile_kernel<true, true> : render_tile_kernel<true, false>)
+              : (general ? render_tile_kernel<false, true> : render_tile_kernel<false, false>);
+  const int qcap = general ? QueueCap<true>::value : QueueCap<false>::value;
+  const size_t smem = ((dom_smem_bytes(dev->ndomains, 8) + 15) & ~(size_t)15) +
+                      8 * queue_words_per_warp(dev->ndomains, qcap) * sizeof(uint32_t);
+  SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  if (counted) {
-    SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tile_kernel<true>, 256, smem));
-  } else {
-    SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_tile_kernel<false>, 256, smem));
-  }
+  SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
   if (per_sm < 1) per_sm = 1;
   // persistent grid: SM count x resident CTAs per SM
   int grid = dev->sm_count * per_sm;
   const uint64_t warps_needed = (slots + 31) / 32;
   if ((uint64_t)grid * 8 > warps_needed) grid = (int)((warps_needed + 7) / 8);
-  if (counted) render_tile_kernel<true><<<grid, 256, smem, dev->stream>>>(P);
-  else render_tile_kernel<false><<<grid, 256, smem, dev->stream>>>(P);
+  kern<<<grid, 256, smem, dev->stream>>>(P);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
