@@ -149,6 +149,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("SPRAY_WORKLOAD", "c2"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partition", default=os.environ.get("SPRAY_PARTITION", "image"), choices=["image", "insitu", "both"],
+                    help="N > 1: image = the reference's --partition image (spray_ooc: all domains on every rank, "
+                         "row bands, NCCL gather); insitu = --partition insitu (domains sharded, NCCL min-all-reduce "
+                         "on the hit keys); both = headline image, insitu reported beside it")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -191,11 +195,20 @@ def main():
 
     if world > 1:
         from spray_b200 import multigpu
-        mg = multigpu.ShardedRenderer(dev, sc, cam, sh, W, H, rank, world)
+        comm = multigpu.bootstrap_comm(dev, rank, world)
+        mode = "image" if args.partition == "both" else args.partition
+        Renderer = multigpu.ImagePartitionRenderer if mode == "image" else multigpu.InsituRenderer
+        mg = Renderer(dev, sc, cam, sh, W, H, rank, world, comm)
         step_dev = mg.frame_device
         step_e2e = mg.frame_host
-        rays_of = mg.rays_last_frame
-        t_build0 = time.perf_counter()
+        st_mg = mg.count_rays()
+        rr = torch.tensor([st_mg["radiance_rays"] + st_mg["shadow_rays"]], dtype=torch.int64, device="cuda")
+        if mode == "image":
+            dist.all_reduce(rr)          # each rank counted its own band
+        rays_total = int(rr.item())
+
+        def rays_of():
+            return rays_total
     else:
         t_build0 = time.perf_counter()
         scenes_by_id = dev.load_scene(sc)
@@ -261,16 +274,34 @@ def main():
     value = rays / (ms_dev * 1e-3) / 1e6
     e2e_v = rays / (ms_e2e * 1e-3) / 1e6
 
+    par_label = "1 GPU, all domains resident"
+    insitu_extra = None
+    if world > 1:
+        par_label = ("image partition x%d (reference --partition image: all domains on every rank, row bands, NCCL gather to rank 0)" % world
+                     if mode == "image" else
+                     "in-situ domain partition x%d (Morton), NCCL min-all-reduce on 64-bit hit keys + max-all-reduce on occlusion, NCCL image reduce" % world)
+        if args.partition == "both":
+            dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
+            comm2 = multigpu.bootstrap_comm(dev2, rank, world)
+            mg2 = multigpu.InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2)
+            st2 = mg2.count_rays()
+            ms2, _ = timed(mg2.frame_device, max(args.steps // 2, 3), 3)
+            r2 = st2["radiance_rays"] + st2["shadow_rays"]
+            insitu_extra = {"value": r2 / (ms2 * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms2,
+                            "parallelism": "in-situ domain partition x%d, NCCL min-all-reduce on hit keys" % world}
+            comm2.close(); dev2.close()
     if rank == 0:
         peak, peak_src = measured_peak_hbm()
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic camera rays on the reference's example scene (random-free)",
                 "config": {"workload": label, "tiles_per_frame": len(tiles), "l2_flush_between_steps": True,
-                           "rays_per_frame": int(rays), "parallelism": "domains sharded x%d (Morton in-situ partition), NCCL min-allreduce on 64-bit hit keys" % world if world > 1 else "1 GPU, all domains resident"},
+                           "rays_per_frame": int(rays), "parallelism": par_label},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(len(tiles) * (capi.C.sizeof(capi.Camera) + capi.C.sizeof(capi.Shade))),
                         "d2h_bytes_per_step": int(W * H * 16)}}
+        if insitu_extra:
+            line["insitu"] = insitu_extra
         if world == 1:
             nn, nt, nh = stats_tot["nodes_visited"], stats_tot["tris_tested"], stats_tot["hits"]
             nrays = rays
@@ -291,6 +322,7 @@ def main():
                                         "sample": "rows %d..%d of the frame (%d rays), 3 steps; CPU restatement (oracle O2), NOT Embree" % (tile[1], tile[1] + tile[3], crays)}
         print(json.dumps(line))
     if world > 1:
+        comm.close()
         dist.destroy_process_group()
     dev.close()
 

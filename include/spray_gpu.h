@@ -186,6 +186,51 @@ SPRAYGPU_API int spraygpu_trace_tile(spraygpu_device dev, const spraygpu_camera*
 SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                 spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
 
+/* ---- multi-GPU: one process (rank) per GPU on one NVLink/NVSwitch box.  Replaces the reference's MPI
+ *      (SURVEY.md section 2.2): MPI_Init/Comm_rank (src/apps/spray_insitu_*.cc:33-38), the in-situ domain
+ *      partition (src/render/data_partition.h:59-137), the t-buffer MPI_Allreduce(MIN)
+ *      (src/insitu/insitu_vbuf.h:113), the occlusion MPI_Allreduce(BOR) (:124), the MPI_Isend/Recv ray
+ *      forwarding (src/insitu/insitu_comm.inl:40-98) and HdrImage::composite's MPI_Reduce(SUM)
+ *      (src/display/image.h:167-181).  NCCL is loaded at run time (libnccl.so.2); without it these
+ *      entry points return SPRAYGPU_ERR_STATE. ---- */
+typedef struct spraygpu_comm_s* spraygpu_comm;
+#define SPRAYGPU_UNIQUE_ID_BYTES 128
+/* ncclGetUniqueId: rank 0 creates it, the host application broadcasts the 128 bytes (any transport). */
+SPRAYGPU_API int spraygpu_comm_unique_id(char id[SPRAYGPU_UNIQUE_ID_BYTES]);
+/* ncclCommInitRank on dev's GPU (collective over all ranks). */
+SPRAYGPU_API int spraygpu_comm_create(spraygpu_device dev, int nranks, int rank, const char id[SPRAYGPU_UNIQUE_ID_BYTES],
+                                      spraygpu_comm* out);
+SPRAYGPU_API int spraygpu_comm_destroy(spraygpu_comm comm);
+/* InsituPartition::partition (data_partition.h:59-137; morton.h:33-52): 30-bit Morton code of each
+ * domain's AABB centre normalised to the scene AABB, sorted, contiguous runs of ndomains/nranks per rank;
+ * round_robin != 0 = the reference's `#else` branch (:139-155).  Pure host function (no GPU needed).
+ * codes may be NULL. */
+SPRAYGPU_API int spraygpu_partition_domains(int ndomains, const float* world_aabb6, const float scene_aabb6[6], int nranks,
+                                            int round_robin, int32_t* domain_to_rank, uint32_t* codes);
+/* The in-situ blocking tile: same contract and result as spraygpu_trace_tile, but every rank holds only
+ * ITS domains (spraygpu_domain_bind) and all ranks call this collectively with identical arguments.
+ * Per ray generation: eye / bounce rays are identical on every rank; each rank traces them against its
+ * resident domains; hits are resolved by ncclAllReduce(ncclUint64, ncclMin) on the packed keys
+ * (insitu::VBuf::compositeTbuf); the rank owning the winning domain shades; shadow directions travel by
+ * an all-reduce, occlusion by ncclAllReduce(max) on one byte per ray (compositeObuf); the owner adds the
+ * radiance into ITS frame buffer.  fb therefore holds this rank's partial image: sum the ranks with
+ * spraygpu_image_reduce.  fb must be a device pointer.  stats (may be NULL) are summed over ranks.
+ * insitu::{SingleThread,MultiThread}Tracer::trace (src/insitu/insitu_singlethread_tracer.inl:381-466). */
+SPRAYGPU_API int spraygpu_trace_tile_insitu(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
+                                            const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
+                                            spraygpu_stats* stats);
+/* HdrImage::composite (image.h:167-181): fb = sum over ranks, valid on `root` (in place, device pointer). */
+SPRAYGPU_API int spraygpu_image_reduce(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, size_t npixels, int root);
+/* Image-partition composite for DISJOINT row bands (rank r rendered rows [row_begin[r], row_begin[r+1])):
+ * root receives every band in place (ncclSend/ncclRecv group) — 1/nranks of the reduce's traffic. */
+SPRAYGPU_API int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, int image_w,
+                                            const int32_t* row_begin /* nranks + 1 */, int root);
+/* ncclAllReduce(ncclUint64, ncclMin) on hit keys / ncclAllReduce(ncclUint8, ncclMax) on occlusion bytes,
+ * in place on device buffers: the building blocks for callers that drive spraygpu_intersect_domains /
+ * spraygpu_occluded_domains themselves. */
+SPRAYGPU_API int spraygpu_allreduce_keys_min(spraygpu_device dev, spraygpu_comm comm, spraygpu_key* keys, size_t n);
+SPRAYGPU_API int spraygpu_allreduce_occ_max(spraygpu_device dev, spraygpu_comm comm, uint8_t* occ, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

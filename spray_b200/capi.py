@@ -105,7 +105,18 @@ _PROTOS = {
     "spraygpu_gen_eye_rays": (C.c_int, [_vp, C.POINTER(Camera), Tile, C.c_int, _vp]),
     "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
+    # multi-GPU (NCCL resolved at run time)
+    "spraygpu_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "spraygpu_comm_create": (C.c_int, [_vp, C.c_int, C.c_int, C.c_char_p, C.POINTER(_vp)]),
+    "spraygpu_comm_destroy": (C.c_int, [_vp]),
+    "spraygpu_partition_domains": (C.c_int, [C.c_int, _vp, _vp, C.c_int, C.c_int, _vp, _vp]),
+    "spraygpu_trace_tile_insitu": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
+    "spraygpu_image_reduce": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "spraygpu_image_gather_rows": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int]),
+    "spraygpu_allreduce_keys_min": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "spraygpu_allreduce_occ_max": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
 }
+UNIQUE_ID_BYTES = 128
 
 _lib = None
 
@@ -266,6 +277,59 @@ class Device:
         fn = lib().spraygpu_trace_tile_counted if counted else lib().spraygpu_trace_tile
         _check(fn(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb), C.byref(st) if st is not None else None))
         return st
+
+
+def partition_domains(world_bounds, scene_bounds, nranks, round_robin=False, return_codes=False):
+    """InsituPartition::partition (reference src/render/data_partition.h:59-137) — host function of the C ABI."""
+    wb = np.ascontiguousarray(world_bounds, np.float32).reshape(-1, 6)
+    sb = np.ascontiguousarray(scene_bounds, np.float32).reshape(6)
+    d2r = np.zeros(len(wb), np.int32)
+    codes = np.zeros(len(wb), np.uint32)
+    _check(lib().spraygpu_partition_domains(len(wb), wb.ctypes.data, sb.ctypes.data, int(nranks), int(round_robin),
+                                            d2r.ctypes.data, codes.ctypes.data))
+    return (d2r, codes) if return_codes else d2r
+
+
+def comm_unique_id():
+    """ncclGetUniqueId; rank 0 calls it and the application broadcasts the bytes."""
+    buf = C.create_string_buffer(UNIQUE_ID_BYTES)
+    _check(lib().spraygpu_comm_unique_id(buf))
+    return buf.raw
+
+
+class Comm:
+    """One rank of the NCCL communicator that replaces the reference's MPI world."""
+
+    def __init__(self, dev, nranks, rank, unique_id):
+        self.dev, self.nranks, self.rank = dev, int(nranks), int(rank)
+        self.h = _vp()
+        assert len(unique_id) == UNIQUE_ID_BYTES
+        _check(lib().spraygpu_comm_create(dev.h, self.nranks, self.rank, unique_id, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().spraygpu_comm_destroy(self.h)
+            self.h = _vp()
+
+    def trace_tile_insitu(self, cam, shade, tile, fb, stats=False):
+        st = Stats() if stats else None
+        _check(lib().spraygpu_trace_tile_insitu(self.dev.h, self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb),
+                                                C.byref(st) if st is not None else None))
+        return st
+
+    def image_reduce(self, fb, npixels, root=0):
+        _check(lib().spraygpu_image_reduce(self.dev.h, self.h, _ptr(fb), int(npixels), int(root)))
+
+    def image_gather_rows(self, fb, image_w, row_begin, root=0):
+        rb = np.ascontiguousarray(row_begin, np.int32)
+        assert len(rb) == self.nranks + 1
+        _check(lib().spraygpu_image_gather_rows(self.dev.h, self.h, _ptr(fb), int(image_w), rb.ctypes.data, int(root)))
+
+    def allreduce_keys_min(self, keys, n):
+        _check(lib().spraygpu_allreduce_keys_min(self.dev.h, self.h, _ptr(keys), int(n)))
+
+    def allreduce_occ_max(self, occ, n):
+        _check(lib().spraygpu_allreduce_occ_max(self.dev.h, self.h, _ptr(occ), int(n)))
 
 
 class Scene:

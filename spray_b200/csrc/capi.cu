@@ -135,6 +135,7 @@ int spraygpu_device_destroy(spraygpu_device dev) {
   if (d->scratch.ptr) cudaFree(d->scratch.ptr);
   if (d->stage_in.ptr) cudaFree(d->stage_in.ptr);
   if (d->stage_out.ptr) cudaFree(d->stage_out.ptr);
+  if (d->wave.ptr) cudaFree(d->wave.ptr);
   if (d->pinned) cudaFreeHost(d->pinned);
   cudaFree(d->d_domains);
   cudaFree(d->d_counters);

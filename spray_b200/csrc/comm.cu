@@ -1,0 +1,232 @@
+// comm.cu — NCCL plumbing of libspraygpu (multi-GPU section of include/spray_gpu.h).
+// NCCL is resolved at RUN time (dlopen of libnccl.so.2; an already-loaded copy, e.g. PyTorch's, is
+// reused), so the library loads — and the single-GPU path works — on hosts without NCCL.
+#include <dlfcn.h>
+#include <nccl.h>   // types and enums only; no link-time dependency
+
+#include <algorithm>
+#include <mutex>
+
+#include "internal.cuh"
+
+namespace spraygpu {
+
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  const char* (*GetErrorString)(ncclResult_t);
+  bool ok = false;
+};
+
+static NcclApi g_nccl;
+static std::once_flag g_nccl_once;
+
+static void load_nccl() {
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);   // reuse the process's copy if there is one
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+  if (!h) return;
+  bool ok = true;
+  auto sym = [&](const char* name) -> void* {
+    void* p = dlsym(h, name);
+    if (!p) ok = false;
+    return p;
+  };
+  g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))sym("ncclGetUniqueId");
+  g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))sym("ncclCommInitRank");
+  g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))sym("ncclCommDestroy");
+  g_nccl.AllReduce = (decltype(g_nccl.AllReduce))sym("ncclAllReduce");
+  g_nccl.Reduce = (decltype(g_nccl.Reduce))sym("ncclReduce");
+  g_nccl.Send = (decltype(g_nccl.Send))sym("ncclSend");
+  g_nccl.Recv = (decltype(g_nccl.Recv))sym("ncclRecv");
+  g_nccl.GroupStart = (decltype(g_nccl.GroupStart))sym("ncclGroupStart");
+  g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))sym("ncclGroupEnd");
+  g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))sym("ncclGetErrorString");
+  g_nccl.ok = ok;
+}
+
+static const NcclApi* nccl() {
+  std::call_once(g_nccl_once, load_nccl);
+  return g_nccl.ok ? &g_nccl : nullptr;
+}
+
+#define SG_NCCL(call)                                                                                  \
+  do {                                                                                                 \
+    ncclResult_t r__ = (call);                                                                         \
+    if (r__ != ncclSuccess) {                                                                          \
+      set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r__));        \
+      return SPRAYGPU_ERR_CUDA;                                                                        \
+    }                                                                                                  \
+  } while (0)
+
+struct Comm {
+  Device* dev = nullptr;
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+};
+
+// collectives used by insitu.cu (all on dev->stream, in place)
+int comm_allreduce_u64_min(Comm* c, uint64_t* p, size_t n) {
+  if (c->nranks == 1 || !n) return SPRAYGPU_OK;
+  SG_NCCL(g_nccl.AllReduce(p, p, n, ncclUint64, ncclMin, c->comm, c->dev->stream));
+  return SPRAYGPU_OK;
+}
+int comm_allreduce_u8_max(Comm* c, uint8_t* p, size_t n) {
+  if (c->nranks == 1 || !n) return SPRAYGPU_OK;
+  SG_NCCL(g_nccl.AllReduce(p, p, n, ncclUint8, ncclMax, c->comm, c->dev->stream));
+  return SPRAYGPU_OK;
+}
+// Buffers with DISJOINT support across ranks (exactly one rank writes a non-zero word, the rest hold 0):
+// an integer sum moves the bit patterns unchanged (a float sum would turn -0.0 into +0.0).
+int comm_allreduce_bits_sum(Comm* c, uint32_t* p, size_t nwords) {
+  if (c->nranks == 1 || !nwords) return SPRAYGPU_OK;
+  SG_NCCL(g_nccl.AllReduce(p, p, nwords, ncclUint32, ncclSum, c->comm, c->dev->stream));
+  return SPRAYGPU_OK;
+}
+int comm_allreduce_u64_sum(Comm* c, unsigned long long* p, size_t n) {
+  if (c->nranks == 1 || !n) return SPRAYGPU_OK;
+  SG_NCCL(g_nccl.AllReduce(p, p, n, ncclUint64, ncclSum, c->comm, c->dev->stream));
+  return SPRAYGPU_OK;
+}
+int comm_rank(const Comm* c) { return c->rank; }
+int comm_size(const Comm* c) { return c->nranks; }
+Device* comm_device(const Comm* c) { return c->dev; }
+
+}  // namespace spraygpu
+
+using namespace spraygpu;
+
+extern "C" {
+
+int spraygpu_comm_unique_id(char id[SPRAYGPU_UNIQUE_ID_BYTES]) {
+  SG_CHECK(id, SPRAYGPU_ERR_ARG, "comm_unique_id: id is NULL");
+  SG_CHECK(nccl(), SPRAYGPU_ERR_STATE, "NCCL (libnccl.so.2) is not available on this host");
+  static_assert(sizeof(ncclUniqueId) == SPRAYGPU_UNIQUE_ID_BYTES, "unique id size");
+  ncclUniqueId u;
+  SG_NCCL(g_nccl.GetUniqueId(&u));
+  memcpy(id, &u, sizeof(u));
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_comm_create(spraygpu_device dev, int nranks, int rank, const char id[SPRAYGPU_UNIQUE_ID_BYTES],
+                         spraygpu_comm* out) {
+  SG_CHECK(dev && out && id, SPRAYGPU_ERR_ARG, "comm_create: NULL argument");
+  SG_CHECK(nranks >= 1 && rank >= 0 && rank < nranks, SPRAYGPU_ERR_ARG, "comm_create: bad rank %d of %d", rank, nranks);
+  SG_CHECK(nccl(), SPRAYGPU_ERR_STATE, "NCCL (libnccl.so.2) is not available on this host");
+  Device* d = (Device*)dev;
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  Comm* c = new Comm();
+  c->dev = d; c->nranks = nranks; c->rank = rank;
+  ncclUniqueId u;
+  memcpy(&u, id, sizeof(u));
+  ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, u, rank);
+  if (r != ncclSuccess) {
+    set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+    delete c;
+    return SPRAYGPU_ERR_CUDA;
+  }
+  *out = (spraygpu_comm)c;
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_comm_destroy(spraygpu_comm comm) {
+  if (!comm) return SPRAYGPU_OK;
+  Comm* c = (Comm*)comm;
+  cudaSetDevice(c->dev->cuda_device);
+  cudaStreamSynchronize(c->dev->stream);
+  if (c->comm && nccl()) g_nccl.CommDestroy(c->comm);
+  delete c;
+  return SPRAYGPU_OK;
+}
+
+// InsituPartition::partition, src/render/data_partition.h:59-137 (GROUP_CLOSE_DOMAINS branch) and :139-155
+int spraygpu_partition_domains(int nd, const float* wb, const float sb[6], int nranks, int round_robin, int32_t* d2r,
+                               uint32_t* codes_out) {
+  SG_CHECK(nd > 0 && wb && sb && d2r && nranks > 0, SPRAYGPU_ERR_ARG, "partition_domains: bad argument");
+  // data_partition.h:71-77: scale = 1 / diagonal, offset = 0 - lo * scale (per component, FP32)
+  float sf[3], off[3];
+  for (int a = 0; a < 3; ++a) {
+    const float diag = sb[3 + a] - sb[a];
+    sf[a] = 1.0f / diag;
+    off[a] = 0.0f - sb[a] * sf[a];
+  }
+  std::vector<std::pair<uint32_t, int>> order(nd);
+  for (int i = 0; i < nd; ++i) {
+    float p[3];
+    for (int a = 0; a < 3; ++a) {
+      const float c = (wb[6 * i + a] + wb[6 * i + 3 + a]) * 0.5f;   // Aabb::getCenter
+      p[a] = sf[a] * c + off[a];
+    }
+    order[i] = {morton30(p[0], p[1], p[2]), i};
+    if (codes_out) codes_out[i] = order[i].first;
+  }
+  // the reference's std::sort is unstable on equal codes; ties are broken by domain id here
+  std::sort(order.begin(), order.end());
+  if (round_robin) {
+    for (int k = 0; k < nd; ++k) d2r[order[k].second] = k % nranks;
+    return SPRAYGPU_OK;
+  }
+  const int shares = std::max(nd / nranks, 1);
+  int rank = 0, s = 0;
+  for (int k = 0; k < nd; ++k) {
+    d2r[order[k].second] = rank;
+    if (++s == shares) {
+      s = 0;
+      if (++rank == nranks) rank = 0;
+    }
+  }
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_image_reduce(spraygpu_device dev, spraygpu_comm comm, float* fb, size_t npixels, int root) {
+  SG_CHECK(dev && comm && fb, SPRAYGPU_ERR_ARG, "image_reduce: NULL argument");
+  Comm* c = (Comm*)comm;
+  SG_CHECK(root >= 0 && root < c->nranks, SPRAYGPU_ERR_ARG, "image_reduce: bad root %d", root);
+  if (c->nranks == 1 || !npixels) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  SG_NCCL(g_nccl.Reduce(fb, fb, npixels * 4, ncclFloat32, ncclSum, root, c->comm, c->dev->stream));
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm comm, float* fb, int image_w, const int32_t* row_begin,
+                               int root) {
+  SG_CHECK(dev && comm && fb && row_begin && image_w > 0, SPRAYGPU_ERR_ARG, "image_gather_rows: bad argument");
+  Comm* c = (Comm*)comm;
+  SG_CHECK(root >= 0 && root < c->nranks, SPRAYGPU_ERR_ARG, "image_gather_rows: bad root %d", root);
+  if (c->nranks == 1) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  const size_t row_floats = (size_t)image_w * 4;
+  SG_NCCL(g_nccl.GroupStart());
+  if (c->rank == root) {
+    for (int r = 0; r < c->nranks; ++r) {
+      if (r == root) continue;
+      const size_t n = (size_t)(row_begin[r + 1] - row_begin[r]) * row_floats;
+      if (n) SG_NCCL(g_nccl.Recv(fb + (size_t)row_begin[r] * row_floats, n, ncclFloat32, r, c->comm, c->dev->stream));
+    }
+  } else {
+    const size_t n = (size_t)(row_begin[c->rank + 1] - row_begin[c->rank]) * row_floats;
+    if (n) SG_NCCL(g_nccl.Send(fb + (size_t)row_begin[c->rank] * row_floats, n, ncclFloat32, root, c->comm, c->dev->stream));
+  }
+  SG_NCCL(g_nccl.GroupEnd());
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_allreduce_keys_min(spraygpu_device dev, spraygpu_comm comm, spraygpu_key* keys, size_t n) {
+  SG_CHECK(dev && comm && (keys || !n), SPRAYGPU_ERR_ARG, "allreduce_keys_min: NULL argument");
+  SG_CUDA(cudaSetDevice(((Comm*)comm)->dev->cuda_device));
+  return comm_allreduce_u64_min((Comm*)comm, keys, n);
+}
+int spraygpu_allreduce_occ_max(spraygpu_device dev, spraygpu_comm comm, uint8_t* occ, size_t n) {
+  SG_CHECK(dev && comm && (occ || !n), SPRAYGPU_ERR_ARG, "allreduce_occ_max: NULL argument");
+  SG_CUDA(cudaSetDevice(((Comm*)comm)->dev->cuda_device));
+  return comm_allreduce_u8_max((Comm*)comm, occ, n);
+}
+
+}  // extern "C"

@@ -61,6 +61,7 @@ struct Device {
   int sm_count = 148;
   Scratch scratch;                 // build scratch (grown on demand)
   Scratch stage_in, stage_out;     // device staging for host-pointer calls
+  Scratch wave;                    // in-situ wavefront buffers (insitu.cu)
   void* pinned = nullptr;          // pinned bounce buffer for small D2H reads
   size_t pinned_bytes = 0;
   // domain table

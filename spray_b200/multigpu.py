@@ -1,0 +1,114 @@
+"""Multi-GPU frame loops (one process per GPU, launched by torchrun).  Thin host-side harness over the C ABI:
+torch.distributed is used ONLY to bootstrap (broadcast of the NCCL unique id, barriers, max-over-ranks
+timing); every data-path collective is issued by libspraygpu itself on its own NCCL communicator.
+
+Two decompositions, as in the reference:
+
+* ``ImagePartitionRenderer`` — the reference's ``--partition image`` (spray_ooc, src/ooc/ooc_tracer.inl:29-82,
+  src/render/tile.cc:317-391): every rank holds ALL domains and renders its own pixels; no ray traffic;
+  the image is composited on rank 0 (HdrImage::composite, src/display/image.h:167-181).  Ranks own
+  contiguous ROW bands (the reference cuts vertical stripes; rows are contiguous in memory, so the
+  composite is one NCCL send per rank instead of a whole-image reduce).
+* ``InsituRenderer`` — the reference's ``--partition insitu`` (spray_insitu_*, src/insitu/): domains are
+  sharded with the Morton partition (src/render/data_partition.h:59-137); every rank traces every ray
+  against ITS domains; hits are resolved by an NCCL min-all-reduce on the packed 64-bit keys
+  (replaces insitu::VBuf::compositeTbuf, insitu_vbuf.h:109-117), occlusion by a max-all-reduce
+  (compositeObuf, :119-129); partial images are summed on rank 0.
+"""
+import numpy as np
+
+from . import capi, scenes
+
+
+def row_bands(image_h, nranks):
+    """rank r renders rows [b[r], b[r+1]): equal bands, the remainder spread over the first ranks."""
+    base, rem = divmod(int(image_h), int(nranks))
+    b = [0]
+    for r in range(nranks):
+        b.append(b[-1] + base + (1 if r < rem else 0))
+    return np.asarray(b, np.int32)
+
+
+def band_tiles(image_w, band, spp, max_samples=1024 * 1024):
+    """Blocking tiles (<= max_samples samples each, cfg.maximum_num_samples_per_rank) of one row band."""
+    y0, y1 = int(band[0]), int(band[1])
+    if y1 <= y0:
+        return []
+    rows = max(int(max_samples // max(image_w * spp, 1)), 1)
+    return [(0, y, image_w, min(rows, y1 - y)) for y in range(y0, y1, rows)]
+
+
+def bootstrap_comm(dev, rank, world):
+    """Create the library's NCCL communicator; the unique id travels over torch.distributed."""
+    import torch.distributed as dist
+    obj = [capi.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(obj, src=0)
+    return capi.Comm(dev, world, rank, obj[0])
+
+
+class ImagePartitionRenderer:
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm):
+        import torch
+        self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
+        dev.load_scene(scene)
+        self.bands = row_bands(H, world)
+        self.tiles = band_tiles(W, self.bands[rank:rank + 2], shade.pixel_samples)
+        self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
+
+    def frame_device(self):
+        y0, y1 = int(self.bands[self.rank]), int(self.bands[self.rank + 1])
+        self.fb[y0:y1].zero_()                                   # image_.clear() on the rows this rank renders
+        for t in self.tiles:
+            self.dev.trace_tile(self.cam, self.shade, t, self.fb)
+        self.comm.image_gather_rows(self.fb, self.W, self.bands, 0)
+
+    def frame_host(self):
+        self.frame_device()
+        if self.rank == 0:
+            self.fb_host.copy_(self.fb, non_blocking=True)
+        self.dev.synchronize()
+
+    def count_rays(self):
+        """Deterministic per-frame ray counts of this rank's band (one extra frame with stats)."""
+        tot = {}
+        self.fb.zero_()
+        for t in self.tiles:
+            st = self.dev.trace_tile(self.cam, self.shade, t, self.fb, stats=True)
+            for k, v in st.as_dict().items():
+                tot[k] = tot.get(k, 0) + v
+        return tot
+
+
+class InsituRenderer:
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, round_robin=False):
+        import torch
+        self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
+        wb = np.stack([d["bounds"] for d in scene["domains"]])
+        self.domain_to_rank = capi.partition_domains(wb, scenes.scene_bounds(scene), world, round_robin)
+        self.owned = [i for i, r in enumerate(self.domain_to_rank) if r == rank]
+        dev.load_scene(scene, owned=self.owned)
+        self.tiles = band_tiles(W, (0, H), shade.pixel_samples)   # every rank walks every blocking tile
+        self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
+
+    def frame_device(self):
+        self.fb.zero_()
+        for t in self.tiles:
+            self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb)
+        self.comm.image_reduce(self.fb, self.W * self.H, 0)
+
+    def frame_host(self):
+        self.frame_device()
+        if self.rank == 0:
+            self.fb_host.copy_(self.fb, non_blocking=True)
+        self.dev.synchronize()
+
+    def count_rays(self):
+        tot = {}
+        self.fb.zero_()
+        for t in self.tiles:
+            st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=True)
+            for k, v in st.as_dict().items():
+                tot[k] = tot.get(k, 0) + v
+        return tot

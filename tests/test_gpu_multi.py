@@ -1,0 +1,86 @@
+"""GPU tests of the multi-GPU section of the C ABI (pytest -m gpu).
+
+* nranks = 1: spraygpu_trace_tile_insitu (wavefront kernels + NCCL calls on a 1-rank communicator) must
+  reproduce the fused persistent kernel — ray counts exactly, image to float-atomic-order accuracy.
+* >= 2 GPUs visible: tests/multigpu_check.py under torchrun, 2 ranks (domain sharding + NCCL min-all-reduce
+  on the hit keys, image partition + NCCL gather), compared with the single-GPU render."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from spray_b200 import capi, scenes
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _rmse(a, b):
+    return float(np.sqrt(np.mean((a[..., :3].astype(np.float64) - b[..., :3].astype(np.float64)) ** 2)))
+
+
+@pytest.mark.parametrize("kw", [dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=2),
+                                dict(shader=1, bounces=2, pixel_samples=1, ao_samples=3)])
+def test_insitu_single_rank_equals_fused(kw):
+    import torch
+    sc = scenes.wavelets64(16)
+    if kw.get("shader", 0) == 0:
+        sc["lights"] = sc["lights"] + [(scenes.LIGHT_DIFFUSE, (0, 0, 0), (0.3, 0.3, 0.3))] if kw["bounces"] == 3 else sc["lights"]
+    mt = [(scenes.MTL_DIFFUSE, (1, 1, 1)), (scenes.MTL_MIRROR, (1, 1, 1)), (scenes.MTL_TRANSMISSION, (1.0, 1.5, 0))]
+    if kw["bounces"] == 3:
+        for i, d in enumerate(sc["domains"]):
+            d["mtl"] = mt[i % 3]
+    W = 160
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cd = scenes.camera_frame(pos + np.array([25, 15, 5], np.float32), lookat, up, 75.0, W, W)
+    cam = capi.make_camera(cd)
+    sh = capi.make_shade(lights=sc["lights"], **dict(dict(ao_samples=2), **kw), **scenes.WAVELETS64_BLINN)
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
+    tiles = scenes.image_schedule_tiles(W, W, sh.pixel_samples, 1, 0, 1 << 13)
+    fb_a = torch.zeros((W, W, 4), dtype=torch.float32, device="cuda")
+    fb_b = torch.zeros_like(fb_a)
+    ta, tb = {}, {}
+    for t in tiles:
+        for fb, tot, fn in ((fb_a, ta, lambda: dev.trace_tile(cam, sh, t, fb_a, stats=True)),
+                            (fb_b, tb, lambda: comm.trace_tile_insitu(cam, sh, t, fb_b, stats=True))):
+            for k, v in fn().as_dict().items():
+                tot[k] = tot.get(k, 0) + v
+    dev.synchronize()
+    for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"):
+        assert ta[k] == tb[k], (k, ta[k], tb[k])
+    a, b = fb_a.cpu().numpy(), fb_b.cpu().numpy()
+    assert a[..., :3].max() > 0.05
+    assert _rmse(a, b) <= 1e-6
+    comm.image_reduce(fb_b, W * W, 0)          # 1-rank collectives are no-ops
+    comm.close(); dev.close()
+
+
+def test_insitu_rejects_glass_and_host_fb():
+    sc = scenes.wavelets64(2)
+    sc["domains"][1]["mtl"] = (scenes.MTL_GLASS, (1.0, 1.5, 0))
+    dev = capi.Device(0); dev.load_scene(sc)
+    comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
+    cd = scenes.camera_frame((40, 10, 40), (10, 0, 0), (0, 1, 0), 60.0, 32, 32)
+    sh = capi.make_shade(lights=sc["lights"], bounces=2, **scenes.WAVELETS64_BLINN)
+    import torch
+    fb = torch.zeros((32, 32, 4), dtype=torch.float32, device="cuda")
+    with pytest.raises(capi.SprayGpuError):
+        comm.trace_tile_insitu(capi.make_camera(cd), sh, (0, 0, 32, 32), fb)
+    with pytest.raises(capi.SprayGpuError):
+        comm.trace_tile_insitu(capi.make_camera(cd), sh, (0, 0, 32, 32), np.zeros((32, 32, 4), np.float32))
+    comm.close(); dev.close()
+
+
+def test_two_ranks_torchrun():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs (run with gpurun --gpus 2)")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "multigpu_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    print(r.stdout[-3000:], r.stderr[-3000:])
+    assert r.returncode == 0 and "MULTIGPU_CHECK_OK" in r.stdout

@@ -7,9 +7,9 @@ cd "$(dirname "$0")/../spray_b200/csrc"
 mkdir -p ../variants
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
-  rm -f capi.o build.o trace.o
+  rm -f *.o
   make -s OUT=../variants/libspraygpu_$name.so EXTRA="$flags" > /dev/null
   grep -A2 "render_tile_kernelILb0" trace.ptxas.log | grep -E "registers|spill" | tr '\n' ' ' | sed "s/^/$name: /"; echo
 done
-rm -f capi.o build.o trace.o
+rm -f *.o
 make -s > /dev/null
