@@ -142,8 +142,9 @@ __global__ void __launch_bounds__(128)
   }
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
   warp_cull(D, live, o, d, true);
-  if (!valid) return;
-  occ[i] = (live && scene_occluded<false>(table, D, o, d, nullptr)) ? 1 : 0;
+  SceneHit hs;
+  const bool oc = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, true, hs, nullptr);
+  if (valid) occ[i] = oc ? 1 : 0;
 }
 
 // step 6: TContext::retireShadows -> HdrImage::add on the owner (slr is non-zero only there)

@@ -52,13 +52,14 @@ __global__ void __launch_bounds__(128)
                            const spraygpu_ray* __restrict__ rays, size_t n, uint64_t* __restrict__ keys,
                            float* __restrict__ uv) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const spraygpu_ray ry = rays[i];
-  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  const bool valid = i < n;
+  spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
+  if (valid) ry = rays[i];
   const RayCtx r = make_ray_ctx(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), ry.tmin);
-  Closest c; c.t = INFINITY; c.u = c.v = 0.f; c.prim = 0xFFFFFFFFu;
-  bvh8_closest(NodeLoaderG{nodes}, TriLoaderG{tris}, r, c, sx, sy, nullptr, nullptr);
-  const bool hit = c.prim != 0xFFFFFFFFu;
+  OneDomainSource src{nodes, tris, domain_id, false};
+  SceneHit c;
+  const bool hit = trace_warp<false>(src, valid, r, false, c, nullptr);
+  if (!valid) return;
   keys[i] = hit ? make_key(c.t, domain_id, c.prim) : SPRAY_KEY_MISS;
   if (uv) { uv[2 * i] = hit ? c.u : 0.f; uv[2 * i + 1] = hit ? c.v : 0.f; }
 }
@@ -67,11 +68,14 @@ __global__ void __launch_bounds__(128)
     occluded_scene_kernel(const uint4* __restrict__ nodes, const float4* __restrict__ tris,
                           const spraygpu_ray* __restrict__ rays, size_t n, uint8_t* __restrict__ occ) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const spraygpu_ray ry = rays[i];
-  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  const bool valid = i < n;
+  spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
+  if (valid) ry = rays[i];
   const RayCtx r = make_ray_ctx(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), ry.tmin);
-  occ[i] = bvh8_any(NodeLoaderG{nodes}, TriLoaderG{tris}, r, sx, sy, nullptr, nullptr) ? 1 : 0;
+  OneDomainSource src{nodes, tris, 0u, false};
+  SceneHit c;
+  const bool oc = trace_warp<false>(src, valid, r, true, c, nullptr);
+  if (valid) occ[i] = oc ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(128)
@@ -87,11 +91,9 @@ __global__ void __launch_bounds__(128)
   // a zero direction marks an inactive slot of a ray wave (terminated sample): it hits nothing
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
   warp_cull(D, live, o, d, true);
+  SceneHit h;
+  const bool hit = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, false, h, nullptr);
   if (!valid) return;
-  SceneHit h; h.t = INFINITY;
-  if (live)
-  scene_closest<false>(table, D, o, d, h, nullptr);
-  const bool hit = h.t < INFINITY;
   const uint64_t key = hit ? make_key(h.t, h.dom, h.prim) : SPRAY_KEY_MISS;
   if (merge) {
     // speculative resolution: whichever GPU / pass holds the smallest (t, domain, prim) wins
@@ -116,8 +118,9 @@ __global__ void __launch_bounds__(128)
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
   warp_cull(D, live, o, d, true);
+  SceneHit hs;
+  const bool oc = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, true, hs, nullptr);
   if (!valid) return;
-  const bool oc = live && scene_occluded<false>(table, D, o, d, nullptr);
   if (merge) { if (oc) occ[i] = 1; }
   else occ[i] = oc ? 1 : 0;
 }
@@ -332,7 +335,7 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
     const bool shadow = (dk & 1u) != 0u;
     SceneHit h; h.t = INFINITY; h.dom = 0; h.prim = 0; h.u = h.v = 0.f;
     bool found = false;
-    if (act) found = scene_trace<COUNT>(P.table, D, StridedCand{qe + QF_MASK * QCAP, QCAP}, ro, rd, shadow, h, cnt);
+    found = scene_trace_warp<COUNT>(P.table, D, StridedCand{qe + QF_MASK * QCAP, QCAP}, act, ro, rd, shadow, h, cnt);
     // payload (read before any push overwrites the popped entries)
     const vec3 Lin = mk3(__uint_as_float(qe[(QF_W + 0) * QCAP]), __uint_as_float(qe[(QF_W + 1) * QCAP]),
                          __uint_as_float(qe[(QF_W + 2) * QCAP]));
@@ -381,10 +384,9 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
         } else {
           // queue full (many light samples per hit): trace this pass in place
           warp_cull(D, emit, c.pos, wi, true);
-          if (emit) {
-            SceneHit hs;
-            if (!scene_trace<COUNT>(P.table, D, WarpCand{D.cand}, c.pos, wi, true, hs, cnt)) fb_add(P.fb, pixid, scale, Lr);
-          }
+          SceneHit hs;
+          const bool oc = scene_trace_warp<COUNT>(P.table, D, WarpCand{D.cand}, emit, c.pos, wi, true, hs, cnt);
+          if (emit && !oc) fb_add(P.fb, pixid, scale, Lr);
         }
       }
     }

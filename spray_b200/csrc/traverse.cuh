@@ -221,6 +221,128 @@ __device__ __forceinline__ bool scene_trace(const DomainEntry* __restrict__ tabl
   return !any && out.t < INFINITY;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Warp-synchronous traversal.
+//
+// ncu on the per-lane while-while walk above (profiles/r01c): 4.7 active threads per warp instruction on
+// incoherent bounce rays — once lanes split inside the nested loops (domain loop x node loop x triangle
+// loop, with early returns) they never re-merge.  Here ALL 32 lanes of the warp run ONE flat loop and meet
+// at a __syncwarp at its head; a lane's own progress is a small state machine:
+//     idle  -> pop the traversal stack, or pull its next entered domain (front to back)
+//     node  -> fetch + test one 80-byte BVH8 node        (only when it has no pending triangles)
+//     tri   -> fetch + test ONE pending triangle
+// so every pass of the loop executes the node test once and the triangle test once for the whole warp.
+// The arithmetic per (ray, node) and (ray, triangle) is unchanged, and the closest hit is the
+// lexicographic min of (t, domain, prim) — independent of visiting order — so results are bit-identical
+// to the per-lane walk.
+//
+// DomainSource: next(best_t, nodes, tris, dom) -> false when the lane has no further domain to walk.
+// ------------------------------------------------------------------------------------------------
+struct OneDomainSource {   // seam 2: a single committed scene
+  const uint4* nodes; const float4* tris; uint32_t id; bool used;
+  __device__ __forceinline__ bool next(float, const uint4*& n, const float4*& t, uint32_t& dom) {
+    if (used) return false;
+    used = true; n = nodes; t = tris; dom = id;
+    return true;
+  }
+};
+
+template <typename CandF>
+struct ListDomainSource {  // the ray's entered resident domains, front to back by (tmin, id)
+  const DomainEntry* table; const DomSmem& D; const CandF& cand; vec3 o, d;
+  uint64_t list[MAXLIST];
+  int n, k; bool more;
+  __device__ __forceinline__ ListDomainSource(const DomainEntry* table_, const DomSmem& D_, const CandF& cand_, bool act,
+                                              vec3 o_, vec3 d_)
+      : table(table_), D(D_), cand(cand_), o(o_), d(d_), n(0), k(0), more(false) {
+    if (act) n = domain_list(D, cand, o, d, false, 0ull, list, &more);
+  }
+  __device__ __forceinline__ bool next(float best_t, const uint4*& nn, const float4*& tt, uint32_t& dom) {
+    for (;;) {
+      if (k < n) {
+        const uint64_t key = list[k];
+        const float tdom = sortable_float((uint32_t)(key >> 32));
+        // front-to-back early out (an optimisation only; the slack keeps it conservative)
+        if (best_t < INFINITY && tdom > best_t * 1.0001f + 1e-4f) return false;
+        const DomainEntry* e = table + (uint32_t)key;
+        nn = e->nodes; tt = e->tris; dom = (uint32_t)key; ++k;
+        return true;
+      }
+      if (!more || n == 0) return false;
+      const uint64_t after = list[n - 1];   // more than MAXLIST entered domains: next chunk
+      n = domain_list(D, cand, o, d, true, after, list, &more);
+      k = 0;
+    }
+  }
+};
+
+// Call with ALL 32 lanes of the warp (act = this lane carries a ray).  Returns: any == false -> out.t < inf;
+// any == true -> occluded.
+template <bool COUNT, typename Source>
+__device__ __forceinline__ bool trace_warp(Source& src, const bool act, const RayCtx& r, const bool any, SceneHit& out,
+                                           uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  out.t = INFINITY; out.prim = 0xFFFFFFFFu; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
+  bool alive = act, found = false;
+  uint32_t ngx = 0, ngy = 0, tgx = 0, tgy = 0, dom = 0;
+  const uint4* nodes = nullptr;
+  const float4* tris = nullptr;
+  int sp = 0;
+  for (;;) {
+    __syncwarp();
+    if (alive && ngy <= 0x00FFFFFFu && tgy == 0u) {   // idle: pop, or pull the next domain
+      if (sp > 0) { --sp; ngx = sx[sp]; ngy = sy[sp]; }
+      else if (src.next(out.t, nodes, tris, dom)) { ngx = 0u; ngy = 0x80000000u; if (COUNT) cnt[0]++; }
+      else alive = false;
+    }
+    if (!__any_sync(0xffffffffu, alive)) break;
+    if (alive && tgy == 0u) {                          // node step (ngy has an inner child here)
+      const uint32_t imask = ngy & 0xffu;
+      const int bit = 31 - __clz((int)ngy);
+      ngy &= ~(1u << bit);
+      if (ngy > 0x00FFFFFFu && sp < SPRAY_STACK_SIZE) { sx[sp] = ngx; sy[sp] = ngy; ++sp; }
+      const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
+      const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+      u4 q0, q1, q2, q3, q4;
+      NodeLoaderG{nodes}(ngx + rel, q0, q1, q2, q3, q4);
+      if (COUNT) cnt[1]++;
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, out.t);
+      ngx = q1.x; tgx = q1.y;
+      ngy = (hm & 0xFF000000u) | (q0.w >> 24);
+      tgy = hm & 0x00FFFFFFu;
+    }
+    __syncwarp();
+    if (alive && tgy) {                                // triangle step: ONE pending triangle
+      const int ti = __ffs((int)tgy) - 1;
+      tgy &= tgy - 1;
+      vec3 v0, e1, e2; uint32_t prim;
+      TriLoaderG{tris}(tgx + (uint32_t)ti, v0, e1, e2, prim);
+      if (COUNT) cnt[2]++;
+      float T, U, V, ad;
+      if (tri_test_raw(r.o, r.d, v0, e1, e2, r.tnear, &T, &U, &V, &ad)) {
+        if (any) { found = true; alive = false; }
+        else {
+          const float t = div_rn(T, ad);
+          if (t < out.t || (t == out.t && (dom < out.dom || (dom == out.dom && prim < out.prim)))) {
+            out.t = t; out.u = div_rn(U, ad); out.v = div_rn(V, ad); out.prim = prim; out.dom = dom;
+          }
+        }
+      }
+    }
+  }
+  return any ? found : (out.t < INFINITY);
+}
+
+// closest / any hit over the ray's entered resident domains; all 32 lanes call.
+template <bool COUNT, typename CandF>
+__device__ __forceinline__ bool scene_trace_warp(const DomainEntry* __restrict__ table, const DomSmem& D,
+                                                 const CandF& cand, const bool act, vec3 o, vec3 d, const bool any,
+                                                 SceneHit& out, uint32_t* cnt) {
+  const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
+  ListDomainSource<CandF> src(table, D, cand, act, o, d);
+  return trace_warp<COUNT>(src, act, r, any, out, cnt);
+}
+
 template <bool COUNT>
 __device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
                                               SceneHit& out, uint32_t* cnt) {
