@@ -86,6 +86,12 @@ class GpuTracer {
   // one frame: SprayRenderer clears the image, then calls trace(), then image.composite() if clustered
   void trace() {
     const spraygpu_camera cam = camera_->toGpu();
+    // The reference loads domains on demand inside PContext::isectPrims (ooc_pcontext.h:145-154); the fused
+    // kernel wants them resident before the tile starts.  With an LRU cache that holds every domain this is
+    // the first frame's one-time load (InfiniteCache scenes were warmed in Scene::init).
+    if (!insitu_)
+      for (std::size_t id = 0; id < scene_->getNumDomains(); ++id)
+        if (!scene_->isResident((int)id)) scene_->load((int)id);
     SPRAY_CHECK(cudaMemsetAsync(d_fb_, 0, npixels_ * 16, 0) == cudaSuccess, "");  // image_.clear() on the device
     for (const Tile& t : tile_list_.tiles()) {
       const spraygpu_tile gt = {t.x, t.y, t.w, t.h};

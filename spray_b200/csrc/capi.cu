@@ -1,7 +1,11 @@
 // capi.cu — the C ABI of libspraygpu (include/spray_gpu.h).  Thin: argument checks, host/device pointer
 // staging, and launches.  There is NO CPU fallback anywhere: every entry point that computes needs a
 // CUDA device and fails with SPRAYGPU_ERR_CUDA otherwise.
+#include <limits.h>
+#include <math.h>
 #include <stdarg.h>
+
+#include <algorithm>
 
 #include <mutex>
 
@@ -78,9 +82,83 @@ struct Stager {
   }
 };
 
+// ---- top-level BVH4 over the resident domains' world boxes (replaces WbvhEmbree::build,
+// src/render/wbvh_embree.cc:58-111, an Embree user-geometry BVH over the same boxes) ----
+static void tlas_bounds(const std::vector<DomainEntry>& doms, const int* ids, int n, float lo[3], float hi[3]) {
+  for (int a = 0; a < 3; ++a) { lo[a] = INFINITY; hi[a] = -INFINITY; }
+  for (int i = 0; i < n; ++i)
+    for (int a = 0; a < 3; ++a) {
+      // boxes may be inverted by a mirroring transform (scene_loader.cc:352-357 keeps min/max corners as given)
+      const float b0 = doms[ids[i]].box[a], b1 = doms[ids[i]].box[3 + a];
+      lo[a] = fminf(lo[a], fminf(b0, b1)); hi[a] = fmaxf(hi[a], fmaxf(b0, b1));
+    }
+}
+static void tlas_split(const std::vector<DomainEntry>& doms, int* ids, int n, int* nleft) {
+  // median split along the axis with the widest centroid spread
+  float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = 0; i < n; ++i)
+    for (int a = 0; a < 3; ++a) {
+      const float c = 0.5f * (doms[ids[i]].box[a] + doms[ids[i]].box[3 + a]);
+      clo[a] = fminf(clo[a], c); chi[a] = fmaxf(chi[a], c);
+    }
+  int ax = 0;
+  if (chi[1] - clo[1] > chi[ax] - clo[ax]) ax = 1;
+  if (chi[2] - clo[2] > chi[ax] - clo[ax]) ax = 2;
+  std::stable_sort(ids, ids + n, [&](int x, int y) {
+    return doms[x].box[ax] + doms[x].box[3 + ax] < doms[y].box[ax] + doms[y].box[3 + ax];
+  });
+  *nleft = n / 2;
+}
+static int tlas_build(Device* dev, int* ids, int n) {
+  const int me = (int)dev->h_tlas.size();
+  dev->h_tlas.push_back(TlasNode());
+  // up to four groups: halves of halves
+  int start[4], cnt[4], ng = 0;
+  if (n <= 4) {
+    for (int i = 0; i < n; ++i) { start[ng] = i; cnt[ng] = 1; ++ng; }
+  } else {
+    int nl; tlas_split(dev->h_domains, ids, n, &nl);
+    int half[2][2] = {{0, nl}, {nl, n - nl}};
+    for (int h = 0; h < 2; ++h) {
+      if (half[h][1] >= 2) {
+        int q; tlas_split(dev->h_domains, ids + half[h][0], half[h][1], &q);
+        start[ng] = half[h][0]; cnt[ng] = q; ++ng;
+        start[ng] = half[h][0] + q; cnt[ng] = half[h][1] - q; ++ng;
+      } else {
+        start[ng] = half[h][0]; cnt[ng] = half[h][1]; ++ng;
+      }
+    }
+  }
+  TlasNode node;
+  for (int c = 0; c < 4; ++c) {
+    for (int a = 0; a < 3; ++a) { node.lo[a][c] = INFINITY; node.hi[a][c] = -INFINITY; }
+    node.child[c] = INT32_MIN;
+  }
+  for (int g = 0; g < ng; ++g) {
+    float lo[3], hi[3];
+    tlas_bounds(dev->h_domains, ids + start[g], cnt[g], lo, hi);
+    for (int a = 0; a < 3; ++a) { node.lo[a][g] = lo[a]; node.hi[a][g] = hi[a]; }
+    node.child[g] = cnt[g] == 1 ? ~ids[start[g]] : tlas_build(dev, ids + start[g], cnt[g]);
+  }
+  dev->h_tlas[me] = node;
+  return me;
+}
+
 int upload_domain_table(Device* dev) {
   if (!dev->table_dirty) return SPRAYGPU_OK;
   SG_CHECK(dev->ndomains > 0, SPRAYGPU_ERR_STATE, "no domain table: call spraygpu_domains_set first");
+  {
+    std::vector<int> ids;
+    for (int i = 0; i < dev->ndomains; ++i)
+      if (dev->h_domains[i].resident) ids.push_back(i);
+    dev->h_tlas.clear();
+    if (!ids.empty()) tlas_build(dev, ids.data(), (int)ids.size());
+    dev->tlas_n = (int)dev->h_tlas.size();
+    SG_CHECK(dev->tlas_n <= SPRAY_TLAS_MAX_NODES, SPRAYGPU_ERR_LIMIT, "top-level BVH: %d nodes", dev->tlas_n);
+    if (dev->tlas_n)
+      SG_CUDA(cudaMemcpyAsync(dev->d_tlas, dev->h_tlas.data(), sizeof(TlasNode) * dev->tlas_n, cudaMemcpyHostToDevice,
+                              dev->stream));
+  }
   SG_CUDA(cudaMemcpyAsync(dev->d_domains, dev->h_domains.data(), sizeof(DomainEntry) * dev->ndomains,
                           cudaMemcpyHostToDevice, dev->stream));
   // h_domains is pageable: the runtime stages it before returning, so later host edits are safe
@@ -119,6 +197,7 @@ int spraygpu_device_create(int cuda_device, spraygpu_device* out) {
   SG_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
   d->sm_count = prop.multiProcessorCount;
   SG_CUDA(cudaMalloc(&d->d_domains, sizeof(DomainEntry) * SPRAYGPU_MAX_DOMAINS));
+  SG_CUDA(cudaMalloc(&d->d_tlas, sizeof(TlasNode) * SPRAY_TLAS_MAX_NODES));
   SG_CUDA(cudaMalloc(&d->d_counters, sizeof(unsigned long long) * 8));
   SG_CUDA(cudaMemset(d->d_counters, 0, sizeof(unsigned long long) * 8));
   SG_CUDA(cudaMallocHost(&d->pinned, 4096));
@@ -138,6 +217,7 @@ int spraygpu_device_destroy(spraygpu_device dev) {
   if (d->wave.ptr) cudaFree(d->wave.ptr);
   if (d->pinned) cudaFreeHost(d->pinned);
   cudaFree(d->d_domains);
+  cudaFree(d->d_tlas);
   cudaFree(d->d_counters);
   delete d;
   return SPRAYGPU_OK;

@@ -124,11 +124,12 @@ __global__ void __launch_bounds__(128)
 
 // step 5: shadow ray = (hit position from the reduced key, exchanged direction), any hit over the local domains
 __global__ void __launch_bounds__(128)
-    insitu_shadow_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays,
+    insitu_shadow_kernel(const DomainEntry* __restrict__ table, int nd, const TlasNode* __restrict__ tlas, int tlas_n,
+                         const spraygpu_ray* __restrict__ rays,
                          const uint64_t* __restrict__ keys, const float* __restrict__ sdir, size_t n,
                          uint8_t* __restrict__ occ) {
   extern __shared__ float smem[];
-  const DomSmem D = load_domain_smem(table, nd, smem);
+  const DomSmem D = load_domain_smem(table, nd, tlas, tlas_n, smem);
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   vec3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
@@ -141,9 +142,8 @@ __global__ void __launch_bounds__(128)
     }
   }
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
-  warp_cull(D, live, o, d, true);
   SceneHit hs;
-  const bool oc = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, true, hs, nullptr);
+  const bool oc = scene_trace_warp<false>(table, D, live, o, d, true, hs, nullptr);
   if (valid) occ[i] = oc ? 1 : 0;
 }
 
@@ -241,7 +241,7 @@ extern "C" int spraygpu_trace_tile_insitu(spraygpu_device dev_h, spraygpu_comm c
     if (rc) return rc;
     insitu_init_wave_kernel<<<grid_for(3 * n, 256), 256, 0, st>>>(w, n);
     dev->launches++;
-    const size_t dsmem = dom_smem_bytes(dev->ndomains, 4);
+    const size_t dsmem = dom_smem_bytes(dev->ndomains, dev->tlas_n, 0);
     for (int depth = 0; depth < shade->bounces; ++depth) {
       P.depth = depth;
       rc = launch_intersect_domains(dev, rays, n, keys, nullptr, 0);                       // 1
@@ -255,7 +255,7 @@ extern "C" int spraygpu_trace_tile_insitu(spraygpu_device dev_h, spraygpu_comm c
         if (npasses == 0) break;
         rc = comm_allreduce_bits_sum(comm, (uint32_t*)sdir, 3 * n);                        // 4
         if (rc) return rc;
-        insitu_shadow_kernel<<<grid_for(n, 128), 128, dsmem, st>>>(dev->d_domains, dev->ndomains, rays, keys, sdir, n, occ);  // 5
+        insitu_shadow_kernel<<<grid_for(n, 128), 128, dsmem, st>>>(dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, keys, sdir, n, occ);  // 5
         dev->launches++;
         rc = comm_allreduce_u8_max(comm, occ, n);
         if (rc) return rc;

@@ -47,6 +47,16 @@ struct DomainEntry {
 };
 static_assert(sizeof(DomainEntry) == 96, "DomainEntry layout");
 
+// Top-level BVH4 over the world boxes of the RESIDENT domains (rebuilt on the host whenever the table
+// changes; <= 512 leaves).  Plain float boxes, SoA per axis so a node is 7 x 16-byte shared-memory loads.
+// child >= 0: inner node index; child < 0: ~domain id; unused slots carry an inverted box.
+struct TlasNode {
+  float lo[3][4], hi[3][4];
+  int32_t child[4];
+};
+static_assert(sizeof(TlasNode) == 112, "TlasNode layout");
+#define SPRAY_TLAS_MAX_NODES 384
+
 struct Scratch {
   void* ptr = nullptr;
   size_t bytes = 0;
@@ -70,6 +80,9 @@ struct Device {
   std::vector<Scene*> bound;
   DomainEntry* d_domains = nullptr;
   bool table_dirty = true;
+  std::vector<TlasNode> h_tlas;    // built in upload_domain_table
+  TlasNode* d_tlas = nullptr;
+  int tlas_n = 0;                  // 0: no resident domain
   unsigned long long* d_counters = nullptr;  // [0] work counter, [1..] stats
   uint64_t launches = 0;           // kernels launched by this library (bench "gpu_launches")
 };

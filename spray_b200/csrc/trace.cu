@@ -8,6 +8,8 @@
 //                           (64-bit atomicMin merge for multi-GPU / out-of-core accumulation)
 //   intersect_scene_kernel / occluded_scene_kernel       batched single-domain queries (seam 2)
 //   domain_lists_kernel, hit_attributes_kernel, eye_rays_kernel   parity surfaces for a6 / a3 / a9
+#include <stdlib.h>
+
 #include "internal.cuh"
 #include "traverse.cuh"
 #include "shade.cuh"
@@ -19,10 +21,10 @@ namespace spraygpu {
 // inactive participants.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-    domain_lists_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays, size_t n,
-                        int cap, int32_t* __restrict__ counts, int32_t* __restrict__ ids, float* __restrict__ tmins) {
+    domain_lists_kernel(const DomainEntry* __restrict__ table, int nd, const TlasNode* __restrict__ tlas, int tlas_n,
+                        const spraygpu_ray* __restrict__ rays, size_t n, int cap, int32_t* __restrict__ counts, int32_t* __restrict__ ids, float* __restrict__ tmins) {
   extern __shared__ float smem[];
-  const DomSmem D = load_domain_smem(table, nd, smem);
+  const DomSmem D = load_domain_smem(table, nd, tlas, tlas_n, smem);
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
@@ -79,10 +81,10 @@ __global__ void __launch_bounds__(128)
 }
 
 __global__ void __launch_bounds__(128)
-    intersect_domains_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays,
-                             size_t n, uint64_t* __restrict__ keys, float* __restrict__ uv, int merge) {
+    intersect_domains_kernel(const DomainEntry* __restrict__ table, int nd, const TlasNode* __restrict__ tlas, int tlas_n,
+                             const spraygpu_ray* __restrict__ rays, size_t n, uint64_t* __restrict__ keys, float* __restrict__ uv, int merge) {
   extern __shared__ float smem[];
-  const DomSmem D = load_domain_smem(table, nd, smem);
+  const DomSmem D = load_domain_smem(table, nd, tlas, tlas_n, smem);
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
@@ -90,9 +92,8 @@ __global__ void __launch_bounds__(128)
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   // a zero direction marks an inactive slot of a ray wave (terminated sample): it hits nothing
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
-  warp_cull(D, live, o, d, true);
   SceneHit h;
-  const bool hit = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, false, h, nullptr);
+  const bool hit = scene_trace_warp<false>(table, D, live, o, d, false, h, nullptr);
   if (!valid) return;
   const uint64_t key = hit ? make_key(h.t, h.dom, h.prim) : SPRAY_KEY_MISS;
   if (merge) {
@@ -106,10 +107,10 @@ __global__ void __launch_bounds__(128)
 }
 
 __global__ void __launch_bounds__(128)
-    occluded_domains_kernel(const DomainEntry* __restrict__ table, int nd, const spraygpu_ray* __restrict__ rays,
-                            size_t n, uint8_t* __restrict__ occ, int merge) {
+    occluded_domains_kernel(const DomainEntry* __restrict__ table, int nd, const TlasNode* __restrict__ tlas, int tlas_n,
+                            const spraygpu_ray* __restrict__ rays, size_t n, uint8_t* __restrict__ occ, int merge) {
   extern __shared__ float smem[];
-  const DomSmem D = load_domain_smem(table, nd, smem);
+  const DomSmem D = load_domain_smem(table, nd, tlas, tlas_n, smem);
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   // merge: rays already occluded elsewhere (or flagged 1 by the caller as "not a ray") are skipped
   const bool valid = i < n && !(merge && occ[i]);
@@ -117,9 +118,8 @@ __global__ void __launch_bounds__(128)
   if (valid) ry = rays[i];
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
-  warp_cull(D, live, o, d, true);
   SceneHit hs;
-  const bool oc = scene_trace_warp<false>(table, D, WarpCand{D.cand}, live, o, d, true, hs, nullptr);
+  const bool oc = scene_trace_warp<false>(table, D, live, o, d, true, hs, nullptr);
   if (!valid) return;
   if (merge) { if (oc) occ[i] = 1; }
   else occ[i] = oc ? 1 : 0;
@@ -197,6 +197,8 @@ __global__ void __launch_bounds__(256)
 struct RenderParams {
   const DomainEntry* table;
   int nd;
+  const TlasNode* tlas;
+  int tlas_n;
   CameraDev cam;
   spraygpu_tile tile;
   spraygpu_shade shade;
@@ -218,7 +220,7 @@ struct Pending { vec3 o, d, w; int depth; };
 // lanes traverse (ballot / prefix-sum compaction of the speculative ray stream).  Rays that enter no
 // domain never occupy a lane.
 // fields (QCAP entries each): 0-2 origin, 3-5 direction, 6-8 throughput (radiance) or radiance to add
-// (shadow), 9 pixid, 10 samid, 11 depth << 1 | kind (0 radiance, 1 shadow), 12.. exact domain mask words
+// (shadow), 9 pixid, 10 samid, 11 depth << 1 | kind (0 radiance, 1 shadow)
 // ------------------------------------------------------------------------------------------------
 #define QF_O 0
 #define QF_D 3
@@ -229,32 +231,21 @@ struct Pending { vec3 o, d, w; int depth; };
 #define QF_MASK 12
 
 struct RayQueue {
-  uint32_t* q;        // this warp's fields, field f entry s at q[f * cap + s]
-  uint32_t* scratch;  // this warp's provisional mask words, word w of lane l at scratch[w * 32 + l]
-  int cap, nwords;
+  uint32_t* q;   // this warp's fields, field f entry s at q[f * cap + s]
+  int cap;
 };
 
-__host__ __device__ inline size_t queue_words_per_warp(int nd, int cap) {
-  const int nw = (nd + 31) >> 5;
-  return (size_t)(QF_MASK + nw) * cap + (size_t)nw * 32;
-}
+__host__ __device__ inline size_t queue_words_per_warp(int cap) { return (size_t)QF_MASK * cap; }
 
-// Warp-cooperative push.  Returns true for lanes whose ray is live (emit) but enters NO resident domain:
-// such a ray is resolved on the spot (radiance: miss, shadow: unoccluded).  `count` is warp-uniform.
+// Warp-cooperative push (ballot / prefix-sum compaction).  A ray that misses every top-level box is not
+// queued: the function returns true for those lanes and the caller resolves the ray on the spot
+// (radiance: miss, shadow: unoccluded).  `count` is warp-uniform.
 __device__ __forceinline__ bool queue_push(const RayQueue& Q, const DomSmem& D, int& count, bool emit, vec3 o, vec3 d,
                                            vec3 w, uint32_t pixid, uint32_t samid, uint32_t depthkind) {
   const int lane = threadIdx.x & 31;
-  warp_cull(D, emit, o, d, true);
-  bool nonempty = false;
-  if (emit) {
-    for (int k = 0; k < Q.nwords; ++k) {
-      const uint32_t m = exact_mask_word(D, k, D.cand[k], o, d);
-      Q.scratch[k * 32 + lane] = m;
-      nonempty = nonempty || (m != 0u);
-    }
-  }
-  const bool go = emit && nonempty;
+  const bool go = emit && tlas_any(D, make_ray_ctx(o, d, SPRAY_RAY_EPS));
   const uint32_t b = __ballot_sync(0xffffffffu, go);
+  if (count + __popc(b) > Q.cap) __trap();   // the queue bound is an invariant of the callers
   if (go) {
     const int s = count + __popc(b & ((1u << lane) - 1u));
     uint32_t* q = Q.q + s;
@@ -263,11 +254,10 @@ __device__ __forceinline__ bool queue_push(const RayQueue& Q, const DomSmem& D, 
     q[(QF_D + 0) * c] = __float_as_uint(d.x); q[(QF_D + 1) * c] = __float_as_uint(d.y); q[(QF_D + 2) * c] = __float_as_uint(d.z);
     q[(QF_W + 0) * c] = __float_as_uint(w.x); q[(QF_W + 1) * c] = __float_as_uint(w.y); q[(QF_W + 2) * c] = __float_as_uint(w.z);
     q[QF_PIX * c] = pixid; q[QF_SAM * c] = samid; q[QF_DK * c] = depthkind;
-    for (int k = 0; k < Q.nwords; ++k) q[(QF_MASK + k) * c] = Q.scratch[k * 32 + lane];
   }
   count += __popc(b);
   __syncwarp();
-  return emit && !nonempty;
+  return emit && !go;
 }
 
 // GENERAL == false is the lean variant for the common configuration (PT shader, ONE point light, every
@@ -278,15 +268,14 @@ template <bool GENERAL> struct QueueCap { static constexpr int value = GENERAL ?
 template <bool COUNT, bool GENERAL>
 __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
   extern __shared__ float smem[];
-  const DomSmem D = load_domain_smem(P.table, P.nd, smem);
+  const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
   constexpr int QCAP = QueueCap<GENERAL>::value;
   const int lane = threadIdx.x & 31;
   RayQueue Q;
-  Q.cap = QCAP; Q.nwords = (P.nd + 31) >> 5;
+  Q.cap = QCAP;
   {
-    uint32_t* qbase = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, 8) + 15) & ~(size_t)15));
-    Q.q = qbase + (size_t)(threadIdx.x >> 5) * queue_words_per_warp(P.nd, QCAP);
-    Q.scratch = Q.q + (size_t)(QF_MASK + Q.nwords) * QCAP;
+    uint32_t* qbase = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, P.tlas_n, 0) + 15) & ~(size_t)15));
+    Q.q = qbase + (size_t)(threadIdx.x >> 5) * queue_words_per_warp(QCAP);
   }
   const int spp = P.shade.pixel_samples;
   const float scale = (float)(1.0 / (double)spp);
@@ -335,7 +324,7 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
     const bool shadow = (dk & 1u) != 0u;
     SceneHit h; h.t = INFINITY; h.dom = 0; h.prim = 0; h.u = h.v = 0.f;
     bool found = false;
-    found = scene_trace_warp<COUNT>(P.table, D, StridedCand{qe + QF_MASK * QCAP, QCAP}, act, ro, rd, shadow, h, cnt);
+    found = scene_trace_warp<COUNT>(P.table, D, act, ro, rd, shadow, h, cnt);
     // payload (read before any push overwrites the popped entries)
     const vec3 Lin = mk3(__uint_as_float(qe[(QF_W + 0) * QCAP]), __uint_as_float(qe[(QF_W + 1) * QCAP]),
                          __uint_as_float(qe[(QF_W + 2) * QCAP]));
@@ -383,9 +372,8 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
           if (queue_push(Q, D, count, emit, c.pos, wi, Lr, pixid, samid, 1u)) fb_add(P.fb, pixid, scale, Lr);
         } else {
           // queue full (many light samples per hit): trace this pass in place
-          warp_cull(D, emit, c.pos, wi, true);
           SceneHit hs;
-          const bool oc = scene_trace_warp<COUNT>(P.table, D, WarpCand{D.cand}, emit, c.pos, wi, true, hs, cnt);
+          const bool oc = scene_trace_warp<COUNT>(P.table, D, emit, c.pos, wi, true, hs, cnt);
           if (emit && !oc) fb_add(P.fb, pixid, scale, Lr);
         }
       }
@@ -393,6 +381,167 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
   }
 
   // statistics: warp-reduce, one atomic per warp per counter
+  uint32_t vals[7] = {n_eye, n_rad, n_shadow, cnt[0], cnt[1], cnt[2], n_hit};
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    unsigned long long v = vals[k];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0 && v) atomicAdd(P.counters + 1 + k, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// The STREAMING variant of the fused kernel (lean configuration: PT shader, one point light, diffuse
+// domains — the reference's example scenes).
+//
+// render_tile_kernel above traces rays in batches of 32: every lane waits for the slowest ray of its batch
+// (ncu r01e: 8 of 32 lanes active in the node test on incoherent bounce rays).  Here a lane whose ray is
+// finished does not wait: as soon as SPRAY_FETCH_THRESH lanes are idle the warp runs ONE service pass —
+// the idle lanes shade their finished rays, push the bounce and shadow rays (ballot / prefix-sum
+// compaction into the warp's shared-memory queue), the queue is topped up with eye rays, and the idle
+// lanes pop new rays — while the other lanes keep their traversal state in registers.  The traversal
+// loop itself is the same LaneTrav state machine (one node step + one triangle step per pass).
+//
+// Queue bound (QCAP = 128): a ray lineage owns at most one radiance ray; shadow rays are pushed last and
+// at least as many rays are popped right after (n_idle >= shadows pushed), so shadow rays never pile up;
+// eye rays are only added when fewer than 32 rays are queued.  => queued <= 95 radiance + 32 transient.
+// ------------------------------------------------------------------------------------------------
+#ifndef SPRAY_FETCH_THRESH
+#define SPRAY_FETCH_THRESH 12
+#endif
+#define STREAM_QCAP 128
+// per-lane in-flight record (shared memory, field f of lane l at base[f * 32 + l]): the popped ray's payload
+#define IF_W 0
+#define IF_PIX 3
+#define IF_SAM 4
+#define IF_DK 5
+#define IF_WORDS 6
+
+__host__ __device__ inline size_t stream_words_per_warp() { return queue_words_per_warp(STREAM_QCAP) + (size_t)IF_WORDS * 32; }
+
+template <bool COUNT>
+__global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_stream_kernel(RenderParams P) {
+  extern __shared__ float smem[];
+  const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
+  const int lane = threadIdx.x & 31;
+  RayQueue Q;
+  Q.cap = STREAM_QCAP;
+  uint32_t* inflight;
+  {
+    uint32_t* qbase = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, P.tlas_n, 0) + 15) & ~(size_t)15));
+    Q.q = qbase + (size_t)(threadIdx.x >> 5) * stream_words_per_warp();
+    inflight = Q.q + queue_words_per_warp(STREAM_QCAP) + lane;
+  }
+  const int spp = P.shade.pixel_samples;
+  const float scale = (float)(1.0 / (double)spp);
+  uint32_t cnt[3] = {0, 0, 0};
+  uint32_t n_eye = 0, n_rad = 0, n_shadow = 0, n_hit = 0;
+  int count = 0;      // rays in this warp's queue (warp-uniform)
+  bool more = true;   // the tile still has unclaimed sample slots (warp-uniform)
+
+  LaneTrav T;
+  T.begin(false);
+  TlasSource src(P.table, D);
+  RayCtx r = make_ray_ctx(mk3(0, 0, 0), mk3(0, 0, 1), SPRAY_RAY_EPS);
+  bool busy = false;  // this lane holds a ray (being traced)
+  bool done = false;  // this lane holds a finished ray waiting for the service pass
+  bool any = false;   // the held ray is a shadow ray
+
+  for (;;) {
+    __syncwarp();
+    if (busy && !T.alive) { busy = false; done = true; }
+    const uint32_t am = __ballot_sync(0xffffffffu, T.alive);
+    const int n_idle = 32 - __popc(am);
+    if (n_idle >= SPRAY_FETCH_THRESH || am == 0u) {
+      const bool work = count > 0 || more || __any_sync(0xffffffffu, done);
+      if (work) {
+        // ================= service pass =================
+        const vec3 Lin = mk3(__uint_as_float(inflight[(IF_W + 0) * 32]), __uint_as_float(inflight[(IF_W + 1) * 32]),
+                             __uint_as_float(inflight[(IF_W + 2) * 32]));
+        const uint32_t pixid = inflight[IF_PIX * 32], samid = inflight[IF_SAM * 32], dk = inflight[IF_DK * 32];
+        // ---- A. retire shadow rays, shade radiance hits (ooc_shader_pt.h:94-227)
+        if (done && any && !T.found) fb_add(P.fb, pixid, scale, Lin);
+        const bool hit = done && !any && T.out.t < INFINITY;
+        const int next_depth = (int)(dk >> 1) + 1;
+        HitCtx c;
+        c.pos = r.o; c.kd = mk3(0, 0, 0); c.nff = mk3(0, 0, 1); c.wo = gneg(r.d);
+        c.cos_theta_i = 0.f; c.entering = false; c.mtl = SPRAYGPU_MTL_DIFFUSE; c.eta0 = c.eta1 = 1.f;
+        bool em1 = false, em2 = false, emit = false;
+        vec3 d1 = mk3(0, 0, 1), w1 = mk3(0, 0, 0), d2 = mk3(0, 0, 1), w2 = mk3(0, 0, 0), wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
+        if (hit) {
+          ++n_hit;
+          make_hit_ctx<false>(P.table + T.out.dom, r.o, r.d, T.out.t, T.out.u, T.out.v, T.out.prim, c);
+          if (next_depth < P.shade.bounces) shade_secondary<false>(c, Lin, samid, next_depth, &em1, &d1, &w1, &em2, &d2, &w2);
+          uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
+          int l = 0, k = 0; bool more_lights = true;
+          emit = shade_light_pass<false>(P.shade, true, 1, c, Lin, pixid, l, k, ls, &wi, &Lr, &more_lights);
+        }
+        done = false;
+        // ---- B. push: bounce rays first, shadow rays on top (popped first)
+        if (em1) ++n_rad;
+        if (__any_sync(0xffffffffu, em1))
+          queue_push(Q, D, count, em1, c.pos, d1, w1, pixid, samid, (uint32_t)next_depth << 1);
+        if (emit) ++n_shadow;
+        if (__any_sync(0xffffffffu, emit)) {
+          // a shadow ray that enters no resident domain is unoccluded
+          if (queue_push(Q, D, count, emit, c.pos, wi, Lr, pixid, samid, 1u)) fb_add(P.fb, pixid, scale, Lr);
+        }
+        // ---- C. top up with one 8x4 pixel block of eye rays (ooc_tracer.inl:84-172)
+        if (count < 32 && more) {
+          unsigned long long base = 0;
+          if (lane == 0) base = atomicAdd(P.counters, 32ull);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (base >= P.total_slots) more = false;
+          else {
+            const uint32_t slot = (uint32_t)base + lane;
+            const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
+            const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
+            const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
+            const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
+            const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
+            uint32_t esam = 0, epix = 0;
+            vec3 dir = mk3(0.f, 0.f, 1.f);
+            if (has_ray) {
+              eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &esam, &epix, &dir);
+              ++n_eye; ++n_rad;
+            }
+            queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), epix,
+                       esam, 0u);
+          }
+        }
+        // ---- D. idle lanes pop new rays (top of the queue first)
+        {
+          const bool idle = !T.alive;
+          const uint32_t im = __ballot_sync(0xffffffffu, idle);
+          const int nf = min(__popc(im), count);
+          const int rnk = __popc(im & ((1u << lane) - 1u));
+          const bool take = idle && rnk < nf;
+          if (take) {
+            const uint32_t* qe = Q.q + (count - 1 - rnk);
+            const vec3 ro = mk3(__uint_as_float(qe[(QF_O + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_O + 1) * STREAM_QCAP]),
+                                __uint_as_float(qe[(QF_O + 2) * STREAM_QCAP]));
+            const vec3 rd = mk3(__uint_as_float(qe[(QF_D + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_D + 1) * STREAM_QCAP]),
+                                __uint_as_float(qe[(QF_D + 2) * STREAM_QCAP]));
+#pragma unroll
+            for (int f = 0; f < 6; ++f) inflight[(IF_W + f) * 32] = qe[(QF_W + f) * STREAM_QCAP];
+            any = (qe[QF_DK * STREAM_QCAP] & 1u) != 0u;
+            r = make_ray_ctx(ro, rd, SPRAY_RAY_EPS);
+            busy = true;
+          }
+          if (take) {
+            src.reset(true);             // the new ray starts at the top-level root (other lanes keep their walk)
+            T.begin(true);
+          }
+          count -= nf;
+        }
+        continue;
+      }
+      if (am == 0u) break;   // nothing in flight, nothing queued, tile exhausted
+    }
+    T.pass<COUNT>(src, r, any, cnt);
+  }
+
   uint32_t vals[7] = {n_eye, n_rad, n_shadow, cnt[0], cnt[1], cnt[2], n_hit};
 #pragma unroll
   for (int k = 0; k < 7; ++k) {
@@ -418,8 +567,8 @@ static CameraDev to_camdev(const spraygpu_camera* c) {
 int launch_domain_lists(Device* dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts, int32_t* ids,
                         float* tmins) {
   if (!n) return SPRAYGPU_OK;
-  domain_lists_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
-      dev->d_domains, dev->ndomains, rays, n, cap, counts, ids, tmins);
+  domain_lists_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 4), dev->stream>>>(
+      dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, cap, counts, ids, tmins);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
@@ -441,16 +590,16 @@ int launch_occluded_scene(Scene* sc, const spraygpu_ray* rays, size_t n, uint8_t
 }
 int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint64_t* keys, float* uv, int merge) {
   if (!n) return SPRAYGPU_OK;
-  intersect_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
-      dev->d_domains, dev->ndomains, rays, n, keys, uv, merge);
+  intersect_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0), dev->stream>>>(
+      dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, keys, uv, merge);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
 }
 int launch_occluded_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge) {
   if (!n) return SPRAYGPU_OK;
-  occluded_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, 4), dev->stream>>>(
-      dev->d_domains, dev->ndomains, rays, n, occ, merge);
+  occluded_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0), dev->stream>>>(
+      dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, occ, merge);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
@@ -475,7 +624,7 @@ int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile,
 int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                        float* fb, bool counted) {
   RenderParams P;
-  P.table = dev->d_domains; P.nd = dev->ndomains;
+  P.table = dev->d_domains; P.nd = dev->ndomains; P.tlas = dev->d_tlas; P.tlas_n = dev->tlas_n;
   P.cam = to_camdev(cam); P.tile = tile; P.shade = *shade; P.fb = fb;
   P.counters = dev->d_counters;
   P.blocks_per_row = (uint32_t)((tile.w + 7) / 8);
@@ -488,12 +637,17 @@ int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_s
   bool general = shade->shader != SPRAYGPU_SHADER_PT || shade->nlights != 1;
   for (int i = 0; i < shade->nlights; ++i) general = general || shade->lights[i].type != SPRAYGPU_LIGHT_POINT;
   for (int i = 0; i < dev->ndomains; ++i) general = general || dev->h_domains[i].mtl_type != SPRAYGPU_MTL_DIFFUSE;
+  // The streaming variant is opt-in (SPRAYGPU_STREAM=1): on B200 it lost to the batch-of-32 kernel on both
+  // measured workloads (C2 2.7-3.2 vs 4.8 Grays/s, C3 0.76-0.81 vs 0.85 Grays/s).
+  static const bool want_stream = getenv("SPRAYGPU_STREAM") && atoi(getenv("SPRAYGPU_STREAM")) != 0;
+  const bool stream = !general && want_stream;
   void (*kern)(RenderParams) =
-      counted ? (general ? render_tile_kernel<true, true> : render_tile_kernel<true, false>)
-              : (general ? render_tile_kernel<false, true> : render_tile_kernel<false, false>);
+      stream ? (counted ? render_tile_stream_kernel<true> : render_tile_stream_kernel<false>)
+             : counted ? (general ? render_tile_kernel<true, true> : render_tile_kernel<true, false>)
+                       : (general ? render_tile_kernel<false, true> : render_tile_kernel<false, false>);
   const int qcap = general ? QueueCap<true>::value : QueueCap<false>::value;
-  const size_t smem = ((dom_smem_bytes(dev->ndomains, 8) + 15) & ~(size_t)15) +
-                      8 * queue_words_per_warp(dev->ndomains, qcap) * sizeof(uint32_t);
+  const size_t smem = ((dom_smem_bytes(dev->ndomains, dev->tlas_n, 0) + 15) & ~(size_t)15) +
+                      8 * (stream ? stream_words_per_warp() : queue_words_per_warp(qcap)) * sizeof(uint32_t);
   SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));

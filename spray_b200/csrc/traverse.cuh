@@ -46,18 +46,24 @@ struct TriLoaderG {
 struct DomSmem {
   const float* boxes;       // nd x 6
   const uint8_t* resident;  // nd
-  uint32_t* cand;           // this warp's CAND_WORDS candidate words
-  int nd;
+  uint32_t* cand;           // this warp's CAND_WORDS candidate words (domain_lists parity kernel only)
+  const TlasNode* tlas;     // top-level BVH4 over the resident domains (16-byte aligned)
+  int nd, tlas_n;
 };
 
-__host__ __device__ inline size_t dom_smem_bytes(int nd, int nwarps) {
-  return (size_t)nd * 6 * sizeof(float) + (((size_t)nd + 15) & ~(size_t)15) + (size_t)nwarps * CAND_WORDS * 4;
+// layout: tlas nodes | boxes | resident | [candidate words]
+__host__ __device__ inline size_t dom_smem_bytes(int nd, int tlas_n, int cand_warps) {
+  return (size_t)tlas_n * sizeof(TlasNode) + (size_t)nd * 6 * sizeof(float) + (((size_t)nd + 15) & ~(size_t)15) +
+         (size_t)cand_warps * CAND_WORDS * 4;
 }
 
-__device__ __forceinline__ DomSmem load_domain_smem(const DomainEntry* __restrict__ table, int nd, float* smem) {
-  float* boxes = smem;
+__device__ __forceinline__ DomSmem load_domain_smem(const DomainEntry* __restrict__ table, int nd,
+                                                    const TlasNode* __restrict__ tlas, int tlas_n, float* smem) {
+  uint4* tl = (uint4*)smem;
+  float* boxes = (float*)(tl + 7 * tlas_n);
   uint8_t* resident = (uint8_t*)(boxes + 6 * nd);
   uint32_t* cand = (uint32_t*)(resident + ((nd + 15) & ~15));
+  for (int i = threadIdx.x; i < 7 * tlas_n; i += blockDim.x) tl[i] = ((const uint4*)tlas)[i];
   for (int i = threadIdx.x; i < nd; i += blockDim.x) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) boxes[6 * i + k] = table[i].box[k];
@@ -66,6 +72,7 @@ __device__ __forceinline__ DomSmem load_domain_smem(const DomainEntry* __restric
   __syncthreads();
   DomSmem d;
   d.boxes = boxes; d.resident = resident; d.cand = cand + (threadIdx.x >> 5) * CAND_WORDS; d.nd = nd;
+  d.tlas = (const TlasNode*)tl; d.tlas_n = tlas_n;
   return d;
 }
 
@@ -183,44 +190,6 @@ struct SceneHit {
   uint32_t prim, dom;
 };
 
-// ONE routine for both query kinds over the warp-culled candidate domains (call warp_cull(..., true) first,
-// all lanes).  A single instance keeps the persistent kernel's code small (instruction cache).
-//   any == false: closest hit = lexicographic min of (t, domain, prim); returns out.t < inf.
-//   any == true : returns true as soon as any resident entered domain occludes the ray.
-template <bool COUNT, typename CandF>
-__device__ __forceinline__ bool scene_trace(const DomainEntry* __restrict__ table, const DomSmem& D, const CandF& cand,
-                                            vec3 o, vec3 d, const bool any, SceneHit& out,
-                                            uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
-  uint64_t list[MAXLIST];
-  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
-  out.t = INFINITY; out.prim = 0; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
-  const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
-  bool have_after = false, more = false, done = false;
-  uint64_t after = 0;
-  do {
-    const int n = domain_list(D, cand, o, d, have_after, after, list, &more);
-    for (int k = 0; k < n && !done; ++k) {
-      const float tdom = sortable_float((uint32_t)(list[k] >> 32));
-      // front-to-back early out (an optimisation only; slack keeps it conservative)
-      if (out.t < INFINITY && tdom > out.t * 1.0001f + 1e-4f) { done = true; break; }
-      const uint32_t id = (uint32_t)list[k];
-      const DomainEntry* e = table + id;
-      // Seed with the best t so far (prim = max): the traversal then admits hits with t < best, or
-      // t == best (exact tie, resolved below to the lowest (domain, prim)).
-      Closest cc; cc.t = out.t; cc.u = cc.v = 0.f; cc.prim = 0xFFFFFFFFu;
-      if (COUNT) cnt[0]++;
-      const bool occ = bvh8_trace(NodeLoaderG{e->nodes}, TriLoaderG{e->tris}, r, any, cc, sx, sy,
-                                  COUNT ? cnt + 1 : nullptr, COUNT ? cnt + 2 : nullptr);
-      if (occ) return true;
-      if (cc.prim != 0xFFFFFFFFu && (cc.t < out.t || (cc.t == out.t && id < out.dom))) {
-        out.t = cc.t; out.u = cc.u; out.v = cc.v; out.prim = cc.prim; out.dom = id;
-      }
-    }
-    if (n > 0) { after = list[n - 1]; have_after = true; }
-  } while (more && !done);
-  return !any && out.t < INFINITY;
-}
-
 // ------------------------------------------------------------------------------------------------
 // Warp-synchronous traversal.
 //
@@ -240,63 +209,149 @@ __device__ __forceinline__ bool scene_trace(const DomainEntry* __restrict__ tabl
 // ------------------------------------------------------------------------------------------------
 struct OneDomainSource {   // seam 2: a single committed scene
   const uint4* nodes; const float4* tris; uint32_t id; bool used;
-  __device__ __forceinline__ bool next(float, const uint4*& n, const float4*& t, uint32_t& dom) {
-    if (used) return false;
+  // one step of "find my next domain": 0 = no further domain, 1 = domain found, 2 = progressed, call again
+  __device__ __forceinline__ int step(const RayCtx&, float, const uint4*& n, const float4*& t, uint32_t& dom) {
+    if (used) return 0;
     used = true; n = nodes; t = tris; dom = id;
-    return true;
+    return 1;
   }
 };
 
-template <typename CandF>
-struct ListDomainSource {  // the ray's entered resident domains, front to back by (tmin, id)
-  const DomainEntry* table; const DomSmem& D; const CandF& cand; vec3 o, d;
-  uint64_t list[MAXLIST];
-  int n, k; bool more;
-  __device__ __forceinline__ ListDomainSource(const DomainEntry* table_, const DomSmem& D_, const CandF& cand_, bool act,
-                                              vec3 o_, vec3 d_)
-      : table(table_), D(D_), cand(cand_), o(o_), d(d_), n(0), k(0), more(false) {
-    if (act) n = domain_list(D, cand, o, d, false, 0ull, list, &more);
+// ------------------------------------------------------------------------------------------------
+// TlasSource — the ray's entered resident domains found LAZILY by walking the top-level BVH4 (shared
+// memory) front to back.  ncu/A-B on the flat scheme (exact slab test of every candidate box at push time):
+// incoherent bounce rays tested all 64 boxes (~1.4 k instructions per ray) although 3 of 4 rays end in the
+// first domain they enter.  Here a ray only opens the top-level nodes in front of its current best hit.
+//   inner boxes : conservative float slab test (same (plane - o) * idir form as the exact test, which is
+//                 monotone in the box, plus a relative tolerance)
+//   leaf (domain): the reference's exact slab test (aabb.h:139-169) decides entry, as before
+// Order only affects speed: the closest hit is the lexicographic min of (t, domain, prim).
+// ------------------------------------------------------------------------------------------------
+#define SPRAY_TLAS_STACK 24
+
+__device__ __forceinline__ bool tlas_box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayCtx& r,
+                                             float* tmin_o) {
+  const bool nx = r.idir.x < 0.0f, ny = r.idir.y < 0.0f, nz = r.idir.z < 0.0f;
+  const float t0x = ((nx ? hix : lox) - r.o.x) * r.idir.x, t1x = ((nx ? lox : hix) - r.o.x) * r.idir.x + r.far_bias.x;
+  const float t0y = ((ny ? hiy : loy) - r.o.y) * r.idir.y, t1y = ((ny ? loy : hiy) - r.o.y) * r.idir.y + r.far_bias.y;
+  const float t0z = ((nz ? hiz : loz) - r.o.z) * r.idir.z, t1z = ((nz ? loz : hiz) - r.o.z) * r.idir.z + r.far_bias.z;
+  const float cmin = fmaxf(fmaxf(t0x, t0y), t0z), cmax = fminf(fminf(t1x, t1y), t1z);
+  const float tol = 1e-5f * (fabsf(cmin) + fabsf(cmax)) + 1e-30f;
+  *tmin_o = cmin - tol;
+  return (cmin <= cmax + tol) && (cmax >= -tol);
+}
+
+struct TlasSource {
+  const DomainEntry* table; const DomSmem& D;
+  float st[SPRAY_TLAS_STACK];
+  int sr[SPRAY_TLAS_STACK];
+  int sp;
+  __device__ __forceinline__ TlasSource(const DomainEntry* table_, const DomSmem& D_) : table(table_), D(D_), sp(0) {}
+  __device__ __forceinline__ void reset(bool act) {
+    sp = 0;
+    if (act && D.tlas_n > 0) { st[0] = -INFINITY; sr[0] = 0; sp = 1; }
   }
-  __device__ __forceinline__ bool next(float best_t, const uint4*& nn, const float4*& tt, uint32_t& dom) {
-    for (;;) {
-      if (k < n) {
-        const uint64_t key = list[k];
-        const float tdom = sortable_float((uint32_t)(key >> 32));
-        // front-to-back early out (an optimisation only; the slack keeps it conservative)
-        if (best_t < INFINITY && tdom > best_t * 1.0001f + 1e-4f) return false;
-        const DomainEntry* e = table + (uint32_t)key;
-        nn = e->nodes; tt = e->tris; dom = (uint32_t)key; ++k;
-        return true;
+  // ONE top-level step: pops one entry; 0 = stack empty, 1 = entered a domain, 2 = progressed
+  __device__ __forceinline__ int step(const RayCtx& r, float best_t, const uint4*& nn, const float4*& tt, uint32_t& dom) {
+    {
+      // entries behind the current best hit are dropped without a step of their own (cheap)
+      while (sp > 0 && best_t < INFINITY && st[sp - 1] > best_t * 1.0001f + 1e-4f) --sp;
+      if (sp == 0) return 0;
+      --sp;
+      const int ref = sr[sp];
+      if (ref < 0) {
+        const uint32_t id = (uint32_t)~ref;
+        float tmin;
+        if (!domain_slab(D.boxes + 6 * id, r.o, r.d, SPRAY_RAY_EPS, INFINITY, &tmin)) return 2;
+        const DomainEntry* e = table + id;
+        nn = e->nodes; tt = e->tris; dom = id;
+        return 1;
       }
-      if (!more || n == 0) return false;
-      const uint64_t after = list[n - 1];   // more than MAXLIST entered domains: next chunk
-      n = domain_list(D, cand, o, d, true, after, list, &more);
-      k = 0;
+      const float4* n4 = (const float4*)(D.tlas + ref);
+      const float4 lx = n4[0], ly = n4[1], lz = n4[2], hx = n4[3], hy = n4[4], hz = n4[5];
+      const int4 ch = *(const int4*)(n4 + 6);
+      float t[4]; int c[4];
+      bool h0 = tlas_box_hit(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, &t[0]);
+      bool h1 = tlas_box_hit(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, &t[1]);
+      bool h2 = tlas_box_hit(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, &t[2]);
+      bool h3 = tlas_box_hit(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, &t[3]);
+      c[0] = ch.x; c[1] = ch.y; c[2] = ch.z; c[3] = ch.w;
+      if (!h0) t[0] = INFINITY;
+      if (!h1) t[1] = INFINITY;
+      if (!h2) t[2] = INFINITY;
+      if (!h3) t[3] = INFINITY;
+      // sort the four children far -> near (5 compare-exchanges), push the hits: nearest ends on top
+#define SPRAY_CSWAP(a, b) { if (t[a] < t[b]) { const float tf = t[a]; t[a] = t[b]; t[b] = tf; const int ti = c[a]; c[a] = c[b]; c[b] = ti; } }
+      SPRAY_CSWAP(0, 1) SPRAY_CSWAP(2, 3) SPRAY_CSWAP(0, 2) SPRAY_CSWAP(1, 3) SPRAY_CSWAP(1, 2)
+#undef SPRAY_CSWAP
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (t[k] < INFINITY && sp < SPRAY_TLAS_STACK) { st[sp] = t[k]; sr[sp] = c[k]; ++sp; }
     }
+    return 2;
   }
 };
 
-// Call with ALL 32 lanes of the warp (act = this lane carries a ray).  Returns: any == false -> out.t < inf;
-// any == true -> occluded.
-template <bool COUNT, typename Source>
-__device__ __forceinline__ bool trace_warp(Source& src, const bool act, const RayCtx& r, const bool any, SceneHit& out,
-                                           uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+// conservative "does this ray enter any resident domain at all" (the top-level root's children): rays that
+// miss the whole scene never take a queue slot
+__device__ __forceinline__ bool tlas_any(const DomSmem& D, const RayCtx& r) {
+  if (D.tlas_n == 0) return false;
+  const float4* n4 = (const float4*)D.tlas;
+  const float4 lx = n4[0], ly = n4[1], lz = n4[2], hx = n4[3], hy = n4[4], hz = n4[5];
+  float t;
+  return tlas_box_hit(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, &t) || tlas_box_hit(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, &t) ||
+         tlas_box_hit(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, &t) || tlas_box_hit(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, &t);
+}
+
+// One lane's traversal state and its three step kinds.
+struct LaneTrav {
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
-  out.t = INFINITY; out.prim = 0xFFFFFFFFu; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
-  bool alive = act, found = false;
-  uint32_t ngx = 0, ngy = 0, tgx = 0, tgy = 0, dom = 0;
-  const uint4* nodes = nullptr;
-  const float4* tris = nullptr;
-  int sp = 0;
-  for (;;) {
+  uint32_t ngx, ngy, tgx, tgy, dom;
+  const uint4* nodes;
+  const float4* tris;
+  int sp;
+  bool alive, found;
+  SceneHit out;
+
+  __device__ __forceinline__ void begin(bool act) {
+    alive = act; found = false;
+    ngx = ngy = tgx = tgy = 0u; dom = 0u; sp = 0;
+    nodes = nullptr; tris = nullptr;
+    out.t = INFINITY; out.prim = 0xFFFFFFFFu; out.dom = 0xFFFFFFFFu; out.u = out.v = 0.f;
+  }
+  // What this lane needs next.
+  enum { WANT_NONE = 0, WANT_SOURCE = 1, WANT_NODE = 2, WANT_TRI = 3 };
+  __device__ __forceinline__ int want() {
+    if (!alive) return WANT_NONE;
+    if (tgy) return WANT_TRI;
+    if (ngy <= 0x00FFFFFFu && sp > 0) { --sp; ngx = sx[sp]; ngy = sy[sp]; }   // popping costs nothing: do it now
+    return ngy > 0x00FFFFFFu ? WANT_NODE : WANT_SOURCE;
+  }
+  // one step of the domain source (top-level BVH walk); a lane whose source is exhausted is finished
+  template <bool COUNT, typename Source>
+  __device__ __forceinline__ void source_step(Source& src, const RayCtx& r, uint32_t* cnt) {
+    int rc;
+    do { rc = src.step(r, out.t, nodes, tris, dom); } while (rc == 2);   // A/B: one top-level step per pass was 3-4 % slower
+    if (rc == 1) { ngx = 0u; ngy = 0x80000000u; if (COUNT) cnt[0]++; }
+    else if (rc == 0) alive = false;
+  }
+  // One pass of the warp-synchronous loop: every lane takes at most one step of each kind, in the order
+  // source -> node -> triangle, so a lane that just entered a domain tests its root in the same pass.
+  // (A/B on B200: letting the warp vote for ONE kind of step per pass was 8-12 % slower — the minority lanes
+  // stall instead of riding along.)
+  template <bool COUNT, typename Source>
+  __device__ __forceinline__ void pass(Source& src, const RayCtx& r, const bool any, uint32_t* cnt) {
+    int w = want();
+    if (w == WANT_SOURCE) { source_step<COUNT>(src, r, cnt); w = want(); }
     __syncwarp();
-    if (alive && ngy <= 0x00FFFFFFu && tgy == 0u) {   // idle: pop, or pull the next domain
-      if (sp > 0) { --sp; ngx = sx[sp]; ngy = sy[sp]; }
-      else if (src.next(out.t, nodes, tris, dom)) { ngx = 0u; ngy = 0x80000000u; if (COUNT) cnt[0]++; }
-      else alive = false;
-    }
-    if (!__any_sync(0xffffffffu, alive)) break;
-    if (alive && tgy == 0u) {                          // node step (ngy has an inner child here)
+    if (w == WANT_NODE) node_step<COUNT>(r, cnt);
+    __syncwarp();
+    if (alive && tgy) tri_step<COUNT>(r, any, cnt);
+  }
+  // fetch + test one 80-byte node (only when no triangle is pending; ngy has an inner child here)
+  template <bool COUNT>
+  __device__ __forceinline__ void node_step(const RayCtx& r, uint32_t* cnt) {
+    {
       const uint32_t imask = ngy & 0xffu;
       const int bit = 31 - __clz((int)ngy);
       ngy &= ~(1u << bit);
@@ -311,8 +366,11 @@ __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const Ra
       ngy = (hm & 0xFF000000u) | (q0.w >> 24);
       tgy = hm & 0x00FFFFFFu;
     }
-    __syncwarp();
-    if (alive && tgy) {                                // triangle step: ONE pending triangle
+  }
+  // fetch + test ONE pending triangle
+  template <bool COUNT>
+  __device__ __forceinline__ void tri_step(const RayCtx& r, const bool any, uint32_t* cnt) {
+    {
       const int ti = __ffs((int)tgy) - 1;
       tgy &= tgy - 1;
       vec3 v0, e1, e2; uint32_t prim;
@@ -330,29 +388,32 @@ __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const Ra
       }
     }
   }
-  return any ? found : (out.t < INFINITY);
+};
+
+// Call with ALL 32 lanes of the warp (act = this lane carries a ray).  Returns: any == false -> out.t < inf;
+// any == true -> occluded.
+template <bool COUNT, typename Source>
+__device__ __forceinline__ bool trace_warp(Source& src, const bool act, const RayCtx& r, const bool any, SceneHit& out,
+                                           uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+  LaneTrav T;
+  T.begin(act);
+  for (;;) {
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, T.alive)) break;
+    T.pass<COUNT>(src, r, any, cnt);
+  }
+  out = T.out;
+  return any ? T.found : (out.t < INFINITY);
 }
 
 // closest / any hit over the ray's entered resident domains; all 32 lanes call.
-template <bool COUNT, typename CandF>
-__device__ __forceinline__ bool scene_trace_warp(const DomainEntry* __restrict__ table, const DomSmem& D,
-                                                 const CandF& cand, const bool act, vec3 o, vec3 d, const bool any,
-                                                 SceneHit& out, uint32_t* cnt) {
+template <bool COUNT>
+__device__ __forceinline__ bool scene_trace_warp(const DomainEntry* __restrict__ table, const DomSmem& D, const bool act,
+                                                 vec3 o, vec3 d, const bool any, SceneHit& out, uint32_t* cnt) {
   const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
-  ListDomainSource<CandF> src(table, D, cand, act, o, d);
+  TlasSource src(table, D);
+  src.reset(act);
   return trace_warp<COUNT>(src, act, r, any, out, cnt);
-}
-
-template <bool COUNT>
-__device__ __forceinline__ void scene_closest(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
-                                              SceneHit& out, uint32_t* cnt) {
-  scene_trace<COUNT>(table, D, WarpCand{D.cand}, o, d, false, out, cnt);
-}
-template <bool COUNT>
-__device__ __forceinline__ bool scene_occluded(const DomainEntry* __restrict__ table, const DomSmem& D, vec3 o, vec3 d,
-                                               uint32_t* cnt) {
-  SceneHit h;
-  return scene_trace<COUNT>(table, D, WarpCand{D.cand}, o, d, true, h, cnt);
 }
 
 }  // namespace spraygpu
