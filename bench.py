@@ -225,8 +225,12 @@ def main():
                 dev.trace_tile(cam, sh, t, fb_d)
 
         def step_e2e():
-            for t in tiles:                               # host frame buffer: D2H of each tile inside the call
-                dev.trace_tile(cam, sh, t, fb_h_np)
+            # the public C-ABI call with a pinned HOST frame buffer: camera/shade/tile descriptors go H2D as
+            # kernel arguments, every tile's rows come back D2H (copy of tile k overlaps the kernel of tile k+1);
+            # the frame is complete after the synchronize
+            for t in tiles:
+                dev.trace_tile_async(cam, sh, t, fb_h_np)
+            dev.synchronize()
 
         # ray counts (deterministic): one counted frame, also gives N_node / N_tri for the roofline
         fb_d.zero_()

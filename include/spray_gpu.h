@@ -182,6 +182,11 @@ SPRAYGPU_API int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camer
  * stats may be NULL. */
 SPRAYGPU_API int spraygpu_trace_tile(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                         spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
+/* Same call, but with a HOST frame buffer it returns as soon as the tile is enqueued: the tile's rows reach
+ * fb after spraygpu_device_synchronize(dev).  The D2H copy of tile k runs on a second stream and overlaps the
+ * kernel of tile k+1 (a film-mode frame = a loop of these + one synchronize).  fb should be pinned memory. */
+SPRAYGPU_API int spraygpu_trace_tile_async(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                           spraygpu_tile tile, float* fb_rgba);
 /* Same, with BVH node / triangle fetch counters (slower; used for the roofline's N_node, N_tri). */
 SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                 spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);

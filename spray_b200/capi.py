@@ -105,6 +105,7 @@ _PROTOS = {
     "spraygpu_gen_eye_rays": (C.c_int, [_vp, C.POINTER(Camera), Tile, C.c_int, _vp]),
     "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
+    "spraygpu_trace_tile_async": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp]),
     # multi-GPU (NCCL resolved at run time)
     "spraygpu_comm_unique_id": (C.c_int, [C.c_char_p]),
     "spraygpu_comm_create": (C.c_int, [_vp, C.c_int, C.c_int, C.c_char_p, C.POINTER(_vp)]),
@@ -271,6 +272,10 @@ class Device:
 
     def gen_eye_rays(self, cam, tile, spp, rays):
         _check(lib().spraygpu_gen_eye_rays(self.h, C.byref(cam), Tile(*tile), spp, _ptr(rays)))
+
+    def trace_tile_async(self, cam, shade, tile, fb):
+        """Host frame buffer: returns once the tile is enqueued; rows are valid after synchronize()."""
+        _check(lib().spraygpu_trace_tile_async(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb)))
 
     def trace_tile(self, cam, shade, tile, fb, stats=False, counted=False):
         st = Stats() if stats else None

@@ -202,6 +202,11 @@ int spraygpu_device_create(int cuda_device, spraygpu_device* out) {
   SG_CUDA(cudaMemset(d->d_counters, 0, sizeof(unsigned long long) * 8));
   SG_CUDA(cudaMallocHost(&d->pinned, 4096));
   d->pinned_bytes = 4096;
+  SG_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) {
+    SG_CUDA(cudaEventCreateWithFlags(&d->ev_render[i], cudaEventDisableTiming));
+    SG_CUDA(cudaEventCreateWithFlags(&d->ev_copy[i], cudaEventDisableTiming));
+  }
   *out = (spraygpu_device)d;
   return SPRAYGPU_OK;
 }
@@ -211,6 +216,12 @@ int spraygpu_device_destroy(spraygpu_device dev) {
   Device* d = DEV(dev);
   cudaSetDevice(d->cuda_device);
   cudaStreamSynchronize(d->stream);
+  if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); cudaStreamDestroy(d->copy_stream); }
+  for (int i = 0; i < 2; ++i) {
+    if (d->ev_render[i]) cudaEventDestroy(d->ev_render[i]);
+    if (d->ev_copy[i]) cudaEventDestroy(d->ev_copy[i]);
+    if (d->fb_stage[i].ptr) cudaFree(d->fb_stage[i].ptr);
+  }
   if (d->scratch.ptr) cudaFree(d->scratch.ptr);
   if (d->stage_in.ptr) cudaFree(d->stage_in.ptr);
   if (d->stage_out.ptr) cudaFree(d->stage_out.ptr);
@@ -232,6 +243,7 @@ int spraygpu_device_set_stream(spraygpu_device dev, void* cuda_stream) {
 int spraygpu_device_synchronize(spraygpu_device dev) {
   SG_CHECK(dev, SPRAYGPU_ERR_ARG, "synchronize: dev is NULL");
   SG_CUDA(cudaStreamSynchronize(DEV(dev)->stream));
+  if (DEV(dev)->copy_stream) SG_CUDA(cudaStreamSynchronize(DEV(dev)->copy_stream));
   return SPRAYGPU_OK;
 }
 
@@ -530,7 +542,7 @@ int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spray
 }
 
 static int trace_tile_impl(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
-                           spraygpu_tile tile, float* fb, spraygpu_stats* stats, bool counted) {
+                           spraygpu_tile tile, float* fb, spraygpu_stats* stats, bool counted, bool async) {
   SG_CHECK(dev && cam && shade && fb, SPRAYGPU_ERR_ARG, "trace_tile: NULL argument");
   SG_CHECK(shade->pixel_samples >= 1 && shade->bounces >= 1, SPRAYGPU_ERR_ARG, "trace_tile: pixel_samples and bounces must be >= 1");
   SG_CHECK(shade->nlights >= 0 && shade->nlights <= SPRAYGPU_MAX_LIGHTS, SPRAYGPU_ERR_LIMIT, "trace_tile: %d lights (limit %d)",
@@ -550,20 +562,28 @@ static int trace_tile_impl(spraygpu_device dev, const spraygpu_camera* cam, cons
   float* dfb = fb;
   const size_t img_bytes = sizeof(float) * 4 * (size_t)cam->image_w * cam->image_h;
   const size_t row_bytes = sizeof(float) * 4 * (size_t)cam->image_w;
+  const int sb = (int)(d->fb_calls & 1);
   if (host_fb) {
     // Host frame buffer: render into a zeroed device image, then copy the tile's rows back.  (The
     // reference clears the image each frame and tiles are disjoint, src/render/spray_renderer.inl:363.)
-    rc = ensure_scratch(d->stage_out, img_bytes + 4096);
+    // Two staging images alternate and the copy runs on its own stream: tile k's D2H overlaps tile k+1.
+    ++d->fb_calls;
+    if (d->fb_stage[sb].bytes < img_bytes + 4096) SG_CUDA(cudaEventSynchronize(d->ev_copy[sb]));  // about to reallocate
+    rc = ensure_scratch(d->fb_stage[sb], img_bytes + 4096);
     if (rc) return rc;
-    dfb = (float*)d->stage_out.ptr;
+    dfb = (float*)d->fb_stage[sb].ptr;
+    SG_CUDA(cudaStreamWaitEvent(d->stream, d->ev_copy[sb], 0));   // the copy that last read this staging image
     SG_CUDA(cudaMemsetAsync((char*)dfb + row_bytes * tile.y, 0, row_bytes * tile.h, d->stream));
   }
   rc = launch_render_tile(d, cam, shade, tile, dfb, counted);
   if (rc) return rc;
   if (host_fb && tile.w > 0 && tile.h > 0) {
     const size_t off = (size_t)tile.y * cam->image_w + tile.x;
+    SG_CUDA(cudaEventRecord(d->ev_render[sb], d->stream));
+    SG_CUDA(cudaStreamWaitEvent(d->copy_stream, d->ev_render[sb], 0));
     SG_CUDA(cudaMemcpy2DAsync(fb + 4 * off, row_bytes, dfb + 4 * off, row_bytes, sizeof(float) * 4 * tile.w, tile.h,
-                              cudaMemcpyDeviceToHost, d->stream));
+                              cudaMemcpyDeviceToHost, d->copy_stream));
+    SG_CUDA(cudaEventRecord(d->ev_copy[sb], d->copy_stream));
   }
   if (stats) {
     unsigned long long* h = (unsigned long long*)d->pinned;
@@ -571,19 +591,22 @@ static int trace_tile_impl(spraygpu_device dev, const spraygpu_camera* cam, cons
     SG_CUDA(cudaStreamSynchronize(d->stream));
     stats->eye_rays = h[1]; stats->radiance_rays = h[2]; stats->shadow_rays = h[3]; stats->domain_tests = h[4];
     stats->nodes_visited = h[5]; stats->tris_tested = h[6]; stats->hits = h[7];
-  } else if (host_fb) {
-    SG_CUDA(cudaStreamSynchronize(d->stream));
   }
+  if (host_fb && !async) SG_CUDA(cudaStreamSynchronize(d->copy_stream));
   return SPRAYGPU_OK;
 }
 
 int spraygpu_trace_tile(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                         float* fb, spraygpu_stats* stats) {
-  return trace_tile_impl(dev, cam, shade, tile, fb, stats, false);
+  return trace_tile_impl(dev, cam, shade, tile, fb, stats, false, false);
+}
+int spraygpu_trace_tile_async(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                              spraygpu_tile tile, float* fb) {
+  return trace_tile_impl(dev, cam, shade, tile, fb, nullptr, false, true);
 }
 int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                 spraygpu_tile tile, float* fb, spraygpu_stats* stats) {
-  return trace_tile_impl(dev, cam, shade, tile, fb, stats, true);
+  return trace_tile_impl(dev, cam, shade, tile, fb, stats, true, false);
 }
 
 }  // extern "C"

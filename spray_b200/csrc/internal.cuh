@@ -72,6 +72,12 @@ struct Device {
   Scratch scratch;                 // build scratch (grown on demand)
   Scratch stage_in, stage_out;     // device staging for host-pointer calls
   Scratch wave;                    // in-situ wavefront buffers (insitu.cu)
+  // host frame buffers: two device staging images, D2H on a copy stream so that tile k's copy overlaps
+  // tile k+1's kernel
+  Scratch fb_stage[2];
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_render[2] = {nullptr, nullptr}, ev_copy[2] = {nullptr, nullptr};
+  uint64_t fb_calls = 0;
   void* pinned = nullptr;          // pinned bounce buffer for small D2H reads
   size_t pinned_bytes = 0;
   // domain table

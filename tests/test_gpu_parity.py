@@ -375,3 +375,31 @@ def test_full_size_properties_c2(oracle, dev_c2, c2):
     dev_c2.trace_tile(cam_g, sh, (0, 0, W, W), fb2)
     dev_c2.synchronize()
     assert torch.equal(fb, fb2)
+
+
+@pytest.mark.gpu
+def test_trace_tile_async_host_frame_buffer(oracle, dev_c2, c2):
+    """spraygpu_trace_tile_async (overlapped D2H on a second stream, two staging images): same image as the
+    synchronous call, over several frames so that both staging images are reused."""
+    import torch
+    from spray_b200 import capi
+    sc = c2[0]
+    p = scenes.WAVELETS64_CAMERA
+    W = 192
+    cd = scenes.camera_frame(p["pos"], p["lookat"], p["up"], p["vfov"], W, W)
+    cam = capi.make_camera(cd)
+    sh = capi.make_shade(bounces=1, pixel_samples=1, lights=sc["lights"], **scenes.WAVELETS64_BLINN)
+    tiles = [(0, y, W, 48) for y in range(0, W, 48)]
+    ref = np.zeros((W, W, 4), np.float32)
+    for t in tiles:
+        dev_c2.trace_tile(cam, sh, t, ref)
+    fb = torch.zeros((W, W, 4), dtype=torch.float32).pin_memory()
+    fbn = fb.numpy()
+    for frame in range(3):
+        fbn[:] = -1.0
+        for t in tiles:
+            dev_c2.trace_tile_async(cam, sh, t, fbn)
+        dev_c2.synchronize()
+        assert np.abs(fbn[..., :3] - ref[..., :3]).max() <= 1e-6
+        assert (fbn[..., 3] == 0).all()
+    assert ref[..., :3].max() > 0.1
