@@ -213,6 +213,10 @@ struct Pending { vec3 o, d, w; int depth; };
 #ifndef SPRAY_RENDER_MINBLOCKS
 #define SPRAY_RENDER_MINBLOCKS 2
 #endif
+#ifndef SPRAY_RENDER_THREADS
+#define SPRAY_RENDER_THREADS 256
+#endif
+#define SPRAY_RENDER_WARPS (SPRAY_RENDER_THREADS / 32)
 
 // ------------------------------------------------------------------------------------------------
 // Per-warp ray queue (shared memory, SoA, LIFO).  Every ray that enters at least one resident domain
@@ -266,7 +270,7 @@ __device__ __forceinline__ bool queue_push(const RayQueue& Q, const DomSmem& D, 
 template <bool GENERAL> struct QueueCap { static constexpr int value = GENERAL ? 128 : 96; };
 
 template <bool COUNT, bool GENERAL>
-__global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
+__global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
   extern __shared__ float smem[];
   const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
   constexpr int QCAP = QueueCap<GENERAL>::value;
@@ -421,7 +425,7 @@ __global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_kerne
 __host__ __device__ inline size_t stream_words_per_warp() { return queue_words_per_warp(STREAM_QCAP) + (size_t)IF_WORDS * 32; }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(256, SPRAY_RENDER_MINBLOCKS) render_tile_stream_kernel(RenderParams P) {
+__global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) render_tile_stream_kernel(RenderParams P) {
   extern __shared__ float smem[];
   const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
   const int lane = threadIdx.x & 31;
@@ -647,16 +651,16 @@ int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_s
                        : (general ? render_tile_kernel<false, true> : render_tile_kernel<false, false>);
   const int qcap = general ? QueueCap<true>::value : QueueCap<false>::value;
   const size_t smem = ((dom_smem_bytes(dev->ndomains, dev->tlas_n, 0) + 15) & ~(size_t)15) +
-                      8 * (stream ? stream_words_per_warp() : queue_words_per_warp(qcap)) * sizeof(uint32_t);
+                      SPRAY_RENDER_WARPS * (stream ? stream_words_per_warp() : queue_words_per_warp(qcap)) * sizeof(uint32_t);
   SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+  SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SPRAY_RENDER_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   // persistent grid: SM count x resident CTAs per SM
   int grid = dev->sm_count * per_sm;
   const uint64_t warps_needed = (slots + 31) / 32;
-  if ((uint64_t)grid * 8 > warps_needed) grid = (int)((warps_needed + 7) / 8);
-  kern<<<grid, 256, smem, dev->stream>>>(P);
+  if ((uint64_t)grid * SPRAY_RENDER_WARPS > warps_needed) grid = (int)((warps_needed + SPRAY_RENDER_WARPS - 1) / SPRAY_RENDER_WARPS);
+  kern<<<grid, SPRAY_RENDER_THREADS, smem, dev->stream>>>(P);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
