@@ -71,10 +71,9 @@ class GpuTracer {
                     cfg.maximum_num_screen_space_samples_per_rank);
     SPRAY_CHECK(insitu_ || !tile_list_.empty() || num_ranks_ > cfg.image_w, "");
 
-    if (!insitu_)
-      SPRAY_CHECK(scene->cacheCapacity() >= (int)scene->getNumDomains(),
-                  "--cache-size " << scene->cacheCapacity() << " < " << scene->getNumDomains()
-                                  << " domains: the fused tile kernel needs every entered domain resident");
+    // --cache-size k < #domains: the out-of-core sweep (spraygpu_trace_tile_ooc) with Scene::load as its
+    // residency callback, the reference's `scene->load(id)` inside PContext::isectPrims (ooc_pcontext.h:145-154)
+    out_of_core_ = !insitu_ && scene->cacheCapacity() < (int)scene->getNumDomains();
 
     npixels_ = (std::size_t)cfg.image_w * cfg.image_h;
     SPRAY_CHECK(cudaSetDevice(cfg.cuda_device) == cudaSuccess, "cudaSetDevice");
@@ -89,13 +88,16 @@ class GpuTracer {
     // The reference loads domains on demand inside PContext::isectPrims (ooc_pcontext.h:145-154); the fused
     // kernel wants them resident before the tile starts.  With an LRU cache that holds every domain this is
     // the first frame's one-time load (InfiniteCache scenes were warmed in Scene::init).
-    if (!insitu_)
+    if (!insitu_ && !out_of_core_)
       for (std::size_t id = 0; id < scene_->getNumDomains(); ++id)
         if (!scene_->isResident((int)id)) scene_->load((int)id);
     SPRAY_CHECK(cudaMemsetAsync(d_fb_, 0, npixels_ * 16, 0) == cudaSuccess, "");  // image_.clear() on the device
     for (const Tile& t : tile_list_.tiles()) {
       const spraygpu_tile gt = {t.x, t.y, t.w, t.h};
-      if (insitu_ && num_ranks_ > 1) SPRAY_GPU_CALL(spraygpu_trace_tile_insitu(dev_, comm_, &cam, &shade_, gt, d_fb_, nullptr));
+      if (out_of_core_)
+        SPRAY_GPU_CALL(spraygpu_trace_tile_ooc(dev_, &cam, &shade_, gt, d_fb_, scene_->cacheCapacity(), &GpuTracer::loadDomain,
+                                               scene_, nullptr));
+      else if (insitu_ && num_ranks_ > 1) SPRAY_GPU_CALL(spraygpu_trace_tile_insitu(dev_, comm_, &cam, &shade_, gt, d_fb_, nullptr));
       else SPRAY_GPU_CALL(spraygpu_trace_tile(dev_, &cam, &shade_, gt, d_fb_, nullptr));
     }
     if (num_ranks_ == 1) download();
@@ -103,6 +105,11 @@ class GpuTracer {
   void traceInOmp() { trace(); }  // the reference's --dev-mode variant; there is no OpenMP team here
 
  private:
+  // spraygpu_load_fn: Scene::load (LRU hit, or PLY parse + commit + bind on a miss)
+  static int loadDomain(void* user, int domain_id) {
+    static_cast<SceneType*>(user)->load(domain_id);
+    return 0;
+  }
   void composite() {
     if (num_ranks_ == 1) return;
     if (insitu_) {
@@ -130,6 +137,7 @@ class GpuTracer {
   std::size_t npixels_ = 0;
   int rank_ = 0, num_ranks_ = 1;
   bool insitu_ = false;
+  bool out_of_core_ = false;
 };
 
 }  // namespace spray

@@ -191,6 +191,22 @@ SPRAYGPU_API int spraygpu_trace_tile_async(spraygpu_device dev, const spraygpu_c
 SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                 spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
 
+/* ---- out-of-core: the device cache holds fewer domains than the tile enters.
+ * Replaces ooc::PContext::isectPrims' domain loop (src/ooc/ooc_pcontext.h:92-181): per round, schedule the
+ * domains by queued rays (DomainStats::schedule, src/ooc/ooc_domain_stats.cc:60-111), `scene->load(id)` each one
+ * (LruCache miss -> PlyLoader + rtcCommit, :145-154) and drain its radiance + shadow queues.  Here the tile runs
+ * as a wavefront swept over groups of <= max_resident domains; per-ray state is merged across groups with a
+ * 64-bit atomicMin on the hit keys and an OR on the occlusion bytes.  bounces + 1 sweeps per tile.
+ *
+ * spraygpu_load_fn = Scene::load (src/render/scene.inl:135-187): on return 0 the domain must be bound on `dev`
+ * (spraygpu_domain_bind); the callback may evict (unbind) other domains, but none it loaded since the current
+ * group started — true for an LRU cache of capacity >= max_resident.  Called on the calling thread.
+ * Same result as spraygpu_trace_tile with every domain resident.  fb must be a device pointer. */
+typedef int (*spraygpu_load_fn)(void* user, int domain_id);
+SPRAYGPU_API int spraygpu_trace_tile_ooc(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                         spraygpu_tile tile, float* fb_rgba, int max_resident, spraygpu_load_fn load,
+                                         void* user, spraygpu_stats* stats);
+
 /* ---- multi-GPU: one process (rank) per GPU on one NVLink/NVSwitch box.  Replaces the reference's MPI
  *      (SURVEY.md section 2.2): MPI_Init/Comm_rank (src/apps/spray_insitu_*.cc:33-38), the in-situ domain
  *      partition (src/render/data_partition.h:59-137), the t-buffer MPI_Allreduce(MIN)

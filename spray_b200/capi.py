@@ -106,6 +106,7 @@ _PROTOS = {
     "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_async": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp]),
+    "spraygpu_trace_tile_ooc": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.c_int, _vp, _vp, C.POINTER(Stats)]),
     # multi-GPU (NCCL resolved at run time)
     "spraygpu_comm_unique_id": (C.c_int, [C.c_char_p]),
     "spraygpu_comm_create": (C.c_int, [_vp, C.c_int, C.c_int, C.c_char_p, C.POINTER(_vp)]),
@@ -282,6 +283,70 @@ class Device:
         fn = lib().spraygpu_trace_tile_counted if counted else lib().spraygpu_trace_tile
         _check(fn(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb), C.byref(st) if st is not None else None))
         return st
+
+
+    def trace_tile_ooc(self, cam, shade, tile, fb, max_resident, load, stats=False):
+        """Out-of-core tile: `load(domain_id) -> 0` makes a domain resident (Scene::load)."""
+        st = Stats() if stats else None
+
+        def _cb(user, domain_id):
+            try:
+                return int(load(int(domain_id)) or 0)
+            except Exception as e:   # never unwind through the C frame
+                self._cb_error = e
+                return 1
+        cb = LOAD_FN(_cb)
+        self._cb_error = None
+        rc = lib().spraygpu_trace_tile_ooc(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb), int(max_resident),
+                                           C.cast(cb, _vp), None, C.byref(st) if st is not None else None)
+        if self._cb_error is not None:
+            raise self._cb_error
+        _check(rc)
+        return st
+
+
+LOAD_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)
+
+
+class LruDomainCache:
+    """Device-side domain cache for the out-of-core path: the reference's LruCache (src/render/lru_cache.cc:65-171)
+    driving Scene::load (src/render/scene.inl:135-187) — a miss uploads the domain's mesh into the cache block's
+    scene, commits it (BVH build) and binds it; the evicted domain is unbound.  Harness for tests / bench; the
+    C++ mirror is host/spray/scene.h."""
+
+    def __init__(self, dev, scene_desc, capacity):
+        self.dev, self.doms, self.capacity = dev, scene_desc["domains"], int(capacity)
+        dev.set_domains(np.stack([d["bounds"] for d in self.doms]), [d.get("mtl", (0, (1, 1, 1))) for d in self.doms])
+        self.blocks = [dev.new_scene() for _ in range(self.capacity)]
+        self.block_domain = [-1] * self.capacity
+        self.lru = []            # block indices, least recently used first
+        self.where = {}          # domain id -> block
+        self.hits = self.misses = 0
+
+    def load(self, domain_id):
+        b = self.where.get(domain_id)
+        if b is not None:
+            self.hits += 1
+            self.lru.remove(b); self.lru.append(b)
+            return 0
+        self.misses += 1
+        if len(self.where) < self.capacity:
+            b = len(self.where)
+        else:
+            b = self.lru.pop(0)
+            old = self.block_domain[b]
+            self.dev.bind(old, None)
+            del self.where[old]
+        d = self.doms[domain_id]
+        s = self.blocks[b]
+        s.set_mesh(d["verts"], d["faces"], d.get("rgb"))
+        s.set_transform(d.get("transform"))
+        s.commit()
+        self.dev.bind(domain_id, s)
+        self.block_domain[b] = domain_id
+        self.where[domain_id] = b
+        self.lru.append(b)
+        return 0
 
 
 def partition_domains(world_bounds, scene_bounds, nranks, round_robin=False, return_codes=False):

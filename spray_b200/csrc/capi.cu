@@ -150,7 +150,7 @@ int upload_domain_table(Device* dev) {
   {
     std::vector<int> ids;
     for (int i = 0; i < dev->ndomains; ++i)
-      if (dev->h_domains[i].resident) ids.push_back(i);
+      if (dev->h_domains[i].resident && (dev->active.empty() || dev->active[(size_t)i])) ids.push_back(i);
     dev->h_tlas.clear();
     if (!ids.empty()) tlas_build(dev, ids.data(), (int)ids.size());
     dev->tlas_n = (int)dev->h_tlas.size();
@@ -159,8 +159,16 @@ int upload_domain_table(Device* dev) {
       SG_CUDA(cudaMemcpyAsync(dev->d_tlas, dev->h_tlas.data(), sizeof(TlasNode) * dev->tlas_n, cudaMemcpyHostToDevice,
                               dev->stream));
   }
-  SG_CUDA(cudaMemcpyAsync(dev->d_domains, dev->h_domains.data(), sizeof(DomainEntry) * dev->ndomains,
-                          cudaMemcpyHostToDevice, dev->stream));
+  if (dev->active.empty()) {
+    SG_CUDA(cudaMemcpyAsync(dev->d_domains, dev->h_domains.data(), sizeof(DomainEntry) * dev->ndomains,
+                            cudaMemcpyHostToDevice, dev->stream));
+  } else {
+    std::vector<DomainEntry> masked(dev->h_domains);
+    for (int i = 0; i < dev->ndomains; ++i)
+      if (!dev->active[(size_t)i]) masked[(size_t)i].resident = 0;
+    SG_CUDA(cudaMemcpyAsync(dev->d_domains, masked.data(), sizeof(DomainEntry) * dev->ndomains, cudaMemcpyHostToDevice,
+                            dev->stream));
+  }
   // h_domains is pageable: the runtime stages it before returning, so later host edits are safe
   dev->table_dirty = false;
   return SPRAYGPU_OK;

@@ -86,6 +86,9 @@ struct Device {
   std::vector<Scene*> bound;
   DomainEntry* d_domains = nullptr;
   bool table_dirty = true;
+  // out-of-core sweeps (ooc.cu): when non-empty, only resident domains with active[id] != 0 are visible to
+  // the kernels (uploaded table + top-level BVH); empty = every resident domain
+  std::vector<uint8_t> active;
   std::vector<TlasNode> h_tlas;    // built in upload_domain_table
   TlasNode* d_tlas = nullptr;
   int tlas_n = 0;                  // 0: no resident domain

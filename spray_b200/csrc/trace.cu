@@ -210,11 +210,13 @@ struct RenderParams {
 
 struct Pending { vec3 o, d, w; int depth; };
 
+// CTA shape: A/B on B200 (profiles/r01f_ab_occupancy.txt): 128 threads x 5 CTAs/SM (20 warps, 92-96 registers, no
+// spills) beat 256 x 2 (16 warps) by 9 % on C3 and 4 % on C2; 6-8 CTAs/SM (<= 80 / 64 registers) spill and lose.
 #ifndef SPRAY_RENDER_MINBLOCKS
-#define SPRAY_RENDER_MINBLOCKS 2
+#define SPRAY_RENDER_MINBLOCKS 5
 #endif
 #ifndef SPRAY_RENDER_THREADS
-#define SPRAY_RENDER_THREADS 256
+#define SPRAY_RENDER_THREADS 128
 #endif
 #define SPRAY_RENDER_WARPS (SPRAY_RENDER_THREADS / 32)
 

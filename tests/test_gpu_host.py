@@ -30,7 +30,8 @@ def read_ppm(path):
     return np.array(toks[4:], np.int64).reshape(h, w, 3)[::-1]      # rows are written bottom-up
 
 
-@pytest.mark.parametrize("cache_size,extra", [(-1, []), (64, []), (-1, ["--bounces", "2", "--pixel-samples", "2"])])
+@pytest.mark.parametrize("cache_size,extra", [(-1, []), (64, []), (-1, ["--bounces", "2", "--pixel-samples", "2"]),
+                                              (6, []), (3, ["--bounces", "2", "--pixel-samples", "2"])])   # out-of-core LRU
 def test_spray_gpu_film_wavelets64(spray_gpu, oracle, tmp_path, cache_size, extra):
     sc = scenes.wavelets64()
     verts, faces, rgb = scenes.load_wavelet_mesh()
