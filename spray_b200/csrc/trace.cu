@@ -450,102 +450,108 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
   T.begin(false);
   TlasSource src(P.table, D);
   RayCtx r = make_ray_ctx(mk3(0, 0, 0), mk3(0, 0, 1), SPRAY_RAY_EPS);
-  bool busy = false;  // this lane holds a ray (being traced)
-  bool done = false;  // this lane holds a finished ray waiting for the service pass
+  bool busy = false;  // this lane holds a ray (being traced, or finished and not yet shaded)
   bool any = false;   // the held ray is a shadow ray
 
   for (;;) {
     __syncwarp();
-    if (busy && !T.alive) { busy = false; done = true; }
-    const uint32_t am = __ballot_sync(0xffffffffu, T.alive);
-    const int n_idle = 32 - __popc(am);
-    if (n_idle >= SPRAY_FETCH_THRESH || am == 0u) {
-      const bool work = count > 0 || more || __any_sync(0xffffffffu, done);
-      if (work) {
-        // ================= service pass =================
-        const vec3 Lin = mk3(__uint_as_float(inflight[(IF_W + 0) * 32]), __uint_as_float(inflight[(IF_W + 1) * 32]),
-                             __uint_as_float(inflight[(IF_W + 2) * 32]));
-        const uint32_t pixid = inflight[IF_PIX * 32], samid = inflight[IF_SAM * 32], dk = inflight[IF_DK * 32];
-        // ---- A. retire shadow rays, shade radiance hits (ooc_shader_pt.h:94-227)
-        if (done && any && !T.found) fb_add(P.fb, pixid, scale, Lin);
-        const bool hit = done && !any && T.out.t < INFINITY;
-        const int next_depth = (int)(dk >> 1) + 1;
-        HitCtx c;
-        c.pos = r.o; c.kd = mk3(0, 0, 0); c.nff = mk3(0, 0, 1); c.wo = gneg(r.d);
-        c.cos_theta_i = 0.f; c.entering = false; c.mtl = SPRAYGPU_MTL_DIFFUSE; c.eta0 = c.eta1 = 1.f;
-        bool em1 = false, em2 = false, emit = false;
-        vec3 d1 = mk3(0, 0, 1), w1 = mk3(0, 0, 0), d2 = mk3(0, 0, 1), w2 = mk3(0, 0, 0), wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
-        if (hit) {
-          ++n_hit;
-          make_hit_ctx<false>(P.table + T.out.dom, r.o, r.d, T.out.t, T.out.u, T.out.v, T.out.prim, c);
-          if (next_depth < P.shade.bounces) shade_secondary<false>(c, Lin, samid, next_depth, &em1, &d1, &w1, &em2, &d2, &w2);
-          uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
-          int l = 0, k = 0; bool more_lights = true;
-          emit = shade_light_pass<false>(P.shade, true, 1, c, Lin, pixid, l, k, ls, &wi, &Lr, &more_lights);
-        }
-        done = false;
-        // ---- B. push: bounce rays first, shadow rays on top (popped first)
-        if (em1) ++n_rad;
-        if (__any_sync(0xffffffffu, em1))
-          queue_push(Q, D, count, em1, c.pos, d1, w1, pixid, samid, (uint32_t)next_depth << 1);
-        if (emit) ++n_shadow;
-        if (__any_sync(0xffffffffu, emit)) {
-          // a shadow ray that enters no resident domain is unoccluded
-          if (queue_push(Q, D, count, emit, c.pos, wi, Lr, pixid, samid, 1u)) fb_add(P.fb, pixid, scale, Lr);
-        }
-        // ---- C. top up with one 8x4 pixel block of eye rays (ooc_tracer.inl:84-172)
-        if (count < 32 && more) {
-          unsigned long long base = 0;
-          if (lane == 0) base = atomicAdd(P.counters, 32ull);
-          base = __shfl_sync(0xffffffffu, base, 0);
-          if (base >= P.total_slots) more = false;
-          else {
-            const uint32_t slot = (uint32_t)base + lane;
-            const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
-            const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-            const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
-            const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
-            const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
-            uint32_t esam = 0, epix = 0;
-            vec3 dir = mk3(0.f, 0.f, 1.f);
-            if (has_ray) {
-              eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &esam, &epix, &dir);
-              ++n_eye; ++n_rad;
-            }
-            queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), epix,
-                       esam, 0u);
-          }
-        }
-        // ---- D. idle lanes pop new rays (top of the queue first)
-        {
-          const bool idle = !T.alive;
-          const uint32_t im = __ballot_sync(0xffffffffu, idle);
-          const int nf = min(__popc(im), count);
-          const int rnk = __popc(im & ((1u << lane) - 1u));
-          const bool take = idle && rnk < nf;
-          if (take) {
-            const uint32_t* qe = Q.q + (count - 1 - rnk);
-            const vec3 ro = mk3(__uint_as_float(qe[(QF_O + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_O + 1) * STREAM_QCAP]),
-                                __uint_as_float(qe[(QF_O + 2) * STREAM_QCAP]));
-            const vec3 rd = mk3(__uint_as_float(qe[(QF_D + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_D + 1) * STREAM_QCAP]),
-                                __uint_as_float(qe[(QF_D + 2) * STREAM_QCAP]));
-#pragma unroll
-            for (int f = 0; f < 6; ++f) inflight[(IF_W + f) * 32] = qe[(QF_W + f) * STREAM_QCAP];
-            any = (qe[QF_DK * STREAM_QCAP] & 1u) != 0u;
-            r = make_ray_ctx(ro, rd, SPRAY_RAY_EPS);
-            busy = true;
-          }
-          if (take) {
-            src.reset(true);             // the new ray starts at the top-level root (other lanes keep their walk)
-            T.begin(true);
-          }
-          count -= nf;
-        }
-        continue;
+    // lane state: running (has a node or a triangle to test), waiting (needs its next domain from the top-level
+    // BVH: done in the service pass, all waiting lanes together), finished (ray done, to be shaded), empty
+    int w = T.want();
+    const bool running = w == LaneTrav::WANT_NODE || w == LaneTrav::WANT_TRI;
+    const bool waiting = w == LaneTrav::WANT_SOURCE;
+    const bool fin = busy && !T.alive;
+    const uint32_t rm = __ballot_sync(0xffffffffu, running);
+    const bool pending = __any_sync(0xffffffffu, waiting || fin) || count > 0 || more;
+    if (rm == 0u && !pending) break;   // nothing in flight, nothing queued, tile exhausted
+    if (pending && (rm == 0u || 32 - __popc(rm) >= SPRAY_FETCH_THRESH)) {
+      // ================= service pass =================
+      const vec3 Lin = mk3(__uint_as_float(inflight[(IF_W + 0) * 32]), __uint_as_float(inflight[(IF_W + 1) * 32]),
+                           __uint_as_float(inflight[(IF_W + 2) * 32]));
+      const uint32_t pixid = inflight[IF_PIX * 32], samid = inflight[IF_SAM * 32], dk = inflight[IF_DK * 32];
+      // ---- A. retire shadow rays, shade radiance hits (ooc_shader_pt.h:94-227)
+      if (fin && any && !T.found) fb_add(P.fb, pixid, scale, Lin);
+      const bool hit = fin && !any && T.out.t < INFINITY;
+      const int next_depth = (int)(dk >> 1) + 1;
+      HitCtx c;
+      c.pos = r.o; c.kd = mk3(0, 0, 0); c.nff = mk3(0, 0, 1); c.wo = gneg(r.d);
+      c.cos_theta_i = 0.f; c.entering = false; c.mtl = SPRAYGPU_MTL_DIFFUSE; c.eta0 = c.eta1 = 1.f;
+      bool em1 = false, em2 = false, emit = false;
+      vec3 d1 = mk3(0, 0, 1), w1 = mk3(0, 0, 0), d2 = mk3(0, 0, 1), w2 = mk3(0, 0, 0), wi = mk3(0, 0, 1), Lr = mk3(0, 0, 0);
+      if (hit) {
+        ++n_hit;
+        make_hit_ctx<false>(P.table + T.out.dom, r.o, r.d, T.out.t, T.out.u, T.out.v, T.out.prim, c);
+        if (next_depth < P.shade.bounces) shade_secondary<false>(c, Lin, samid, next_depth, &em1, &d1, &w1, &em2, &d2, &w2);
+        uint32_t ls = rng_init1(samid * (uint32_t)next_depth);  // ShaderPt light_sampler (ooc_shader_pt.h:129-130)
+        int l = 0, k = 0; bool more_lights = true;
+        emit = shade_light_pass<false>(P.shade, true, 1, c, Lin, pixid, l, k, ls, &wi, &Lr, &more_lights);
       }
-      if (am == 0u) break;   // nothing in flight, nothing queued, tile exhausted
+      if (fin) busy = false;
+      // ---- B. push: bounce rays first, shadow rays on top (popped first)
+      if (em1) ++n_rad;
+      if (__any_sync(0xffffffffu, em1))
+        queue_push(Q, D, count, em1, c.pos, d1, w1, pixid, samid, (uint32_t)next_depth << 1);
+      if (emit) ++n_shadow;
+      if (__any_sync(0xffffffffu, emit)) {
+        // a shadow ray that enters no resident domain is unoccluded
+        if (queue_push(Q, D, count, emit, c.pos, wi, Lr, pixid, samid, 1u)) fb_add(P.fb, pixid, scale, Lr);
+      }
+      // ---- C. top up with one 8x4 pixel block of eye rays (ooc_tracer.inl:84-172)
+      if (count < 32 && more) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(P.counters, 32ull);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= P.total_slots) more = false;
+        else {
+          const uint32_t slot = (uint32_t)base + lane;
+          const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
+          const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
+          const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
+          const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
+          const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
+          uint32_t esam = 0, epix = 0;
+          vec3 dir = mk3(0.f, 0.f, 1.f);
+          if (has_ray) {
+            eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &esam, &epix, &dir);
+            ++n_eye; ++n_rad;
+          }
+          queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), epix,
+                     esam, 0u);
+        }
+      }
+      // ---- D. empty lanes pop new rays (top of the queue first)
+      {
+        const bool idle = !busy;
+        const uint32_t im = __ballot_sync(0xffffffffu, idle);
+        const int nf = min(__popc(im), count);
+        const int rnk = __popc(im & ((1u << lane) - 1u));
+        const bool take = idle && rnk < nf;
+        if (take) {
+          const uint32_t* qe = Q.q + (count - 1 - rnk);
+          const vec3 ro = mk3(__uint_as_float(qe[(QF_O + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_O + 1) * STREAM_QCAP]),
+                              __uint_as_float(qe[(QF_O + 2) * STREAM_QCAP]));
+          const vec3 rd = mk3(__uint_as_float(qe[(QF_D + 0) * STREAM_QCAP]), __uint_as_float(qe[(QF_D + 1) * STREAM_QCAP]),
+                              __uint_as_float(qe[(QF_D + 2) * STREAM_QCAP]));
+#pragma unroll
+          for (int f = 0; f < 6; ++f) inflight[(IF_W + f) * 32] = qe[(QF_W + f) * STREAM_QCAP];
+          any = (qe[QF_DK * STREAM_QCAP] & 1u) != 0u;
+          r = make_ray_ctx(ro, rd, SPRAY_RAY_EPS);
+          busy = true;
+          src.reset(true);             // the new ray starts at the top-level root (other lanes keep their walk)
+          T.begin(true);
+        }
+        count -= nf;
+      }
+      __syncwarp();
+      // ---- E. top-level BVH steps for every lane that needs its next domain (old and new), together
+      w = T.want();
+      if (w == LaneTrav::WANT_SOURCE) { T.source_step<COUNT>(src, r, cnt); w = T.want(); }
+      __syncwarp();
     }
-    T.pass<COUNT>(src, r, any, cnt);
+    // ================= traversal pass: one node step + one triangle step per lane =================
+    if (w == LaneTrav::WANT_NODE) T.node_step<COUNT>(r, cnt);
+    __syncwarp();
+    if (T.alive && T.tgy) T.tri_step<COUNT>(r, any, cnt);
   }
 
   uint32_t vals[7] = {n_eye, n_rad, n_shadow, cnt[0], cnt[1], cnt[2], n_hit};
