@@ -27,6 +27,11 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE render launch (= one frame) from the committed ncu --set full
+# capture of this command (bench.py cannot run under ncu itself); refreshed with every profile round.
+NCU_TRAFFIC = {"c2": 18489856 + 1807104, "c3": 676312064 + 44970752}
+NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/r01j_{c2,c3}_render_tile_ncu_full_details.csv (one launch = one frame)"
+
 METRIC = "Mrays/s (primary+shadow, device-timed)"
 UNIT = "Mrays/s"
 
@@ -221,8 +226,7 @@ def main():
 
         def step_dev():
             fb_d.zero_()                                  # image_.clear(), spray_renderer.inl:363
-            for t in tiles:
-                dev.trace_tile(cam, sh, t, fb_d)
+            dev.trace_frame(cam, sh, tiles, fb_d)         # the frame's blocking tiles in one persistent launch
 
         def step_e2e():
             # the public C-ABI call with a pinned HOST frame buffer: camera/shade/tile descriptors go H2D as
@@ -311,11 +315,13 @@ def main():
             nrays = rays
             # algorithmic bytes: per ray 16 B frame-buffer + 80 B/node + 48 B/triangle (+48 B attribute record per hit)
             bytes_frame = 16 * W * H + 80 * nn + 48 * nt + 48 * nh
-            per_launch = bytes_frame / len(tiles)
-            dur_s = ms_dev * 1e-3 / len(tiles)
+            nl = max(int(launches) // max(args.steps, 1), 1)        # render launches per frame (1: spraygpu_trace_frame)
+            per_launch = bytes_frame / nl
+            dur_s = ms_dev * 1e-3 / nl
             achieved = per_launch / dur_s / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "render_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                                "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(args.workload), "peak_source": peak_src,
+                                "traffic_source": NCU_TRAFFIC_SOURCE if args.workload in NCU_TRAFFIC else None,
                                 "algorithmic_bytes_per_launch": per_launch, "launch_ms": dur_s * 1e3,
                                 "nodes_per_ray": nn / nrays, "tris_per_ray": nt / nrays, "bytes_per_ray": bytes_frame / nrays,
                                 "domain_tests_per_ray": stats_tot["domain_tests"] / nrays}

@@ -92,6 +92,14 @@ class GpuTracer {
       for (std::size_t id = 0; id < scene_->getNumDomains(); ++id)
         if (!scene_->isResident((int)id)) scene_->load((int)id);
     SPRAY_CHECK(cudaMemsetAsync(d_fb_, 0, npixels_ * 16, 0) == cudaSuccess, "");  // image_.clear() on the device
+    if (!out_of_core_ && !(insitu_ && num_ranks_ > 1)) {
+      // resident scene: the whole tile loop in one persistent launch
+      std::vector<spraygpu_tile> gts;
+      for (const Tile& t : tile_list_.tiles()) gts.push_back(spraygpu_tile{t.x, t.y, t.w, t.h});
+      SPRAY_GPU_CALL(spraygpu_trace_frame(dev_, &cam, &shade_, gts.data(), (int)gts.size(), d_fb_, nullptr));
+      if (num_ranks_ == 1) download();
+      return;
+    }
     for (const Tile& t : tile_list_.tiles()) {
       const spraygpu_tile gt = {t.x, t.y, t.w, t.h};
       if (out_of_core_)

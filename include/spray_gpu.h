@@ -191,6 +191,13 @@ SPRAYGPU_API int spraygpu_trace_tile_async(spraygpu_device dev, const spraygpu_c
 SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                 spraygpu_tile tile, float* fb_rgba, spraygpu_stats* stats);
 
+/* A whole frame = ooc::Tracer::trace's loop over the blocking tiles (ooc_tracer.inl:184-234) in ONE persistent
+ * launch (per 32 tiles): the tiles' sample slots are concatenated, so there is one ramp-up / tail per frame instead of
+ * one per tile; samid stays the index within its tile.  Same result as calling spraygpu_trace_tile per tile.
+ * With a host fb it falls back to per-tile launches whose D2H copies overlap the next tile (and synchronises). [h|d] */
+SPRAYGPU_API int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                      const spraygpu_tile* tiles, int ntiles, float* fb_rgba, spraygpu_stats* stats);
+
 /* ---- out-of-core: the device cache holds fewer domains than the tile enters.
  * Replaces ooc::PContext::isectPrims' domain loop (src/ooc/ooc_pcontext.h:92-181): per round, schedule the
  * domains by queued rays (DomainStats::schedule, src/ooc/ooc_domain_stats.cc:60-111), `scene->load(id)` each one

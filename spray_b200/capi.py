@@ -106,6 +106,7 @@ _PROTOS = {
     "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_async": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp]),
+    "spraygpu_trace_frame": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), _vp, C.c_int, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_ooc": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.c_int, _vp, _vp, C.POINTER(Stats)]),
     # multi-GPU (NCCL resolved at run time)
     "spraygpu_comm_unique_id": (C.c_int, [C.c_char_p]),
@@ -284,6 +285,14 @@ class Device:
         _check(fn(self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb), C.byref(st) if st is not None else None))
         return st
 
+
+    def trace_frame(self, cam, shade, tiles, fb, stats=False):
+        """Every blocking tile of a frame in one persistent launch (device fb) / overlapped per-tile copies (host fb)."""
+        st = Stats() if stats else None
+        arr = (Tile * len(tiles))(*[Tile(*t) for t in tiles])
+        _check(lib().spraygpu_trace_frame(self.h, C.byref(cam), C.byref(shade), C.cast(arr, _vp), len(tiles), _ptr(fb),
+                                          C.byref(st) if st is not None else None))
+        return st
 
     def trace_tile_ooc(self, cam, shade, tile, fb, max_resident, load, stats=False):
         """Out-of-core tile: `load(domain_id) -> 0` makes a domain resident (Scene::load)."""

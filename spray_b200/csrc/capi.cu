@@ -617,4 +617,54 @@ int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam,
   return trace_tile_impl(dev, cam, shade, tile, fb, stats, true, false);
 }
 
+int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                         const spraygpu_tile* tiles, int ntiles, float* fb, spraygpu_stats* stats) {
+  SG_CHECK(dev && cam && shade && fb && (tiles || ntiles == 0) && ntiles >= 0, SPRAYGPU_ERR_ARG, "trace_frame: bad argument");
+  Device* d = DEV(dev);
+  if (!is_device_ptr(fb)) {
+    // host frame buffer: per-tile launches so that tile k's D2H overlaps tile k+1's kernel
+    spraygpu_stats tot = {0, 0, 0, 0, 0, 0, 0}, st;
+    for (int t = 0; t < ntiles; ++t) {
+      const int rc = trace_tile_impl(dev, cam, shade, tiles[t], fb, stats ? &st : nullptr, false, true);
+      if (rc) return rc;
+      if (stats) {
+        tot.eye_rays += st.eye_rays; tot.radiance_rays += st.radiance_rays; tot.shadow_rays += st.shadow_rays;
+        tot.domain_tests += st.domain_tests; tot.hits += st.hits;
+      }
+    }
+    SG_CUDA(cudaStreamSynchronize(d->copy_stream));
+    if (stats) *stats = tot;
+    return SPRAYGPU_OK;
+  }
+  SG_CHECK(shade->pixel_samples >= 1 && shade->bounces >= 1, SPRAYGPU_ERR_ARG, "trace_frame: pixel_samples and bounces must be >= 1");
+  SG_CHECK(shade->nlights >= 0 && shade->nlights <= SPRAYGPU_MAX_LIGHTS, SPRAYGPU_ERR_LIMIT, "trace_frame: %d lights (limit %d)",
+           shade->nlights, SPRAYGPU_MAX_LIGHTS);
+  SG_CHECK(shade->shader == SPRAYGPU_SHADER_AO || shade->nlights > 0, SPRAYGPU_ERR_ARG,
+           "trace_frame: the PT shader needs at least one light (ooc_tracer.inl:68)");
+  SG_CHECK(shade->shader == SPRAYGPU_SHADER_PT || shade->ao_samples > 0, SPRAYGPU_ERR_ARG, "trace_frame: ao_samples must be > 0");
+  for (int t = 0; t < ntiles; ++t)
+    SG_CHECK(tiles[t].x >= 0 && tiles[t].y >= 0 && tiles[t].w >= 0 && tiles[t].h >= 0 && tiles[t].x + tiles[t].w <= cam->image_w &&
+                 tiles[t].y + tiles[t].h <= cam->image_h,
+             SPRAYGPU_ERR_ARG, "trace_frame: tile %d (%d,%d,%d,%d) outside the %dx%d image", t, tiles[t].x, tiles[t].y, tiles[t].w,
+             tiles[t].h, cam->image_w, cam->image_h);
+  SG_CUDA(cudaSetDevice(d->cuda_device));
+  int rc = upload_domain_table(d);
+  if (rc) return rc;
+  const int per = 32;   // SPRAY_MAX_FRAME_TILES
+  for (int t0 = 0; t0 < ntiles || t0 == 0; t0 += per) {
+    const int nt = ntiles - t0 < per ? ntiles - t0 : per;
+    rc = launch_render_tiles(d, cam, shade, tiles + t0, nt, fb, false, t0 == 0);
+    if (rc) return rc;
+    if (ntiles == 0) break;
+  }
+  if (stats) {
+    unsigned long long* h = (unsigned long long*)d->pinned;
+    SG_CUDA(cudaMemcpyAsync(h, d->d_counters, sizeof(unsigned long long) * 8, cudaMemcpyDeviceToHost, d->stream));
+    SG_CUDA(cudaStreamSynchronize(d->stream));
+    stats->eye_rays = h[1]; stats->radiance_rays = h[2]; stats->shadow_rays = h[3]; stats->domain_tests = h[4];
+    stats->nodes_visited = h[5]; stats->tris_tested = h[6]; stats->hits = h[7];
+  }
+  return SPRAYGPU_OK;
+}
+
 }  // extern "C"

@@ -132,5 +132,7 @@ int launch_hit_attributes(Device* dev, const spraygpu_ray* rays, const uint64_t*
 int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, spraygpu_ray* rays);
 int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                        float* fb, bool counted);
+int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, const spraygpu_tile* tiles,
+                        int ntiles, float* fb, bool counted, bool reset_counters);
 
 }  // namespace spraygpu

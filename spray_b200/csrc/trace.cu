@@ -194,19 +194,33 @@ __global__ void __launch_bounds__(256)
 // Reference: ooc::Tracer::trace tile body (ooc_tracer.inl:184-234), TContext::procRads/procShads/retire
 // (ooc_tcontext.inl:29-135), ShaderPt / ShaderAo (ooc_shader_pt.h:94-227, ooc_shader_ao.h:92-197).
 // ------------------------------------------------------------------------------------------------
+#define SPRAY_MAX_FRAME_TILES 32
 struct RenderParams {
   const DomainEntry* table;
   int nd;
   const TlasNode* tlas;
   int tlas_n;
   CameraDev cam;
-  spraygpu_tile tile;
   spraygpu_shade shade;
   float* fb;                     // image_w * image_h * 4
   unsigned long long* counters;  // [0] work counter; [1..7] stats
-  uint32_t total_slots;          // 32 * pixel blocks * spp
-  uint32_t blocks_per_row;
+  // One launch walks up to SPRAY_MAX_FRAME_TILES blocking tiles (a whole frame of the reference's tile loop,
+  // ooc_tracer.inl:184-234): the sample slots of the tiles are concatenated, every tile's share is a multiple of
+  // 32, so a warp's 32 slots never straddle tiles and samid stays the index WITHIN the tile.
+  int ntiles;
+  spraygpu_tile tiles[SPRAY_MAX_FRAME_TILES];
+  uint32_t slot_end[SPRAY_MAX_FRAME_TILES];        // exclusive prefix end of tile t's slots (32 * pixel blocks * spp)
+  uint32_t blocks_per_row[SPRAY_MAX_FRAME_TILES];
+  uint32_t total_slots;
 };
+
+// slot base (multiple of 32) -> its tile, the slot index inside the tile
+__device__ __forceinline__ int tile_of_slot(const RenderParams& P, uint32_t base, uint32_t* local) {
+  int t = 0;
+  while (t + 1 < P.ntiles && base >= P.slot_end[t]) ++t;
+  *local = base - (t ? P.slot_end[t - 1] : 0u);
+  return t;
+}
 
 struct Pending { vec3 o, d, w; int depth; };
 
@@ -299,16 +313,20 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
       if (lane == 0) base = atomicAdd(P.counters, 32ull);
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= P.total_slots) { more = false; continue; }
-      const uint32_t slot = (uint32_t)base + lane;
+      uint32_t local;
+      const int ti = tile_of_slot(P, (uint32_t)base, &local);
+      const spraygpu_tile tile = P.tiles[ti];
+      const uint32_t bpr = P.blocks_per_row[ti];
+      const uint32_t slot = local + lane;
       const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
       const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-      const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
-      const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
-      const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
+      const uint32_t x0 = (blk % bpr) * 8u + (within & 7u);
+      const uint32_t y0 = (blk / bpr) * 4u + (within >> 3);
+      const bool has_ray = x0 < (uint32_t)tile.w && y0 < (uint32_t)tile.h;
       uint32_t samid = 0, pixid = 0;
       vec3 dir = mk3(0.f, 0.f, 1.f);
       if (has_ray) {
-        eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &samid, &pixid, &dir);
+        eye_sample(P.cam, tile, spp, x0, y0, sidx, &samid, &pixid, &dir);
         ++n_eye; ++n_rad;
       }
       queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), pixid,
@@ -503,16 +521,20 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= P.total_slots) more = false;
         else {
-          const uint32_t slot = (uint32_t)base + lane;
+          uint32_t local;
+          const int ti = tile_of_slot(P, (uint32_t)base, &local);
+          const spraygpu_tile tile = P.tiles[ti];
+          const uint32_t bpr = P.blocks_per_row[ti];
+          const uint32_t slot = local + lane;
           const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
           const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-          const uint32_t x0 = (blk % P.blocks_per_row) * 8u + (within & 7u);
-          const uint32_t y0 = (blk / P.blocks_per_row) * 4u + (within >> 3);
-          const bool has_ray = slot < P.total_slots && x0 < (uint32_t)P.tile.w && y0 < (uint32_t)P.tile.h;
+          const uint32_t x0 = (blk % bpr) * 8u + (within & 7u);
+          const uint32_t y0 = (blk / bpr) * 4u + (within >> 3);
+          const bool has_ray = x0 < (uint32_t)tile.w && y0 < (uint32_t)tile.h;
           uint32_t esam = 0, epix = 0;
           vec3 dir = mk3(0.f, 0.f, 1.f);
           if (has_ray) {
-            eye_sample(P.cam, P.tile, spp, x0, y0, sidx, &esam, &epix, &dir);
+            eye_sample(P.cam, tile, spp, x0, y0, sidx, &esam, &epix, &dir);
             ++n_eye; ++n_rad;
           }
           queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), epix,
@@ -635,16 +657,35 @@ int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile,
 
 int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                        float* fb, bool counted) {
+  return launch_render_tiles(dev, cam, shade, &tile, 1, fb, counted, true);
+}
+
+// up to SPRAY_MAX_FRAME_TILES tiles in ONE persistent launch; reset_counters = false keeps accumulating the
+// statistics of a frame that needs several launches
+int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, const spraygpu_tile* tiles,
+                        int ntiles, float* fb, bool counted, bool reset_counters) {
+  SG_CHECK(ntiles >= 0 && ntiles <= SPRAY_MAX_FRAME_TILES, SPRAYGPU_ERR_LIMIT, "%d tiles in one launch (max %d)", ntiles, SPRAY_MAX_FRAME_TILES);
   RenderParams P;
   P.table = dev->d_domains; P.nd = dev->ndomains; P.tlas = dev->d_tlas; P.tlas_n = dev->tlas_n;
-  P.cam = to_camdev(cam); P.tile = tile; P.shade = *shade; P.fb = fb;
+  P.cam = to_camdev(cam); P.shade = *shade; P.fb = fb;
   P.counters = dev->d_counters;
-  P.blocks_per_row = (uint32_t)((tile.w + 7) / 8);
-  const uint64_t slots = (uint64_t)P.blocks_per_row * (uint64_t)((tile.h + 3) / 4) * 32ull * (uint64_t)shade->pixel_samples;
-  SG_CHECK(slots < 0xFFFFFFFFull, SPRAYGPU_ERR_LIMIT, "tile too large: %llu sample slots", (unsigned long long)slots);
+  uint64_t slots = 0;
+  P.ntiles = 0;
+  for (int t = 0; t < ntiles; ++t) {
+    const spraygpu_tile tile = tiles[t];
+    const uint32_t bpr = (uint32_t)((tile.w + 7) / 8);
+    const uint64_t ts = (uint64_t)bpr * (uint64_t)((tile.h + 3) / 4) * 32ull * (uint64_t)shade->pixel_samples;
+    if (!ts) continue;
+    slots += ts;
+    SG_CHECK(slots < 0xFFFFFFFFull, SPRAYGPU_ERR_LIMIT, "tiles too large: %llu sample slots", (unsigned long long)slots);
+    P.tiles[P.ntiles] = tile; P.blocks_per_row[P.ntiles] = bpr; P.slot_end[P.ntiles] = (uint32_t)slots;
+    ++P.ntiles;
+  }
+  for (int t = P.ntiles; t < SPRAY_MAX_FRAME_TILES; ++t) { P.tiles[t] = spraygpu_tile{0, 0, 0, 0}; P.blocks_per_row[t] = 1; P.slot_end[t] = (uint32_t)slots; }
   P.total_slots = (uint32_t)slots;
+  if (reset_counters) SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long) * 8, dev->stream));
+  else SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long), dev->stream));   // the work counter only
   if (!slots) return SPRAYGPU_OK;
-  SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long) * 8, dev->stream));
   // lean variant: PT shader, ONE point light, all domains diffuse
   bool general = shade->shader != SPRAYGPU_SHADER_PT || shade->nlights != 1;
   for (int i = 0; i < shade->nlights; ++i) general = general || shade->lights[i].type != SPRAYGPU_LIGHT_POINT;

@@ -403,3 +403,45 @@ def test_trace_tile_async_host_frame_buffer(oracle, dev_c2, c2):
         assert np.abs(fbn[..., :3] - ref[..., :3]).max() <= 1e-6
         assert (fbn[..., 3] == 0).all()
     assert ref[..., :3].max() > 0.1
+
+
+@pytest.mark.parametrize("kw", [dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=1), dict(bounces=2, pixel_samples=3)])
+def test_trace_frame_equals_tile_loop(oracle, dev_c2, c2, kw):
+    """spraygpu_trace_frame (all blocking tiles in one persistent launch) == the per-tile loop: same counters, same
+    image bit for bit at 1 spp (one atomic add per pixel and depth), RMSE <= 1e-4 vs the oracle otherwise; ragged
+    tile sizes, > 32 tiles (several launches), host frame buffer and the empty frame included."""
+    import torch
+    sc, osc = c2
+    p = scenes.WAVELETS64_CAMERA
+    W, H = 200, 150
+    cd = scenes.camera_frame(p["pos"], p["lookat"], p["up"], p["vfov"], W, H)
+    cam_g = capi.make_camera(cd)
+    kw = dict(kw, **scenes.WAVELETS64_BLINN)
+    spp = kw["pixel_samples"]
+    sh = capi.make_shade(lights=sc["lights"], **kw)
+    for cap in (1 << 12, 700):                       # 8 tiles ; 43+ tiles of 3 rows (ragged last one)
+        tiles = scenes.image_schedule_tiles(W, H, spp, 1, 0, cap)
+        assert (len(tiles) > 32) == (cap == 700)
+        fb1 = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        tot = {}
+        for t in tiles:
+            st = dev_c2.trace_tile(cam_g, sh, t, fb1, stats=True)
+            for k, v in st.as_dict().items():
+                tot[k] = tot.get(k, 0) + v
+        fb2 = torch.zeros_like(fb1)
+        st2 = dev_c2.trace_frame(cam_g, sh, tiles, fb2, stats=True).as_dict()
+        dev_c2.synchronize()
+        for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"):
+            assert st2[k] == tot[k], k
+        if spp == 1 and kw["bounces"] == 1:
+            assert torch.equal(fb1, fb2)
+        sh_o, keep = oracle.make_shade(lights=sc["lights"], **kw)
+        fb_o, st_o = osc.render(oracle.camera_from_desc(cd), sh_o, tiles)
+        assert st2["radiance_rays"] == st_o.radiance_rays and st2["shadow_rays"] == st_o.shadow_rays
+        assert _rmse(fb2.cpu().numpy(), fb_o) <= RMSE_TOL
+        fbh = np.zeros((H, W, 4), np.float32)
+        dev_c2.trace_frame(cam_g, sh, tiles, fbh)     # host frame buffer path
+        assert _rmse(fbh, fb_o) <= RMSE_TOL
+    fb3 = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    st3 = dev_c2.trace_frame(cam_g, sh, [], fb3, stats=True).as_dict()
+    assert st3["eye_rays"] == 0 and not fb3.any()
