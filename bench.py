@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """bench.py — headline benchmark of the per-domain ray-tracing hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5]
 
 A step = one frame of the hot path on the named workload: every blocking tile of the image goes through
 spraygpu_trace_tile (eye rays -> domain culling -> per-domain BVH8 closest hit -> shading -> shadow rays
@@ -60,6 +60,16 @@ def workload(name):
         cd = scenes.camera_frame((95.0, 90.0, 85.0), (40.0, 40.0, 40.0), (0, 1, 0), 90.0, W, H)
         shade = dict(shader=0, bounces=3, pixel_samples=1, ao_samples=1, **scenes.WAVELETS64_BLINN)
         label = "C3: synthetic 64-domain triangle soup, %d tris/domain, 2048x2048, bounces 3 + shadow rays" % tris
+    elif name == "c5":
+        # in-situ configuration: 8 wavelet domains per GPU (8 / 16 / 32 / 64 domains at 1 / 2 / 4 / 8 GPUs), 4096^2 x 4 spp
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        nd = min(8 * world, 64)
+        sc = scenes.wavelets64(nd)
+        W = H = int(os.environ.get("SPRAY_C5_SIZE", "4096"))
+        pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+        cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+        shade = dict(shader=0, bounces=1, pixel_samples=4, ao_samples=1, **scenes.WAVELETS64_BLINN)
+        label = "C5: in situ, %d wavelet domains (8 per GPU), %dx%d, 4 spp" % (nd, W, H)
     else:
         raise SystemExit("unknown workload " + name)
     return sc, cd, shade, label, W, H
@@ -202,6 +212,8 @@ def main():
         from spray_b200 import multigpu
         comm = multigpu.bootstrap_comm(dev, rank, world)
         mode = "image" if args.partition == "both" else args.partition
+        if args.workload == "c5" and "SPRAY_PARTITION" not in os.environ and "--partition" not in sys.argv:
+            mode = "insitu"                               # C5 is the reference's in-situ configuration
         Renderer = multigpu.ImagePartitionRenderer if mode == "image" else multigpu.InsituRenderer
         mg = Renderer(dev, sc, cam, sh, W, H, rank, world, comm)
         step_dev = mg.frame_device

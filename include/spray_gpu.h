@@ -253,6 +253,11 @@ SPRAYGPU_API int spraygpu_image_reduce(spraygpu_device dev, spraygpu_comm comm, 
  * root receives every band in place (ncclSend/ncclRecv group) — 1/nranks of the reduce's traffic. */
 SPRAYGPU_API int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, int image_w,
                                             const int32_t* row_begin /* nranks + 1 */, int root);
+/* The same for INTERLEAVED row blocks (block b = rows [block_row_begin[b], block_row_begin[b+1]) rendered by rank
+ * block_owner[b]): image-space load balancing — a contiguous band per rank leaves the ranks that own sky idle. */
+SPRAYGPU_API int spraygpu_image_gather_blocks(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, int image_w, int nblocks,
+                                              const int32_t* block_row_begin /* nblocks + 1 */,
+                                              const int32_t* block_owner /* nblocks */, int root);
 /* ncclAllReduce(ncclUint64, ncclMin) on hit keys / ncclAllReduce(ncclUint8, ncclMax) on occlusion bytes,
  * in place on device buffers: the building blocks for callers that drive spraygpu_intersect_domains /
  * spraygpu_occluded_domains themselves. */

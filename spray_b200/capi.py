@@ -116,6 +116,7 @@ _PROTOS = {
     "spraygpu_trace_tile_insitu": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_image_reduce": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
     "spraygpu_image_gather_rows": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int]),
+    "spraygpu_image_gather_blocks": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, _vp, _vp, C.c_int]),
     "spraygpu_allreduce_keys_min": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "spraygpu_allreduce_occ_max": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
 }
@@ -403,6 +404,13 @@ class Comm:
         rb = np.ascontiguousarray(row_begin, np.int32)
         assert len(rb) == self.nranks + 1
         _check(lib().spraygpu_image_gather_rows(self.dev.h, self.h, _ptr(fb), int(image_w), rb.ctypes.data, int(root)))
+
+    def image_gather_blocks(self, fb, image_w, block_row_begin, block_owner, root=0):
+        rb = np.ascontiguousarray(block_row_begin, np.int32)
+        ow = np.ascontiguousarray(block_owner, np.int32)
+        assert len(rb) == len(ow) + 1
+        _check(lib().spraygpu_image_gather_blocks(self.dev.h, self.h, _ptr(fb), int(image_w), len(ow), rb.ctypes.data,
+                                                  ow.ctypes.data, int(root)))
 
     def allreduce_keys_min(self, keys, n):
         _check(lib().spraygpu_allreduce_keys_min(self.dev.h, self.h, _ptr(keys), int(n)))

@@ -218,6 +218,29 @@ int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm comm, float* f
   return SPRAYGPU_OK;
 }
 
+int spraygpu_image_gather_blocks(spraygpu_device dev, spraygpu_comm comm, float* fb, int image_w, int nblocks,
+                                 const int32_t* block_row_begin, const int32_t* block_owner, int root) {
+  SG_CHECK(dev && comm && fb && block_row_begin && block_owner && image_w > 0 && nblocks >= 0, SPRAYGPU_ERR_ARG,
+           "image_gather_blocks: bad argument");
+  Comm* c = (Comm*)comm;
+  SG_CHECK(root >= 0 && root < c->nranks, SPRAYGPU_ERR_ARG, "image_gather_blocks: bad root %d", root);
+  if (c->nranks == 1) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  const size_t row_floats = (size_t)image_w * 4;
+  SG_NCCL(g_nccl.GroupStart());
+  for (int b = 0; b < nblocks; ++b) {
+    const int owner = block_owner[b];
+    SG_CHECK(owner >= 0 && owner < c->nranks, SPRAYGPU_ERR_ARG, "image_gather_blocks: block %d owner %d", b, owner);
+    const size_t n = (size_t)(block_row_begin[b + 1] - block_row_begin[b]) * row_floats;
+    if (!n || owner == root) continue;
+    float* p = fb + (size_t)block_row_begin[b] * row_floats;
+    if (c->rank == root) SG_NCCL(g_nccl.Recv(p, n, ncclFloat32, owner, c->comm, c->dev->stream));
+    else if (c->rank == owner) SG_NCCL(g_nccl.Send(p, n, ncclFloat32, root, c->comm, c->dev->stream));
+  }
+  SG_NCCL(g_nccl.GroupEnd());
+  return SPRAYGPU_OK;
+}
+
 int spraygpu_allreduce_keys_min(spraygpu_device dev, spraygpu_comm comm, spraygpu_key* keys, size_t n) {
   SG_CHECK(dev && comm && (keys || !n), SPRAYGPU_ERR_ARG, "allreduce_keys_min: NULL argument");
   SG_CUDA(cudaSetDevice(((Comm*)comm)->dev->cuda_device));

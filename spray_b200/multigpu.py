@@ -38,6 +38,19 @@ def band_tiles(image_w, band, spp, max_samples=1024 * 1024):
     return [(0, y, image_w, min(rows, y1 - y)) for y in range(y0, y1, rows)]
 
 
+def interleaved_blocks(image_h, nranks, max_tiles_per_rank=32):
+    """Optional image-space load balancing (ImagePartitionRenderer(interleave=True)); measured on 2 B200s it LOST to
+    contiguous bands (C2 5811 vs 9127 Mrays/s, C3 1646 vs 1681: many small sends + whole-image clear), so bands
+    stay the default.  The image is cut into row blocks dealt round-robin to the ranks (block b -> rank
+    b % nranks).  Block height = the smallest multiple of 4 (the kernel's 8x4 pixel blocks) that keeps a rank's
+    share within one persistent launch (<= max_tiles_per_rank tiles).  Returns (row_begin[nb + 1], owner[nb])."""
+    rows = -(-int(image_h) // (max_tiles_per_rank * int(nranks)))
+    rows = max(4, (rows + 3) // 4 * 4)
+    begin = list(range(0, int(image_h), rows)) + [int(image_h)]
+    owner = [b % int(nranks) for b in range(len(begin) - 1)]
+    return np.asarray(begin, np.int32), np.asarray(owner, np.int32)
+
+
 def bootstrap_comm(dev, rank, world):
     """Create the library's NCCL communicator; the unique id travels over torch.distributed."""
     import torch.distributed as dist
@@ -47,20 +60,33 @@ def bootstrap_comm(dev, rank, world):
 
 
 class ImagePartitionRenderer:
-    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm):
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, interleave=False):
         import torch
         self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
         dev.load_scene(scene)
+        self.interleave = interleave
         self.bands = row_bands(H, world)
-        self.tiles = band_tiles(W, self.bands[rank:rank + 2], shade.pixel_samples)
+        if interleave:
+            self.block_begin, self.block_owner = interleaved_blocks(H, world)
+            self.tiles = []
+            for b in range(len(self.block_owner)):
+                if self.block_owner[b] == rank:
+                    self.tiles += band_tiles(W, self.block_begin[b:b + 2], shade.pixel_samples)
+        else:
+            self.tiles = band_tiles(W, self.bands[rank:rank + 2], shade.pixel_samples)
         self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
         self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
 
     def frame_device(self):
+        if self.interleave:
+            self.fb.zero_()                                      # image_.clear()
+            for t0 in range(0, len(self.tiles), 32):             # this rank's row blocks, 32 per persistent launch
+                self.dev.trace_frame(self.cam, self.shade, self.tiles[t0:t0 + 32], self.fb)
+            self.comm.image_gather_blocks(self.fb, self.W, self.block_begin, self.block_owner, 0)
+            return
         y0, y1 = int(self.bands[self.rank]), int(self.bands[self.rank + 1])
         self.fb[y0:y1].zero_()                                   # image_.clear() on the rows this rank renders
-        for t in self.tiles:
-            self.dev.trace_tile(self.cam, self.shade, t, self.fb)
+        self.dev.trace_frame(self.cam, self.shade, self.tiles, self.fb)   # this rank's band in one persistent launch
         self.comm.image_gather_rows(self.fb, self.W, self.bands, 0)
 
     def frame_host(self):

@@ -41,9 +41,15 @@ def main():
         # image partition: all domains everywhere, row bands, NCCL gather
         d2 = capi.Device(local, stream=stream)
         c2 = multigpu.bootstrap_comm(d2, rank, world)
-        r2 = multigpu.ImagePartitionRenderer(d2, sc, cam, sh, W, H, rank, world, c2)
+        r2 = multigpu.ImagePartitionRenderer(d2, sc, cam, sh, W, H, rank, world, c2, interleave=True)
         r2.frame_device(); d2.synchronize()
         img_image = r2.fb.cpu().numpy()
+        d3 = capi.Device(local, stream=stream)
+        c3 = multigpu.bootstrap_comm(d3, rank, world)
+        r3 = multigpu.ImagePartitionRenderer(d3, sc, cam, sh, W, H, rank, world, c3, interleave=False)
+        r3.frame_device(); d3.synchronize()
+        img_rows = r3.fb.cpu().numpy()
+        c3.close(); d3.close()
         # keys: local trace of the owned domains + min-all-reduce == the full single-device answer
         n = W * H
         rays = torch.zeros((n, 8), dtype=torch.float32, device="cuda")
@@ -67,15 +73,19 @@ def main():
             # sample ids (RNG seeds) are tile-relative, as in the reference (ooc_tracer.inl:84-172): compare each
             # decomposition with a single-GPU render over the SAME blocking tiles
             ref, tot = render(multigpu.band_tiles(W, (0, H), sh.pixel_samples))
+            bb, bo = r2.block_begin, r2.block_owner          # interleaved row blocks (load balancing)
+            ref_bands, _ = render([t for b in range(len(bo)) for t in multigpu.band_tiles(W, bb[b:b + 2], sh.pixel_samples)])
+            # contiguous bands + row gather (the non-interleaved variant)
             bands = multigpu.row_bands(H, world)
-            ref_bands, _ = render([t for r in range(world) for t in multigpu.band_tiles(W, bands[r:r + 2], sh.pixel_samples)])
+            ref_rows, _ = render([t for r in range(world) for t in multigpu.band_tiles(W, bands[r:r + 2], sh.pixel_samples)])
+            e3 = float(np.sqrt(np.mean((img_rows[..., :3].astype(np.float64) - ref_rows[..., :3]) ** 2)))
             e1 = float(np.sqrt(np.mean((img_insitu[..., :3].astype(np.float64) - ref[..., :3]) ** 2)))
             e2 = float(np.sqrt(np.mean((img_image[..., :3].astype(np.float64) - ref_bands[..., :3]) ** 2)))
             same_keys = bool(torch.equal(keys, keys_full))
             same_stats = all(st1[k] == tot[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))
             print("multigpu_check %s world=%d: insitu rmse %.3g | image-partition rmse %.3g | keys equal %s | stats equal %s (%s)"
                   % (kw, world, e1, e2, same_keys, same_stats, {k: st1[k] for k in ("radiance_rays", "shadow_rays", "hits")}))
-            ok = ok and e1 <= 1e-6 and e2 <= 1e-6 and same_keys and same_stats and ref[..., :3].max() > 0.1
+            ok = ok and e1 <= 1e-6 and e2 <= 1e-6 and e3 <= 1e-6 and same_keys and same_stats and ref[..., :3].max() > 0.1
         c1.close(); c2.close(); d1.close(); d2.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)
