@@ -303,6 +303,9 @@ __device__ __forceinline__ bool tlas_any(const DomSmem& D, const RayCtx& r) {
          tlas_box_hit(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, &t) || tlas_box_hit(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, &t);
 }
 
+#ifndef SPRAY_TRI_PER_PASS
+#define SPRAY_TRI_PER_PASS 8
+#endif
 // One lane's traversal state and its three step kinds.
 struct LaneTrav {
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
@@ -346,7 +349,15 @@ struct LaneTrav {
     __syncwarp();
     if (w == WANT_NODE) node_step<COUNT>(r, cnt);
     __syncwarp();
+#if SPRAY_TRI_PER_PASS <= 1
     if (alive && tgy) tri_step<COUNT>(r, any, cnt);
+#else
+    // a triangle test costs ~35 thread instructions, a node step ~450 (ncu r01j): let a lane work off several
+    // pending triangles per pass so that it is back in the node test sooner.  A/B on B200 (profiles/r01l_ab_tri_per_pass.txt):
+    // 1 -> 8 triangles per pass = C2 5862 -> 6776 Mrays/s, C3 928 -> 1041
+#pragma unroll 1
+    for (int k = 0; k < SPRAY_TRI_PER_PASS && alive && tgy; ++k) tri_step<COUNT>(r, any, cnt);
+#endif
   }
   // fetch + test one 80-byte node (only when no triangle is pending; ngy has an inner child here)
   template <bool COUNT>
