@@ -573,7 +573,8 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
     // ================= traversal pass: one node step + one triangle step per lane =================
     if (w == LaneTrav::WANT_NODE) T.node_step<COUNT>(r, cnt);
     __syncwarp();
-    if (T.alive && T.tgy) T.tri_step<COUNT>(r, any, cnt);
+#pragma unroll 1
+    for (int k = 0; k < SPRAY_TRI_PER_PASS && T.alive && T.tgy; ++k) T.tri_step<COUNT>(r, any, cnt);
   }
 
   uint32_t vals[7] = {n_eye, n_rad, n_shadow, cnt[0], cnt[1], cnt[2], n_hit};
