@@ -177,6 +177,8 @@ def main():
     sc, cd, shade, label, W, H = workload(args.workload)
 
     if args.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every host core (set before libgomp loads)
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
         # The reference's own CPU implementation cannot be built (Embree 2.x, MPI, IceT, OpenGL absent);
         # this arm times the oracle port on all host threads.  Rank 0 only.
         if rank != 0:
@@ -231,6 +233,9 @@ def main():
         scenes_by_id = dev.load_scene(sc)
         dev.synchronize()
         build_s = time.perf_counter() - t_build0
+        infos = [s_.info() for s_ in scenes_by_id.values()]
+        build_dev_ms = float(sum(i.build_ms for i in infos))          # CUDA-event time of every spraygpu_scene_commit
+        build_tris = int(sum(i.num_faces for i in infos))
         fb_d = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
         fb_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
         fb_h_np = fb_h.numpy()
@@ -338,6 +343,11 @@ def main():
                                 "nodes_per_ray": nn / nrays, "tris_per_ray": nt / nrays, "bytes_per_ray": bytes_frame / nrays,
                                 "domain_tests_per_ray": stats_tot["domain_tests"] / nrays}
             line["config"]["build_s_all_domains"] = build_s
+            # per-domain acceleration-structure build (= rtcCommit): device time of the commits alone; the wall-clock
+            # figure above also holds the H2D upload of the meshes from pageable host memory
+            line["build"] = {"triangles": build_tris, "device_ms": build_dev_ms,
+                             "mtris_per_s": build_tris / max(build_dev_ms, 1e-9) / 1e3,
+                             "algorithmic_gb_per_s": build_tris * 300.0 / max(build_dev_ms, 1e-9) / 1e6}
             if not args.no_cpu_baseline:
                 v, sec, crays, cores, tile = run_cpu(sc, cd, shade, W, H, 3, 1)
                 line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",

@@ -15,6 +15,8 @@ Two decompositions, as in the reference:
   (replaces insitu::VBuf::compositeTbuf, insitu_vbuf.h:109-117), occlusion by a max-all-reduce
   (compositeObuf, :119-129); partial images are summed on rank 0.
 """
+import os
+
 import numpy as np
 
 from . import capi, scenes
@@ -38,10 +40,10 @@ def band_tiles(image_w, band, spp, max_samples=1024 * 1024):
     return [(0, y, image_w, min(rows, y1 - y)) for y in range(y0, y1, rows)]
 
 
-def interleaved_blocks(image_h, nranks, max_tiles_per_rank=32):
-    """Optional image-space load balancing (ImagePartitionRenderer(interleave=True)); measured on 2 B200s it LOST to
-    contiguous bands (C2 5811 vs 9127 Mrays/s, C3 1646 vs 1681: many small sends + whole-image clear), so bands
-    stay the default.  The image is cut into row blocks dealt round-robin to the ranks (block b -> rank
+def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4):
+    """Image-space load balancing for the image partition (default from 4 GPUs up).  A fine cut (32 blocks per rank)
+    lost badly to contiguous bands (one NCCL send per block); 4 blocks per rank is the measured compromise.
+    The image is cut into row blocks dealt round-robin to the ranks (block b -> rank
     b % nranks).  Block height = the smallest multiple of 4 (the kernel's 8x4 pixel blocks) that keeps a rank's
     share within one persistent launch (<= max_tiles_per_rank tiles).  Returns (row_begin[nb + 1], owner[nb])."""
     rows = -(-int(image_h) // (max_tiles_per_rank * int(nranks)))
@@ -60,15 +62,21 @@ def bootstrap_comm(dev, rank, world):
 
 
 class ImagePartitionRenderer:
-    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, interleave=False):
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, interleave=None):
         import torch
         self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
         dev.load_scene(scene)
+        if interleave is None:
+            # measured (profiles/bench_r01q_*): contiguous bands win at 2 GPUs (C2 10401 vs 9475 Mrays/s), 4 interleaved
+            # blocks per rank win at 8 (C2 18343 vs 16645, C3 4279 vs 3654)
+            env = os.environ.get("SPRAY_INTERLEAVE")
+            interleave = (world >= 4) if env is None else env != "0"
         self.interleave = interleave
         self.bands = row_bands(H, world)
         if interleave:
             self.block_begin, self.block_owner = interleaved_blocks(H, world)
             self.tiles = []
+            self.my_blocks = [b for b in range(len(self.block_owner)) if self.block_owner[b] == rank]
             for b in range(len(self.block_owner)):
                 if self.block_owner[b] == rank:
                     self.tiles += band_tiles(W, self.block_begin[b:b + 2], shade.pixel_samples)
@@ -79,7 +87,8 @@ class ImagePartitionRenderer:
 
     def frame_device(self):
         if self.interleave:
-            self.fb.zero_()                                      # image_.clear()
+            for b in self.my_blocks:                             # image_.clear() on the rows this rank renders
+                self.fb[int(self.block_begin[b]):int(self.block_begin[b + 1])].zero_()
             for t0 in range(0, len(self.tiles), 32):             # this rank's row blocks, 32 per persistent launch
                 self.dev.trace_frame(self.cam, self.shade, self.tiles[t0:t0 + 32], self.fb)
             self.comm.image_gather_blocks(self.fb, self.W, self.block_begin, self.block_owner, 0)
