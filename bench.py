@@ -241,9 +241,15 @@ def main():
         fb_h_np = fb_h.numpy()
         stats_tot = {}
 
+        kernel_events = []                                # (start, end) around the render launch alone, per timed frame
+
         def step_dev():
             fb_d.zero_()                                  # image_.clear(), spray_renderer.inl:363
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
             dev.trace_frame(cam, sh, tiles, fb_d)         # the frame's blocking tiles in one persistent launch
+            b.record(stream)
+            kernel_events.append((a, b))
 
         def step_e2e():
             # the public C-ABI call with a pinned HOST frame buffer: camera/shade/tile descriptors go H2D as
@@ -334,7 +340,9 @@ def main():
             bytes_frame = 16 * W * H + 80 * nn + 48 * nt + 48 * nh
             nl = max(int(launches) // max(args.steps, 1), 1)        # render launches per frame (1: spraygpu_trace_frame)
             per_launch = bytes_frame / nl
-            dur_s = ms_dev * 1e-3 / nl
+            # the kernel's own duration: events around the launch inside every TIMED frame (the step also clears the image)
+            kern_ms = float(np.mean([a.elapsed_time(b) for a, b in kernel_events[-args.steps:]]))
+            dur_s = kern_ms * 1e-3 / nl
             achieved = per_launch / dur_s / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "render_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(args.workload), "peak_source": peak_src,
