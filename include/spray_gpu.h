@@ -49,7 +49,8 @@ typedef struct spraygpu_scene_s* spraygpu_scene;
 
 /* Ray record, 32 B.  Replaces the org/dir/tnear/tfar head of RTCRay / RTCRayIntersection
  * (src/render/rays.h:117-170,246-274).  tmin is honoured; tmax is IGNORED (= inf) exactly like every
- * reference call site (rays.h:345-363,389-423 set tfar = SPRAY_FLOAT_INF for radiance AND shadow). */
+ * reference call site (rays.h:345-363,389-423 set tfar = SPRAY_FLOAT_INF for radiance AND shadow).
+ * DEVICE arrays of rays must be 16-byte aligned (any cudaMalloc / torch allocation is); host arrays need not be. */
 typedef struct { float ox, oy, oz, tmin, dx, dy, dz, tmax; } spraygpu_ray;
 
 /* Hit key: (float_bits(t) << 32) | (domain << 23) | primID ; SPRAYGPU_KEY_MISS when nothing was hit.

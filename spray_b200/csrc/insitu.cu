@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(128)
     if (key != SPRAY_KEY_MISS) {
       const DomainEntry* e = P.table + key_domain(key);
       if (e->resident) {
-        const spraygpu_ray ry = rays[i];
+        const spraygpu_ray ry = load_ray(rays + (i));
         const vec3 ro = mk3(ry.ox, ry.oy, ry.oz), rd = mk3(ry.dx, ry.dy, ry.dz);
         const uint32_t prim = key_prim(key);
         // (u, v) re-derived from (ray, prim) with the S1 arithmetic on the same vertex values: bit-identical
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(128)
     d = mk3(sdir[3 * i], sdir[3 * i + 1], sdir[3 * i + 2]);
     const uint64_t key = keys[i];
     if (key != SPRAY_KEY_MISS) {
-      const spraygpu_ray ry = rays[i];
+      const spraygpu_ray ry = load_ray(rays + (i));
       o = hit_position(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), key_t(key));
     }
   }
@@ -164,14 +164,14 @@ __global__ void __launch_bounds__(256)
                             const float* __restrict__ bnext, float* __restrict__ w, size_t n) {
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  spraygpu_ray ry = rays[i];
+  spraygpu_ray ry = load_ray(rays + (i));
   const vec3 d = mk3(bnext[6 * i], bnext[6 * i + 1], bnext[6 * i + 2]);
   const uint64_t key = keys[i];
   vec3 o = mk3(0, 0, 0);
   if (key != SPRAY_KEY_MISS) o = hit_position(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), key_t(key));
   ry.ox = o.x; ry.oy = o.y; ry.oz = o.z; ry.tmin = SPRAY_RAY_EPS;
   ry.dx = d.x; ry.dy = d.y; ry.dz = d.z; ry.tmax = INFINITY;
-  rays[i] = ry;
+  store_ray(rays + i, ry);
   w[3 * i] = bnext[6 * i + 3]; w[3 * i + 1] = bnext[6 * i + 4]; w[3 * i + 2] = bnext[6 * i + 5];
 }
 

@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i < n) {
-    const spraygpu_ray ry = rays[i];
+    const spraygpu_ray ry = load_ray(rays + (i));
     const vec3 o = mk3(ry.ox, ry.oy, ry.oz);
     for (int p = rad ? -1 : 0; p < np; ++p) {
       const vec3 d = p < 0 ? mk3(ry.dx, ry.dy, ry.dz)
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(128)
   if (key == SPRAY_KEY_MISS) return;
   const DomainEntry* e = table + key_domain(key);
   if (!e->resident) return;
-  const spraygpu_ray ry = rays[i];
+  const spraygpu_ray ry = load_ray(rays + (i));
   const uint32_t prim = key_prim(key);
   const uint32_t i0 = e->faces[3 * (size_t)prim], i1 = e->faces[3 * (size_t)prim + 1], i2 = e->faces[3 * (size_t)prim + 2];
   const vec3 v0 = mk3(e->verts[3 * (size_t)i0], e->verts[3 * (size_t)i0 + 1], e->verts[3 * (size_t)i0 + 2]);
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(128)
   vec3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
   if (valid) {
     d = mk3(sdir[3 * j], sdir[3 * j + 1], sdir[3 * j + 2]);
-    const spraygpu_ray ry = rays[j % n];   // the next wave's origin = this shadow ray's hit position
+    const spraygpu_ray ry = load_ray(rays + (j % n));   // the next wave's origin = this shadow ray's hit position
     o = mk3(ry.ox, ry.oy, ry.oz);
   }
   const bool live = valid && !is_zero(d);
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(128)
   if (i < P.n) {
     vec3 bd = mk3(0, 0, 0), bw = mk3(0, 0, 0);
     const uint64_t key = keys[i];
-    const spraygpu_ray ry = rays[i];
+    const spraygpu_ray ry = load_ray(rays + (i));
     const vec3 ro = mk3(ry.ox, ry.oy, ry.oz), rd = mk3(ry.dx, ry.dy, ry.dz);
     const bool hit = key != SPRAY_KEY_MISS && !is_zero(rd);
     HitCtx c;
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(256)
                          float* __restrict__ w, size_t n) {
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  spraygpu_ray ry = rays[i];
+  spraygpu_ray ry = load_ray(rays + (i));
   const vec3 rd = mk3(ry.dx, ry.dy, ry.dz);
   const uint64_t key = keys[i];
   vec3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(256)
   }
   ry.ox = o.x; ry.oy = o.y; ry.oz = o.z; ry.tmin = SPRAY_RAY_EPS;
   ry.dx = d.x; ry.dy = d.y; ry.dz = d.z; ry.tmax = INFINITY;
-  rays[i] = ry;
+  store_ray(rays + i, ry);
   w[3 * i] = bnext[6 * i + 3]; w[3 * i + 1] = bnext[6 * i + 4]; w[3 * i + 2] = bnext[6 * i + 5];
 }
 

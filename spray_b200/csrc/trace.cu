@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(128)
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
-  if (valid) ry = rays[i];
+  if (valid) ry = load_ray(rays + (i));
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   warp_cull(D, valid, o, d, false);
   if (!valid) return;
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(128)
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
-  if (valid) ry = rays[i];
+  if (valid) ry = load_ray(rays + (i));
   const RayCtx r = make_ray_ctx(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), ry.tmin);
   OneDomainSource src{nodes, tris, domain_id, false};
   SceneHit c;
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(128)
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
-  if (valid) ry = rays[i];
+  if (valid) ry = load_ray(rays + (i));
   const RayCtx r = make_ray_ctx(mk3(ry.ox, ry.oy, ry.oz), mk3(ry.dx, ry.dy, ry.dz), ry.tmin);
   OneDomainSource src{nodes, tris, 0u, false};
   SceneHit c;
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(128)
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const bool valid = i < n;
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
-  if (valid) ry = rays[i];
+  if (valid) ry = load_ray(rays + (i));
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   // a zero direction marks an inactive slot of a ray wave (terminated sample): it hits nothing
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(128)
   // merge: rays already occluded elsewhere (or flagged 1 by the caller as "not a ray") are skipped
   const bool valid = i < n && !(merge && occ[i]);
   spraygpu_ray ry = {0, 0, 0, 0, 0, 0, 1, 0};
-  if (valid) ry = rays[i];
+  if (valid) ry = load_ray(rays + (i));
   const vec3 o = mk3(ry.ox, ry.oy, ry.oz), d = mk3(ry.dx, ry.dy, ry.dz);
   const bool live = valid && !(d.x == 0.0f && d.y == 0.0f && d.z == 0.0f);
   SceneHit hs;
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(128)
     if (e->resident) {
       // re-derive (u,v) from (ray, primID) with the same S1 arithmetic on the same vertex values: the
       // result is bit-identical to what the traversal computed, so no (u,v) has to travel with the key.
-      const spraygpu_ray ry = rays[i];
+      const spraygpu_ray ry = load_ray(rays + (i));
       const uint32_t prim = key_prim(key);
       const uint32_t i0 = e->faces[3 * (size_t)prim], i1 = e->faces[3 * (size_t)prim + 1], i2 = e->faces[3 * (size_t)prim + 2];
       const vec3 v0 = mk3(e->verts[3 * (size_t)i0], e->verts[3 * (size_t)i0 + 1], e->verts[3 * (size_t)i0 + 2]);
@@ -177,10 +177,10 @@ __global__ void __launch_bounds__(256)
   const uint32_t pix = (uint32_t)(i / spp);
   uint32_t samid, pixid; vec3 d;
   eye_sample(cam, tile, spp, pix % (uint32_t)tile.w, pix / (uint32_t)tile.w, sidx, &samid, &pixid, &d);
-  spraygpu_ray r;
-  r.ox = cam.pos[0]; r.oy = cam.pos[1]; r.oz = cam.pos[2]; r.tmin = SPRAY_RAY_EPS;
-  r.dx = d.x; r.dy = d.y; r.dz = d.z; r.tmax = INFINITY;
-  rays[samid] = r;
+  // two 16-byte stores per ray (the 8 scalar stores of a struct copy ran at ~0.9 TB/s: ncu r01s)
+  float4* out = reinterpret_cast<float4*>(rays + samid);
+  out[0] = make_float4(cam.pos[0], cam.pos[1], cam.pos[2], SPRAY_RAY_EPS);
+  out[1] = make_float4(d.x, d.y, d.z, INFINITY);
 }
 
 // ------------------------------------------------------------------------------------------------

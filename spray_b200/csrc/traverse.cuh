@@ -9,6 +9,18 @@ namespace spraygpu {
 #define MAXLIST 16
 #define MAX_PENDING 8
 
+// ray records move as two 16-byte transactions (spraygpu_ray arrays are 16-byte aligned: include/spray_gpu.h)
+__device__ __forceinline__ spraygpu_ray load_ray(const spraygpu_ray* p) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  spraygpu_ray r;
+  r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+  return r;
+}
+__device__ __forceinline__ void store_ray(spraygpu_ray* p, const spraygpu_ray& r) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(r.ox, r.oy, r.oz, r.tmin);
+  reinterpret_cast<float4*>(p)[1] = make_float4(r.dx, r.dy, r.dz, r.tmax);
+}
+
 struct NodeLoaderG {
   const uint4* nodes;
   __device__ __forceinline__ void operator()(uint32_t idx, u4& q0, u4& q1, u4& q2, u4& q3, u4& q4) const {
