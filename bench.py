@@ -236,6 +236,10 @@ def main():
         infos = [s_.info() for s_ in scenes_by_id.values()]
         build_dev_ms = float(sum(i.build_ms for i in infos))          # CUDA-event time of every spraygpu_scene_commit
         build_tris = int(sum(i.num_faces for i in infos))
+        # steady state of a cache block that is re-loaded (out-of-core LRU miss): same buffers, no allocation
+        for s_ in scenes_by_id.values():
+            s_.commit()
+        rebuild_dev_ms = float(sum(s_.info().build_ms for s_ in scenes_by_id.values()))
         fb_d = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
         fb_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
         fb_h_np = fb_h.numpy()
@@ -353,9 +357,11 @@ def main():
             line["config"]["build_s_all_domains"] = build_s
             # per-domain acceleration-structure build (= rtcCommit): device time of the commits alone; the wall-clock
             # figure above also holds the H2D upload of the meshes from pageable host memory
-            line["build"] = {"triangles": build_tris, "device_ms": build_dev_ms,
-                             "mtris_per_s": build_tris / max(build_dev_ms, 1e-9) / 1e3,
-                             "algorithmic_gb_per_s": build_tris * 300.0 / max(build_dev_ms, 1e-9) / 1e6}
+            line["build"] = {"triangles": build_tris, "first_commit_device_ms": build_dev_ms,
+                             "recommit_device_ms": rebuild_dev_ms,
+                             "mtris_per_s": build_tris / max(rebuild_dev_ms, 1e-9) / 1e3,
+                             "algorithmic_gb_per_s": build_tris * 300.0 / max(rebuild_dev_ms, 1e-9) / 1e6,
+                             "note": "first commit includes cudaMalloc of the domain's buffers; mtris_per_s is the re-commit"}
             if not args.no_cpu_baseline:
                 v, sec, crays, cores, tile = run_cpu(sc, cd, shade, W, H, 3, 1)
                 line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",

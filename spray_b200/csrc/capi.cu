@@ -267,7 +267,7 @@ int spraygpu_scene_create(spraygpu_device dev, spraygpu_scene* out) {
 }
 
 static void scene_free_mesh(Scene* s) {
-  if (s->d_verts && s->d_verts != s->d_verts_obj) cudaFree(s->d_verts);
+  if (s->d_verts_xf) cudaFree(s->d_verts_xf);
   if (s->d_verts_obj) cudaFree(s->d_verts_obj);
   if (s->d_faces) cudaFree(s->d_faces);
   if (s->d_rgb) cudaFree(s->d_rgb);
@@ -275,8 +275,9 @@ static void scene_free_mesh(Scene* s) {
   if (s->d_nodes) cudaFree(s->d_nodes);
   if (s->d_tris) cudaFree(s->d_tris);
   if (s->d_attr) cudaFree(s->d_attr);
-  s->d_verts = s->d_verts_obj = nullptr; s->d_faces = s->d_rgb = nullptr; s->d_normals = nullptr;
+  s->d_verts = s->d_verts_obj = s->d_verts_xf = nullptr; s->d_faces = s->d_rgb = nullptr; s->d_normals = nullptr;
   s->d_nodes = nullptr; s->d_tris = s->d_attr = nullptr;
+  s->cap_verts_obj = s->cap_faces = s->cap_rgb = s->cap_verts_xf = s->cap_normals = s->cap_tris = s->cap_attr = s->cap_nodes = 0;
   s->committed = false; s->n_nodes = 0;
 }
 
@@ -309,15 +310,19 @@ int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, c
   Device* d = s->dev;
   SG_CUDA(cudaSetDevice(d->cuda_device));
   SG_CUDA(cudaStreamSynchronize(d->stream));
-  scene_free_mesh(s);
+  // a re-used cache block keeps its allocations when the new mesh fits (grow_buffer)
+  s->committed = false; s->n_nodes = 0; s->d_verts = nullptr;
   s->nv = nv; s->nf = nf;
-  SG_CUDA(cudaMalloc(&s->d_verts_obj, sizeof(float) * 3 * nv));
-  SG_CUDA(cudaMalloc(&s->d_faces, sizeof(uint32_t) * 3 * nf));
+  int grc;
+  if ((grc = grow_buffer(&s->d_verts_obj, &s->cap_verts_obj, sizeof(float) * 3 * nv))) return grc;
+  if ((grc = grow_buffer(&s->d_faces, &s->cap_faces, sizeof(uint32_t) * 3 * nf))) return grc;
   SG_CUDA(cudaMemcpyAsync(s->d_verts_obj, xyz, sizeof(float) * 3 * nv, cudaMemcpyDefault, d->stream));
   SG_CUDA(cudaMemcpyAsync(s->d_faces, idx, sizeof(uint32_t) * 3 * nf, cudaMemcpyDefault, d->stream));
   if (rgb) {
-    SG_CUDA(cudaMalloc(&s->d_rgb, sizeof(uint32_t) * nv));
+    if ((grc = grow_buffer(&s->d_rgb, &s->cap_rgb, sizeof(uint32_t) * nv))) return grc;
     SG_CUDA(cudaMemcpyAsync(s->d_rgb, rgb, sizeof(uint32_t) * nv, cudaMemcpyDefault, d->stream));
+  } else if (s->d_rgb) {
+    cudaFree(s->d_rgb); s->d_rgb = nullptr; s->cap_rgb = 0;
   }
   SG_CUDA(cudaStreamSynchronize(d->stream));  // host arrays may be freed after return
   return SPRAYGPU_OK;

@@ -106,7 +106,12 @@ struct Scene {
   float xf[16];
   // committed
   bool committed = false;
-  float* d_verts = nullptr;    // world space (aliases d_verts_obj when no transform)
+  float* d_verts = nullptr;    // world space (aliases d_verts_obj when no transform, else d_verts_xf)
+  float* d_verts_xf = nullptr;
+  // capacities (bytes) of the buffers above: a cache block that is re-loaded with a domain of the same size (the
+  // out-of-core LRU path) re-uses its allocations instead of cudaFree (a device-wide sync) + cudaMalloc
+  size_t cap_verts_obj = 0, cap_faces = 0, cap_rgb = 0, cap_verts_xf = 0, cap_normals = 0, cap_tris = 0, cap_attr = 0,
+         cap_nodes = 0;
   float* d_normals = nullptr;  // nv*3
   uint4* d_nodes = nullptr;
   uint32_t n_nodes = 0;
@@ -117,6 +122,16 @@ struct Scene {
 };
 
 int ensure_scratch(Scratch& s, size_t bytes);
+// make *p hold at least `bytes` (re-using the allocation when it is large enough and not more than 2x too large)
+template <typename T>
+inline int grow_buffer(T** p, size_t* cap, size_t bytes) {
+  if (*p && *cap >= bytes && *cap <= 2 * bytes + 4096) return SPRAYGPU_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  SG_CUDA(cudaMalloc((void**)p, bytes));
+  *cap = bytes;
+  return SPRAYGPU_OK;
+}
 int build_scene(Scene* sc);   // build.cu
 int upload_domain_table(Device* dev);
 
