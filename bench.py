@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """bench.py — headline benchmark of the per-domain ray-tracing hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4s|c5]
 
 A step = one frame of the hot path on the named workload: every blocking tile of the image goes through
 spraygpu_trace_tile (eye rays -> domain culling -> per-domain BVH8 closest hit -> shading -> shadow rays
@@ -60,6 +60,16 @@ def workload(name):
         cd = scenes.camera_frame((95.0, 90.0, 85.0), (40.0, 40.0, 40.0), (0, 1, 0), 90.0, W, H)
         shade = dict(shader=0, bounces=3, pixel_samples=1, ao_samples=1, **scenes.WAVELETS64_BLINN)
         label = "C3: synthetic 64-domain triangle soup, %d tris/domain, 2048x2048, bounces 3 + shadow rays" % tris
+    elif name == "c4s":
+        # C4's mechanism at a size one GPU holds: the C3 scene behind a device LRU of SPRAY_C4_CAP cache blocks
+        # (default 16 of 64 domains) -> spraygpu_trace_tile_ooc; every sweep re-uploads and re-builds what it evicted
+        tris = int(os.environ.get("SPRAY_C3_TRIS", str(1 << 20)))
+        sc = scenes.soup_scene((4, 4, 4), tris)
+        W = H = 2048
+        cd = scenes.camera_frame((95.0, 90.0, 85.0), (40.0, 40.0, 40.0), (0, 1, 0), 90.0, W, H)
+        shade = dict(shader=0, bounces=1, pixel_samples=1, ao_samples=1, **scenes.WAVELETS64_BLINN)
+        label = ("C4 (reduced): 64-domain triangle soup, %d tris/domain, out-of-core with a %s-block device LRU, 2048x2048, bounces 1"
+                 % (tris, os.environ.get("SPRAY_C4_CAP", "16")))
     elif name == "c5":
         # in-situ configuration: 8 wavelet domains per GPU (8 / 16 / 32 / 64 domains at 1 / 2 / 4 / 8 GPUs), 4096^2 x 4 spp
         world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -228,6 +238,40 @@ def main():
 
         def rays_of():
             return rays_total
+    elif args.workload == "c4s":
+        # out-of-core: meshes wait in PINNED host memory, the LRU uploads + commits on every miss
+        cap = int(os.environ.get("SPRAY_C4_CAP", "16"))
+        rt = torch.cuda.cudart()
+        for d in sc["domains"]:
+            d["verts"] = np.ascontiguousarray(d["verts"], np.float32)
+            d["faces"] = np.ascontiguousarray(d["faces"], np.uint32)
+            d["rgb"] = np.ascontiguousarray(d["rgb"], np.uint32)
+            for k in ("verts", "faces", "rgb"):
+                rt.cudaHostRegister(d[k].ctypes.data, d[k].nbytes, 0)     # page-lock in place
+        cache = capi.LruDomainCache(dev, sc, cap)
+        fb_d = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        fb_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
+        ooc_stats = {}
+
+        def step_dev():
+            fb_d.zero_()
+            for t in tiles:
+                dev.trace_tile_ooc(cam, sh, t, fb_d, cap, cache.load)
+
+        def step_e2e():
+            step_dev()
+            fb_h.copy_(fb_d, non_blocking=True)
+            dev.synchronize()
+
+        fb_d.zero_()
+        for t in tiles:
+            st = dev.trace_tile_ooc(cam, sh, t, fb_d, cap, cache.load, stats=True)
+            for k, v in st.as_dict().items():
+                ooc_stats[k] = ooc_stats.get(k, 0) + v
+        misses_per_frame = cache.misses
+
+        def rays_of():
+            return ooc_stats["radiance_rays"] + ooc_stats["shadow_rays"]
     else:
         t_build0 = time.perf_counter()
         scenes_by_id = dev.load_scene(sc)
@@ -337,7 +381,14 @@ def main():
                         "d2h_bytes_per_step": int(W * H * 16)}}
         if insitu_extra:
             line["insitu"] = insitu_extra
-        if world == 1:
+        if world == 1 and args.workload == "c4s":
+            line["config"]["parallelism"] = "1 GPU, out-of-core: %d cache blocks for %d domains" % (cap, len(sc["domains"]))
+            mesh_bytes = int(sum(d["verts"].nbytes + d["faces"].nbytes + d["rgb"].nbytes for d in sc["domains"]) // len(sc["domains"]))
+            line["e2e"]["h2d_bytes_per_step"] += int(misses_per_frame) * mesh_bytes     # meshes re-uploaded by the LRU
+            line["ooc"] = {"cache_blocks": cap, "mesh_bytes_per_domain": mesh_bytes, "domains": len(sc["domains"]), "misses_first_frame": int(misses_per_frame),
+                           "misses_total": int(cache.misses), "hits_total": int(cache.hits),
+                           "note": "every miss = H2D of the domain's mesh from pinned memory + spraygpu_scene_commit"}
+        elif world == 1:
             nn, nt, nh = stats_tot["nodes_visited"], stats_tot["tris_tested"], stats_tot["hits"]
             nrays = rays
             # algorithmic bytes: per ray 16 B frame-buffer + 80 B/node + 48 B/triangle (+48 B attribute record per hit)
