@@ -241,6 +241,9 @@ def main():
     elif args.workload == "c4s":
         # out-of-core: meshes wait in PINNED host memory, the LRU uploads + commits on every miss
         cap = int(os.environ.get("SPRAY_C4_CAP", "16"))
+        # one blocking tile for the whole frame (the reference's --max-samples-per-rank, config.cc:66, raised to W*H):
+        # every sweep loads each entered domain once per FRAME instead of once per 1 Mi-sample tile
+        tiles = [(0, 0, W, H)]
         rt = torch.cuda.cudart()
         for d in sc["domains"]:
             d["verts"] = np.ascontiguousarray(d["verts"], np.float32)

@@ -334,6 +334,11 @@ extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_cam
       std::sort(order.begin(), order.end(), [](const std::pair<unsigned int, int>& a, const std::pair<unsigned int, int>& b) {
         return a.first != b.first ? a.first > b.first : a.second < b.second;
       });
+      // domains that are still resident from the previous sweep go first: their group costs no load at all (an
+      // LRU cache walked in the same order every sweep would miss on every domain)
+      std::stable_partition(order.begin(), order.end(), [&](const std::pair<unsigned int, int>& a) {
+        return dev->h_domains[(size_t)a.second].resident != 0;
+      });
       // 3. groups
       for (size_t g0 = 0; g0 < order.size() && rc == SPRAYGPU_OK; g0 += (size_t)max_resident) {
         const size_t g1 = std::min(order.size(), g0 + (size_t)max_resident);
