@@ -94,6 +94,10 @@ struct Device {
   int tlas_n = 0;                  // 0: no resident domain
   unsigned long long* d_counters = nullptr;  // [0] work counter, [1..] stats
   uint64_t launches = 0;           // kernels launched by this library (bench "gpu_launches")
+  // last render-kernel configuration (function attribute + occupancy are queried once per kernel / smem size)
+  const void* render_kern = nullptr;
+  size_t render_smem = 0;
+  int render_per_sm = 0;
 };
 
 struct Scene {

@@ -702,10 +702,15 @@ int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_
   const int qcap = general ? QueueCap<true>::value : QueueCap<false>::value;
   const size_t smem = ((dom_smem_bytes(dev->ndomains, dev->tlas_n, 0) + 15) & ~(size_t)15) +
                       SPRAY_RENDER_WARPS * (stream ? stream_words_per_warp() : queue_words_per_warp(qcap)) * sizeof(uint32_t);
-  SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SPRAY_RENDER_THREADS, smem));
-  if (per_sm < 1) per_sm = 1;
+  // attribute + occupancy are per (kernel, shared-memory size): cached, the frame loop is host-latency sensitive at
+  // 8 GPUs (0.1 ms of kernel per rank)
+  int per_sm = dev->render_per_sm;
+  if (dev->render_kern != (const void*)kern || dev->render_smem != smem) {
+    SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SPRAY_RENDER_THREADS, smem));
+    if (per_sm < 1) per_sm = 1;
+    dev->render_kern = (const void*)kern; dev->render_smem = smem; dev->render_per_sm = per_sm;
+  }
   // persistent grid: SM count x resident CTAs per SM
   int grid = dev->sm_count * per_sm;
   const uint64_t warps_needed = (slots + 31) / 32;
