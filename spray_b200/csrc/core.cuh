@@ -261,8 +261,7 @@ SPRAY_HD float byte_to_biased_float(uint32_t w, int j, uint32_t k47) {
 // its quantised plane, so the test stays conservative.  The far side carries the 1e-5 relative slack
 // (FP32 rounding of the plane distances, and rays the FP32 triangle test accepts although they graze
 // just outside the exact triangle) pre-multiplied into its coefficients.
-// The two halves (children 0..3 / 4..7) run as a real loop: the traversal loop must stay small enough
-// for the 6 KB L0 instruction cache (ncu: a fully unrolled node test stalled ~40 % on instruction fetch).
+// The two halves (children 0..3 / 4..7) are written as a loop that is unrolled by default (see below).
 SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4, const RayCtx& r,
                              float tmax) {
   const uint32_t e = q0.w;
@@ -280,8 +279,13 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
   const bool nx = r.idir.x < 0.0f, ny = r.idir.y < 0.0f, nz = r.idir.z < 0.0f;
   uint32_t hitmask = 0;
   const uint32_t k47 = opaque_k47();
-#if defined(__CUDA_ARCH__)
+  // Both halves unrolled: the 12 per-half word selects fold away.  (The first fused kernel kept this a real loop —
+  // ncu then showed ~40 % instruction-fetch stalls with everything unrolled; with the lean kernel variant and the
+  // flat warp-synchronous loop the unrolled form wins: C2 6742 -> 7042 Mrays/s, C3 1041 -> 1087, profiles/r01x.)
+#if defined(__CUDA_ARCH__) && defined(SPRAY_NODE_ROLLED)
 #pragma unroll 1
+#elif defined(__CUDA_ARCH__)
+#pragma unroll
 #endif
   for (int half = 0; half < 2; ++half) {
     const uint32_t meta4 = half ? q1.w : q1.z;
