@@ -29,8 +29,8 @@ sys.path.insert(0, ROOT)
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE render launch (= one frame) from the committed ncu --set full
 # capture of this command (bench.py cannot run under ncu itself); refreshed with every profile round.
-NCU_TRAFFIC = {"c2": 18489856 + 1807104, "c3": 676312064 + 44970752}
-NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/r01j_{c2,c3}_render_tile_ncu_full_details.csv (one launch = one frame)"
+NCU_TRAFFIC = {"c2": 18517504 + 2016768, "c3": 675356160 + 45847040}
+NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/r01y_{c2,c3}_render_tile_ncu_full_details.csv (one launch = one frame)"
 
 METRIC = "Mrays/s (primary+shadow, device-timed)"
 UNIT = "Mrays/s"
