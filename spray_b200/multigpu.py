@@ -40,7 +40,7 @@ def band_tiles(image_w, band, spp, max_samples=1024 * 1024):
     return [(0, y, image_w, min(rows, y1 - y)) for y in range(y0, y1, rows)]
 
 
-def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4):
+def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4, root=0, root_share=1.0):
     """Image-space load balancing for the image partition (default from 4 GPUs up).  A fine cut (32 blocks per rank)
     lost badly to contiguous bands (one NCCL send per block); 4 blocks per rank is the measured compromise.
     The image is cut into row blocks dealt round-robin to the ranks (block b -> rank
@@ -49,7 +49,24 @@ def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4):
     rows = -(-int(image_h) // (max_tiles_per_rank * int(nranks)))
     rows = max(4, (rows + 3) // 4 * 4)
     begin = list(range(0, int(image_h), rows)) + [int(image_h)]
-    owner = [b % int(nranks) for b in range(len(begin) - 1)]
+    # root_share < 1: the compositing rank renders a smaller share, so its receives are posted (and the other ranks'
+    # rows start to flow) while the slower ranks still render; 0 makes it a pure compositor
+    owner, b, acc = [], 0, 0.0
+    nb = len(begin) - 1
+    order = []
+    cycle = 0
+    while len(order) < nb:
+        for r in range(int(nranks)):
+            if r == root and nranks > 1:
+                acc += float(root_share)
+                if acc < 1.0 - 1e-9:
+                    continue
+                acc -= 1.0
+            order.append(r)
+            if len(order) == nb:
+                break
+        cycle += 1
+    owner = order
     return np.asarray(begin, np.int32), np.asarray(owner, np.int32)
 
 
@@ -74,7 +91,8 @@ class ImagePartitionRenderer:
         self.interleave = interleave
         self.bands = row_bands(H, world)
         if interleave:
-            self.block_begin, self.block_owner = interleaved_blocks(H, world)
+            share = float(os.environ.get("SPRAY_ROOT_SHARE", "1.0"))
+            self.block_begin, self.block_owner = interleaved_blocks(H, world, root=0, root_share=share)
             self.tiles = []
             self.my_blocks = [b for b in range(len(self.block_owner)) if self.block_owner[b] == rank]
             for b in range(len(self.block_owner)):
@@ -106,7 +124,7 @@ class ImagePartitionRenderer:
 
     def count_rays(self):
         """Deterministic per-frame ray counts of this rank's band (one extra frame with stats)."""
-        tot = {}
+        tot = {k: 0 for k, _ in capi.Stats._fields_}   # a rank may own no tile at all
         self.fb.zero_()
         for t in self.tiles:
             st = self.dev.trace_tile(self.cam, self.shade, t, self.fb, stats=True)
@@ -140,7 +158,7 @@ class InsituRenderer:
         self.dev.synchronize()
 
     def count_rays(self):
-        tot = {}
+        tot = {k: 0 for k, _ in capi.Stats._fields_}   # a rank may own no tile at all
         self.fb.zero_()
         for t in self.tiles:
             st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=True)
