@@ -143,3 +143,20 @@ def test_row_bands_and_band_tiles_cover_the_image():
                 assert x == 0 and w == 2048 and w * h * 4 <= 1024 * 1024 and b[r] <= y and y + h <= b[r + 1]
                 rows += h
         assert rows == H
+
+
+def test_interleaved_blocks_cover_and_balance():
+    from spray_b200 import multigpu
+    for H, world in ((2048, 8), (2048, 4), (4096, 8), (150, 3), (8, 8)):
+        for share in (1.0, 0.5, 0.0):
+            b, o = multigpu.interleaved_blocks(H, world, root=0, root_share=share)
+            assert b[0] == 0 and b[-1] == H and np.all(np.diff(b) > 0) and len(o) == len(b) - 1
+            assert np.all(np.diff(b)[:-1] % 4 == 0)                    # whole 8x4 pixel blocks except the ragged last one
+            assert o.min() >= 0 and o.max() < world
+            cnt = np.bincount(o, minlength=world)
+            if share == 1.0:
+                assert cnt.max() - cnt.min() <= 1
+            if share == 0.0 and world > 1:
+                assert cnt[0] == 0                                   # a pure compositor renders nothing
+            if share < 1.0:
+                assert cnt[0] <= cnt[1:].max()
