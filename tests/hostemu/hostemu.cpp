@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <vector>
@@ -45,6 +46,78 @@ static void write_tri(const EmuScene& s, uint32_t prim, float* out) {
   out[0] = v0.x; out[1] = v0.y; out[2] = v0.z; memcpy(out + 3, &prim, 4);
   out[4] = e1.x; out[5] = e1.y; out[6] = e1.z; out[7] = 0;
   out[8] = e2.x; out[9] = e2.y; out[10] = e2.z; out[11] = 0;
+}
+
+// Binned-SAH top-down binary builder (16 bins on the widest centroid axis... all three axes tried), used only to
+// MEASURE how far the shipped Morton LBVH is from a SAH-quality tree (tools/bvh_quality.py, EMU_BUILDER=sah).
+struct SahCtx {
+  const float* tlo; const float* thi;      // per-primitive boxes
+  std::vector<uint32_t>* order;            // permutation being partitioned in place
+  std::vector<int>*bl, *br, *bfirst, *blast;
+  std::vector<float>*blo, *bhi;
+  int next = 0;
+};
+static float half_area(const float* lo, const float* hi) {
+  float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+  return dx * dy + dy * dz + dz * dx;
+}
+static int sah_build(SahCtx& c, int first, int last, int self) {   // returns child ref; self < 0 -> allocate
+  if (first == last) return ~first;
+  const int me = self >= 0 ? self : c.next++;
+  std::vector<uint32_t>& ord = *c.order;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = first; i <= last; ++i)
+    for (int a = 0; a < 3; ++a) {
+      float l = c.tlo[3 * (size_t)ord[i] + a], h = c.thi[3 * (size_t)ord[i] + a], m = 0.5f * (l + h);
+      lo[a] = fminf(lo[a], l); hi[a] = fmaxf(hi[a], h); clo[a] = fminf(clo[a], m); chi[a] = fmaxf(chi[a], m);
+    }
+  for (int a = 0; a < 3; ++a) { (*c.blo)[3 * (size_t)me + a] = lo[a]; (*c.bhi)[3 * (size_t)me + a] = hi[a]; }
+  (*c.bfirst)[me] = first; (*c.blast)[me] = last;
+  const int NB = 16;
+  float best = INFINITY; int best_axis = -1, best_bin = -1;
+  for (int a = 0; a < 3; ++a) {
+    float ext = chi[a] - clo[a];
+    if (!(ext > 0.f)) continue;
+    float bl_[NB][3], bh_[NB][3]; int bc[NB];
+    for (int b = 0; b < NB; ++b) { bc[b] = 0; for (int k = 0; k < 3; ++k) { bl_[b][k] = INFINITY; bh_[b][k] = -INFINITY; } }
+    for (int i = first; i <= last; ++i) {
+      const float* l = c.tlo + 3 * (size_t)ord[i]; const float* h = c.thi + 3 * (size_t)ord[i];
+      int b = (int)((0.5f * (l[a] + h[a]) - clo[a]) / ext * NB); b = b < 0 ? 0 : (b >= NB ? NB - 1 : b);
+      bc[b]++;
+      for (int k = 0; k < 3; ++k) { bl_[b][k] = fminf(bl_[b][k], l[k]); bh_[b][k] = fmaxf(bh_[b][k], h[k]); }
+    }
+    float ra[NB]; int rc[NB];
+    float al[3] = {INFINITY, INFINITY, INFINITY}, ah[3] = {-INFINITY, -INFINITY, -INFINITY}; int cnt = 0;
+    for (int b = NB - 1; b > 0; --b) {
+      for (int k = 0; k < 3; ++k) { al[k] = fminf(al[k], bl_[b][k]); ah[k] = fmaxf(ah[k], bh_[b][k]); }
+      cnt += bc[b]; ra[b] = cnt ? half_area(al, ah) : 0.f; rc[b] = cnt;
+    }
+    for (int k = 0; k < 3; ++k) { al[k] = INFINITY; ah[k] = -INFINITY; }
+    cnt = 0;
+    for (int b = 0; b < NB - 1; ++b) {
+      for (int k = 0; k < 3; ++k) { al[k] = fminf(al[k], bl_[b][k]); ah[k] = fmaxf(ah[k], bh_[b][k]); }
+      cnt += bc[b];
+      if (cnt == 0 || rc[b + 1] == 0) continue;
+      float cost = half_area(al, ah) * (float)cnt + ra[b + 1] * (float)rc[b + 1];
+      if (cost < best) { best = cost; best_axis = a; best_bin = b; }
+    }
+  }
+  int mid;
+  if (best_axis < 0) {
+    mid = (first + last) / 2;       // coincident centroids: split the range in the middle
+  } else {
+    const int a = best_axis; const float ext = chi[a] - clo[a];
+    auto it = std::stable_partition(ord.begin() + first, ord.begin() + last + 1, [&](uint32_t p) {
+      int b = (int)((0.5f * (c.tlo[3 * (size_t)p + a] + c.thi[3 * (size_t)p + a]) - clo[a]) / ext * NB);
+      b = b < 0 ? 0 : (b >= NB ? NB - 1 : b);
+      return b <= best_bin; });
+    mid = (int)(it - ord.begin()) - 1;
+  }
+  int l = sah_build(c, first, mid, -1);
+  int r = sah_build(c, mid + 1, last, -1);
+  (*c.bl)[me] = l; (*c.br)[me] = r;
+  return me;
 }
 
 extern "C" {
@@ -98,16 +171,25 @@ EmuScene* emu_build(const float* verts, size_t nv, const uint32_t* faces, size_t
     for (int a = 0; a < 3; ++a) { llo[3 * i + a] = tlo[3 * (size_t)order[i] + a]; lhi[3 * i + a] = thi[3 * (size_t)order[i] + a]; }
   }
   std::vector<int> bl(n), br(n), bfirst(n), blast(n), parent(2 * n, -1);
-  for (int i = 0; i < n - 1; ++i) {
+  std::vector<float> blo(3 * nf, INFINITY), bhi(3 * nf, -INFINITY);
+  const char* builder = getenv("EMU_BUILDER");
+  const bool sah = builder && !strcmp(builder, "sah");
+  if (sah) {
+    SahCtx c{tlo.data(), thi.data(), &order, &bl, &br, &bfirst, &blast, &blo, &bhi, 1};
+    std::iota(order.begin(), order.end(), 0u);
+    sah_build(c, 0, n - 1, 0);
+    for (size_t i = 0; i < nf; ++i)
+      for (int a = 0; a < 3; ++a) { llo[3 * i + a] = tlo[3 * (size_t)order[i] + a]; lhi[3 * i + a] = thi[3 * (size_t)order[i] + a]; }
+  }
+  for (int i = 0; i < n - 1 && !sah; ++i) {
     lbvh_node(skeys.data(), n, i, &bl[i], &br[i], &bfirst[i], &blast[i]);
     parent[bl[i] < 0 ? (n - 1 + ~bl[i]) : bl[i]] = i;
     parent[br[i] < 0 ? (n - 1 + ~br[i]) : br[i]] = i;
   }
   parent[0] = -1;
   // structural check: every node except the root has exactly one parent
-  std::vector<float> blo(3 * nf, INFINITY), bhi(3 * nf, -INFINITY);
   std::vector<int> flags(n, 0);
-  for (int i = 0; i < n; ++i) {
+  for (int i = 0; i < n && !sah; ++i) {
     int p = parent[n - 1 + i];
     while (p >= 0) {
       if (flags[p]++ == 0) break;

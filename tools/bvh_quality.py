@@ -32,7 +32,10 @@ sets = [("wavelet", np.ascontiguousarray(wv, np.float32), np.ascontiguousarray(w
         ("soup128k", np.ascontiguousarray(sv, np.float32), np.ascontiguousarray(sf, np.uint32), random_rays(40000, lo, hi, seed=2))]
 ref = {}
 for i, flags in enumerate(sys.argv[1:] or [""]):
-    E = build(flags, str(i))
+    env = [t for t in flags.split() if t.startswith("EMU_")]          # e.g. EMU_BUILDER=sah (read by emu_build)
+    for k in [k for k in os.environ if k.startswith("EMU_")]: del os.environ[k]
+    for t in env: os.environ[t.split("=")[0]] = t.split("=", 1)[1]
+    E = build(" ".join(t for t in flags.split() if not t.startswith("EMU_")), str(i))
     for name, v, f, rays in sets:
         nodes, nn, nt, keys = run(E, v, f, rays)
         same = "" if name not in ref else (" keys==variant0: %s" % np.array_equal(keys, ref[name]))
