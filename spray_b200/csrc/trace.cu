@@ -464,9 +464,11 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
   int count = 0;      // rays in this warp's queue (warp-uniform)
   bool more = true;   // the tile still has unclaimed sample slots (warp-uniform)
 
-  LaneTrav T;
+  LaneStack stack;
+  LaneTrav T(stack);
   T.begin(false);
-  TlasSource src(P.table, D);
+  TlasStack tstack;
+  TlasSource src(P.table, D, tstack);
   RayCtx r = make_ray_ctx(mk3(0, 0, 0), mk3(0, 0, 1), SPRAY_RAY_EPS);
   bool busy = false;  // this lane holds a ray (being traced, or finished and not yet shaded)
   bool any = false;   // the held ray is a shadow ray

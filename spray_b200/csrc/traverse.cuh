@@ -253,12 +253,17 @@ __device__ __forceinline__ bool tlas_box_hit(float lox, float loy, float loz, fl
   return (cmin <= cmax + tol) && (cmax >= -tol);
 }
 
+// The stacks are objects of their own, NOT members of the state structs: a store to st[sp] inside the struct may
+// alias every scalar member as far as ptxas can tell, and the first build reloaded sp / ngx / ngy / the node
+// pointers from local memory after each push (LDL/STL pairs all over the hot loop in the SASS).
+struct TlasStack { float t[SPRAY_TLAS_STACK]; int r[SPRAY_TLAS_STACK]; };
 struct TlasSource {
   const DomainEntry* table; const DomSmem& D;
-  float st[SPRAY_TLAS_STACK];
-  int sr[SPRAY_TLAS_STACK];
+  float* const st;
+  int* const sr;
   int sp;
-  __device__ __forceinline__ TlasSource(const DomainEntry* table_, const DomSmem& D_) : table(table_), D(D_), sp(0) {}
+  __device__ __forceinline__ TlasSource(const DomainEntry* table_, const DomSmem& D_, TlasStack& S)
+      : table(table_), D(D_), st(S.t), sr(S.r), sp(0) {}
   __device__ __forceinline__ void reset(bool act) {
     sp = 0;
     if (act && D.tlas_n > 0) { st[0] = -INFINITY; sr[0] = 0; sp = 1; }
@@ -319,8 +324,10 @@ __device__ __forceinline__ bool tlas_any(const DomSmem& D, const RayCtx& r) {
 #define SPRAY_TRI_PER_PASS 8
 #endif
 // One lane's traversal state and its three step kinds.
+struct LaneStack { uint32_t x[SPRAY_STACK_SIZE], y[SPRAY_STACK_SIZE]; };   // separate object: see TlasStack
 struct LaneTrav {
-  uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  uint32_t* const sx;
+  uint32_t* const sy;
   uint32_t ngx, ngy, tgx, tgy, dom;
   const uint4* nodes;
   const float4* tris;
@@ -328,6 +335,7 @@ struct LaneTrav {
   bool alive, found;
   SceneHit out;
 
+  __device__ __forceinline__ explicit LaneTrav(LaneStack& S) : sx(S.x), sy(S.y) {}
   __device__ __forceinline__ void begin(bool act) {
     alive = act; found = false;
     ngx = ngy = tgx = tgy = 0u; dom = 0u; sp = 0;
@@ -418,7 +426,8 @@ struct LaneTrav {
 template <bool COUNT, typename Source>
 __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const RayCtx& r, const bool any, SceneHit& out,
                                            uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
-  LaneTrav T;
+  LaneStack stack;
+  LaneTrav T(stack);
   T.begin(act);
   for (;;) {
     __syncwarp();
@@ -434,7 +443,8 @@ template <bool COUNT>
 __device__ __forceinline__ bool scene_trace_warp(const DomainEntry* __restrict__ table, const DomSmem& D, const bool act,
                                                  vec3 o, vec3 d, const bool any, SceneHit& out, uint32_t* cnt) {
   const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
-  TlasSource src(table, D);
+  TlasStack tstack;
+  TlasSource src(table, D, tstack);
   src.reset(act);
   return trace_warp<COUNT>(src, act, r, any, out, cnt);
 }
