@@ -50,6 +50,28 @@ def test_bvh8_wavelet_equals_oracle(oracle, hostemu):
     hostemu.emu_destroy(h)
 
 
+def test_bvh8_quality_regression(hostemu, monkeypatch):
+    """Traversal cost of the shipped builder (Morton LBVH -> area-ordered 8-wide collapse with split leaves) on
+    incoherent rays: pinned to the values tools/bvh_quality.py measured (wavelet domain 8.40 node visits and 4.45
+    triangle tests per ray), and within 8 % of a binned-SAH binary tree pushed through the same collapse
+    (EMU_BUILDER=sah, measurement-only code in tests/hostemu)."""
+    wv, wf, _ = scenes.load_wavelet_mesh()
+    wv = np.ascontiguousarray(wv, np.float32); wf = np.ascontiguousarray(wf, np.uint32)
+    rays = random_rays(20000, wv.min(0), wv.max(0), seed=1)
+    res = {}
+    for builder in ["lbvh", "sah"]:
+        monkeypatch.setenv("EMU_BUILDER", builder)
+        h = hostemu.emu_build(wv.ctypes.data, len(wv), wf.ctypes.data, len(wf))
+        assert h
+        k, _, nn, nt = _emu_intersect(hostemu, h, rays)
+        res[builder] = (k, nn, nt)
+        hostemu.emu_destroy(h)
+    monkeypatch.delenv("EMU_BUILDER")
+    assert np.array_equal(res["lbvh"][0], res["sah"][0])          # the closest hit does not depend on the tree
+    assert res["lbvh"][1] < 8.7 and res["lbvh"][2] < 4.7
+    assert res["lbvh"][1] < 1.08 * res["sah"][1]
+
+
 @pytest.mark.parametrize("ntris", [1, 2, 3, 4, 9, 100, 5000])
 def test_bvh8_soup_and_tiny_meshes(oracle, hostemu, ntris):
     v, f, rgb = scenes.soup_domain(3, ntris, (0, 0, 0), (20, 20, 20))
