@@ -126,8 +126,9 @@ SPRAY_HD uint32_t morton30(float x, float y, float z) {
 // Domain slab test — reference src/render/aabb.h:139-169, behaviour-identical (early-out order, NaN
 // handling through the comparison directions, tmin not clamped).  b = {lo.xyz, hi.xyz}.
 // ---------------------------------------------------------------------------------------------
-SPRAY_HD bool domain_slab(const float* b, vec3 o, vec3 d, float t0, float t1, float* tmin_o) {
-  float ix = div_rn(1.0f, d.x), iy = div_rn(1.0f, d.y), iz = div_rn(1.0f, d.z);
+// domain_slab_inv takes the three reciprocals 1/d (IEEE, as the reference computes them per test) so that a caller
+// testing many boxes with one ray divides once.
+SPRAY_HD bool domain_slab_inv(const float* b, vec3 o, float ix, float iy, float iz, float t0, float t1, float* tmin_o) {
   int sx = ix < 0.0f, sy = iy < 0.0f, sz = iz < 0.0f;
   float tmin = mul_rn(sub_rn(b[sx * 3 + 0], o.x), ix);
   float tmax = mul_rn(sub_rn(b[(1 - sx) * 3 + 0], o.x), ix);
@@ -143,6 +144,9 @@ SPRAY_HD bool domain_slab(const float* b, vec3 o, vec3 d, float t0, float t1, fl
   if (tzmax < tmax) tmax = tzmax;
   *tmin_o = tmin;
   return (tmin < t1) && (tmax > t0);
+}
+SPRAY_HD bool domain_slab(const float* b, vec3 o, vec3 d, float t0, float t1, float* tmin_o) {
+  return domain_slab_inv(b, o, div_rn(1.0f, d.x), div_rn(1.0f, d.y), div_rn(1.0f, d.z), t0, t1, tmin_o);
 }
 
 // order-preserving float -> uint (handles negative entry distances: origin inside the box)
@@ -208,10 +212,11 @@ struct RayCtx {
   float tnear;
 };
 
+#define SPRAY_IDIR_CLAMP 8.271806125530277e-25f   // 2^-80
 SPRAY_HD RayCtx make_ray_ctx(vec3 o, vec3 d, float tnear) {
   RayCtx r;
   r.o = o; r.d = d; r.tnear = tnear;
-  const float eps = 8.271806125530277e-25f; // 2^-80
+  const float eps = SPRAY_IDIR_CLAMP;
   float dx = fabsf(d.x) > eps ? d.x : copysignf(eps, d.x);
   float dy = fabsf(d.y) > eps ? d.y : copysignf(eps, d.y);
   float dz = fabsf(d.z) > eps ? d.z : copysignf(eps, d.z);
@@ -223,6 +228,12 @@ SPRAY_HD RayCtx make_ray_ctx(vec3 o, vec3 d, float tnear) {
   uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
   r.octinv = 7u - oct;
   return r;
+}
+
+// 1/d exactly as domain_slab wants it: idir IS div_rn(1, d) on every axis that make_ray_ctx did not clamp
+// (|d| > 2^-80); the clamped axes (zero / denormal-small components) take the division.
+SPRAY_HD float exact_inv(float d, float idir) {
+  return fabsf(d) > SPRAY_IDIR_CLAMP ? idir : div_rn(1.0f, d);
 }
 
 SPRAY_HD uint32_t byte_of(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }

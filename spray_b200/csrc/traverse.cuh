@@ -240,6 +240,9 @@ struct OneDomainSource {   // seam 2: a single committed scene
 // Order only affects speed: the closest hit is the lexicographic min of (t, domain, prim).
 // ------------------------------------------------------------------------------------------------
 #define SPRAY_TLAS_STACK 24
+#ifndef SPRAY_SLAB_HOIST
+#define SPRAY_SLAB_HOIST 0
+#endif
 
 __device__ __forceinline__ bool tlas_box_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayCtx& r,
                                              float* tmin_o) {
@@ -279,7 +282,17 @@ struct TlasSource {
       if (ref < 0) {
         const uint32_t id = (uint32_t)~ref;
         float tmin;
+#if SPRAY_SLAB_HOIST
+        // A/B knob (r02c, not yet measured on its own): the reference divides 1/d in every box test; idir already
+        // holds those quotients except on clamped axes (tests/test_hostemu.py checks the equivalence bit for bit)
+        float ix = r.idir.x, iy = r.idir.y, iz = r.idir.z;
+        if (!(fminf(fminf(fabsf(r.d.x), fabsf(r.d.y)), fabsf(r.d.z)) > SPRAY_IDIR_CLAMP)) {
+          ix = exact_inv(r.d.x, ix); iy = exact_inv(r.d.y, iy); iz = exact_inv(r.d.z, iz);
+        }
+        if (!domain_slab_inv(D.boxes + 6 * id, r.o, ix, iy, iz, SPRAY_RAY_EPS, INFINITY, &tmin)) return 2;
+#else
         if (!domain_slab(D.boxes + 6 * id, r.o, r.d, SPRAY_RAY_EPS, INFINITY, &tmin)) return 2;
+#endif
         const DomainEntry* e = table + id;
         nn = e->nodes; tt = e->tris; dom = id;
         return 1;

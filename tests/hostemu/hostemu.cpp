@@ -268,6 +268,12 @@ uint32_t emu_morton(float x, float y, float z) { return morton30(x, y, z); }
 int emu_domain_slab(const float* b, const float* o, const float* d, float* tmin) {
   return domain_slab(b, mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), SPRAY_RAY_EPS, INFINITY, tmin) ? 1 : 0;
 }
+// the same test through the ray context's reciprocals (what the fused kernel's top-level walk calls)
+int emu_domain_slab_ctx(const float* b, const float* o, const float* d, float* tmin) {
+  RayCtx r = make_ray_ctx(mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), SPRAY_RAY_EPS);
+  return domain_slab_inv(b, r.o, exact_inv(r.d.x, r.idir.x), exact_inv(r.d.y, r.idir.y), exact_inv(r.d.z, r.idir.z),
+                         SPRAY_RAY_EPS, INFINITY, tmin) ? 1 : 0;
+}
 uint32_t emu_interp_color(uint32_t c0, uint32_t c1, uint32_t c2, float u, float v) {
   return interp_color(c0, c1, c2, u, v, sub_rn(sub_rn(1.f, u), v));
 }

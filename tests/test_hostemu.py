@@ -127,16 +127,21 @@ def test_closed_forms_equal_oracle(oracle, hostemu):
     for _ in range(500):
         o = rng.uniform(-30, 30, 3).astype(np.float32); d = rng.normal(size=3).astype(np.float32)
         if rng.random() < 0.3:
-            d[rng.integers(0, 3)] = 0.0
+            d[rng.integers(0, 3)] = rng.choice(np.array([0.0, -0.0, 1e-30, -1e-30, 1e-24, -1e-24, 1e-40], np.float32))
         if rng.random() < 0.3:
             o = np.round(o / 10) * 10
             o = o.astype(np.float32)
-        t1, t2, tm = C.c_float(), C.c_float(), C.c_float()
+        t1, t2, tm, tc = C.c_float(), C.c_float(), C.c_float(), C.c_float()
         a = L.orc_intersect_aabb(fp(box), fp(o), fp(d), f32(1e-3), f32(np.inf), C.byref(t1), C.byref(t2))
         b = E.emu_domain_slab(box.ctypes.data, o.ctypes.data, d.ctypes.data, C.byref(tm))
         assert bool(a) == bool(b)
         if a:
             assert t1.value == tm.value
+        # the fused kernel's form: reciprocals taken from the ray context (divides only on clamped axes)
+        c = E.emu_domain_slab_ctx(box.ctypes.data, o.ctypes.data, d.ctypes.data, C.byref(tc))
+        assert bool(c) == bool(b)
+        if b:
+            assert np.float32(tc.value).tobytes() == np.float32(tm.value).tobytes()
     for _ in range(300):
         cs = [int(x) for x in rng.integers(0, 1 << 24, 3)]
         u = f32(rng.uniform(0, 1)); v = f32(rng.uniform(0, 1 - u))
