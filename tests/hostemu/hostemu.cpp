@@ -252,6 +252,83 @@ void emu_intersect(EmuScene* s, uint32_t domain, const float* rays, size_t n, ui
   if (n_tris) *n_tris = tt;
 }
 
+// MEASUREMENT ONLY (tools/bvh_quality.py): the same BVH8 walked with the hit children of every node visited in
+// order of their entry distance (decoded from the quantised planes) instead of the fixed octant order the product
+// uses — how many node visits / triangle tests would distance ordering save?
+void emu_intersect_sorted(EmuScene* s, const float* rays, size_t n, uint64_t* keys, uint64_t* n_nodes, uint64_t* n_tris) {
+  uint64_t tn = 0, tt = 0;
+  struct Ent { uint32_t node; float t; };
+  std::vector<Ent> stack;
+  for (size_t i = 0; i < n; ++i) {
+    const float* rr = rays + 8 * i;
+    RayCtx r = make_ray_ctx(mk3(rr[0], rr[1], rr[2]), mk3(rr[4], rr[5], rr[6]), rr[3]);
+    Closest best; best.t = INFINITY; best.u = best.v = 0; best.prim = 0xFFFFFFFFu;
+    stack.clear(); stack.push_back({0u, -INFINITY});
+    while (!stack.empty()) {
+      Ent e = stack.back(); stack.pop_back();
+      if (e.t > best.t) continue;
+      const u4* q = &s->nodes[5 * (size_t)e.node];
+      ++tn;
+      const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], r, best.t);
+      uint32_t tg = hm & 0x00FFFFFFu;
+      while (tg) {
+        const int ti = ffs32(tg) - 1; tg &= tg - 1;
+        vec3 v0, e1, e2; uint32_t prim;
+        TriLoaderH{s->tris.data()}(q[1].y + (uint32_t)ti, v0, e1, e2, prim);
+        ++tt;
+        float T, U, V, ad;
+        if (tri_test_raw(r.o, r.d, v0, e1, e2, r.tnear, &T, &U, &V, &ad)) {
+          const float t = div_rn(T, ad);
+          if (t < best.t || (t == best.t && prim < best.prim)) { best.t = t; best.u = div_rn(U, ad); best.v = div_rn(V, ad); best.prim = prim; }
+        }
+      }
+      const uint32_t imask = q[0].w >> 24, ex = q[0].w & 0xff, ey = (q[0].w >> 8) & 0xff, ez = (q[0].w >> 16) & 0xff;
+      Ent kids[8]; int nk = 0;
+      for (uint32_t bits = hm >> 24; bits; bits &= bits - 1) {
+        const uint32_t slot = (uint32_t)(ffs32(bits) - 1) ^ r.octinv;
+        const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+        const uint32_t w = slot >> 2, j = slot & 3;
+        const uint32_t lo3[3] = {byte_of(w ? q[2].y : q[2].x, j), byte_of(w ? q[2].w : q[2].z, j), byte_of(w ? q[3].y : q[3].x, j)};
+        const uint32_t hi3[3] = {byte_of(w ? q[3].w : q[3].z, j), byte_of(w ? q[4].y : q[4].x, j), byte_of(w ? q[4].w : q[4].z, j)};
+        const float sc[3] = {u2f(ex << 23), u2f(ey << 23), u2f(ez << 23)};
+        const float org[3] = {u2f(q[0].x), u2f(q[0].y), u2f(q[0].z)};
+        const float o3[3] = {r.o.x, r.o.y, r.o.z}, id3[3] = {r.idir.x, r.idir.y, r.idir.z};
+        float tmin = r.tnear;
+        for (int a = 0; a < 3; ++a) {
+          const float pl = org[a] + (float)(id3[a] < 0.f ? hi3[a] : lo3[a]) * sc[a];
+          tmin = fmaxf(tmin, (pl - o3[a]) * id3[a]);
+        }
+        kids[nk++] = {q[1].x + rel, tmin};
+      }
+      const char* ord0 = getenv("EMU_ORDER");
+      if (ord0 && !strcmp(ord0, "group")) {      // one distance per node: the nearest hit child's (what a 1-float-per-entry stack could hold)
+        float m = INFINITY;
+        for (int k = 0; k < nk; ++k) m = fminf(m, kids[k].t);
+        for (int k = 0; k < nk; ++k) kids[k].t = m;
+      }
+      if (ord0 && !strncmp(ord0, "q", 1)) {      // "q<bits>": per-child distance quantised DOWN to <bits> bits of [nearest, farthest hit child]
+        const int nb = atoi(ord0 + 1);
+        float m = INFINITY;
+        for (int k = 0; k < nk; ++k) m = fminf(m, kids[k].t);
+        float hi = m;
+        for (int k = 0; k < nk; ++k) hi = fmaxf(hi, kids[k].t);
+        const float step = (hi - m) / (float)((1 << nb) - 1);
+        for (int k = 0; k < nk; ++k) kids[k].t = step > 0.f && step < 1e29f ? m + floorf((kids[k].t - m) / step) * step : m;
+      }
+      if (ord0 && !strncmp(ord0, "m", 1)) {      // "m<bits>": absolute distance truncated to <bits> mantissa bits (a minifloat byte per child)
+        const int nb = atoi(ord0 + 1);
+        for (int k = 0; k < nk; ++k) kids[k].t = kids[k].t > 0.f ? u2f(f2u(kids[k].t) & ~((1u << (23 - nb)) - 1u)) : -INFINITY;
+      }
+      const char* ord = (ord0 && (!strcmp(ord0, "group") || !strncmp(ord0, "q", 1) || !strncmp(ord0, "m", 1))) ? "octant" : ord0;   // "distance": nearest first; "octant": product order, entries culled at pop
+      if (!ord || strcmp(ord, "octant"))
+        std::sort(kids, kids + nk, [](const Ent& a, const Ent& b) { return a.t > b.t; });   // far first: nearest on top
+      for (int k = 0; k < nk; ++k) stack.push_back(kids[k]);
+    }
+    keys[i] = best.prim != 0xFFFFFFFFu ? make_key(best.t, 0, best.prim) : SPRAY_KEY_MISS;
+  }
+  *n_nodes = tn; *n_tris = tt;
+}
+
 void emu_occluded(EmuScene* s, const float* rays, size_t n, uint8_t* occ) {
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
   for (size_t i = 0; i < n; ++i) {

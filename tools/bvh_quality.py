@@ -23,6 +23,8 @@ def run(E, verts, faces, rays):
     h = E.emu_build(verts.ctypes.data, len(verts), faces.ctypes.data, len(faces))
     n = len(rays); keys = np.zeros(n, np.uint64); nn, nt = C.c_uint64(), C.c_uint64()
     E.emu_intersect(h, 0, rays.ctypes.data, n, keys.ctypes.data, None, C.byref(nn), C.byref(nt))
+    if os.environ.get("EMU_ORDER"):                  # measurement-only walk, children by entry distance
+        E.emu_intersect_sorted(C.c_void_p(h), rays.ctypes.data, C.c_size_t(n), keys.ctypes.data, C.byref(nn), C.byref(nt))
     return E.emu_num_nodes(h), nn.value / n, nt.value / n, keys
 
 wv, wf, _ = scenes.load_wavelet_mesh()
