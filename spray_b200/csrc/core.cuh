@@ -263,6 +263,41 @@ SPRAY_HD float byte_to_biased_float(uint32_t w, int j, uint32_t k47) {
 #endif
 }
 
+// ---------------------------------------------------------------------------------------------
+// SPRAY_POP_CULL (A/B knob, default off; CPU measurement in DESIGN.md section 6: 24-29 % fewer node visits).
+// The node test also returns ONE BYTE per child slot: the child's entry distance cmin truncated to a minifloat
+// (5 exponent bits, 3 mantissa bits: float bits 27..20, exponent bit 4 flipped so that bytes order like the
+// distances for 2^-15 <= t < 2^17).  A (child base, mask) group keeps its two distance words, and children whose
+// byte exceeds the byte of the current best hit are dropped from the mask without a node fetch: when the group
+// is popped, and when the best hit improves.  Conservative by construction: truncation rounds the child's
+// distance DOWN, the best hit's byte is compared with '>', out-of-range distances wrap to SMALLER bytes on the
+// child side and switch the pruning off on the best-hit side.
+// ---------------------------------------------------------------------------------------------
+#ifndef SPRAY_POP_CULL
+#define SPRAY_POP_CULL 0
+#endif
+#if SPRAY_POP_CULL
+// per byte: x > y (unsigned); result has bit 7 of each byte set where true
+SPRAY_HD uint32_t gt_u8x4(uint32_t x, uint32_t y) {
+  const uint32_t d = (y | 0x80808080u) - (x & 0x7f7f7f7fu);     // bit 7 of each byte: low7(x) <= low7(y)
+  return ((x & ~y) | (~(x ^ y) & ~d)) & 0x80808080u;
+}
+SPRAY_HD uint32_t gather_bit7(uint32_t flags) {                 // bytes 0..3 -> bits 0..3
+  return ((((flags >> 7) & 0x01010101u) * 0x01020408u) >> 24) & 0xfu;
+}
+// drops from a group's pending-children mask (bits 31..24 of ngy, bit 24+k <-> slot k ^ octinv) every child whose
+// distance byte says it starts behind best_t
+SPRAY_HD uint32_t prune_group(uint32_t ngy, uint32_t d0, uint32_t d1, float best_t, uint32_t octinv) {
+  if (!(best_t < 65536.0f)) return ngy;                         // INF / far hits: bytes would wrap
+  const uint32_t tq = ((((f2u(best_t) >> 20) ^ 0x80u) & 0xffu)) * 0x01010101u;
+  uint32_t m = gather_bit7(gt_u8x4(d0, tq)) | (gather_bit7(gt_u8x4(d1, tq)) << 4);    // stale SLOTS
+  if (octinv & 1u) m = ((m & 0x55u) << 1) | ((m >> 1) & 0x55u);                        // slot k -> bit k ^ octinv
+  if (octinv & 2u) m = ((m & 0x33u) << 2) | ((m >> 2) & 0x33u);
+  if (octinv & 4u) m = ((m & 0x0fu) << 4) | ((m >> 4) & 0x0fu);
+  return ngy & ~(m << 24);
+}
+#endif
+
 // returns the 32-bit hit mask of one node: bits 31..24 internal children in traversal priority order,
 // bits 23..0 one bit per leaf triangle.
 //
@@ -274,7 +309,11 @@ SPRAY_HD float byte_to_biased_float(uint32_t w, int j, uint32_t k47) {
 // just outside the exact triangle) pre-multiplied into its coefficients.
 // The two halves (children 0..3 / 4..7) are written as a loop that is unrolled by default (see below).
 SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4, const RayCtx& r,
-                             float tmax) {
+                             float tmax
+#if SPRAY_POP_CULL
+                             , uint32_t* dist0, uint32_t* dist1      // out: distance byte of slots 0..3 / 4..7
+#endif
+                             ) {
   const uint32_t e = q0.w;
   const float slack = 1.00001f;
   const float aix = u2f((e & 0xffu) << 23) * r.idir.x;
@@ -289,6 +328,9 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
   const uint32_t octinv4 = r.octinv * 0x01010101u;
   const bool nx = r.idir.x < 0.0f, ny = r.idir.y < 0.0f, nz = r.idir.z < 0.0f;
   uint32_t hitmask = 0;
+#if SPRAY_POP_CULL
+  uint32_t dd = 0u;
+#endif
   const uint32_t k47 = opaque_k47();
   // Both halves unrolled: the 12 per-half word selects fold away.  (The first fused kernel kept this a real loop —
   // ncu then showed ~40 % instruction-fetch stalls with everything unrolled; with the lean kernel variant and the
@@ -322,7 +364,16 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
       // branch-free: a per-child branch costs a fetch redirect and a reconvergence barrier
       const uint32_t sh = byte_of(child_bits4, j) << byte_of(bit_index4, j);
       hitmask |= (cmin <= cmax) ? sh : 0u;
+#if SPRAY_POP_CULL
+      dd |= ((f2u(cmin) >> 20) & 0xffu) << (8 * j);
+#endif
     }
+#if SPRAY_POP_CULL
+    // tnear below 2^-15 (a caller's own tmin) would wrap upwards: such rays keep zero bytes = never pruned
+    dd = r.tnear >= 3.0517578125e-05f ? (dd ^ 0x80808080u) : 0u;
+    if (half) *dist1 = dd; else *dist0 = dd;
+    dd = 0u;
+#endif
   }
   return hitmask;
 }
@@ -347,6 +398,10 @@ SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const 
                          uint32_t* n_tris) {
   uint32_t ngx = 0, ngy = 0x80000000u;
   int sp = 0;
+#if SPRAY_POP_CULL
+  uint32_t gd0 = 0u, gd1 = 0u;                                  // distance bytes of the current group
+  uint32_t stack_d0[SPRAY_STACK_SIZE], stack_d1[SPRAY_STACK_SIZE];
+#endif
   for (;;) {
     uint32_t tgx = 0, tgy = 0;
     if (ngy > 0x00FFFFFFu) {
@@ -354,6 +409,9 @@ SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const 
       const int bit = 31 - clz32(ngy);
       ngy &= ~(1u << bit);
       if (ngy > 0x00FFFFFFu) {
+#if SPRAY_POP_CULL
+        if (sp < SPRAY_STACK_SIZE) { stack_d0[sp] = gd0; stack_d1[sp] = gd1; }
+#endif
         if (sp < SPRAY_STACK_SIZE) { stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp; }
       }
       const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
@@ -361,7 +419,11 @@ SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const 
       u4 q0, q1, q2, q3, q4;
       loadn(ngx + rel, q0, q1, q2, q3, q4);
       if (n_nodes) ++*n_nodes;
+#if SPRAY_POP_CULL
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, best.t, &gd0, &gd1);
+#else
       const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, best.t);
+#endif
       ngx = q1.x; tgx = q1.y;
       ngy = (hm & 0xFF000000u) | (q0.w >> 24);
       tgy = hm & 0x00FFFFFFu;
@@ -378,13 +440,24 @@ SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const 
         const float t = div_rn(T, ad);
         if (t < best.t || (t == best.t && prim < best.prim)) {
           best.t = t; best.u = div_rn(U, ad); best.v = div_rn(V, ad); best.prim = prim;
+#if SPRAY_POP_CULL
+          ngy = prune_group(ngy, gd0, gd1, best.t, r.octinv);
+#endif
         }
       }
     }
+#if SPRAY_POP_CULL
+    while (ngy <= 0x00FFFFFFu && sp > 0) {
+      --sp; ngx = stack_x[sp]; gd0 = stack_d0[sp]; gd1 = stack_d1[sp];
+      ngy = prune_group(stack_y[sp], gd0, gd1, best.t, r.octinv);
+    }
+    if (ngy <= 0x00FFFFFFu) break;
+#else
     if (ngy <= 0x00FFFFFFu) {
       if (sp == 0) break;
       --sp; ngx = stack_x[sp]; ngy = stack_y[sp];
     }
+#endif
   }
   return false;
 }

@@ -477,6 +477,9 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
     __syncwarp();
     // lane state: running (has a node or a triangle to test), waiting (needs its next domain from the top-level
     // BVH: done in the service pass, all waiting lanes together), finished (ray done, to be shaded), empty
+#if SPRAY_POP_CULL
+    T.oct = r.octinv;
+#endif
     int w = T.want();
     const bool running = w == LaneTrav::WANT_NODE || w == LaneTrav::WANT_TRI;
     const bool waiting = w == LaneTrav::WANT_SOURCE;
@@ -568,6 +571,9 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
       }
       __syncwarp();
       // ---- E. top-level BVH steps for every lane that needs its next domain (old and new), together
+#if SPRAY_POP_CULL
+      T.oct = r.octinv;   // r may have just been replaced by a new ray
+#endif
       w = T.want();
       if (w == LaneTrav::WANT_SOURCE) { T.source_step<COUNT>(src, r, cnt); w = T.want(); }
       __syncwarp();

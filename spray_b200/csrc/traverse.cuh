@@ -337,10 +337,20 @@ __device__ __forceinline__ bool tlas_any(const DomSmem& D, const RayCtx& r) {
 #define SPRAY_TRI_PER_PASS 8
 #endif
 // One lane's traversal state and its three step kinds.
+#if SPRAY_POP_CULL
+struct LaneStack { uint4 e[SPRAY_STACK_SIZE]; };   // (child base, pending mask, distance bytes of slots 0..3, 4..7)
+#else
 struct LaneStack { uint32_t x[SPRAY_STACK_SIZE], y[SPRAY_STACK_SIZE]; };   // separate object: see TlasStack
+#endif
 struct LaneTrav {
+#if SPRAY_POP_CULL
+  uint4* const stk;
+  uint32_t gd0, gd1;   // distance bytes of the current group (core.cuh, SPRAY_POP_CULL)
+  uint32_t oct;        // the ray's octinv, for the pruning done inside want()
+#else
   uint32_t* const sx;
   uint32_t* const sy;
+#endif
   uint32_t ngx, ngy, tgx, tgy, dom;
   const uint4* nodes;
   const float4* tris;
@@ -348,7 +358,11 @@ struct LaneTrav {
   bool alive, found;
   SceneHit out;
 
+#if SPRAY_POP_CULL
+  __device__ __forceinline__ explicit LaneTrav(LaneStack& S) : stk(S.e), gd0(0u), gd1(0u), oct(0u) {}
+#else
   __device__ __forceinline__ explicit LaneTrav(LaneStack& S) : sx(S.x), sy(S.y) {}
+#endif
   __device__ __forceinline__ void begin(bool act) {
     alive = act; found = false;
     ngx = ngy = tgx = tgy = 0u; dom = 0u; sp = 0;
@@ -360,7 +374,16 @@ struct LaneTrav {
   __device__ __forceinline__ int want() {
     if (!alive) return WANT_NONE;
     if (tgy) return WANT_TRI;
+#if SPRAY_POP_CULL
+    while (ngy <= 0x00FFFFFFu && sp > 0) {   // pop; children that the best hit has overtaken since the push are dropped here
+      --sp;
+      const uint4 e = stk[sp];
+      ngx = e.x; gd0 = e.z; gd1 = e.w;
+      ngy = prune_group(e.y, gd0, gd1, out.t, oct);
+    }
+#else
     if (ngy <= 0x00FFFFFFu && sp > 0) { --sp; ngx = sx[sp]; ngy = sy[sp]; }   // popping costs nothing: do it now
+#endif
     return ngy > 0x00FFFFFFu ? WANT_NODE : WANT_SOURCE;
   }
   // one step of the domain source (top-level BVH walk); a lane whose source is exhausted is finished
@@ -368,7 +391,12 @@ struct LaneTrav {
   __device__ __forceinline__ void source_step(Source& src, const RayCtx& r, uint32_t* cnt) {
     int rc;
     do { rc = src.step(r, out.t, nodes, tris, dom); } while (rc == 2);   // A/B: one top-level step per pass was 3-4 % slower
-    if (rc == 1) { ngx = 0u; ngy = 0x80000000u; if (COUNT) cnt[0]++; }
+    if (rc == 1) {
+      ngx = 0u; ngy = 0x80000000u; if (COUNT) cnt[0]++;
+#if SPRAY_POP_CULL
+      gd0 = gd1 = 0u;
+#endif
+    }
     else if (rc == 0) alive = false;
   }
   // One pass of the warp-synchronous loop: every lane takes at most one step of each kind, in the order
@@ -377,6 +405,9 @@ struct LaneTrav {
   // stall instead of riding along.)
   template <bool COUNT, typename Source>
   __device__ __forceinline__ void pass(Source& src, const RayCtx& r, const bool any, uint32_t* cnt) {
+#if SPRAY_POP_CULL
+    oct = r.octinv;
+#endif
     int w = want();
     if (w == WANT_SOURCE) { source_step<COUNT>(src, r, cnt); w = want(); }
     __syncwarp();
@@ -399,13 +430,21 @@ struct LaneTrav {
       const uint32_t imask = ngy & 0xffu;
       const int bit = 31 - __clz((int)ngy);
       ngy &= ~(1u << bit);
+#if SPRAY_POP_CULL
+      if (ngy > 0x00FFFFFFu && sp < SPRAY_STACK_SIZE) { stk[sp] = make_uint4(ngx, ngy, gd0, gd1); ++sp; }
+#else
       if (ngy > 0x00FFFFFFu && sp < SPRAY_STACK_SIZE) { sx[sp] = ngx; sy[sp] = ngy; ++sp; }
+#endif
       const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
       const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
       u4 q0, q1, q2, q3, q4;
       NodeLoaderG{nodes}(ngx + rel, q0, q1, q2, q3, q4);
       if (COUNT) cnt[1]++;
+#if SPRAY_POP_CULL
+      const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, out.t, &gd0, &gd1);
+#else
       const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, out.t);
+#endif
       ngx = q1.x; tgx = q1.y;
       ngy = (hm & 0xFF000000u) | (q0.w >> 24);
       tgy = hm & 0x00FFFFFFu;
@@ -427,6 +466,9 @@ struct LaneTrav {
           const float t = div_rn(T, ad);
           if (t < out.t || (t == out.t && (dom < out.dom || (dom == out.dom && prim < out.prim)))) {
             out.t = t; out.u = div_rn(U, ad); out.v = div_rn(V, ad); out.prim = prim; out.dom = dom;
+#if SPRAY_POP_CULL
+            ngy = prune_group(ngy, gd0, gd1, out.t, r.octinv);
+#endif
           }
         }
       }

@@ -23,18 +23,16 @@ def oracle():
     return pyoracle
 
 
-@pytest.fixture(scope="session")
-def hostemu():
-    """Host emulation of spray_b200/csrc/core.cuh (development harness, tests/hostemu)."""
+def _load_hostemu(soname, flags):
     import ctypes as C
     d = os.path.join(ROOT, "tests", "hostemu")
-    so = os.path.join(d, "libhostemu.so")
+    so = os.path.join(d, soname)
     src = os.path.join(d, "hostemu.cpp")
     core = os.path.join(ROOT, "spray_b200", "csrc", "core.cuh")
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(core)):
         cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
         subprocess.run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-mavx2", "-mfma",
-                        "-Wno-unknown-pragmas", "-o", so, src], check=True)
+                        "-Wno-unknown-pragmas"] + flags + ["-o", so, src], check=True)
     E = C.CDLL(so)
     E.emu_build.restype = C.c_void_p
     E.emu_build.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
@@ -57,6 +55,18 @@ def hostemu():
     E.emu_blinn_phong.argtypes = [C.c_float, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     E.emu_camera_dir.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p]
     return E
+
+
+@pytest.fixture(scope="session")
+def hostemu():
+    """Host emulation of spray_b200/csrc/core.cuh (development harness, tests/hostemu)."""
+    return _load_hostemu("libhostemu.so", [])
+
+
+@pytest.fixture(scope="session")
+def hostemu_popcull():
+    """The same with the SPRAY_POP_CULL traversal knob on (stale stack entries pruned by distance bytes)."""
+    return _load_hostemu("libhostemu_popcull.so", ["-DSPRAY_POP_CULL=1"])
 
 
 def make_rays(o, d, tmin=1e-3):

@@ -269,7 +269,12 @@ void emu_intersect_sorted(EmuScene* s, const float* rays, size_t n, uint64_t* ke
       if (e.t > best.t) continue;
       const u4* q = &s->nodes[5 * (size_t)e.node];
       ++tn;
+#if SPRAY_POP_CULL
+      uint32_t unused0, unused1;
+      const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], r, best.t, &unused0, &unused1);
+#else
       const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], r, best.t);
+#endif
       uint32_t tg = hm & 0x00FFFFFFu;
       while (tg) {
         const int ti = ffs32(tg) - 1; tg &= tg - 1;

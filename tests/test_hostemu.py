@@ -72,6 +72,47 @@ def test_bvh8_quality_regression(hostemu, monkeypatch):
     assert res["lbvh"][1] < 1.08 * res["sah"][1]
 
 
+def test_pop_cull_knob_same_hits_fewer_nodes(oracle, hostemu, hostemu_popcull):
+    """-DSPRAY_POP_CULL=1 (default off in the shipped library): identical hit records and occlusion, >= 20 % fewer
+    node visits; includes rays whose own tmin is 0 (pruning must switch itself off) and far-away origins (distance
+    bytes wrap)."""
+    sc = scenes.wavelet_single()
+    d = sc["domains"][0]
+    osc = oracle.Scene(sc["domains"])
+    v, f = d["verts"], d["faces"]
+    lo, hi = v.min(0), v.max(0)
+    sets = [random_rays(20000, lo, hi, seed=5),
+            random_rays(5000, lo, hi, seed=6, spread=4000.0),          # origins ~1e5 away: t beyond the byte range
+            make_rays(random_rays(5000, lo, hi, seed=7)[:, 0:3], random_rays(5000, lo, hi, seed=7)[:, 4:7], tmin=0.0)]
+    for i, rays in enumerate(sets):
+        res = []
+        for E in (hostemu, hostemu_popcull):
+            h = E.emu_build(v.ctypes.data, len(v), f.ctypes.data, len(f))
+            k, uv, nn, nt = _emu_intersect(E, h, rays)
+            occ = np.zeros(len(rays), np.uint8)
+            E.emu_occluded(h, rays.ctypes.data, len(rays), occ.ctypes.data)
+            res.append((k, uv, nn, nt, occ))
+            E.emu_destroy(h)
+        assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])
+        assert np.array_equal(res[0][4], res[1][4])
+        assert res[1][2] <= res[0][2]
+        if i == 0:
+            ko, uvo = osc.intersect_domain(0, rays)
+            assert np.array_equal(res[1][0], ko) and np.array_equal(res[1][1], uvo)
+            assert res[1][2] < 0.8 * res[0][2]
+    # the byte compare and the slot -> bit permutation against a plain loop are exercised through the trees above;
+    # tiny and degenerate meshes:
+    for ntris in [1, 2, 9, 100]:
+        sv, sf, _ = scenes.soup_domain(3, ntris, (0, 0, 0), (20, 20, 20))
+        rays = random_rays(4000, [0] * 3, [20] * 3, seed=ntris)
+        ks = []
+        for E in (hostemu, hostemu_popcull):
+            h = E.emu_build(sv.ctypes.data, len(sv), sf.ctypes.data, len(sf))
+            ks.append(_emu_intersect(E, h, rays)[0])
+            E.emu_destroy(h)
+        assert np.array_equal(ks[0], ks[1])
+
+
 @pytest.mark.parametrize("ntris", [1, 2, 3, 4, 9, 100, 5000])
 def test_bvh8_soup_and_tiny_meshes(oracle, hostemu, ntris):
     v, f, rgb = scenes.soup_domain(3, ntris, (0, 0, 0), (20, 20, 20))
