@@ -276,8 +276,30 @@ void emu_intersect_sorted(EmuScene* s, const float* rays, size_t n, uint64_t* ke
       const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], r, best.t);
 #endif
       uint32_t tg = hm & 0x00FFFFFFu;
+      const char* lc = getenv("EMU_LEAFCULL");   // measurement: a leaf child's triangles are skipped when its box starts behind the best hit
+      const uint32_t metas[2] = {q[1].z, q[1].w};
       while (tg) {
         const int ti = ffs32(tg) - 1; tg &= tg - 1;
+        if (lc) {
+          int slot = -1;
+          for (int sl = 0; sl < 8; ++sl) {
+            const uint32_t mb = byte_of(metas[sl >> 2], sl & 3);
+            const uint32_t first = mb & 31u, cnt = (mb >> 5) == 1 ? 1u : ((mb >> 5) == 3 ? 2u : ((mb >> 5) == 7 ? 3u : 0u));
+            if (mb != 0 && first < 24u && (uint32_t)ti >= first && (uint32_t)ti < first + cnt) slot = sl;
+          }
+          if (slot >= 0) {
+            const uint32_t w = (uint32_t)slot >> 2, j = (uint32_t)slot & 3;
+            const uint32_t lo3[3] = {byte_of(w ? q[2].y : q[2].x, j), byte_of(w ? q[2].w : q[2].z, j), byte_of(w ? q[3].y : q[3].x, j)};
+            const uint32_t hi3[3] = {byte_of(w ? q[3].w : q[3].z, j), byte_of(w ? q[4].y : q[4].x, j), byte_of(w ? q[4].w : q[4].z, j)};
+            const float sc[3] = {u2f((q[0].w & 0xff) << 23), u2f(((q[0].w >> 8) & 0xff) << 23), u2f(((q[0].w >> 16) & 0xff) << 23)};
+            const float org[3] = {u2f(q[0].x), u2f(q[0].y), u2f(q[0].z)};
+            const float o3[3] = {r.o.x, r.o.y, r.o.z}, id3[3] = {r.idir.x, r.idir.y, r.idir.z};
+            float tmin = r.tnear;
+            for (int a = 0; a < 3; ++a)
+              tmin = fmaxf(tmin, (org[a] + (float)(id3[a] < 0.f ? hi3[a] : lo3[a]) * sc[a] - o3[a]) * id3[a]);
+            if (tmin > best.t) continue;
+          }
+        }
         vec3 v0, e1, e2; uint32_t prim;
         TriLoaderH{s->tris.data()}(q[1].y + (uint32_t)ti, v0, e1, e2, prim);
         ++tt;
