@@ -356,6 +356,89 @@ void emu_intersect_sorted(EmuScene* s, const float* rays, size_t n, uint64_t* ke
   *n_nodes = tn; *n_tris = tt;
 }
 
+// MEASUREMENT ONLY: a 32-lane model of the product's warp-synchronous loop (traverse.cuh LaneTrav::pass, one
+// domain): per pass every lane that wants a node step takes one together, then up to 8 rounds of triangle steps.
+// Counts how often each step kind is EXECUTED by the warp and by how many lanes, for two scheduling policies:
+//   refill = 0: the product's — a warp takes 32 rays and runs until the longest one ends
+//   refill = K: a stream — once K lanes are idle they all take their next rays together (K = 1: the upper bound
+//               of what any refill scheme can reach)
+// out[0..6] = node executions, node lanes, triangle executions, triangle lanes, passes, refill executions, lanes
+void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* out) {
+  struct Lane {
+    uint32_t ngx, ngy, tgx, tgy; int sp; bool alive; RayCtx r; Closest best;
+    uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+  };
+  std::vector<Lane> L(32);
+  uint64_t ne = 0, nl = 0, te = 0, tl = 0, passes = 0, rex = 0, rl = 0;
+  size_t next = 0;
+  auto load = [&](Lane& l) {
+    if (next >= n) { l.alive = false; return; }
+    const float* rr = rays + 8 * next++;
+    l.r = make_ray_ctx(mk3(rr[0], rr[1], rr[2]), mk3(rr[4], rr[5], rr[6]), rr[3]);
+    l.best.t = INFINITY; l.best.u = l.best.v = 0; l.best.prim = 0xFFFFFFFFu;
+    l.ngx = 0; l.ngy = 0x80000000u; l.tgx = l.tgy = 0; l.sp = 0; l.alive = true;
+  };
+  while (next < n) {
+    for (auto& l : L) load(l);
+    for (;;) {
+      int want[32]; bool any = false;
+      if (refill) {            // refill = K: all idle lanes take new rays together once at least K lanes are idle
+        int idle = 0;
+        for (auto& l : L) idle += !l.alive;
+        if (idle >= refill && next < n) { ++rex; rl += idle; for (auto& l : L) if (!l.alive) load(l); }
+      }
+      for (int i = 0; i < 32; ++i) {
+        Lane& l = L[i];
+        want[i] = 0;
+        if (!l.alive) continue;
+        if (l.tgy) { want[i] = 3; any = true; continue; }
+        if (l.ngy <= 0x00FFFFFFu && l.sp > 0) { --l.sp; l.ngx = l.sx[l.sp]; l.ngy = l.sy[l.sp]; }
+        if (l.ngy > 0x00FFFFFFu) { want[i] = 2; any = true; } else l.alive = false;
+      }
+      if (!any) { bool left = false; for (auto& l : L) left |= l.alive; if (!left) break; continue; }
+      ++passes;
+      int c = 0;
+      for (int i = 0; i < 32; ++i) if (want[i] == 2) {
+        Lane& l = L[i]; ++c;
+        const uint32_t imask = l.ngy & 0xffu;
+        const int bit = 31 - clz32(l.ngy);
+        l.ngy &= ~(1u << bit);
+        if (l.ngy > 0x00FFFFFFu && l.sp < SPRAY_STACK_SIZE) { l.sx[l.sp] = l.ngx; l.sy[l.sp] = l.ngy; ++l.sp; }
+        const uint32_t slot = (uint32_t)(bit - 24) ^ l.r.octinv;
+        const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+        const u4* q = &s->nodes[5 * (size_t)(l.ngx + rel)];
+#if SPRAY_POP_CULL
+        uint32_t u0, u1;
+        const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], l.r, l.best.t, &u0, &u1);
+#else
+        const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], l.r, l.best.t);
+#endif
+        l.ngx = q[1].x; l.tgx = q[1].y;
+        l.ngy = (hm & 0xFF000000u) | (q[0].w >> 24);
+        l.tgy = hm & 0x00FFFFFFu;
+      }
+      if (c) { ++ne; nl += c; }
+      for (int k = 0; k < 8; ++k) {
+        c = 0;
+        for (auto& l : L) if (l.alive && l.tgy) {
+          ++c;
+          const int ti = ffs32(l.tgy) - 1; l.tgy &= l.tgy - 1;
+          vec3 v0, e1, e2; uint32_t prim;
+          TriLoaderH{s->tris.data()}(l.tgx + (uint32_t)ti, v0, e1, e2, prim);
+          float T, U, V, ad;
+          if (tri_test_raw(l.r.o, l.r.d, v0, e1, e2, l.r.tnear, &T, &U, &V, &ad)) {
+            const float t = div_rn(T, ad);
+            if (t < l.best.t || (t == l.best.t && prim < l.best.prim)) { l.best.t = t; l.best.prim = prim; }
+          }
+        }
+        if (!c) break;
+        ++te; tl += c;
+      }
+    }
+  }
+  out[0] = ne; out[1] = nl; out[2] = te; out[3] = tl; out[4] = passes; out[5] = rex; out[6] = rl;
+}
+
 void emu_occluded(EmuScene* s, const float* rays, size_t n, uint8_t* occ) {
   uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
   for (size_t i = 0; i < n; ++i) {
