@@ -44,7 +44,7 @@ for name, v, f, rays in cases:
     for refill in (0, 1, 4, 8, 16, 24):
         out = np.zeros(7, np.uint64)
         E.emu_simt(C.c_void_p(h), rays.ctypes.data, C.c_size_t(len(rays)), refill, out.ctypes.data)
-        ne, nl, te, tl, _, rex, rl = [float(x) for x in out]
+        ne, nl, te, tl, npass, rex, rl = [float(x) for x in out]
         cost = (ne * CN + te * CT + rex * CR) / len(rays)
         base = base or cost
-        print("%-22s %-10s %9.0f %9.1f %9.0f %9.1f %9.0f %12.1f  (%.2fx)" % (name, "refill>=%d" % refill if refill else "batch32", ne, nl / max(ne, 1), te, tl / max(te, 1), rex, cost, base / cost))
+        print("%-22s %-10s %9.0f %9.1f %9.0f %9.1f %9.0f %12.1f  (%.2fx)  passes/32 rays %6.1f" % (name, "refill>=%d" % refill if refill else "batch32", ne, nl / max(ne, 1), te, tl / max(te, 1), rex, cost, base / cost, npass * 32 / len(rays)))
