@@ -367,6 +367,7 @@ void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* ou
   struct Lane {
     uint32_t ngx, ngy, tgx, tgy; int sp; bool alive; RayCtx r; Closest best;
     uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
+    uint32_t gd0, gd1, s0[SPRAY_STACK_SIZE], s1[SPRAY_STACK_SIZE];   // SPRAY_POP_CULL builds only
   };
   std::vector<Lane> L(32);
   uint64_t ne = 0, nl = 0, te = 0, tl = 0, passes = 0, rex = 0, rl = 0;
@@ -376,7 +377,7 @@ void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* ou
     const float* rr = rays + 8 * next++;
     l.r = make_ray_ctx(mk3(rr[0], rr[1], rr[2]), mk3(rr[4], rr[5], rr[6]), rr[3]);
     l.best.t = INFINITY; l.best.u = l.best.v = 0; l.best.prim = 0xFFFFFFFFu;
-    l.ngx = 0; l.ngy = 0x80000000u; l.tgx = l.tgy = 0; l.sp = 0; l.alive = true;
+    l.ngx = 0; l.ngy = 0x80000000u; l.tgx = l.tgy = 0; l.sp = 0; l.alive = true; l.gd0 = l.gd1 = 0;
   };
   while (next < n) {
     for (auto& l : L) load(l);
@@ -392,7 +393,14 @@ void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* ou
         want[i] = 0;
         if (!l.alive) continue;
         if (l.tgy) { want[i] = 3; any = true; continue; }
+#if SPRAY_POP_CULL
+        while (l.ngy <= 0x00FFFFFFu && l.sp > 0) {
+          --l.sp; l.ngx = l.sx[l.sp]; l.gd0 = l.s0[l.sp]; l.gd1 = l.s1[l.sp];
+          l.ngy = prune_group(l.sy[l.sp], l.gd0, l.gd1, l.best.t, l.r.octinv);
+        }
+#else
         if (l.ngy <= 0x00FFFFFFu && l.sp > 0) { --l.sp; l.ngx = l.sx[l.sp]; l.ngy = l.sy[l.sp]; }
+#endif
         if (l.ngy > 0x00FFFFFFu) { want[i] = 2; any = true; } else l.alive = false;
       }
       if (!any) { bool left = false; for (auto& l : L) left |= l.alive; if (!left) break; continue; }
@@ -403,13 +411,12 @@ void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* ou
         const uint32_t imask = l.ngy & 0xffu;
         const int bit = 31 - clz32(l.ngy);
         l.ngy &= ~(1u << bit);
-        if (l.ngy > 0x00FFFFFFu && l.sp < SPRAY_STACK_SIZE) { l.sx[l.sp] = l.ngx; l.sy[l.sp] = l.ngy; ++l.sp; }
+        if (l.ngy > 0x00FFFFFFu && l.sp < SPRAY_STACK_SIZE) { l.sx[l.sp] = l.ngx; l.sy[l.sp] = l.ngy; l.s0[l.sp] = l.gd0; l.s1[l.sp] = l.gd1; ++l.sp; }
         const uint32_t slot = (uint32_t)(bit - 24) ^ l.r.octinv;
         const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
         const u4* q = &s->nodes[5 * (size_t)(l.ngx + rel)];
 #if SPRAY_POP_CULL
-        uint32_t u0, u1;
-        const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], l.r, l.best.t, &u0, &u1);
+        const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], l.r, l.best.t, &l.gd0, &l.gd1);
 #else
         const uint32_t hm = node8_hits(q[0], q[1], q[2], q[3], q[4], l.r, l.best.t);
 #endif
@@ -428,7 +435,12 @@ void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* ou
           float T, U, V, ad;
           if (tri_test_raw(l.r.o, l.r.d, v0, e1, e2, l.r.tnear, &T, &U, &V, &ad)) {
             const float t = div_rn(T, ad);
-            if (t < l.best.t || (t == l.best.t && prim < l.best.prim)) { l.best.t = t; l.best.prim = prim; }
+            if (t < l.best.t || (t == l.best.t && prim < l.best.prim)) {
+              l.best.t = t; l.best.prim = prim;
+#if SPRAY_POP_CULL
+              l.ngy = prune_group(l.ngy, l.gd0, l.gd1, l.best.t, l.r.octinv);
+#endif
+            }
           }
         }
         if (!c) break;

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """CPU model of the warp-synchronous traversal loop (tests/hostemu emu_simt): lanes per executed step for the
 product's 32-ray batches vs an ideal refill stream, on coherent (camera) and incoherent rays.
-usage: tools/simt_model.py"""
+usage: tools/simt_model.py [-DSPRAY_POP_CULL=1]"""
 import ctypes as C, os, subprocess, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -11,12 +11,12 @@ from conftest import random_rays, make_rays
 
 so = "/tmp/libhostemu_simt.so"
 subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-mavx2", "-mfma",
-                "-Wno-unknown-pragmas", "-o", so, os.path.join(ROOT, "tests/hostemu/hostemu.cpp")], check=True)
+                "-Wno-unknown-pragmas"] + sys.argv[1:] + ["-o", so, os.path.join(ROOT, "tests/hostemu/hostemu.cpp")], check=True)
 E = C.CDLL(so)
 E.emu_build.restype = C.c_void_p
 E.emu_build.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
 E.emu_simt.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
-CN, CT = 257.0, 35.0     # SASS instructions of one node step / one triangle step (r02c build)
+CN, CT = (281.0 if "-DSPRAY_POP_CULL=1" in sys.argv else 257.0), 35.0     # SASS instructions of one node step / one triangle step (r02c build)
 CR = 150.0               # assumed cost of one refill execution (park the hits, pop + set up the next rays)
 
 def camera_rays(lo, hi, w=256, h=256):
