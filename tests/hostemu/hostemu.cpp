@@ -360,30 +360,46 @@ void emu_intersect_sorted(EmuScene* s, const float* rays, size_t n, uint64_t* ke
 // domain): per pass every lane that wants a node step takes one together, then up to 8 rounds of triangle steps.
 // Counts how often each step kind is EXECUTED by the warp and by how many lanes, for two scheduling policies:
 //   refill = 0: the product's — a warp takes 32 rays and runs until the longest one ends
+//   refill = -K: batches that END once fewer than K lanes are alive; the unfinished rays go back to the queue with
+//               their best hit so far and are later restarted from the root (each ray is cut at most once)
 //   refill = K: a stream — once K lanes are idle they all take their next rays together (K = 1: the upper bound
 //               of what any refill scheme can reach)
 // out[0..6] = node executions, node lanes, triangle executions, triangle lanes, passes, refill executions, lanes
 void emu_simt(EmuScene* s, const float* rays, size_t n, int refill, uint64_t* out) {
   struct Lane {
     uint32_t ngx, ngy, tgx, tgy; int sp; bool alive; RayCtx r; Closest best;
+    size_t ray; bool again;      // ray index; again: this ray was cut once already and must run to its end
     uint32_t sx[SPRAY_STACK_SIZE], sy[SPRAY_STACK_SIZE];
     uint32_t gd0, gd1, s0[SPRAY_STACK_SIZE], s1[SPRAY_STACK_SIZE];   // SPRAY_POP_CULL builds only
   };
   std::vector<Lane> L(32);
   uint64_t ne = 0, nl = 0, te = 0, tl = 0, passes = 0, rex = 0, rl = 0;
   size_t next = 0;
+  struct Cut { size_t ray; Closest best; };
+  std::vector<Cut> cut;          // refill < 0: rays cut out of a thinning batch, restarted from the root with their best hit
   auto load = [&](Lane& l) {
-    if (next >= n) { l.alive = false; return; }
-    const float* rr = rays + 8 * next++;
+    if (cut.empty() && next >= n) { l.alive = false; return; }
+    l.best.t = INFINITY; l.best.u = l.best.v = 0; l.best.prim = 0xFFFFFFFFu; l.again = false;
+    if (!cut.empty()) { l.ray = cut.back().ray; l.best = cut.back().best; l.again = true; cut.pop_back(); }
+    else l.ray = next++;
+    const float* rr = rays + 8 * l.ray;
     l.r = make_ray_ctx(mk3(rr[0], rr[1], rr[2]), mk3(rr[4], rr[5], rr[6]), rr[3]);
-    l.best.t = INFINITY; l.best.u = l.best.v = 0; l.best.prim = 0xFFFFFFFFu;
     l.ngx = 0; l.ngy = 0x80000000u; l.tgx = l.tgy = 0; l.sp = 0; l.alive = true; l.gd0 = l.gd1 = 0;
   };
-  while (next < n) {
+  while (next < n || !cut.empty()) {
     for (auto& l : L) load(l);
     for (;;) {
       int want[32]; bool any = false;
-      if (refill) {            // refill = K: all idle lanes take new rays together once at least K lanes are idle
+      if (refill < 0) {        // refill = -K: the batch ends once fewer than K lanes are alive; the rest is re-queued
+        int alive = 0; bool pinned = false;
+        for (auto& l : L) { alive += l.alive; pinned |= l.alive && l.again; }
+        if (alive > 0 && alive < -refill && !pinned && next < n) {
+          ++rex; rl += alive;
+          for (auto& l : L) if (l.alive) { cut.push_back({l.ray, l.best}); l.alive = false; }
+          break;
+        }
+      }
+      if (refill > 0) {            // refill = K: all idle lanes take new rays together once at least K lanes are idle
         int idle = 0;
         for (auto& l : L) idle += !l.alive;
         if (idle >= refill && next < n) { ++rex; rl += idle; for (auto& l : L) if (!l.alive) load(l); }

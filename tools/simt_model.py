@@ -41,10 +41,10 @@ print("%-22s %-10s %9s %9s %9s %9s %9s %12s" % ("rays", "policy", "node ex", "la
 for name, v, f, rays in cases:
     h = E.emu_build(v.ctypes.data, len(v), f.ctypes.data, len(f))
     base = None
-    for refill in (0, 1, 4, 8, 16, 24):
+    for refill in (0, 1, 4, 8, 16, 24, -4, -8, -12, -16):
         out = np.zeros(7, np.uint64)
         E.emu_simt(C.c_void_p(h), rays.ctypes.data, C.c_size_t(len(rays)), refill, out.ctypes.data)
         ne, nl, te, tl, npass, rex, rl = [float(x) for x in out]
         cost = (ne * CN + te * CT + rex * CR) / len(rays)
         base = base or cost
-        print("%-22s %-10s %9.0f %9.1f %9.0f %9.1f %9.0f %12.1f  (%.2fx)  passes/32 rays %6.1f" % (name, "refill>=%d" % refill if refill else "batch32", ne, nl / max(ne, 1), te, tl / max(te, 1), rex, cost, base / cost, npass * 32 / len(rays)))
+        print("%-22s %-10s %9.0f %9.1f %9.0f %9.1f %9.0f %12.1f  (%.2fx)  passes/32 rays %6.1f" % (name, ("refill>=%d" % refill if refill > 0 else "cut<%d" % -refill) if refill else "batch32", ne, nl / max(ne, 1), te, tl / max(te, 1), rex, cost, base / cost, npass * 32 / len(rays)))
