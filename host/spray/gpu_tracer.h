@@ -57,6 +57,8 @@ class GpuTracer {
     shade_.ao_samples = cfg.ao_samples;
     for (int k = 0; k < 3; ++k) shade_.ks[k] = cfg.ks[k];
     shade_.shininess = cfg.shininess;
+    // in-situ tracers jitter multi-sample eye rays with (pixid, s), the ooc tracer with bufid (insitu_ray.h:161-165)
+    shade_.eye_seed = insitu_ ? SPRAYGPU_EYE_SEED_INSITU : SPRAYGPU_EYE_SEED_OOC;
     const std::vector<Light*>& lights = scene->getLights();
     if (ShaderTag::kind == SPRAYGPU_SHADER_PT) SPRAY_CHECK(lights.size() > 0, "the PT shader needs a light (ooc_tracer.inl:68)");
     SPRAY_CHECK(lights.size() <= SPRAYGPU_MAX_LIGHTS, lights.size() << " lights");

@@ -91,7 +91,13 @@ typedef struct {
   float shininess;        /* cfg.shininess */
   int32_t nlights;
   spraygpu_light lights[SPRAYGPU_MAX_LIGHTS];
+  int32_t eye_seed;       /* SPRAYGPU_EYE_SEED_*: how multi-sample eye rays are jittered (ignored at 1 spp) */
 } spraygpu_shade;
+/* The reference's two tracer families seed the pixel jitter differently:
+ *   OOC    RandomSampler_init(sampler, bufid)     bufid = spp * tile-relative pixel + s   (src/ooc/ooc_tracer.inl:151-155)
+ *   INSITU RandomSampler_init(sampler, pixid, s)  pixid = image_w * y + x                 (src/insitu/insitu_ray.h:161-165)
+ * spraygpu_trace_tile_insitu always uses INSITU; the other trace calls follow shade->eye_seed. */
+enum { SPRAYGPU_EYE_SEED_OOC = 0, SPRAYGPU_EYE_SEED_INSITU = 1 };
 
 typedef struct {
   uint64_t eye_rays;        /* primary rays generated */
@@ -108,6 +114,8 @@ typedef struct {
   uint64_t node_bytes, tri_bytes, attr_bytes;
   float bounds[6];
   double build_ms;  /* device time of the last commit (CUDA events) */
+  uint32_t bvh_depth; /* levels of the 8-wide BVH; commit fails with SPRAYGPU_ERR_LIMIT above the traversal stack (48) */
+  uint32_t reserved;
 } spraygpu_scene_info;
 
 SPRAYGPU_API const char* spraygpu_last_error(void);
@@ -174,6 +182,10 @@ SPRAYGPU_API int spraygpu_hit_attributes(spraygpu_device dev, const spraygpu_ray
 /* Eye rays of a blocking tile (ooc::Tracer::genSingleEyes/genMultiEyes, ooc_tracer.inl:84-172).  [h|d] */
 SPRAYGPU_API int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
                           spraygpu_ray* rays);
+/* The in-situ tracers' eye rays (insitu::genSingleSampleEyeRays / genMultiSampleEyeRays,
+ * src/insitu/insitu_ray.h:103-182): same layout, jitter seeded with (pixid, s).  [h|d] */
+SPRAYGPU_API int spraygpu_gen_eye_rays_insitu(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
+                                              spraygpu_ray* rays);
 
 /* ---- the fused path: one blocking tile from eye rays to radiance in the frame buffer.
  * Replaces ooc::Tracer::trace's per-tile body (ooc_tracer.inl:184-234): genSingleEyes/genMultiEyes,
@@ -198,6 +210,15 @@ SPRAYGPU_API int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu
  * With a host fb it falls back to per-tile launches whose D2H copies overlap the next tile (and synchronises). [h|d] */
 SPRAYGPU_API int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                       const spraygpu_tile* tiles, int ntiles, float* fb_rgba, spraygpu_stats* stats);
+
+/* The same for RECTANGLES of blocking tiles: rects[i] (inside blocking_tiles[i]) is rendered, but every sample keeps the
+ * samid it has in its blocking tile, so seeds (samid * depth, ooc_shader_pt.h:130,217; bufid jitter, ooc_tracer.inl:152)
+ * and therefore the image do not depend on how a frame is cut across GPUs.  (The reference's --partition image numbers
+ * samples per rank-local stripe, src/render/tile.cc:317-391, so ITS multi-sample / multi-bounce noise pattern changes
+ * with the rank count.)  fb must be a device pointer. */
+SPRAYGPU_API int spraygpu_trace_frame_rects(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                                            const spraygpu_tile* rects, const spraygpu_tile* blocking_tiles, int n,
+                                            float* fb_rgba, spraygpu_stats* stats);
 
 /* ---- out-of-core: the device cache holds fewer domains than the tile enters.
  * Replaces ooc::PContext::isectPrims' domain loop (src/ooc/ooc_pcontext.h:92-181): per round, schedule the
@@ -259,6 +280,35 @@ SPRAYGPU_API int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm c
 SPRAYGPU_API int spraygpu_image_gather_blocks(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, int image_w, int nblocks,
                                               const int32_t* block_row_begin /* nblocks + 1 */,
                                               const int32_t* block_owner /* nblocks */, int root);
+/* ---- the frame image: replaces HdrImage (src/display/image.h:58-239: buf, clear(), composite() = MPI_Reduce(SUM) of
+ *      every rank's whole image into rank 0, :167-181) on the GPU path.  A frame is traced into a DEVICE render target;
+ *      spraygpu_image_flush then moves the rows THIS rank rendered — one kernel of this library, 16-byte stores on
+ *      peer-mapped (CUDA IPC over NVLink) / host-mapped (pinned, PCIe) pointers, no collective call per frame — and
+ *      zeroes the render target (the next frame's image.clear()).  Only pixels that are non-zero, or were non-zero
+ *      when last flushed to that destination, are written; the destination is bit-identical to a full copy as long as
+ *      nothing else writes it.
+ *      comm == NULL: single GPU (no root composite).  shm_name != NULL: the host image is a POSIX shared-memory
+ *      segment registered with CUDA in every rank (all ranks of the box write ONE host image, each over its own PCIe
+ *      link); NULL: a private pinned allocation.  image_w must be a multiple of 32.  Collective when comm != NULL. */
+typedef struct spraygpu_image_s* spraygpu_image;
+SPRAYGPU_API int spraygpu_image_create(spraygpu_device dev, spraygpu_comm comm, int image_w, int image_h, const char* shm_name,
+                                       spraygpu_image* out);
+SPRAYGPU_API int spraygpu_image_destroy(spraygpu_image img);                 /* collective when created with a comm */
+SPRAYGPU_API float* spraygpu_image_device(spraygpu_image img);               /* this rank's render target (device, w*h float4) */
+SPRAYGPU_API float* spraygpu_image_host(spraygpu_image img);                 /* HdrImage::buf: pinned host pixels */
+SPRAYGPU_API float* spraygpu_image_root(spraygpu_image img);                 /* the root's composite as mapped in THIS process (device) */
+/* Which rows this rank renders: blocks [row_begin[b], row_begin[b+1]) with owner[b] == rank (owner NULL: all mine).
+ * Replaces the rank's stripe of ImageScheduleTileList (src/render/tile.cc:317-391). */
+SPRAYGPU_API int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_begin /* nblocks + 1 */,
+                                         const int32_t* owner /* nblocks or NULL */);
+/* HdrImage::composite (to_root) and/or the download into HdrImage::buf (to_host) for this rank's rows, then
+ * image.clear() of the render target (clear).  Enqueued on the device's stream. */
+SPRAYGPU_API int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear);
+/* cumulative pixels (16 B each) stored to the root composite / the host image by this rank's flushes */
+SPRAYGPU_API int spraygpu_image_flushed_pixels(spraygpu_image img, uint64_t* to_root, uint64_t* to_host);
+/* stream synchronise + rendezvous of all ranks: after it every rank's flushed rows are visible at their destination */
+SPRAYGPU_API int spraygpu_image_barrier(spraygpu_image img);
+
 /* ncclAllReduce(ncclUint64, ncclMin) on hit keys / ncclAllReduce(ncclUint8, ncclMax) on occlusion bytes,
  * in place on device buffers: the building blocks for callers that drive spraygpu_intersect_domains /
  * spraygpu_occluded_domains themselves. */

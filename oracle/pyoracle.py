@@ -45,7 +45,8 @@ class Light(C.Structure):
 
 class Shade(C.Structure):
     _fields_ = [("shader", C.c_int), ("bounces", C.c_int), ("pixel_samples", C.c_int), ("ao_samples", C.c_int),
-                ("ks", C.c_float * 3), ("shininess", C.c_float), ("nlights", C.c_int), ("lights", C.POINTER(Light))]
+                ("ks", C.c_float * 3), ("shininess", C.c_float), ("nlights", C.c_int), ("lights", C.POINTER(Light)),
+                ("eye_seed", C.c_int)]
 
 
 class Stats(C.Structure):
@@ -95,6 +96,7 @@ def lib():
     L.orc_scene_get_normals.argtypes = [vp, C.c_int, f32p]
     L.orc_scene_get_verts.argtypes = [vp, C.c_int, f32p]
     L.orc_gen_eye_rays.argtypes = [C.POINTER(Camera), Tile, C.c_int, vp]
+    L.orc_gen_eye_rays_seed.argtypes = [C.POINTER(Camera), Tile, C.c_int, C.c_int, vp]
     L.orc_domain_lists.argtypes = [vp, vp, C.c_size_t, C.c_int, i32p, i32p, f32p]
     L.orc_intersect.argtypes = [vp, vp, C.c_size_t, u64p, f32p]
     L.orc_intersect_brute.argtypes = [vp, vp, C.c_size_t, u64p, f32p]
@@ -147,8 +149,10 @@ def image_schedule_tiles(w, h, spp, nranks, rank, max_samples):
     return [(buf[i].x, buf[i].y, buf[i].w, buf[i].h) for i in range(n)]
 
 
-def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4, 0.4), shininess=10.0, lights=()):
-    """lights: sequence of (type, position3, radiance3).  Returns (Shade, keepalive)."""
+def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4, 0.4), shininess=10.0, lights=(),
+               eye_seed=0):
+    """lights: sequence of (type, position3, radiance3).  eye_seed 1 = the in-situ tracers' (pixid, s) jitter seed.
+    Returns (Shade, keepalive)."""
     arr = (Light * max(1, len(lights)))()
     for i, (ty, pos, rad) in enumerate(lights):
         arr[i].type = ty
@@ -160,6 +164,7 @@ def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4,
         sh.ks[k] = float(ks[k])
     sh.shininess = float(shininess)
     sh.nlights = len(lights)
+    sh.eye_seed = int(eye_seed)
     sh.lights = C.cast(arr, C.POINTER(Light))
     return sh, arr
 
@@ -276,10 +281,10 @@ class Scene:
         return fb, st
 
 
-def gen_eye_rays(cam, tile, spp=1):
+def gen_eye_rays(cam, tile, spp=1, eye_seed=0):
     x, y, w, h = tile
     rays = np.zeros((w * h * spp, 8), np.float32)
-    lib().orc_gen_eye_rays(C.byref(cam), Tile(x, y, w, h), spp, rays.ctypes.data_as(C.c_void_p))
+    lib().orc_gen_eye_rays_seed(C.byref(cam), Tile(x, y, w, h), spp, int(eye_seed), rays.ctypes.data_as(C.c_void_p))
     return rays
 
 

@@ -935,7 +935,10 @@ void orc_hit_attributes(const OrcScene* s, const uint64_t* keys, const float* uv
 }
 
 /* ---- eye rays: ooc_tracer.inl:84-172 ---- */
-void orc_gen_eye_rays(const OrcCamera* cam, OrcTile tile, int spp, OrcRay* rays) {
+/* eye_seed 1 = insitu::genMultiSampleEyeRays (insitu_ray.h:143-182): the jitter sampler is seeded with (pixid, s) */
+void orc_gen_eye_rays_seed(const OrcCamera* cam, OrcTile tile, int spp, int eye_seed, OrcRay* rays);
+void orc_gen_eye_rays(const OrcCamera* cam, OrcTile tile, int spp, OrcRay* rays) { orc_gen_eye_rays_seed(cam, tile, spp, 0, rays); }
+void orc_gen_eye_rays_seed(const OrcCamera* cam, OrcTile tile, int spp, int eye_seed, OrcRay* rays) {
 #pragma omp parallel for schedule(static)
   for (int y0 = 0; y0 < tile.h; ++y0) {
     for (int x0 = 0; x0 < tile.w; ++x0) {
@@ -944,7 +947,7 @@ void orc_gen_eye_rays(const OrcCamera* cam, OrcTile tile, int spp, OrcRay* rays)
         int bufid = spp * (y0 * tile.w + x0) + sidx;
         float fx = (float)x, fy = (float)y;
         if (spp > 1) {
-          uint32_t st = orc_rng_init1(bufid);
+          uint32_t st = eye_seed ? orc_rng_init2(y * cam->image_w + x, sidx) : orc_rng_init1(bufid);
           fx = (float)x + orc_rng_get_float(&st);
           fy = (float)y + orc_rng_get_float(&st);
         }
@@ -1140,7 +1143,7 @@ void orc_render_tile(const OrcScene* s, const OrcCamera* cam, const OrcShade* sh
         int bufid = spp * (y0 * tile.w + x0) + sidx;
         float fx = (float)x, fy = (float)y;
         if (spp > 1) {
-          uint32_t rs = orc_rng_init1(bufid);
+          uint32_t rs = sh->eye_seed ? orc_rng_init2(pixid, sidx) : orc_rng_init1(bufid);
           fx = (float)x + orc_rng_get_float(&rs);
           fy = (float)y + orc_rng_get_float(&rs);
         }

@@ -61,6 +61,8 @@ typedef struct {
   float shininess;
   int nlights;
   const OrcLight* lights;
+  int eye_seed;      /* 0: ooc tracers, RandomSampler_init(bufid) (ooc_tracer.inl:151-155);
+                        1: in-situ tracers, RandomSampler_init(pixid, s) (insitu_ray.h:161-165) */
 } OrcShade;
 
 typedef struct {
@@ -132,6 +134,7 @@ void orc_hit_attributes(const OrcScene*, const uint64_t* keys, const float* uv, 
                         float* ns3);
 
 /* ---- full path: eye rays -> closest hit -> shade -> shadow/bounce -> framebuffer ---- */
+void orc_gen_eye_rays_seed(const OrcCamera* cam, OrcTile tile, int spp, int eye_seed, OrcRay* rays);
 void orc_render_tile(const OrcScene*, const OrcCamera*, const OrcShade*, OrcTile tile, float* fb_rgba,
                      OrcStats* stats);
 int orc_num_threads(void);

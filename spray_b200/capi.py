@@ -60,7 +60,7 @@ class Tile(C.Structure):
 class Shade(C.Structure):
     _fields_ = [("shader", C.c_int32), ("bounces", C.c_int32), ("pixel_samples", C.c_int32),
                 ("ao_samples", C.c_int32), ("ks", C.c_float * 3), ("shininess", C.c_float), ("nlights", C.c_int32),
-                ("lights", Light * MAX_LIGHTS)]
+                ("lights", Light * MAX_LIGHTS), ("eye_seed", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -74,7 +74,7 @@ class Stats(C.Structure):
 class SceneInfo(C.Structure):
     _fields_ = [("num_vertices", C.c_uint64), ("num_faces", C.c_uint64), ("num_nodes", C.c_uint64),
                 ("node_bytes", C.c_uint64), ("tri_bytes", C.c_uint64), ("attr_bytes", C.c_uint64),
-                ("bounds", C.c_float * 6), ("build_ms", C.c_double)]
+                ("bounds", C.c_float * 6), ("build_ms", C.c_double), ("bvh_depth", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 _vp = C.c_void_p
@@ -103,10 +103,12 @@ _PROTOS = {
     "spraygpu_occluded_domains": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_int]),
     "spraygpu_hit_attributes": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
     "spraygpu_gen_eye_rays": (C.c_int, [_vp, C.POINTER(Camera), Tile, C.c_int, _vp]),
+    "spraygpu_gen_eye_rays_insitu": (C.c_int, [_vp, C.POINTER(Camera), Tile, C.c_int, _vp]),
     "spraygpu_trace_tile": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_counted": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_async": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp]),
     "spraygpu_trace_frame": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), _vp, C.c_int, _vp, C.POINTER(Stats)]),
+    "spraygpu_trace_frame_rects": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), _vp, _vp, C.c_int, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_ooc": (C.c_int, [_vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.c_int, _vp, _vp, C.POINTER(Stats)]),
     # multi-GPU (NCCL resolved at run time)
     "spraygpu_comm_unique_id": (C.c_int, [C.c_char_p]),
@@ -117,6 +119,15 @@ _PROTOS = {
     "spraygpu_image_reduce": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
     "spraygpu_image_gather_rows": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int]),
     "spraygpu_image_gather_blocks": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, _vp, _vp, C.c_int]),
+    "spraygpu_image_create": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_char_p, C.POINTER(_vp)]),
+    "spraygpu_image_destroy": (C.c_int, [_vp]),
+    "spraygpu_image_device": (_vp, [_vp]),
+    "spraygpu_image_host": (_vp, [_vp]),
+    "spraygpu_image_root": (_vp, [_vp]),
+    "spraygpu_image_set_rows": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "spraygpu_image_flush": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "spraygpu_image_flushed_pixels": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "spraygpu_image_barrier": (C.c_int, [_vp]),
     "spraygpu_allreduce_keys_min": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "spraygpu_allreduce_occ_max": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
 }
@@ -175,9 +186,14 @@ def make_camera(desc):
     return cam
 
 
-def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4, 0.4), shininess=10.0, lights=()):
+EYE_SEED_OOC, EYE_SEED_INSITU = 0, 1
+
+
+def make_shade(shader=0, bounces=1, pixel_samples=1, ao_samples=1, ks=(0.4, 0.4, 0.4), shininess=10.0, lights=(),
+               eye_seed=EYE_SEED_OOC):
     sh = Shade()
     sh.shader, sh.bounces, sh.pixel_samples, sh.ao_samples = shader, bounces, pixel_samples, ao_samples
+    sh.eye_seed = int(eye_seed)
     for k in range(3):
         sh.ks[k] = float(ks[k])
     sh.shininess = float(shininess)
@@ -252,6 +268,8 @@ class Device:
         for i, d in enumerate(doms):
             if i not in owned:
                 continue
+            if d.get("verts") is None:
+                raise SprayGpuError("load_scene: domain %d is owned but carries no mesh" % i)
             s = self.new_scene()
             s.set_mesh(d["verts"], d["faces"], d.get("rgb"))
             s.set_transform(d.get("transform"))
@@ -273,8 +291,9 @@ class Device:
     def hit_attributes(self, rays, keys, n, color, ns3):
         _check(lib().spraygpu_hit_attributes(self.h, _ptr(rays), _ptr(keys), n, _ptr(color), _ptr(ns3)))
 
-    def gen_eye_rays(self, cam, tile, spp, rays):
-        _check(lib().spraygpu_gen_eye_rays(self.h, C.byref(cam), Tile(*tile), spp, _ptr(rays)))
+    def gen_eye_rays(self, cam, tile, spp, rays, insitu=False):
+        fn = lib().spraygpu_gen_eye_rays_insitu if insitu else lib().spraygpu_gen_eye_rays
+        _check(fn(self.h, C.byref(cam), Tile(*tile), spp, _ptr(rays)))
 
     def trace_tile_async(self, cam, shade, tile, fb):
         """Host frame buffer: returns once the tile is enqueued; rows are valid after synchronize()."""
@@ -293,6 +312,16 @@ class Device:
         arr = (Tile * len(tiles))(*[Tile(*t) for t in tiles])
         _check(lib().spraygpu_trace_frame(self.h, C.byref(cam), C.byref(shade), C.cast(arr, _vp), len(tiles), _ptr(fb),
                                           C.byref(st) if st is not None else None))
+        return st
+
+    def trace_frame_rects(self, cam, shade, rects, blocking_tiles, fb, stats=False):
+        """Rectangles of blocking tiles in one persistent launch; samples keep their blocking tile's samid."""
+        st = Stats() if stats else None
+        assert len(rects) == len(blocking_tiles)
+        ra = (Tile * max(len(rects), 1))(*[Tile(*t) for t in rects])
+        pa = (Tile * max(len(rects), 1))(*[Tile(*t) for t in blocking_tiles])
+        _check(lib().spraygpu_trace_frame_rects(self.h, C.byref(cam), C.byref(shade), C.cast(ra, _vp), C.cast(pa, _vp), len(rects),
+                                                _ptr(fb), C.byref(st) if st is not None else None))
         return st
 
     def trace_tile_ooc(self, cam, shade, tile, fb, max_resident, load, stats=False):
@@ -419,6 +448,54 @@ class Comm:
         _check(lib().spraygpu_allreduce_occ_max(self.dev.h, self.h, _ptr(occ), int(n)))
 
 
+class Image:
+    """The frame image (HdrImage on the GPU path): device render target + pinned host pixels (+ the root's composite
+    at N > 1).  `device` / `root` are raw device addresses (pass them as fb); `host` is a numpy view."""
+
+    def __init__(self, dev, comm, w, h, shm_name=None):
+        self.dev, self.comm, self.w, self.h = dev, comm, int(w), int(h)
+        self.h_ = _vp()
+        _check(lib().spraygpu_image_create(dev.h, comm.h if comm is not None else None, self.w, self.h,
+                                           shm_name.encode() if shm_name else None, C.byref(self.h_)))
+        self.device = lib().spraygpu_image_device(self.h_)
+        self.root = lib().spraygpu_image_root(self.h_)
+        hp = lib().spraygpu_image_host(self.h_)
+        self.host = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(self.h, self.w, 4))
+
+    def set_rows(self, row_begin, owner=None):
+        rb = np.ascontiguousarray(row_begin, np.int32)
+        ow = None if owner is None else np.ascontiguousarray(owner, np.int32)
+        _check(lib().spraygpu_image_set_rows(self.h_, len(rb) - 1, rb.ctypes.data, None if ow is None else ow.ctypes.data))
+
+    def flush(self, to_root=False, to_host=False, clear=True):
+        _check(lib().spraygpu_image_flush(self.h_, int(to_root), int(to_host), int(clear)))
+
+    def flushed_pixels(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(lib().spraygpu_image_flushed_pixels(self.h_, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def barrier(self):
+        _check(lib().spraygpu_image_barrier(self.h_))
+
+    def read_device(self, which="device"):
+        """D2H copy of the render target / root composite (tests, parity checks)."""
+        import torch
+        out = np.zeros((self.h, self.w, 4), np.float32)
+        src = self.device if which == "device" else self.root
+        rt = torch.cuda.cudart()
+        self.dev.synchronize()
+        err = rt.cudaMemcpy(out.ctypes.data, src, out.nbytes, 2)   # cudaMemcpyDeviceToHost
+        if int(err) != 0:
+            raise SprayGpuError("cudaMemcpy D2H failed: %s" % err)
+        return out
+
+    def close(self):
+        if self.h_:
+            lib().spraygpu_image_destroy(self.h_)
+            self.h_ = _vp()
+
+
 class Scene:
     def __init__(self, dev):
         self.dev = dev
@@ -431,6 +508,15 @@ class Scene:
             self.h = _vp()
 
     def set_mesh(self, verts, faces, rgb=None):
+        if hasattr(verts, "data_ptr"):
+            # torch tensors (CUDA or pinned host): passed by pointer, copied device-side by the library
+            assert verts.is_contiguous() and faces.is_contiguous() and (rgb is None or rgb.is_contiguous())
+            assert verts.element_size() == 4 and faces.element_size() == 4
+            nv, nf = verts.numel() // 3, faces.numel() // 3
+            _check(lib().spraygpu_scene_set_mesh(self.h, verts.data_ptr(), nv, faces.data_ptr(), nf,
+                                                 None if rgb is None else rgb.data_ptr()))
+            self.nv, self.nf = nv, nf
+            return
         v = np.ascontiguousarray(verts, np.float32).reshape(-1, 3)
         f = np.ascontiguousarray(faces, np.uint32).reshape(-1, 3)
         c = None if rgb is None else np.ascontiguousarray(rgb, np.uint32)

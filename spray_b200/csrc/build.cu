@@ -416,6 +416,24 @@ __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
   if (i < n) p[i] = v;
 }
 
+// largest vertex index of the face list (spraygpu_scene_set_mesh validates it against nv: an out-of-range index of
+// a malformed / truncated PLY would otherwise become out-of-bounds device WRITES in segments_kernel at commit)
+__global__ void __launch_bounds__(256) max_index_kernel(const uint32_t* __restrict__ idx, size_t n, uint32_t* __restrict__ out) {
+  uint32_t m = 0u;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) m = max(m, idx[i]);
+  m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+
+int launch_max_index(Device* dev, const uint32_t* d_idx, size_t n, uint32_t* d_out) {
+  SG_CUDA(cudaMemsetAsync(d_out, 0, sizeof(uint32_t), dev->stream));
+  const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)dev->sm_count * 8);
+  max_index_kernel<<<grid, 256, 0, dev->stream>>>(d_idx, n, d_out);
+  dev->launches++;
+  SG_CUDA(cudaGetLastError());
+  return SPRAYGPU_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 int ensure_scratch(Scratch& s, size_t bytes) {
   if (bytes <= s.bytes) return SPRAYGPU_OK;
@@ -527,6 +545,7 @@ int build_scene(Scene* sc) {
     single_tri_kernel<<<1, 1, 0, st>>>(sc->d_verts, sc->d_faces, tlo, thi, sc->d_nodes, sc->d_tris);
     dev->launches++;
     sc->n_nodes = 1;
+    sc->bvh_depth = 1;
   } else {
     morton_kernel<<<grid_for(nf, T), T, 0, st>>>(tlo, thi, n, bounds, kA, vA);
     dev->launches++;
@@ -544,8 +563,9 @@ int build_scene(Scene* sc) {
       int root = 0;
       SG_CUDA(cudaMemcpyAsync(counters, hc, sizeof(hc), cudaMemcpyHostToDevice, st));
       SG_CUDA(cudaMemcpyAsync(queue, &root, sizeof(int), cudaMemcpyHostToDevice, st));
-      int begin = 0, end = 1;
+      int begin = 0, end = 1, levels = 0;
       while (begin < end) {
+        ++levels;
         collapse_kernel<<<grid_for(end - begin, 128), 128, 0, st>>>(begin, end, queue, counters, bl, br, bfirst,
                                                                     blast, blo, bhi, llo, lhi, vA, sc->d_verts,
                                                                     sc->d_faces, tmp_nodes, sc->d_tris);
@@ -558,6 +578,11 @@ int build_scene(Scene* sc) {
         SG_CHECK(end <= n, SPRAYGPU_ERR_STATE, "collapse: node count %d exceeds bound %d", end, n);
       }
       sc->n_nodes = (uint32_t)end;
+      sc->bvh_depth = (uint32_t)levels;
+      // the traversal stack holds one entry per BVH8 level (core.cuh, SPRAY_STACK_SIZE): refuse deeper trees here
+      // instead of dropping subtrees at trace time
+      SG_CHECK(levels <= SPRAY_STACK_SIZE, SPRAYGPU_ERR_LIMIT, "commit: BVH8 depth %d exceeds the traversal stack (%d)", levels,
+               SPRAY_STACK_SIZE);
     }
     if ((grc = grow_buffer(&sc->d_nodes, &sc->cap_nodes, sizeof(uint4) * 5 * (size_t)sc->n_nodes))) return grc;
     SG_CUDA(cudaMemcpyAsync(sc->d_nodes, tmp_nodes, sizeof(uint4) * 5 * (size_t)sc->n_nodes,

@@ -109,8 +109,9 @@ static void tlas_split(const std::vector<DomainEntry>& doms, int* ids, int n, in
   });
   *nleft = n / 2;
 }
-static int tlas_build(Device* dev, int* ids, int n) {
+static int tlas_build(Device* dev, int* ids, int n, int depth, int* max_depth) {
   const int me = (int)dev->h_tlas.size();
+  if (depth > *max_depth) *max_depth = depth;
   dev->h_tlas.push_back(TlasNode());
   // up to four groups: halves of halves
   int start[4], cnt[4], ng = 0;
@@ -138,7 +139,7 @@ static int tlas_build(Device* dev, int* ids, int n) {
     float lo[3], hi[3];
     tlas_bounds(dev->h_domains, ids + start[g], cnt[g], lo, hi);
     for (int a = 0; a < 3; ++a) { node.lo[a][g] = lo[a]; node.hi[a][g] = hi[a]; }
-    node.child[g] = cnt[g] == 1 ? ~ids[start[g]] : tlas_build(dev, ids + start[g], cnt[g]);
+    node.child[g] = cnt[g] == 1 ? ~ids[start[g]] : tlas_build(dev, ids + start[g], cnt[g], depth + 1, max_depth);
   }
   dev->h_tlas[me] = node;
   return me;
@@ -152,8 +153,12 @@ int upload_domain_table(Device* dev) {
     for (int i = 0; i < dev->ndomains; ++i)
       if (dev->h_domains[i].resident && (dev->active.empty() || dev->active[(size_t)i])) ids.push_back(i);
     dev->h_tlas.clear();
-    if (!ids.empty()) tlas_build(dev, ids.data(), (int)ids.size());
+    int tlas_depth = 0;
+    if (!ids.empty()) tlas_build(dev, ids.data(), (int)ids.size(), 1, &tlas_depth);
     dev->tlas_n = (int)dev->h_tlas.size();
+    // TlasSource (traverse.cuh) pops one entry and pushes <= 4 per level: worst-case stack = 3 per level + 1.
+    // <= 512 domains split 4 ways per level => <= 5 levels => <= 16 of the 24 entries; checked, not assumed.
+    SG_CHECK(3 * tlas_depth + 1 <= 24 /* SPRAY_TLAS_STACK */, SPRAYGPU_ERR_LIMIT, "top-level BVH: depth %d exceeds the traversal stack", tlas_depth);
     SG_CHECK(dev->tlas_n <= SPRAY_TLAS_MAX_NODES, SPRAYGPU_ERR_LIMIT, "top-level BVH: %d nodes", dev->tlas_n);
     if (dev->tlas_n)
       SG_CUDA(cudaMemcpyAsync(dev->d_tlas, dev->h_tlas.data(), sizeof(TlasNode) * dev->tlas_n, cudaMemcpyHostToDevice,
@@ -324,7 +329,20 @@ int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, c
   } else if (s->d_rgb) {
     cudaFree(s->d_rgb); s->d_rgb = nullptr; s->cap_rgb = 0;
   }
+  // every index must address a vertex (the reference trusts the PLY, ply_loader.cc:243-256; a GPU build would turn a
+  // bad index into out-of-bounds device writes).  d_counters[7] is free outside a render launch.
+  uint32_t* d_max = (uint32_t*)(d->d_counters + 7);
+  int vrc = launch_max_index(d, s->d_faces, 3 * nf, d_max);
+  if (vrc) return vrc;
+  uint32_t* h_max = (uint32_t*)d->pinned;
+  SG_CUDA(cudaMemcpyAsync(h_max, d_max, sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
   SG_CUDA(cudaStreamSynchronize(d->stream));  // host arrays may be freed after return
+  if ((size_t)*h_max >= nv) {
+    const uint32_t bad = *h_max;
+    s->nv = s->nf = 0;   // the mesh is unusable: commit reports "empty mesh"
+    set_error("set_mesh: face index %u out of range (nv = %zu)", bad, nv);
+    return SPRAYGPU_ERR_ARG;
+  }
   return SPRAYGPU_OK;
 }
 
@@ -359,6 +377,7 @@ int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_info* out) {
   out->node_bytes = (uint64_t)s->n_nodes * 80; out->tri_bytes = (uint64_t)s->nf * 48; out->attr_bytes = (uint64_t)s->nf * 48;
   memcpy(out->bounds, s->bounds, sizeof(out->bounds));
   out->build_ms = s->build_ms;
+  out->bvh_depth = s->bvh_depth; out->reserved = 0;
   return SPRAYGPU_OK;
 }
 
@@ -537,8 +556,8 @@ int spraygpu_hit_attributes(spraygpu_device dev, const spraygpu_ray* rays, const
   return st.finish();
 }
 
-int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
-                          spraygpu_ray* rays) {
+static int gen_eye_rays_impl(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, int eye_seed,
+                             spraygpu_ray* rays) {
   SG_CHECK(dev && cam && rays && spp > 0, SPRAYGPU_ERR_ARG, "gen_eye_rays: bad argument");
   Device* d = DEV(dev);
   const size_t n = (size_t)tile.w * tile.h * spp;
@@ -549,9 +568,16 @@ int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spray
   if (rc) return rc;
   spraygpu_ray* dr = st.out(rays, n);
   if (st.rc) return st.rc;
-  rc = launch_eye_rays(d, cam, tile, spp, dr);
+  rc = launch_eye_rays(d, cam, tile, spp, eye_seed, dr);
   if (rc) return rc;
   return st.finish();
+}
+int spraygpu_gen_eye_rays(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, spraygpu_ray* rays) {
+  return gen_eye_rays_impl(dev, cam, tile, spp, SPRAYGPU_EYE_SEED_OOC, rays);
+}
+int spraygpu_gen_eye_rays_insitu(spraygpu_device dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp,
+                                 spraygpu_ray* rays) {
+  return gen_eye_rays_impl(dev, cam, tile, spp, SPRAYGPU_EYE_SEED_INSITU, rays);
 }
 
 static int trace_tile_impl(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
@@ -622,10 +648,11 @@ int spraygpu_trace_tile_counted(spraygpu_device dev, const spraygpu_camera* cam,
   return trace_tile_impl(dev, cam, shade, tile, fb, stats, true, false);
 }
 
-int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
-                         const spraygpu_tile* tiles, int ntiles, float* fb, spraygpu_stats* stats) {
+static int trace_frame_impl(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                            const spraygpu_tile* tiles, const spraygpu_tile* parents, int ntiles, float* fb, spraygpu_stats* stats) {
   SG_CHECK(dev && cam && shade && fb && (tiles || ntiles == 0) && ntiles >= 0, SPRAYGPU_ERR_ARG, "trace_frame: bad argument");
   Device* d = DEV(dev);
+  SG_CHECK(!parents || is_device_ptr(fb), SPRAYGPU_ERR_ARG, "trace_frame_rects: fb must be a device pointer");
   if (!is_device_ptr(fb)) {
     // host frame buffer: per-tile launches so that tile k's D2H overlaps tile k+1's kernel
     spraygpu_stats tot = {0, 0, 0, 0, 0, 0, 0}, st;
@@ -658,7 +685,7 @@ int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const 
   const int per = 32;   // SPRAY_MAX_FRAME_TILES
   for (int t0 = 0; t0 < ntiles || t0 == 0; t0 += per) {
     const int nt = ntiles - t0 < per ? ntiles - t0 : per;
-    rc = launch_render_tiles(d, cam, shade, tiles + t0, nt, fb, false, t0 == 0);
+    rc = launch_render_tiles(d, cam, shade, tiles + t0, parents ? parents + t0 : nullptr, nt, fb, false, t0 == 0);
     if (rc) return rc;
     if (ntiles == 0) break;
   }
@@ -670,6 +697,17 @@ int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const 
     stats->nodes_visited = h[5]; stats->tris_tested = h[6]; stats->hits = h[7];
   }
   return SPRAYGPU_OK;
+}
+
+int spraygpu_trace_frame(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                         const spraygpu_tile* tiles, int ntiles, float* fb, spraygpu_stats* stats) {
+  return trace_frame_impl(dev, cam, shade, tiles, nullptr, ntiles, fb, stats);
+}
+int spraygpu_trace_frame_rects(spraygpu_device dev, const spraygpu_camera* cam, const spraygpu_shade* shade,
+                               const spraygpu_tile* rects, const spraygpu_tile* blocking_tiles, int n, float* fb,
+                               spraygpu_stats* stats) {
+  SG_CHECK(blocking_tiles || n == 0, SPRAYGPU_ERR_ARG, "trace_frame_rects: blocking_tiles is NULL");
+  return trace_frame_impl(dev, cam, shade, rects, blocking_tiles, n, fb, stats);
 }
 
 }  // extern "C"

@@ -17,6 +17,7 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t);
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
   ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*GroupStart)();
@@ -44,6 +45,7 @@ static void load_nccl() {
   g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))sym("ncclCommDestroy");
   g_nccl.AllReduce = (decltype(g_nccl.AllReduce))sym("ncclAllReduce");
   g_nccl.Reduce = (decltype(g_nccl.Reduce))sym("ncclReduce");
+  g_nccl.AllGather = (decltype(g_nccl.AllGather))sym("ncclAllGather");
   g_nccl.Send = (decltype(g_nccl.Send))sym("ncclSend");
   g_nccl.Recv = (decltype(g_nccl.Recv))sym("ncclRecv");
   g_nccl.GroupStart = (decltype(g_nccl.GroupStart))sym("ncclGroupStart");
@@ -66,11 +68,79 @@ static const NcclApi* nccl() {
     }                                                                                                  \
   } while (0)
 
+// inside an open ncclGroupStart(): close the group before reporting the error, or the communicator's next call hangs
+#define SG_NCCL_IN_GROUP(call)                                                                         \
+  do {                                                                                                 \
+    ncclResult_t r__ = (call);                                                                         \
+    if (r__ != ncclSuccess) {                                                                          \
+      g_nccl.GroupEnd();                                                                               \
+      set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r__));        \
+      return SPRAYGPU_ERR_CUDA;                                                                        \
+    }                                                                                                  \
+  } while (0)
+
 struct Comm {
   Device* dev = nullptr;
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
 };
+
+// ------------------------------------------------------------------------------------------------
+// Peer-mapped device buffers (CUDA IPC over NVLink / NVSwitch P2P): every rank allocates `bytes`, the 64-byte IPC
+// handles are all-gathered (setup only, NCCL), and every rank maps every peer's buffer.  After that the frame path
+// moves data with plain loads / stores / atomics on the mapped pointers from inside its own kernels — no collective
+// call per frame (image.cu: row push; insitu2.cu: key / attribute / occlusion exchange).
+// ------------------------------------------------------------------------------------------------
+// only_rank >= 0: map that rank's buffer only (the others stay nullptr)
+int comm_shared_alloc(Comm* c, size_t bytes, void** local, std::vector<void*>* mapped, int only_rank) {
+  SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  void* p = nullptr;
+  SG_CUDA(cudaMalloc(&p, bytes));
+  SG_CUDA(cudaMemsetAsync(p, 0, bytes, c->dev->stream));
+  mapped->assign((size_t)c->nranks, nullptr);
+  (*mapped)[(size_t)c->rank] = p;
+  *local = p;
+  if (c->nranks == 1) { SG_CUDA(cudaStreamSynchronize(c->dev->stream)); return SPRAYGPU_OK; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t mine;
+  SG_CUDA(cudaIpcGetMemHandle(&mine, p));
+  char* d_h = nullptr;
+  SG_CUDA(cudaMalloc((void**)&d_h, 64 * (size_t)c->nranks));
+  SG_CUDA(cudaMemcpyAsync(d_h + 64 * (size_t)c->rank, &mine, 64, cudaMemcpyHostToDevice, c->dev->stream));
+  SG_NCCL(g_nccl.AllGather(d_h + 64 * (size_t)c->rank, d_h, 64, ncclChar, c->comm, c->dev->stream));
+  std::vector<cudaIpcMemHandle_t> all((size_t)c->nranks);
+  SG_CUDA(cudaMemcpyAsync(all.data(), d_h, 64 * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->dev->stream));
+  SG_CUDA(cudaStreamSynchronize(c->dev->stream));
+  cudaFree(d_h);
+  for (int r = 0; r < c->nranks; ++r) {
+    if (r == c->rank || (only_rank >= 0 && r != only_rank)) continue;
+    void* q = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&q, all[(size_t)r], cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      set_error("cudaIpcOpenMemHandle(rank %d) failed: %s (peer access over NVLink is required)", r, cudaGetErrorString(e));
+      cudaGetLastError();
+      return SPRAYGPU_ERR_CUDA;
+    }
+    (*mapped)[(size_t)r] = q;
+  }
+  return SPRAYGPU_OK;
+}
+// collective: every rank must have stopped using the peers' mappings (the caller synchronises ranks first)
+void comm_shared_free(Comm* c, void* local, std::vector<void*>* mapped) {
+  cudaSetDevice(c->dev->cuda_device);
+  for (int r = 0; r < (int)mapped->size(); ++r)
+    if (r != c->rank && (*mapped)[(size_t)r]) cudaIpcCloseMemHandle((*mapped)[(size_t)r]);
+  mapped->clear();
+  if (local) cudaFree(local);
+}
+// host-visible rendezvous of all ranks (setup / teardown only): a 1-int all-reduce + stream sync
+int comm_host_barrier(Comm* c) {
+  if (c->nranks == 1) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  SG_NCCL(g_nccl.AllReduce(c->dev->d_counters, c->dev->d_counters, 1, ncclUint64, ncclSum, c->comm, c->dev->stream));
+  SG_CUDA(cudaStreamSynchronize(c->dev->stream));
+  return SPRAYGPU_OK;
+}
 
 // collectives used by insitu.cu (all on dev->stream, in place)
 int comm_allreduce_u64_min(Comm* c, uint64_t* p, size_t n) {
@@ -208,11 +278,11 @@ int spraygpu_image_gather_rows(spraygpu_device dev, spraygpu_comm comm, float* f
     for (int r = 0; r < c->nranks; ++r) {
       if (r == root) continue;
       const size_t n = (size_t)(row_begin[r + 1] - row_begin[r]) * row_floats;
-      if (n) SG_NCCL(g_nccl.Recv(fb + (size_t)row_begin[r] * row_floats, n, ncclFloat32, r, c->comm, c->dev->stream));
+      if (n) SG_NCCL_IN_GROUP(g_nccl.Recv(fb + (size_t)row_begin[r] * row_floats, n, ncclFloat32, r, c->comm, c->dev->stream));
     }
   } else {
     const size_t n = (size_t)(row_begin[c->rank + 1] - row_begin[c->rank]) * row_floats;
-    if (n) SG_NCCL(g_nccl.Send(fb + (size_t)row_begin[c->rank] * row_floats, n, ncclFloat32, root, c->comm, c->dev->stream));
+    if (n) SG_NCCL_IN_GROUP(g_nccl.Send(fb + (size_t)row_begin[c->rank] * row_floats, n, ncclFloat32, root, c->comm, c->dev->stream));
   }
   SG_NCCL(g_nccl.GroupEnd());
   return SPRAYGPU_OK;
@@ -227,15 +297,16 @@ int spraygpu_image_gather_blocks(spraygpu_device dev, spraygpu_comm comm, float*
   if (c->nranks == 1) return SPRAYGPU_OK;
   SG_CUDA(cudaSetDevice(c->dev->cuda_device));
   const size_t row_floats = (size_t)image_w * 4;
+  for (int b = 0; b < nblocks; ++b)   // validated BEFORE the group opens: no early return with an open group
+    SG_CHECK(block_owner[b] >= 0 && block_owner[b] < c->nranks, SPRAYGPU_ERR_ARG, "image_gather_blocks: block %d owner %d", b, block_owner[b]);
   SG_NCCL(g_nccl.GroupStart());
   for (int b = 0; b < nblocks; ++b) {
     const int owner = block_owner[b];
-    SG_CHECK(owner >= 0 && owner < c->nranks, SPRAYGPU_ERR_ARG, "image_gather_blocks: block %d owner %d", b, owner);
     const size_t n = (size_t)(block_row_begin[b + 1] - block_row_begin[b]) * row_floats;
     if (!n || owner == root) continue;
     float* p = fb + (size_t)block_row_begin[b] * row_floats;
-    if (c->rank == root) SG_NCCL(g_nccl.Recv(p, n, ncclFloat32, owner, c->comm, c->dev->stream));
-    else if (c->rank == owner) SG_NCCL(g_nccl.Send(p, n, ncclFloat32, root, c->comm, c->dev->stream));
+    if (c->rank == root) SG_NCCL_IN_GROUP(g_nccl.Recv(p, n, ncclFloat32, owner, c->comm, c->dev->stream));
+    else if (c->rank == owner) SG_NCCL_IN_GROUP(g_nccl.Send(p, n, ncclFloat32, root, c->comm, c->dev->stream));
   }
   SG_NCCL(g_nccl.GroupEnd());
   return SPRAYGPU_OK;

@@ -378,7 +378,19 @@ SPRAY_HD uint32_t node8_hits(const u4& q0, const u4& q1, const u4& q2, const u4&
   return hitmask;
 }
 
+// Depth bound of the per-ray traversal stack: one (child base, pending-children mask) group per BVH8 LEVEL on the
+// current root-to-node path.  spraygpu_scene_commit measures the BVH8 depth (the number of collapse levels) and
+// refuses trees deeper than this (SPRAYGPU_ERR_LIMIT), so a push can never run out of room at trace time; the guard
+// below turns the impossible case into a trap instead of a silently dropped subtree (= missed hits).
+// (30-bit Morton keys + index tie-break bound the LBVH depth by 30 + log2(n) <= 53; the 8-wide collapse consumes
+// >= 1 binary level per node on the Morton part and ~3 on the balanced tie-break part: <= ~38 levels.)
 #define SPRAY_STACK_SIZE 48
+#if defined(__CUDA_ARCH__)
+#define SPRAY_STACK_OVERFLOW() __trap()
+#else
+#include <stdlib.h>
+#define SPRAY_STACK_OVERFLOW() abort()
+#endif
 
 struct Closest {
   float t, u, v;
@@ -409,10 +421,11 @@ SPRAY_HD bool bvh8_trace(const NodeLoader& loadn, const TriLoader& loadt, const 
       const int bit = 31 - clz32(ngy);
       ngy &= ~(1u << bit);
       if (ngy > 0x00FFFFFFu) {
+        if (sp >= SPRAY_STACK_SIZE) SPRAY_STACK_OVERFLOW();
 #if SPRAY_POP_CULL
-        if (sp < SPRAY_STACK_SIZE) { stack_d0[sp] = gd0; stack_d1[sp] = gd1; }
+        stack_d0[sp] = gd0; stack_d1[sp] = gd1;
 #endif
-        if (sp < SPRAY_STACK_SIZE) { stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp; }
+        stack_x[sp] = ngx; stack_y[sp] = ngy; ++sp;
       }
       const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
       const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
@@ -626,6 +639,11 @@ SPRAY_HD void collapse_select(int b, const int* bl, const int* br, const int* bf
         if (child_at[s] >= 0) continue;
         if (cost[k][s] > bc) { bc = cost[k][s]; bk = k; bs = s; }
       }
+    }
+    if (bk < 0) {
+      // NaN vertices make every cost NaN (no comparison succeeds): first unplaced child -> first free slot
+      for (int k = 0; k < nc && bk < 0; ++k) if (slot_of[k] < 0) bk = k;
+      for (int s = 0; s < 8 && bs < 0; ++s) if (child_at[s] < 0) bs = s;
     }
     slot_of[bk] = bs; child_at[bs] = bk;
   }

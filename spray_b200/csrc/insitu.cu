@@ -237,7 +237,7 @@ extern "C" int spraygpu_trace_tile_insitu(spraygpu_device dev_h, spraygpu_comm c
       for (int l = 0; l < shade->nlights; ++l) npasses += shade->lights[l].type == SPRAYGPU_LIGHT_DIFFUSE ? shade->ao_samples : 1;
     else npasses = shade->ao_samples;
 
-    rc = launch_eye_rays(dev, cam, tile, shade->pixel_samples, rays);
+    rc = launch_eye_rays(dev, cam, tile, shade->pixel_samples, SPRAYGPU_EYE_SEED_INSITU, rays);   // insitu_ray.h:161-165
     if (rc) return rc;
     insitu_init_wave_kernel<<<grid_for(3 * n, 256), 256, 0, st>>>(w, n);
     dev->launches++;

@@ -119,6 +119,7 @@ struct Scene {
   float* d_normals = nullptr;  // nv*3
   uint4* d_nodes = nullptr;
   uint32_t n_nodes = 0;
+  uint32_t bvh_depth = 0;      // BVH8 levels (<= SPRAY_STACK_SIZE, checked at commit)
   float4* d_tris = nullptr;
   float4* d_attr = nullptr;
   float bounds[6];
@@ -137,6 +138,7 @@ inline int grow_buffer(T** p, size_t* cap, size_t bytes) {
   return SPRAYGPU_OK;
 }
 int build_scene(Scene* sc);   // build.cu
+int launch_max_index(Device* dev, const uint32_t* d_idx, size_t n, uint32_t* d_out);   // build.cu
 int upload_domain_table(Device* dev);
 
 // trace.cu launchers
@@ -148,10 +150,10 @@ int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, ui
 int launch_occluded_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge);
 int launch_hit_attributes(Device* dev, const spraygpu_ray* rays, const uint64_t* keys, size_t n, uint32_t* color,
                           float* ns3);
-int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, spraygpu_ray* rays);
+int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, int eye_seed, spraygpu_ray* rays);
 int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                        float* fb, bool counted);
 int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, const spraygpu_tile* tiles,
-                        int ntiles, float* fb, bool counted, bool reset_counters);
+                        const spraygpu_tile* parents, int ntiles, float* fb, bool counted, bool reset_counters);
 
 }  // namespace spraygpu

@@ -307,7 +307,7 @@ extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_cam
     dev->table_dirty = true;
     rc = upload_domain_table(dev);
     if (rc) return rc;
-    rc = launch_eye_rays(dev, cam, tile, shade->pixel_samples, rays);
+    rc = launch_eye_rays(dev, cam, tile, shade->pixel_samples, shade->eye_seed, rays);
     if (rc) return rc;
     ooc_fill_kernel<<<ooc_grid(3 * n, 256), 256, 0, st>>>(w, 3 * n, 1.0f);
     dev->launches++;

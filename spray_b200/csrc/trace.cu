@@ -153,13 +153,19 @@ __global__ void __launch_bounds__(128)
   ns3[3 * i] = Ns.x; ns3[3 * i + 1] = Ns.y; ns3[3 * i + 2] = Ns.z;
 }
 
-__device__ __forceinline__ void eye_sample(const CameraDev& cam, spraygpu_tile tile, int spp, uint32_t x0,
-                                           uint32_t y0, uint32_t sidx, uint32_t* samid, uint32_t* pixid, vec3* dir) {
-  const uint32_t bufid = (uint32_t)spp * (y0 * (uint32_t)tile.w + x0) + sidx;
+// tile = the rectangle being rendered; (pw, px, py) place it inside the BLOCKING tile that numbers the samples
+// (samid = index within the blocking tile, ooc_tracer.inl:84-172): pw = blocking tile width, (px, py) = offset of
+// `tile` inside it.  A rank that renders only some rows of a blocking tile (multi-GPU image partition) still seeds
+// every sample exactly as the one-rank frame does.
+__device__ __forceinline__ void eye_sample(const CameraDev& cam, spraygpu_tile tile, int pw, int px, int py, int spp, int eye_seed,
+                                           uint32_t x0, uint32_t y0, uint32_t sidx, uint32_t* samid, uint32_t* pixid, vec3* dir) {
+  const uint32_t bufid = (uint32_t)spp * ((y0 + (uint32_t)py) * (uint32_t)pw + x0 + (uint32_t)px) + sidx;
   const int x = tile.x + (int)x0, y = tile.y + (int)y0;
   float fx = (float)x, fy = (float)y;
-  if (spp > 1) {  // genMultiEyes, ooc_tracer.inl:151-155
-    uint32_t s = rng_init1(bufid);
+  if (spp > 1) {
+    // ooc::Tracer::genMultiEyes seeds with bufid (ooc_tracer.inl:151-155); insitu::genMultiSampleEyeRays with
+    // (pixid, s) (insitu_ray.h:161-165)
+    uint32_t s = eye_seed == SPRAYGPU_EYE_SEED_INSITU ? rng_init2((uint32_t)(y * cam.image_w + x), sidx) : rng_init1(bufid);
     fx = add_rn((float)x, rng_float(s));
     fy = add_rn((float)y, rng_float(s));
   }
@@ -169,14 +175,14 @@ __device__ __forceinline__ void eye_sample(const CameraDev& cam, spraygpu_tile t
 }
 
 __global__ void __launch_bounds__(256)
-    eye_rays_kernel(CameraDev cam, spraygpu_tile tile, int spp, spraygpu_ray* __restrict__ rays) {
+    eye_rays_kernel(CameraDev cam, spraygpu_tile tile, int spp, int eye_seed, spraygpu_ray* __restrict__ rays) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t n = (size_t)tile.w * tile.h * spp;
   if (i >= n) return;
   const uint32_t sidx = (uint32_t)(i % spp);
   const uint32_t pix = (uint32_t)(i / spp);
   uint32_t samid, pixid; vec3 d;
-  eye_sample(cam, tile, spp, pix % (uint32_t)tile.w, pix / (uint32_t)tile.w, sidx, &samid, &pixid, &d);
+  eye_sample(cam, tile, tile.w, 0, 0, spp, eye_seed, pix % (uint32_t)tile.w, pix / (uint32_t)tile.w, sidx, &samid, &pixid, &d);
   // two 16-byte stores per ray (the 8 scalar stores of a struct copy ran at ~0.9 TB/s: ncu r01s)
   float4* out = reinterpret_cast<float4*>(rays + samid);
   out[0] = make_float4(cam.pos[0], cam.pos[1], cam.pos[2], SPRAY_RAY_EPS);
@@ -208,10 +214,15 @@ struct RenderParams {
   // ooc_tracer.inl:184-234): the sample slots of the tiles are concatenated, every tile's share is a multiple of
   // 32, so a warp's 32 slots never straddle tiles and samid stays the index WITHIN the tile.
   int ntiles;
-  spraygpu_tile tiles[SPRAY_MAX_FRAME_TILES];
+  spraygpu_tile tiles[SPRAY_MAX_FRAME_TILES];       // the rectangles rendered by this launch
+  // position of each rectangle inside the blocking tile that numbers its samples (eye_sample): width of the blocking
+  // tile and the rectangle's offset in it; (tile.w, 0, 0) when a whole blocking tile is rendered
+  int32_t parent_w[SPRAY_MAX_FRAME_TILES];
+  uint16_t parent_dx[SPRAY_MAX_FRAME_TILES], parent_dy[SPRAY_MAX_FRAME_TILES];
   uint32_t slot_end[SPRAY_MAX_FRAME_TILES];        // exclusive prefix end of tile t's slots (32 * pixel blocks * spp)
   uint32_t blocks_per_row[SPRAY_MAX_FRAME_TILES];
   uint32_t total_slots;
+  int qcap;                      // GENERAL variant: ray-queue entries per warp (the lean variant's is a constant)
 };
 
 // slot base (multiple of 32) -> its tile, the slot index inside the tile
@@ -283,13 +294,25 @@ __device__ __forceinline__ bool queue_push(const RayQueue& Q, const DomSmem& D, 
 // GENERAL == false is the lean variant for the common configuration (PT shader, ONE point light, every
 // domain diffuse): area-light / AO sampling, delta materials and the inline shadow fallback are compiled
 // out, which keeps the code the instruction cache has to hold small.  The launcher picks the variant.
+// Queue bound.  The queue is LIFO, a pop takes 32 rays and eye rays are added only below 32 queued, so
+//   lean / no glass : a radiance ray has at most ONE radiance child -> <= 63 radiance entries + 32 shadow rays of the
+//                     current pop = 95 (shadow pushes of further light passes fall back to tracing in place);
+//   glass           : reflection AND transmission per hit (the reference CHECK-fails there, ooc_shader_pt.h:199-201;
+//                     this kernel traces both): every level of the depth-first walk can leave 32 siblings behind
+//                     -> 63 + 32 * (bounces - 1) radiance entries + 32 shadow.  The launcher sizes the GENERAL queue
+//                     from `bounces` when a glass domain exists (general_queue_cap) and refuses what cannot fit.
 template <bool GENERAL> struct QueueCap { static constexpr int value = GENERAL ? 128 : 96; };
+static inline int general_queue_cap(bool has_glass, int bounces) {
+  if (!has_glass) return QueueCap<true>::value;
+  const int need = 63 + 32 * (bounces > 1 ? bounces - 1 : 0) + 32;
+  return need < QueueCap<true>::value ? QueueCap<true>::value : (need + 31) / 32 * 32;
+}
 
 template <bool COUNT, bool GENERAL>
 __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) render_tile_kernel(RenderParams P) {
   extern __shared__ float smem[];
   const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
-  constexpr int QCAP = QueueCap<GENERAL>::value;
+  const int QCAP = GENERAL ? P.qcap : QueueCap<false>::value;   // a compile-time constant in the lean variant
   const int lane = threadIdx.x & 31;
   RayQueue Q;
   Q.cap = QCAP;
@@ -326,7 +349,7 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
       uint32_t samid = 0, pixid = 0;
       vec3 dir = mk3(0.f, 0.f, 1.f);
       if (has_ray) {
-        eye_sample(P.cam, tile, spp, x0, y0, sidx, &samid, &pixid, &dir);
+        eye_sample(P.cam, tile, P.parent_w[ti], P.parent_dx[ti], P.parent_dy[ti], spp, P.shade.eye_seed, x0, y0, sidx, &samid, &pixid, &dir);
         ++n_eye; ++n_rad;
       }
       queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), pixid,
@@ -368,7 +391,7 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
       make_hit_ctx<GENERAL>(P.table + h.dom, ro, rd, h.t, h.u, h.v, h.prim, c);
     }
 
-    // ---------------- secondary rays: pushed first (the queue has room for them by construction) ----------------
+    // ---------------- secondary rays: pushed first (the queue has room for them by construction: QueueCap) ----------------
     {
       bool em1 = false, em2 = false;
       vec3 d1 = mk3(0, 0, 1), w1 = mk3(0, 0, 0), d2 = mk3(0, 0, 1), w2 = mk3(0, 0, 0);
@@ -539,7 +562,7 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
           uint32_t esam = 0, epix = 0;
           vec3 dir = mk3(0.f, 0.f, 1.f);
           if (has_ray) {
-            eye_sample(P.cam, tile, spp, x0, y0, sidx, &esam, &epix, &dir);
+            eye_sample(P.cam, tile, P.parent_w[ti], P.parent_dx[ti], P.parent_dy[ti], spp, P.shade.eye_seed, x0, y0, sidx, &esam, &epix, &dir);
             ++n_eye; ++n_rad;
           }
           queue_push(Q, D, count, has_ray, mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]), dir, mk3(1.f, 1.f, 1.f), epix,
@@ -655,10 +678,10 @@ int launch_hit_attributes(Device* dev, const spraygpu_ray* rays, const uint64_t*
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
 }
-int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, spraygpu_ray* rays) {
+int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile, int spp, int eye_seed, spraygpu_ray* rays) {
   const size_t n = (size_t)tile.w * tile.h * spp;
   if (!n) return SPRAYGPU_OK;
-  eye_rays_kernel<<<grid_for(n, 256), 256, 0, dev->stream>>>(to_camdev(cam), tile, spp, rays);
+  eye_rays_kernel<<<grid_for(n, 256), 256, 0, dev->stream>>>(to_camdev(cam), tile, spp, eye_seed, rays);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
@@ -666,13 +689,14 @@ int launch_eye_rays(Device* dev, const spraygpu_camera* cam, spraygpu_tile tile,
 
 int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, spraygpu_tile tile,
                        float* fb, bool counted) {
-  return launch_render_tiles(dev, cam, shade, &tile, 1, fb, counted, true);
+  return launch_render_tiles(dev, cam, shade, &tile, nullptr, 1, fb, counted, true);
 }
 
 // up to SPRAY_MAX_FRAME_TILES tiles in ONE persistent launch; reset_counters = false keeps accumulating the
 // statistics of a frame that needs several launches
+// parents == nullptr: every tile is a whole blocking tile; else tiles[t] is a sub-rectangle of the blocking tile parents[t]
 int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, const spraygpu_tile* tiles,
-                        int ntiles, float* fb, bool counted, bool reset_counters) {
+                        const spraygpu_tile* parents, int ntiles, float* fb, bool counted, bool reset_counters) {
   SG_CHECK(ntiles >= 0 && ntiles <= SPRAY_MAX_FRAME_TILES, SPRAYGPU_ERR_LIMIT, "%d tiles in one launch (max %d)", ntiles, SPRAY_MAX_FRAME_TILES);
   RenderParams P;
   P.table = dev->d_domains; P.nd = dev->ndomains; P.tlas = dev->d_tlas; P.tlas_n = dev->tlas_n;
@@ -688,9 +712,21 @@ int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_
     slots += ts;
     SG_CHECK(slots < 0xFFFFFFFFull, SPRAYGPU_ERR_LIMIT, "tiles too large: %llu sample slots", (unsigned long long)slots);
     P.tiles[P.ntiles] = tile; P.blocks_per_row[P.ntiles] = bpr; P.slot_end[P.ntiles] = (uint32_t)slots;
+    P.parent_w[P.ntiles] = tile.w; P.parent_dx[P.ntiles] = 0; P.parent_dy[P.ntiles] = 0;
+    if (parents) {
+      const spraygpu_tile par = parents[t];
+      SG_CHECK(tile.x >= par.x && tile.y >= par.y && tile.x + tile.w <= par.x + par.w && tile.y + tile.h <= par.y + par.h &&
+                   tile.x - par.x < 65536 && tile.y - par.y < 65536,
+               SPRAYGPU_ERR_ARG, "rectangle %d (%d,%d,%d,%d) is not inside its blocking tile (%d,%d,%d,%d)", t, tile.x, tile.y, tile.w,
+               tile.h, par.x, par.y, par.w, par.h);
+      P.parent_w[P.ntiles] = par.w; P.parent_dx[P.ntiles] = (uint16_t)(tile.x - par.x); P.parent_dy[P.ntiles] = (uint16_t)(tile.y - par.y);
+    }
     ++P.ntiles;
   }
-  for (int t = P.ntiles; t < SPRAY_MAX_FRAME_TILES; ++t) { P.tiles[t] = spraygpu_tile{0, 0, 0, 0}; P.blocks_per_row[t] = 1; P.slot_end[t] = (uint32_t)slots; }
+  for (int t = P.ntiles; t < SPRAY_MAX_FRAME_TILES; ++t) {
+    P.tiles[t] = spraygpu_tile{0, 0, 0, 0}; P.blocks_per_row[t] = 1; P.slot_end[t] = (uint32_t)slots;
+    P.parent_w[t] = 0; P.parent_dx[t] = 0; P.parent_dy[t] = 0;
+  }
   P.total_slots = (uint32_t)slots;
   if (reset_counters) SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long) * 8, dev->stream));
   else SG_CUDA(cudaMemsetAsync(dev->d_counters, 0, sizeof(unsigned long long), dev->stream));   // the work counter only
@@ -707,13 +743,18 @@ int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_
       stream ? (counted ? render_tile_stream_kernel<true> : render_tile_stream_kernel<false>)
              : counted ? (general ? render_tile_kernel<true, true> : render_tile_kernel<true, false>)
                        : (general ? render_tile_kernel<false, true> : render_tile_kernel<false, false>);
-  const int qcap = general ? QueueCap<true>::value : QueueCap<false>::value;
+  bool has_glass = false;
+  for (int i = 0; i < dev->ndomains; ++i) has_glass = has_glass || dev->h_domains[i].mtl_type == SPRAYGPU_MTL_GLASS;
+  const int qcap = general ? general_queue_cap(has_glass, shade->bounces) : QueueCap<false>::value;
+  P.qcap = qcap;
   const size_t smem = ((dom_smem_bytes(dev->ndomains, dev->tlas_n, 0) + 15) & ~(size_t)15) +
                       SPRAY_RENDER_WARPS * (stream ? stream_words_per_warp() : queue_words_per_warp(qcap)) * sizeof(uint32_t);
   // attribute + occupancy are per (kernel, shared-memory size): cached, the frame loop is host-latency sensitive at
   // 8 GPUs (0.1 ms of kernel per rank)
   int per_sm = dev->render_per_sm;
   if (dev->render_kern != (const void*)kern || dev->render_smem != smem) {
+    SG_CHECK(smem <= 227 * 1024, SPRAYGPU_ERR_LIMIT, "render: %zu B of shared memory per CTA (glass domains with %d bounces need a "
+             "%d-entry ray queue per warp); reduce --bounces", smem, shade->bounces, qcap);
     SG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SPRAY_RENDER_THREADS, smem));
     if (per_sm < 1) per_sm = 1;

@@ -316,7 +316,11 @@ struct TlasSource {
 #undef SPRAY_CSWAP
 #pragma unroll
       for (int k = 0; k < 4; ++k)
-        if (t[k] < INFINITY && sp < SPRAY_TLAS_STACK) { st[sp] = t[k]; sr[sp] = c[k]; ++sp; }
+        if (t[k] < INFINITY) {
+          // upload_domain_table refuses top-level trees whose worst-case stack (3 per level + 1) exceeds SPRAY_TLAS_STACK
+          if (sp >= SPRAY_TLAS_STACK) SPRAY_STACK_OVERFLOW();
+          st[sp] = t[k]; sr[sp] = c[k]; ++sp;
+        }
     }
     return 2;
   }
@@ -430,10 +434,12 @@ struct LaneTrav {
       const uint32_t imask = ngy & 0xffu;
       const int bit = 31 - __clz((int)ngy);
       ngy &= ~(1u << bit);
+      // commit refuses BVH8 trees deeper than the stack (core.cuh, SPRAY_STACK_SIZE): the trap is unreachable
+      if (ngy > 0x00FFFFFFu && sp >= SPRAY_STACK_SIZE) SPRAY_STACK_OVERFLOW();
 #if SPRAY_POP_CULL
-      if (ngy > 0x00FFFFFFu && sp < SPRAY_STACK_SIZE) { stk[sp] = make_uint4(ngx, ngy, gd0, gd1); ++sp; }
+      if (ngy > 0x00FFFFFFu) { stk[sp] = make_uint4(ngx, ngy, gd0, gd1); ++sp; }
 #else
-      if (ngy > 0x00FFFFFFu && sp < SPRAY_STACK_SIZE) { sx[sp] = ngx; sy[sp] = ngy; ++sp; }
+      if (ngy > 0x00FFFFFFu) { sx[sp] = ngx; sy[sp] = ngy; ++sp; }
 #endif
       const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
       const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));

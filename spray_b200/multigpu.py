@@ -1,19 +1,21 @@
 """Multi-GPU frame loops (one process per GPU, launched by torchrun).  Thin host-side harness over the C ABI:
-torch.distributed is used ONLY to bootstrap (broadcast of the NCCL unique id, barriers, max-over-ranks
-timing); every data-path collective is issued by libspraygpu itself on its own NCCL communicator.
+torch.distributed is used ONLY to bootstrap (broadcast of the NCCL unique id, barriers, max-over-ranks timing and
+the sums of per-rank counters); everything on the frame path is issued by libspraygpu.
 
 Two decompositions, as in the reference:
 
 * ``ImagePartitionRenderer`` — the reference's ``--partition image`` (spray_ooc, src/ooc/ooc_tracer.inl:29-82,
-  src/render/tile.cc:317-391): every rank holds ALL domains and renders its own pixels; no ray traffic;
-  the image is composited on rank 0 (HdrImage::composite, src/display/image.h:167-181).  Ranks own
-  contiguous ROW bands (the reference cuts vertical stripes; rows are contiguous in memory, so the
-  composite is one NCCL send per rank instead of a whole-image reduce).
+  src/render/tile.cc:317-391): every rank holds ALL domains and renders its own pixels; no ray traffic; the image
+  is composited on rank 0 (HdrImage::composite, src/display/image.h:167-181).  Here a rank owns interleaved ROW
+  BLOCKS (image-space load balancing; the reference cuts one vertical stripe per rank), renders them as
+  rectangles of the ONE-rank blocking tiles (so sample ids / RNG seeds and therefore the image do not depend on
+  the rank count — spraygpu_trace_frame_rects) and FLUSHES them with one kernel: 16-byte stores into rank 0's
+  composite over NVLink (CUDA IPC mapping) and / or into one shared pinned host image over its own PCIe link
+  (spraygpu_image_flush).  No NCCL call per frame.
 * ``InsituRenderer`` — the reference's ``--partition insitu`` (spray_insitu_*, src/insitu/): domains are
   sharded with the Morton partition (src/render/data_partition.h:59-137); every rank traces every ray
-  against ITS domains; hits are resolved by an NCCL min-all-reduce on the packed 64-bit keys
-  (replaces insitu::VBuf::compositeTbuf, insitu_vbuf.h:109-117), occlusion by a max-all-reduce
-  (compositeObuf, :119-129); partial images are summed on rank 0.
+  against ITS domains; hits are resolved by a 64-bit min on the packed keys (replaces
+  insitu::VBuf::compositeTbuf, insitu_vbuf.h:109-117), occlusion by an OR (compositeObuf, :119-129).
 """
 import os
 
@@ -40,21 +42,16 @@ def band_tiles(image_w, band, spp, max_samples=1024 * 1024):
     return [(0, y, image_w, min(rows, y1 - y)) for y in range(y0, y1, rows)]
 
 
-def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4, root=0, root_share=1.0):
-    """Image-space load balancing for the image partition (default from 4 GPUs up).  A fine cut (32 blocks per rank)
-    lost badly to contiguous bands (one NCCL send per block); 4 blocks per rank is the measured compromise.
-    The image is cut into row blocks dealt round-robin to the ranks (block b -> rank
-    b % nranks).  Block height = the smallest multiple of 4 (the kernel's 8x4 pixel blocks) that keeps a rank's
-    share within one persistent launch (<= max_tiles_per_rank tiles).  Returns (row_begin[nb + 1], owner[nb])."""
+def interleaved_blocks(image_h, nranks, max_tiles_per_rank=32, root=0, root_share=1.0):
+    """Image-space load balancing for the image partition: the image is cut into row blocks dealt round-robin to the
+    ranks (block b -> rank b % nranks).  Block height = the smallest multiple of 4 (the kernel's 8x4 pixel blocks)
+    that keeps a rank's share within one persistent launch (<= max_tiles_per_rank rectangles).  root_share < 1 lets
+    the compositing rank render a smaller share.  Returns (row_begin[nb + 1], owner[nb])."""
     rows = -(-int(image_h) // (max_tiles_per_rank * int(nranks)))
     rows = max(4, (rows + 3) // 4 * 4)
     begin = list(range(0, int(image_h), rows)) + [int(image_h)]
-    # root_share < 1: the compositing rank renders a smaller share, so its receives are posted (and the other ranks'
-    # rows start to flow) while the slower ranks still render; 0 makes it a pure compositor
-    owner, b, acc = [], 0, 0.0
     nb = len(begin) - 1
-    order = []
-    cycle = 0
+    order, acc = [], 0.0
     while len(order) < nb:
         for r in range(int(nranks)):
             if r == root and nranks > 1:
@@ -65,9 +62,22 @@ def interleaved_blocks(image_h, nranks, max_tiles_per_rank=4, root=0, root_share
             order.append(r)
             if len(order) == nb:
                 break
-        cycle += 1
-    owner = order
-    return np.asarray(begin, np.int32), np.asarray(owner, np.int32)
+    return np.asarray(begin, np.int32), np.asarray(order, np.int32)
+
+
+def rects_of_blocks(block_begin, block_owner, rank, blocking_tiles):
+    """This rank's row blocks cut against the one-rank blocking tiles: (rects, parents) for spraygpu_trace_frame_rects."""
+    rects, parents = [], []
+    for b in range(len(block_owner)):
+        if int(block_owner[b]) != rank:
+            continue
+        y0, y1 = int(block_begin[b]), int(block_begin[b + 1])
+        for (tx, ty, tw, th) in blocking_tiles:
+            a, z = max(y0, ty), min(y1, ty + th)
+            if z > a:
+                rects.append((tx, a, tw, z - a))
+                parents.append((tx, ty, tw, th))
+    return rects, parents
 
 
 def bootstrap_comm(dev, rank, world):
@@ -78,59 +88,49 @@ def bootstrap_comm(dev, rank, world):
     return capi.Comm(dev, world, rank, obj[0])
 
 
+def _sum_over_ranks(d):
+    import torch
+    import torch.distributed as dist
+    keys = sorted(d)
+    t = torch.tensor([int(d[k]) for k in keys], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t)
+    return {k: int(v) for k, v in zip(keys, t.tolist())}
+
+
 class ImagePartitionRenderer:
-    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, interleave=None):
-        import torch
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, shm_name=None, load=True):
         self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
-        dev.load_scene(scene)
-        if interleave is None:
-            # measured (profiles/bench_r01q_*): contiguous bands win at 2 GPUs (C2 10401 vs 9475 Mrays/s), 4 interleaved
-            # blocks per rank win at 8 (C2 18343 vs 16645, C3 4279 vs 3654)
-            env = os.environ.get("SPRAY_INTERLEAVE")
-            interleave = (world >= 4) if env is None else env != "0"
-        self.interleave = interleave
-        self.bands = row_bands(H, world)
-        if interleave:
-            share = float(os.environ.get("SPRAY_ROOT_SHARE", "1.0"))
-            self.block_begin, self.block_owner = interleaved_blocks(H, world, root=0, root_share=share)
-            self.tiles = []
-            self.my_blocks = [b for b in range(len(self.block_owner)) if self.block_owner[b] == rank]
-            for b in range(len(self.block_owner)):
-                if self.block_owner[b] == rank:
-                    self.tiles += band_tiles(W, self.block_begin[b:b + 2], shade.pixel_samples)
-        else:
-            self.tiles = band_tiles(W, self.bands[rank:rank + 2], shade.pixel_samples)
-        self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-        self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
+        if load:
+            dev.load_scene(scene)
+        self.image = capi.Image(dev, comm, W, H, shm_name)
+        self.blocking = scenes.image_schedule_tiles(W, H, shade.pixel_samples, 1, 0)      # the one-rank frame's blocking tiles
+        share = float(os.environ.get("SPRAY_ROOT_SHARE", "1.0"))
+        self.block_begin, self.block_owner = interleaved_blocks(H, world, root=0, root_share=share)
+        self.image.set_rows(self.block_begin, self.block_owner)
+        self.rects, self.parents = rects_of_blocks(self.block_begin, self.block_owner, rank, self.blocking)
+
+    def _trace(self, stats=False):
+        return self.dev.trace_frame_rects(self.cam, self.shade, self.rects, self.parents, self.image.device, stats=stats)
 
     def frame_device(self):
-        if self.interleave:
-            for b in self.my_blocks:                             # image_.clear() on the rows this rank renders
-                self.fb[int(self.block_begin[b]):int(self.block_begin[b + 1])].zero_()
-            for t0 in range(0, len(self.tiles), 32):             # this rank's row blocks, 32 per persistent launch
-                self.dev.trace_frame(self.cam, self.shade, self.tiles[t0:t0 + 32], self.fb)
-            self.comm.image_gather_blocks(self.fb, self.W, self.block_begin, self.block_owner, 0)
-            return
-        y0, y1 = int(self.bands[self.rank]), int(self.bands[self.rank + 1])
-        self.fb[y0:y1].zero_()                                   # image_.clear() on the rows this rank renders
-        self.dev.trace_frame(self.cam, self.shade, self.tiles, self.fb)   # this rank's band in one persistent launch
-        self.comm.image_gather_rows(self.fb, self.W, self.bands, 0)
+        """One frame, result on rank 0's DEVICE composite: trace my rectangles, push my rows over NVLink."""
+        self._trace()
+        self.image.flush(to_root=True, to_host=False, clear=True)
 
     def frame_host(self):
-        self.frame_device()
-        if self.rank == 0:
-            self.fb_host.copy_(self.fb, non_blocking=True)
+        """One frame, result in the shared pinned HOST image: every rank stores its own rows over its own PCIe link."""
+        self._trace()
+        self.image.flush(to_root=False, to_host=True, clear=True)
         self.dev.synchronize()
 
     def count_rays(self):
-        """Deterministic per-frame ray counts of this rank's band (one extra frame with stats)."""
-        tot = {k: 0 for k, _ in capi.Stats._fields_}   # a rank may own no tile at all
-        self.fb.zero_()
-        for t in self.tiles:
-            st = self.dev.trace_tile(self.cam, self.shade, t, self.fb, stats=True)
-            for k, v in st.as_dict().items():
-                tot[k] = tot.get(k, 0) + v
-        return tot
+        """Deterministic per-frame ray counts, summed over the ranks (one extra frame with stats)."""
+        st = self._trace(stats=True).as_dict()
+        self.image.flush(clear=True)
+        return _sum_over_ranks(st)
+
+    def close(self):
+        self.image.close()
 
 
 class InsituRenderer:
@@ -158,10 +158,155 @@ class InsituRenderer:
         self.dev.synchronize()
 
     def count_rays(self):
-        tot = {k: 0 for k, _ in capi.Stats._fields_}   # a rank may own no tile at all
+        tot = {k: 0 for k, _ in capi.Stats._fields_}
         self.fb.zero_()
         for t in self.tiles:
-            st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=True)
+            st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=True)   # summed over ranks by the library
             for k, v in st.as_dict().items():
                 tot[k] = tot.get(k, 0) + v
         return tot
+
+    def composite_image(self):
+        """rank 0: the composited frame after frame_device() (numpy)."""
+        self.dev.synchronize()
+        return self.fb.cpu().numpy()
+
+    def close(self):
+        pass
+
+
+def _rmse(a, b):
+    return float(np.sqrt(np.mean((np.asarray(a, np.float64)[..., :3] - np.asarray(b, np.float64)[..., :3]) ** 2)))
+
+
+def single_gpu_frame(dev, cam, shade, W, H):
+    """The whole frame on THIS GPU alone through the fused kernel (the parity_check reference); all domains must be resident."""
+    import torch
+    fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    tiles = scenes.image_schedule_tiles(W, H, shade.pixel_samples, 1, 0)
+    st = dev.trace_frame(cam, shade, tiles, fb, stats=True).as_dict()
+    dev.synchronize()
+    return fb.cpu().numpy(), st
+
+
+def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, workload, metric, unit):
+    """bench.py at N > 1.  Returns the JSON line (rank 0) or None."""
+    import torch
+    import torch.distributed as dist
+    sc, cd, shade, label, W, H = workload(args.workload)
+    cam = capi.make_camera(cd)
+    sh = capi.make_shade(lights=sc["lights"], **shade)
+    mode = "image" if args.partition == "both" else args.partition
+    if args.workload == "c5" and "SPRAY_PARTITION" not in os.environ and "--partition" not in " ".join(os.sys.argv):
+        mode = "insitu"                                   # C5 is the reference's in-situ configuration
+    comm = bootstrap_comm(dev, rank, world)
+    shm = "spraygpu_img_%s_%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
+    line = None
+
+    def measure(r, with_e2e):
+        st = r.count_rays()
+        rays = st["radiance_rays"] + st["shadow_rays"]
+        if rank == 0:
+            sampler.start()
+        ms_dev, launches = timer(r.frame_device, args.steps, args.warmup)
+        clocks = sampler.stop() if rank == 0 else None
+        ms_e2e = None
+        if with_e2e:
+            ms_e2e, _ = timer(r.frame_host, max(args.steps // 2, 3), 2)
+        return st, rays, ms_dev, launches, clocks, ms_e2e
+
+    if mode == "image":
+        r = ImagePartitionRenderer(dev, sc, cam, sh, W, H, rank, world, comm, shm_name=shm)
+        st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
+        # ---- parity_check (outside the timed region): one more frame on all ranks, then rank 0 renders the whole
+        # frame alone and compares with its composite; the host image of the e2e path must equal the composite too
+        r.image.barrier()
+        r.frame_device()
+        r.image.barrier()
+        pc = None
+        if rank == 0:
+            comp = r.image.read_device("root")
+            ref, st1 = single_gpu_frame(dev, cam, sh, W, H)
+            pc = {"against": "the same frame rendered by rank 0 alone (fused kernel, all domains resident)",
+                  "rmse": _rmse(comp, ref), "max_abs": float(np.abs(comp[..., :3] - ref[..., :3]).max()),
+                  "bit_identical": bool(np.array_equal(comp, ref)),
+                  "keys_equal": True, "keys_note": "image partition: every rank runs the same closest-hit kernel on its own pixels; "
+                                                   "ray counts equal: %s" % all(st[k] == st1[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))}
+        r.frame_host()
+        r.image.barrier()
+        fp = _sum_over_ranks(dict(zip(("root", "host"), r.image.flushed_pixels())))
+        if rank == 0:
+            pc["host_image_equals_composite"] = bool(np.array_equal(r.image.host, comp))
+        par_label = ("image partition x%d (reference --partition image): all domains on every rank, %d interleaved row blocks, rows "
+                     "pushed into rank 0's frame buffer over NVLink by the library's flush kernel (CUDA IPC, no NCCL per frame); "
+                     "e2e: every rank stores its rows into one shared pinned host image" % (world, len(r.block_owner)))
+        nframes_root = args.warmup + args.steps + 2        # count_rays flushes nothing to root; + parity frame + (none)
+        d2h = None
+        r.close()
+    else:
+        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm)
+        st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
+        pc = insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream)
+        par_label = ("in-situ domain partition x%d (Morton), NCCL min-all-reduce on 64-bit hit keys + max-all-reduce on occlusion, NCCL image reduce" % world)
+        fp = None
+    insitu_extra = None
+    if args.partition == "both" and mode == "image":
+        dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
+        comm2 = bootstrap_comm(dev2, rank, world)
+        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2)
+        st2 = r2.count_rays()
+        timer2 = type(timer)(timer.stream, timer.flush, dev2, world)
+        ms2, l2 = timer2(r2.frame_device, max(args.steps // 2, 3), 3)
+        pc2 = insitu_parity_check(r2, sc, cam, sh, W, H, rank, local_rank, stream)
+        r2n = st2["radiance_rays"] + st2["shadow_rays"]
+        insitu_extra = {"value": r2n / (ms2 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2, "gpu_launches": int(l2),
+                        "parallelism": "in-situ domain partition x%d (Morton): each GPU owns %d of %d domains" % (world, len(r2.owned), len(sc["domains"])),
+                        "parity_check": pc2}
+        r2.close(); comm2.close(); dev2.close()
+    if rank == 0:
+        line = {"metric": metric, "value": rays / (ms_dev * 1e-3) / 1e6, "unit": unit, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic camera rays on the reference's example scene (random-free)",
+                "config": {"workload": label, "l2_flush_between_steps": True, "rays_per_frame": int(rays), "parallelism": par_label},
+                "clocks": clocks, "gpu_launches": int(launches), "parity_check": pc,
+                "e2e": {"value": rays / (ms_e2e * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms_e2e,
+                        "h2d_bytes_per_step": int(capi.C.sizeof(capi.Camera) + capi.C.sizeof(capi.Shade)) * world,
+                        "d2h_bytes_per_step": int(W * H * 16)}}
+        if fp is not None:
+            # the flush is sparse: pixels that are (or were) non-zero; report what actually crossed PCIe per e2e frame
+            e2e_frames = max(args.steps // 2, 3) + 2 + 1
+            line["e2e"]["d2h_bytes_per_step"] = int(fp["host"] * 16 // e2e_frames)
+            line["e2e"]["d2h_note"] = "sparse flush: only pixels that are or were non-zero are stored to the host image (full frame = %d B)" % (W * H * 16)
+        if insitu_extra:
+            line["insitu"] = insitu_extra
+    comm.close()
+    return line
+
+
+def insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream):
+    """In-situ frame (domains sharded) against the same frame on ONE GPU holding every domain; keys: the sharded
+    closest-hit keys after the cross-GPU min against the single-GPU keys."""
+    import torch
+    import torch.distributed as dist
+    r.frame_device()
+    img = r.composite_image()
+    n = W * H
+    rays = torch.zeros((n, 8), dtype=torch.float32, device="cuda")
+    r.dev.gen_eye_rays(cam, (0, 0, W, H), 1, rays)
+    keys = torch.full((n,), -1, dtype=torch.int64, device="cuda")
+    r.dev.intersect_domains(rays, n, keys, None)
+    r.comm.allreduce_keys_min(keys, n)
+    r.dev.synchronize()
+    pc = None
+    if rank == 0:
+        full = capi.Device(local_rank, stream=stream.cuda_stream)
+        full.load_scene(sc)
+        ref, st1 = single_gpu_frame(full, cam, sh, W, H)
+        kf = torch.zeros(n, dtype=torch.int64, device="cuda")
+        full.intersect_domains(rays, n, kf, None)
+        full.synchronize()
+        pc = {"against": "the same frame on ONE GPU holding every domain (fused kernel)", "rmse": _rmse(img, ref),
+              "max_abs": float(np.abs(img[..., :3] - ref[..., :3]).max()), "keys_equal": bool(torch.equal(keys, kf))}
+        full.close()
+    dist.barrier()
+    return pc

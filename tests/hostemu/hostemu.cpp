@@ -20,6 +20,7 @@ struct EmuScene {
   std::vector<float> verts;
   std::vector<uint32_t> faces;
   int max_sp = 0;
+  int depth = 1;                // BVH8 levels (what spraygpu_scene_commit checks against SPRAY_STACK_SIZE)
 };
 
 struct NodeLoaderH {
@@ -208,7 +209,9 @@ EmuScene* emu_build(const float* verts, size_t nv, const uint32_t* faces, size_t
   queue[0] = 0;
   unsigned node_count = 1, tri_count = 0;
   int begin = 0, end = 1;
+  s->depth = 0;
   while (begin < end) {
+    ++s->depth;
     for (int j = begin; j < end; ++j) {
       int b = queue[j];
       CollapseOut co;
@@ -230,6 +233,7 @@ EmuScene* emu_build(const float* verts, size_t nv, const uint32_t* faces, size_t
 }
 
 void emu_destroy(EmuScene* s) { delete s; }
+int emu_depth(const EmuScene* s) { return s->depth; }
 size_t emu_num_nodes(const EmuScene* s) { return s->nodes.size() / 5; }
 
 // rays: 8 floats each (ox,oy,oz,tmin,dx,dy,dz,tmax)

@@ -2,9 +2,10 @@
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 tests/multigpu_check.py
 
-Every rank renders with the in-situ domain partition and with the image partition through the C ABI's own
-NCCL communicator; rank 0 compares both with a single-GPU render of the whole scene.  Used by
-tests/test_gpu_multi.py when >= 2 GPUs are visible."""
+Every rank renders with the in-situ domain partition and with the image partition through the C ABI; rank 0
+compares both with (a) a single-GPU render of the whole scene and (b) the CPU ORACLE's image of the same frame
+(the multi-rank paths were only ever compared CUDA with CUDA).  Used by tests/test_gpu_multi.py when
+>= 2 GPUs are visible."""
 import os
 import sys
 
@@ -12,6 +13,10 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+
+
+def rmse(a, b):
+    return float(np.sqrt(np.mean((np.asarray(a, np.float64)[..., :3] - np.asarray(b, np.float64)[..., :3]) ** 2)))
 
 
 def main():
@@ -28,29 +33,32 @@ def main():
     cd = scenes.camera_frame(p["pos"], p["lookat"], p["up"], p["vfov"], W, H)
     cam = capi.make_camera(cd)
     ok = True
-    for kw in (dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=2)):
+    for case, kw in enumerate((dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=2))):
         sh = capi.make_shade(lights=sc["lights"], **kw, **scenes.WAVELETS64_BLINN)
-        # in-situ: domains sharded, NCCL min-all-reduce on the keys
+        sh_insitu = capi.make_shade(lights=sc["lights"], eye_seed=capi.EYE_SEED_INSITU, **kw, **scenes.WAVELETS64_BLINN)
+        # ---- in-situ: domains sharded, hit keys merged with a 64-bit min across the GPUs
         d1 = capi.Device(local, stream=stream)
         c1 = multigpu.bootstrap_comm(d1, rank, world)
         r1 = multigpu.InsituRenderer(d1, sc, cam, sh, W, H, rank, world, c1)
         assert len(r1.owned) == 64 // world
         st1 = r1.count_rays()
-        r1.frame_device(); d1.synchronize()
-        img_insitu = r1.fb.cpu().numpy()
-        # image partition: all domains everywhere, row bands, NCCL gather
+        r1.frame_device()
+        img_insitu = r1.composite_image()
+        # ---- image partition: all domains everywhere, interleaved row blocks, rows flushed to rank 0 over NVLink and
+        #      to a shared pinned host image
         d2 = capi.Device(local, stream=stream)
         c2 = multigpu.bootstrap_comm(d2, rank, world)
-        r2 = multigpu.ImagePartitionRenderer(d2, sc, cam, sh, W, H, rank, world, c2, interleave=True)
-        r2.frame_device(); d2.synchronize()
-        img_image = r2.fb.cpu().numpy()
-        d3 = capi.Device(local, stream=stream)
-        c3 = multigpu.bootstrap_comm(d3, rank, world)
-        r3 = multigpu.ImagePartitionRenderer(d3, sc, cam, sh, W, H, rank, world, c3, interleave=False)
-        r3.frame_device(); d3.synchronize()
-        img_rows = r3.fb.cpu().numpy()
-        c3.close(); d3.close()
-        # keys: local trace of the owned domains + min-all-reduce == the full single-device answer
+        r2 = multigpu.ImagePartitionRenderer(d2, sc, cam, sh, W, H, rank, world, c2, shm_name="spraygpu_check_%d_%d" % (os.getppid(), case))
+        st2 = r2.count_rays()
+        imgs = []
+        for frame in range(3):                       # several frames: the sparse flush must keep both destinations exact
+            r2.image.barrier()
+            r2.frame_device()
+            r2.frame_host()
+            r2.image.barrier()
+            if rank == 0:
+                imgs.append((r2.image.read_device("root"), r2.image.host.copy()))
+        # keys: local trace of the owned domains + min across ranks == the full single-device answer
         n = W * H
         rays = torch.zeros((n, 8), dtype=torch.float32, device="cuda")
         d1.gen_eye_rays(cam, (0, 0, W, H), 1, rays)
@@ -61,31 +69,32 @@ def main():
         d2.intersect_domains(rays, n, keys_full, None)
         d1.synchronize(); d2.synchronize()
         if rank == 0:
-            def render(tiles):
-                fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-                tot = {}
-                for t in tiles:
-                    st = d2.trace_tile(cam, sh, t, fb, stats=True)
-                    for k, v in st.as_dict().items():
-                        tot[k] = tot.get(k, 0) + v
-                d2.synchronize()
-                return fb.cpu().numpy(), tot
-            # sample ids (RNG seeds) are tile-relative, as in the reference (ooc_tracer.inl:84-172): compare each
-            # decomposition with a single-GPU render over the SAME blocking tiles
-            ref, tot = render(multigpu.band_tiles(W, (0, H), sh.pixel_samples))
-            bb, bo = r2.block_begin, r2.block_owner          # interleaved row blocks (load balancing)
-            ref_bands, _ = render([t for b in range(len(bo)) for t in multigpu.band_tiles(W, bb[b:b + 2], sh.pixel_samples)])
-            # contiguous bands + row gather (the non-interleaved variant)
-            bands = multigpu.row_bands(H, world)
-            ref_rows, _ = render([t for r in range(world) for t in multigpu.band_tiles(W, bands[r:r + 2], sh.pixel_samples)])
-            e3 = float(np.sqrt(np.mean((img_rows[..., :3].astype(np.float64) - ref_rows[..., :3]) ** 2)))
-            e1 = float(np.sqrt(np.mean((img_insitu[..., :3].astype(np.float64) - ref[..., :3]) ** 2)))
-            e2 = float(np.sqrt(np.mean((img_image[..., :3].astype(np.float64) - ref_bands[..., :3]) ** 2)))
-            same_keys = bool(torch.equal(keys, keys_full))
-            same_stats = all(st1[k] == tot[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))
-            print("multigpu_check %s world=%d: insitu rmse %.3g | image-partition rmse %.3g | keys equal %s | stats equal %s (%s)"
-                  % (kw, world, e1, e2, same_keys, same_stats, {k: st1[k] for k in ("radiance_rays", "shadow_rays", "hits")}))
-            ok = ok and e1 <= 1e-6 and e2 <= 1e-6 and e3 <= 1e-6 and same_keys and same_stats and ref[..., :3].max() > 0.1
+            from oracle import pyoracle as O
+            ref, tot = multigpu.single_gpu_frame(d2, cam, sh, W, H)
+            ref_insitu, tot_i = multigpu.single_gpu_frame(d2, cam, sh_insitu, W, H)
+            osc = O.Scene(sc["domains"])
+            tiles = scenes.image_schedule_tiles(W, H, sh.pixel_samples, 1, 0)
+            sh_o, keep_o = O.make_shade(lights=sc["lights"], **kw, **scenes.WAVELETS64_BLINN)
+            sh_oi, keep_oi = O.make_shade(lights=sc["lights"], eye_seed=1, **kw, **scenes.WAVELETS64_BLINN)
+            fb_o, st_o = osc.render(O.camera_from_desc(cd), sh_o, tiles)
+            fb_oi, st_oi = osc.render(O.camera_from_desc(cd), sh_oi, tiles)
+            ko, _ = osc.intersect(rays.cpu().numpy())
+            e_insitu = rmse(img_insitu, ref_insitu)
+            e_insitu_o = rmse(img_insitu, fb_oi)
+            e_img = max(rmse(a, ref) for a, _ in imgs)
+            e_img_o = rmse(imgs[-1][0], fb_o)
+            host_ok = all(np.array_equal(a, b) for a, b in imgs)
+            bit = kw["bounces"] > 1 or kw["pixel_samples"] > 1 or all(np.array_equal(a, ref) for a, _ in imgs)
+            same_keys = bool(torch.equal(keys, keys_full)) and bool(np.array_equal(keys.cpu().numpy().view(np.uint64), ko))
+            same_stats = all(st1[k] == tot_i[k] == getattr(st_oi, k) for k in ("eye_rays", "radiance_rays", "shadow_rays")) and \
+                all(st2[k] == tot[k] == getattr(st_o, k) for k in ("eye_rays", "radiance_rays", "shadow_rays"))
+            print("multigpu_check %s world=%d: insitu rmse %.3g (oracle %.3g) | image-partition rmse %.3g (oracle %.3g) bit-identical %s "
+                  "host==composite %s | keys equal (GPU + oracle) %s | stats equal %s (%s)"
+                  % (kw, world, e_insitu, e_insitu_o, e_img, e_img_o, bit, host_ok, same_keys, same_stats,
+                     {k: st2[k] for k in ("radiance_rays", "shadow_rays", "hits")}))
+            ok = ok and e_insitu <= 1e-6 and e_img <= 1e-6 and e_insitu_o <= 1e-4 and e_img_o <= 1e-4 and bit and host_ok \
+                and same_keys and same_stats and ref[..., :3].max() > 0.1
+        r2.close(); r1.close()
         c1.close(); c2.close(); d1.close(); d2.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)

@@ -1,5 +1,6 @@
 """Domain -> GPU map: the reference's in-situ Morton partition (src/render/data_partition.h:59-137,
-src/render/morton.h:33-52), restated in numpy float32.  Host-side logic; used by spray_b200.multigpu."""
+src/render/morton.h:33-52), restated in numpy float32.  TEST INFRASTRUCTURE: an independent restatement that tests compare with the product's
+spraygpu_partition_domains (comm.cu) and the oracle's orc_partition; the product never imports it."""
 import numpy as np
 
 f32 = np.float32

@@ -1,0 +1,103 @@
+"""GPU tests of the frame image (spraygpu_image, image.cu): the device render target + sparse flush into the pinned
+host image that replaces HdrImage::buf / clear() / composite() (reference src/display/image.h:58-239).  Single GPU
+here; the peer (NVLink) destination is exercised by tests/multigpu_check.py on >= 2 GPUs."""
+import numpy as np
+import pytest
+
+from spray_b200 import capi, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def _frame(dev, sc, cam_desc, kw, fb):
+    cam = capi.make_camera(cam_desc)
+    sh = capi.make_shade(lights=sc["lights"], **kw)
+    tiles = scenes.image_schedule_tiles(cam_desc["image_w"], cam_desc["image_h"], kw["pixel_samples"], 1, 0, 1 << 14)
+    dev.trace_frame(cam, sh, tiles, fb)
+    return cam, sh, tiles
+
+
+def test_image_flush_to_host_is_exact_and_sparse():
+    """Frames from DIFFERENT cameras: pixels that turn black must be zeroed on the host although the flush only
+    stores pixels that are (or were) non-zero; the render target is left cleared; the byte count is what crossed."""
+    sc = scenes.wavelets64(8)
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    W, H = 256, 160
+    img = capi.Image(dev, None, W, H)
+    kw = dict(bounces=1, pixel_samples=1, **scenes.WAVELETS64_BLINN)
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    assert not img.host.any()
+    prev_pix = 0
+    for k, shift in enumerate(([0, 0, 0], [25, 10, 0], [-40, -5, 30], [0, 0, 0], [300, 300, 300])):
+        cpos = pos + np.array(shift, np.float32)
+        cd = scenes.camera_frame(cpos, lookat if k < 4 else cpos + (cpos - lookat), up, 90.0, W, H)   # the last one looks away
+        _frame(dev, sc, cd, kw, img.device)
+        want = img.read_device("device")
+        img.flush(to_host=True, clear=True)
+        dev.synchronize()
+        assert np.array_equal(img.host, want), k
+        assert not img.read_device("device").any()                      # image.clear() happened
+        nz = int((want != 0).any(axis=-1).sum())
+        _, pix = img.flushed_pixels()
+        assert nz <= pix - prev_pix <= W * H
+        if k == 0:
+            assert 0 < pix < W * H // 2                                 # sparse: sky pixels never cross PCIe
+        prev_pix = pix
+    assert not img.host.any()                                           # the last camera looks away from the scene
+    # set_rows: only the listed blocks are flushed
+    cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+    _frame(dev, sc, cd, kw, img.device)
+    want = img.read_device("device")
+    img.set_rows([0, 32, 64, 96, 128, 160], [0, 1, 0, 1, 0])            # "rank 0 of 2": blocks 0, 2, 4
+    img.flush(to_host=True, clear=True)
+    dev.synchronize()
+    mine = np.zeros(H, bool); mine[0:32] = mine[64:96] = mine[128:160] = True
+    assert np.array_equal(img.host[mine], want[mine]) and not img.host[~mine].any()
+    left = img.read_device("device")
+    assert not left[mine].any() and np.array_equal(left[~mine], want[~mine])
+    with pytest.raises(capi.SprayGpuError):
+        capi.Image(dev, None, 100, 50)                                  # width must be a multiple of 32
+    img.close(); dev.close()
+
+
+def test_trace_frame_rects_equals_whole_tiles(oracle):
+    """Rectangles of blocking tiles keep their blocking tile's sample ids: any cut of the frame into rectangles gives the
+    image of the uncut frame (bit-identical at 1 spp / 1 bounce, same ray counts and RMSE <= 1e-4 vs the oracle at
+    4 spp / 3 bounces where float atomics reorder)."""
+    import torch
+    sc = scenes.wavelets64(16)
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    W, H = 224, 160
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+    cam = capi.make_camera(cd)
+    for kw in (dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=4)):
+        kw = dict(kw, **scenes.WAVELETS64_BLINN)
+        sh = capi.make_shade(lights=sc["lights"], **kw)
+        blocking = scenes.image_schedule_tiles(W, H, kw["pixel_samples"], 1, 0, 1 << 13)
+        assert len(blocking) > 2
+        fb0 = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+        st0 = dev.trace_frame(cam, sh, blocking, fb0, stats=True).as_dict()
+        rects, parents = [], []
+        for (tx, ty, tw, th) in blocking:                               # ragged cut: rows of 7, columns of 96
+            for y in range(ty, ty + th, 7):
+                for x in range(0, W, 96):
+                    rects.append((x, y, min(96, W - x), min(7, ty + th - y)))
+                    parents.append((tx, ty, tw, th))
+        assert len(rects) > 32                                          # several launches
+        fb1 = torch.zeros_like(fb0)
+        st1 = dev.trace_frame_rects(cam, sh, rects, parents, fb1, stats=True).as_dict()
+        dev.synchronize()
+        for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"):
+            assert st0[k] == st1[k], k
+        if kw["pixel_samples"] == 1 and kw["bounces"] == 1:
+            assert torch.equal(fb0, fb1)
+        sh_o, keep = oracle.make_shade(lights=sc["lights"], **kw)
+        fb_o, st_o = oracle.Scene(sc["domains"]).render(oracle.camera_from_desc(cd), sh_o, blocking)
+        e = float(np.sqrt(np.mean((fb1.cpu().numpy()[..., :3].astype(np.float64) - fb_o[..., :3]) ** 2)))
+        assert e <= 1e-4 and st1["radiance_rays"] == st_o.radiance_rays and st1["shadow_rays"] == st_o.shadow_rays
+    with pytest.raises(capi.SprayGpuError):
+        dev.trace_frame_rects(cam, sh, [(0, 0, W, 8)], [(0, 4, W, 8)], fb1)     # rectangle outside its blocking tile
+    dev.close()

@@ -59,6 +59,59 @@ def test_insitu_single_rank_equals_fused(kw):
     comm.close(); dev.close()
 
 
+@pytest.mark.parametrize("spp,bounces", [(4, 1), (2, 3), (1, 2)])
+def test_insitu_single_rank_vs_oracle(oracle, spp, bounces):
+    """a13 against the ORACLE (VERDICT r1 "What's weak" 2): the in-situ tile at one rank, C5's shape (wavelet domains,
+    multi-sample), with the in-situ tracers' eye-ray jitter seed RandomSampler_init(pixid, s)
+    (src/insitu/insitu_ray.h:161-165) — NOT the ooc tracer's RandomSampler_init(bufid) the first round used."""
+    import torch
+    sc = scenes.wavelets64(8)
+    W, H = 144, 112
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+    kw = dict(bounces=bounces, pixel_samples=spp, **scenes.WAVELETS64_BLINN)
+    cam_o, cam = oracle.camera_from_desc(cd), capi.make_camera(cd)
+    tiles = scenes.image_schedule_tiles(W, H, spp, 1, 0, 1 << 13)
+    assert len(tiles) > 1
+    # eye rays: bit-exact, and different from the ooc seed at spp > 1
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    for t in tiles[:2]:
+        rays = np.zeros((t[2] * t[3] * spp, 8), np.float32)
+        dev.gen_eye_rays(cam, t, spp, rays, insitu=True)
+        assert np.array_equal(rays, oracle.gen_eye_rays(cam_o, t, spp, eye_seed=1))
+        if spp > 1:
+            assert not np.array_equal(rays, oracle.gen_eye_rays(cam_o, t, spp, eye_seed=0))
+    sh_o, keep = oracle.make_shade(lights=sc["lights"], eye_seed=1, **kw)
+    fb_o, st_o = oracle.Scene(sc["domains"]).render(cam_o, sh_o, tiles)
+    comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
+    sh = capi.make_shade(lights=sc["lights"], **kw)          # trace_tile_insitu forces the in-situ seed
+    fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    tot = {}
+    for t in tiles:
+        for k, v in comm.trace_tile_insitu(cam, sh, t, fb, stats=True).as_dict().items():
+            tot[k] = tot.get(k, 0) + v
+    dev.synchronize()
+    assert tot["eye_rays"] == st_o.eye_rays == W * H * spp
+    assert tot["radiance_rays"] == st_o.radiance_rays and tot["shadow_rays"] == st_o.shadow_rays
+    assert fb_o[..., :3].max() > 0.1
+    assert _rmse(fb.cpu().numpy(), fb_o) <= 1e-4
+    # the fused kernel follows shade.eye_seed (bench.py's C5 at one GPU)
+    sh1 = capi.make_shade(lights=sc["lights"], eye_seed=capi.EYE_SEED_INSITU, **kw)
+    fb1 = np.zeros((H, W, 4), np.float32)
+    t1 = {}
+    for t in tiles:
+        for k, v in dev.trace_tile(cam, sh1, t, fb1, stats=True).as_dict().items():
+            t1[k] = t1.get(k, 0) + v
+    assert t1["radiance_rays"] == st_o.radiance_rays and t1["shadow_rays"] == st_o.shadow_rays
+    assert _rmse(fb1, fb_o) <= 1e-4
+    if spp > 1:
+        sh_o0, keep0 = oracle.make_shade(lights=sc["lights"], eye_seed=0, **kw)
+        fb_o0, _ = oracle.Scene(sc["domains"]).render(cam_o, sh_o0, tiles)
+        assert _rmse(fb_o0, fb_o) > 1e-4                        # the two seeds really give different images
+    comm.close(); dev.close()
+
+
 def test_insitu_rejects_glass_and_host_fb():
     sc = scenes.wavelets64(2)
     sc["domains"][1]["mtl"] = (scenes.MTL_GLASS, (1.0, 1.5, 0))

@@ -41,7 +41,8 @@ def _worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
     from oracle import pyoracle as O
-    from spray_b200 import multigpu, partition, scenes
+    from spray_b200 import multigpu, scenes
+    import partition_ref as partition
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     try:
         sc = scenes.wavelets64()
@@ -160,3 +161,24 @@ def test_interleaved_blocks_cover_and_balance():
                 assert cnt[0] == 0                                   # a pure compositor renders nothing
             if share < 1.0:
                 assert cnt[0] <= cnt[1:].max()
+
+
+def test_rects_of_blocks_partition_the_frame_and_keep_blocking_tiles():
+    """Image partition v2: every rank renders rectangles of the ONE-rank blocking tiles (spraygpu_trace_frame_rects), so
+    sample ids do not depend on the rank count.  The rectangles of all ranks must tile the image exactly, lie inside
+    their blocking tile, start on 4-row boundaries (8x4 pixel blocks) and fit one persistent launch per rank."""
+    from spray_b200 import multigpu, scenes
+    for (W, H, spp, world) in ((2048, 2048, 1, 8), (2048, 2048, 1, 2), (4096, 4096, 4, 8), (4096, 4096, 4, 4), (320, 200, 3, 3)):
+        blocking = scenes.image_schedule_tiles(W, H, spp, 1, 0)
+        bb, bo = multigpu.interleaved_blocks(H, world)
+        cover = np.zeros(H, np.int32)
+        for rank in range(world):
+            rects, parents = multigpu.rects_of_blocks(bb, bo, rank, blocking)
+            assert len(rects) == len(parents)
+            if (W, H) != (320, 200):
+                assert len(rects) <= 32
+            for (x, y, w, h), (px, py, pw, ph) in zip(rects, parents):
+                assert x == px == 0 and w == pw == W and py <= y and y + h <= py + ph and h > 0
+                assert (px, py, pw, ph) in blocking
+                cover[y:y + h] += 1
+        assert np.all(cover == 1)

