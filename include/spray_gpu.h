@@ -306,6 +306,9 @@ SPRAYGPU_API int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const 
 SPRAYGPU_API int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear);
 /* cumulative pixels (16 B each) stored to the root composite / the host image by this rank's flushes */
 SPRAYGPU_API int spraygpu_image_flushed_pixels(spraygpu_image img, uint64_t* to_root, uint64_t* to_host);
+/* Plain full-size D2H copy of this rank's render target (which = 0) or of the root composite as mapped here
+ * (which = 1) into out_host (w*h float4); synchronises.  For checks and PPM output, not the frame path. */
+SPRAYGPU_API int spraygpu_image_read(spraygpu_image img, int which, float* out_host);
 /* stream synchronise + rendezvous of all ranks: after it every rank's flushed rows are visible at their destination */
 SPRAYGPU_API int spraygpu_image_barrier(spraygpu_image img);
 

@@ -128,6 +128,7 @@ _PROTOS = {
     "spraygpu_image_flush": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "spraygpu_image_flushed_pixels": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "spraygpu_image_barrier": (C.c_int, [_vp]),
+    "spraygpu_image_read": (C.c_int, [_vp, C.c_int, _vp]),
     "spraygpu_allreduce_keys_min": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
     "spraygpu_allreduce_occ_max": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
 }
@@ -480,14 +481,8 @@ class Image:
 
     def read_device(self, which="device"):
         """D2H copy of the render target / root composite (tests, parity checks)."""
-        import torch
         out = np.zeros((self.h, self.w, 4), np.float32)
-        src = self.device if which == "device" else self.root
-        rt = torch.cuda.cudart()
-        self.dev.synchronize()
-        err = rt.cudaMemcpy(out.ctypes.data, src, out.nbytes, 2)   # cudaMemcpyDeviceToHost
-        if int(err) != 0:
-            raise SprayGpuError("cudaMemcpy D2H failed: %s" % err)
+        _check(lib().spraygpu_image_read(self.h_, 0 if which == "device" else 1, out.ctypes.data))
         return out
 
     def close(self):

@@ -268,6 +268,17 @@ int spraygpu_image_flushed_pixels(spraygpu_image img, uint64_t* to_root, uint64_
   return SPRAYGPU_OK;
 }
 
+int spraygpu_image_read(spraygpu_image img, int which, float* out_host) {
+  SG_CHECK(img && out_host, SPRAYGPU_ERR_ARG, "image_read: NULL argument");
+  Image* im = (Image*)img;
+  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  const float4* src = im->d_target;
+  if (which == 1) src = im->nranks > 1 ? (const float4*)im->root_mapped[(size_t)im->root] : im->d_target;
+  SG_CUDA(cudaMemcpyAsync(out_host, src, im->bytes, cudaMemcpyDeviceToHost, im->dev->stream));
+  SG_CUDA(cudaStreamSynchronize(im->dev->stream));
+  return SPRAYGPU_OK;
+}
+
 int spraygpu_image_barrier(spraygpu_image img) {
   SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_barrier: img is NULL");
   Image* im = (Image*)img;

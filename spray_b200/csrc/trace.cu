@@ -244,6 +244,7 @@ struct Pending { vec3 o, d, w; int depth; };
 #define SPRAY_RENDER_THREADS 128
 #endif
 #define SPRAY_RENDER_WARPS (SPRAY_RENDER_THREADS / 32)
+static_assert(SPRAY_RENDER_WARPS <= SPRAY_MAX_CTA_WARPS, "CoopScratch (traverse.cuh) is sized for SPRAY_MAX_CTA_WARPS warps per CTA");
 
 // ------------------------------------------------------------------------------------------------
 // Per-warp ray queue (shared memory, SoA, LIFO).  Every ray that enters at least one resident domain

@@ -340,6 +340,32 @@ __device__ __forceinline__ bool tlas_any(const DomSmem& D, const RayCtx& r) {
 #ifndef SPRAY_TRI_PER_PASS
 #define SPRAY_TRI_PER_PASS 8
 #endif
+// ------------------------------------------------------------------------------------------------
+// Warp-cooperative triangle stage (SPRAY_COOP_TRI, north_star's "triangle blocks staged in shared memory").
+// ncu on the per-lane form (profiles/r01y_c3_render_tile_lines.txt): every triangle-test line runs at ~4 of 32 lanes —
+// few lanes have pending triangles in a given pass, each works its own list off serially (up to 8 dependent 48-byte
+// fetches), and the other lanes wait at the next __syncwarp.  Here the warp pools its pending (owner lane, triangle)
+// pairs in a shared-memory list (ballot-free prefix sum), then ALL lanes take one pair each: fetch the 48-byte
+// record, read the owner's ray by shuffle, run the same S1 test, and merge hits into the owner's slot with a 64-bit
+// shared-memory atomicMin on (t bits | primID) — the packed-key update of north_star.  The winner writes (u, v).
+// Same arithmetic per (ray, triangle) and the same (t, domain, prim) tie rule, so hit records stay bit-identical.
+//   1: node step, then the pooled triangle stage (triangles of this pass's node are tested in the same pass)
+//   2: software-pipelined — the triangles found by the PREVIOUS node step are fetched and tested while this pass's
+//      node fetch is in flight (one dependent memory round trip per pass instead of two)
+// ------------------------------------------------------------------------------------------------
+#ifndef SPRAY_COOP_TRI
+#define SPRAY_COOP_TRI 0
+#endif
+#ifndef SPRAY_COOP_K
+#define SPRAY_COOP_K 4          // triangles one lane may contribute per pass
+#endif
+#define SPRAY_MAX_CTA_WARPS 4          // every kernel that traverses runs 128-thread CTAs (static_assert in trace.cu)
+struct CoopScratch {
+  uint32_t pair[32 * SPRAY_COOP_K];     // owner lane << 27 | triangle index (leaf order, < 2^24)
+  unsigned long long best[32];          // per owner: min over this pass of (t bits << 32 | primID)
+  float2 uv[32];                        // (u, v) of that minimum
+  uint32_t anyflag;                     // any-hit mode: bit per owner
+};
 // One lane's traversal state and its three step kinds.
 #if SPRAY_POP_CULL
 struct LaneStack { uint4 e[SPRAY_STACK_SIZE]; };   // (child base, pending mask, distance bytes of slots 0..3, 4..7)
@@ -427,6 +453,159 @@ struct LaneTrav {
     for (int k = 0; k < SPRAY_TRI_PER_PASS && alive && tgy; ++k) tri_step<COUNT>(r, any, cnt);
 #endif
   }
+#if SPRAY_COOP_TRI
+  // what a lane WITHOUT pending triangles needs next (pops the stack on the way)
+  __device__ __forceinline__ int want_no_tri() {
+    if (!alive) return WANT_NONE;
+#if SPRAY_POP_CULL
+    while (ngy <= 0x00FFFFFFu && sp > 0) {
+      --sp;
+      const uint4 e = stk[sp];
+      ngx = e.x; gd0 = e.z; gd1 = e.w;
+      ngy = prune_group(e.y, gd0, gd1, out.t, oct);
+    }
+#else
+    if (ngy <= 0x00FFFFFFu && sp > 0) { --sp; ngx = sx[sp]; ngy = sy[sp]; }
+#endif
+    return ngy > 0x00FFFFFFu ? WANT_NODE : WANT_SOURCE;
+  }
+  // pool this lane's pending triangles (at most SPRAY_COOP_K) into the warp's pair list; returns the warp total
+  template <bool COUNT>
+  __device__ __forceinline__ int coop_contribute(CoopScratch& S, uint32_t* cnt) {
+    const int lane = threadIdx.x & 31;
+    int nt = alive ? min(__popc(tgy), SPRAY_COOP_K) : 0;
+    int incl = nt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += o;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return 0;
+    int at = incl - nt;
+    for (int k = 0; k < nt; ++k) {
+      const int ti = __ffs((int)tgy) - 1;
+      tgy &= tgy - 1;
+      S.pair[at + k] = ((uint32_t)lane << 27) | (tgx + (uint32_t)ti);
+    }
+    if (COUNT) cnt[2] += (uint32_t)nt;
+    S.best[lane] = ~0ull;
+    if (lane == 0) S.anyflag = 0u;
+    __syncwarp();
+    return total;
+  }
+  // all lanes: one pair each per round.  ptris / pdom: the contributing lane's triangle array and domain AT CONTRIBUTION
+  // time (a source step later in the pass may already have moved the lane to its next domain).
+  __device__ __forceinline__ void coop_test(CoopScratch& S, int total, const RayCtx& r, const bool any, const float4* ptris) {
+    const int lane = threadIdx.x & 31;
+    for (int base = 0; base < total; base += 32) {
+      const int idx = base + lane;
+      const bool valid = idx < total;
+      const uint32_t pr = valid ? S.pair[idx] : ((uint32_t)lane << 27);
+      const int owner = (int)(pr >> 27);
+      const vec3 O = mk3(__shfl_sync(0xffffffffu, r.o.x, owner), __shfl_sync(0xffffffffu, r.o.y, owner), __shfl_sync(0xffffffffu, r.o.z, owner));
+      const vec3 D = mk3(__shfl_sync(0xffffffffu, r.d.x, owner), __shfl_sync(0xffffffffu, r.d.y, owner), __shfl_sync(0xffffffffu, r.d.z, owner));
+      const float tn = __shfl_sync(0xffffffffu, r.tnear, owner);
+      const unsigned long long tp = __shfl_sync(0xffffffffu, (unsigned long long)ptris, owner);
+      const bool oany = __shfl_sync(0xffffffffu, (int)any, owner) != 0;
+      bool hit = false;
+      float T = 0.f, U = 0.f, V = 0.f, ad = 1.f;
+      unsigned long long key = ~0ull;
+      if (valid) {
+        vec3 v0, e1, e2; uint32_t prim;
+        TriLoaderG{(const float4*)tp}(pr & 0x07FFFFFFu, v0, e1, e2, prim);
+        hit = tri_test_raw(O, D, v0, e1, e2, tn, &T, &U, &V, &ad);
+        if (hit) {
+          if (oany) atomicOr(&S.anyflag, 1u << owner);
+          else {
+            key = ((unsigned long long)__float_as_uint(div_rn(T, ad)) << 32) | (unsigned long long)prim;
+            atomicMin(&S.best[owner], key);
+          }
+        }
+      }
+      __syncwarp();
+      if (hit && !oany && S.best[owner] == key) S.uv[owner] = make_float2(div_rn(U, ad), div_rn(V, ad));
+      __syncwarp();
+    }
+  }
+  // owner side: fold the pooled result into this lane's closest hit / any-hit flag
+  __device__ __forceinline__ void coop_merge(CoopScratch& S, const RayCtx& r, const bool any, uint32_t pdom) {
+    const int lane = threadIdx.x & 31;
+    if (any) {
+      if ((S.anyflag >> lane) & 1u) { found = true; alive = false; }
+      return;
+    }
+    const unsigned long long key = S.best[lane];
+    if (key == ~0ull) return;
+    const float t = __uint_as_float((uint32_t)(key >> 32));
+    const uint32_t prim = (uint32_t)key;
+    if (t < out.t || (t == out.t && (pdom < out.dom || (pdom == out.dom && prim < out.prim)))) {
+      const float2 uv = S.uv[lane];
+      out.t = t; out.u = uv.x; out.v = uv.y; out.prim = prim; out.dom = pdom;
+#if SPRAY_POP_CULL
+      ngy = prune_group(ngy, gd0, gd1, out.t, r.octinv);
+#endif
+    }
+  }
+  template <bool COUNT, typename Source>
+  __device__ __forceinline__ void pass_coop(Source& src, const RayCtx& r, const bool any, uint32_t* cnt, CoopScratch& S) {
+#if SPRAY_POP_CULL
+    oct = r.octinv;
+#endif
+#if SPRAY_COOP_TRI == 1
+    // node step first; its triangles are pooled and tested in this same pass
+    int w = (alive && !tgy) ? want_no_tri() : WANT_NONE;
+    if (w == WANT_SOURCE) { source_step<COUNT>(src, r, cnt); w = (alive && !tgy) ? want_no_tri() : WANT_NONE; }
+    __syncwarp();
+    if (w == WANT_NODE) node_step<COUNT>(r, cnt);
+    __syncwarp();
+    const float4* ptris = tris; const uint32_t pdom = dom;
+    const int total = coop_contribute<COUNT>(S, cnt);
+    if (total) { coop_test(S, total, r, any, ptris); coop_merge(S, r, any, pdom); }
+#else
+    // pipelined: pool the triangles of the PREVIOUS node step, issue this pass's node fetch, test the triangles while
+    // the node is in flight, then do the node arithmetic
+    const float4* ptris = tris; const uint32_t pdom = dom;
+    const int total = coop_contribute<COUNT>(S, cnt);
+    int w = (alive && !tgy) ? want_no_tri() : WANT_NONE;
+    if (w == WANT_SOURCE) { source_step<COUNT>(src, r, cnt); w = (alive && !tgy) ? want_no_tri() : WANT_NONE; }
+    __syncwarp();
+    u4 q0, q1, q2, q3, q4;
+    const bool donode = w == WANT_NODE;
+    if (donode) node_fetch<COUNT>(r, cnt, q0, q1, q2, q3, q4);
+    if (total) coop_test(S, total, r, any, ptris);
+    if (donode) node_math(r, q0, q1, q2, q3, q4);
+    if (total) coop_merge(S, r, any, pdom);
+#endif
+  }
+  // node_step split in two so that other loads can be issued between the fetch and the arithmetic
+  template <bool COUNT>
+  __device__ __forceinline__ void node_fetch(const RayCtx& r, uint32_t* cnt, u4& q0, u4& q1, u4& q2, u4& q3, u4& q4) {
+    const uint32_t imask = ngy & 0xffu;
+    const int bit = 31 - __clz((int)ngy);
+    ngy &= ~(1u << bit);
+    if (ngy > 0x00FFFFFFu && sp >= SPRAY_STACK_SIZE) SPRAY_STACK_OVERFLOW();
+#if SPRAY_POP_CULL
+    if (ngy > 0x00FFFFFFu) { stk[sp] = make_uint4(ngx, ngy, gd0, gd1); ++sp; }
+#else
+    if (ngy > 0x00FFFFFFu) { sx[sp] = ngx; sy[sp] = ngy; ++sp; }
+#endif
+    const uint32_t slot = (uint32_t)(bit - 24) ^ r.octinv;
+    const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
+    NodeLoaderG{nodes}(ngx + rel, q0, q1, q2, q3, q4);
+    if (COUNT) cnt[1]++;
+  }
+  __device__ __forceinline__ void node_math(const RayCtx& r, const u4& q0, const u4& q1, const u4& q2, const u4& q3, const u4& q4) {
+#if SPRAY_POP_CULL
+    const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, out.t, &gd0, &gd1);
+#else
+    const uint32_t hm = node8_hits(q0, q1, q2, q3, q4, r, out.t);
+#endif
+    ngx = q1.x; tgx = q1.y;
+    ngy = (hm & 0xFF000000u) | (q0.w >> 24);
+    tgy = hm & 0x00FFFFFFu;
+  }
+#endif  // SPRAY_COOP_TRI
   // fetch + test one 80-byte node (only when no triangle is pending; ngy has an inner child here)
   template <bool COUNT>
   __device__ __forceinline__ void node_step(const RayCtx& r, uint32_t* cnt) {
@@ -490,10 +669,18 @@ __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const Ra
   LaneStack stack;
   LaneTrav T(stack);
   T.begin(act);
+#if SPRAY_COOP_TRI
+  __shared__ CoopScratch coop_scratch[SPRAY_MAX_CTA_WARPS];
+  CoopScratch& S = coop_scratch[threadIdx.x >> 5];
+#endif
   for (;;) {
     __syncwarp();
     if (!__any_sync(0xffffffffu, T.alive)) break;
+#if SPRAY_COOP_TRI
+    T.pass_coop<COUNT>(src, r, any, cnt, S);
+#else
     T.pass<COUNT>(src, r, any, cnt);
+#endif
   }
   out = T.out;
   return any ? T.found : (out.t < INFINITY);
