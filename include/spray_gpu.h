@@ -269,6 +269,18 @@ SPRAYGPU_API int spraygpu_partition_domains(int ndomains, const float* world_aab
 SPRAYGPU_API int spraygpu_trace_tile_insitu(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
                                             const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
                                             spraygpu_stats* stats);
+/* The same blocking tile with the exchange done over PEER MEMORY (CUDA IPC mappings of every rank's wave buffers over
+ * NVLink / NVSwitch) inside the compute kernels instead of dense NCCL all-reduces: a hit merges its packed key into
+ * every rank's key array with a 64-bit system-scope atomicMin, the rank owning the winning domain stores 16 B of hit
+ * attributes to every rank, every rank shades every hit (identical arithmetic, nothing else travels), occlusions are
+ * single-byte stores to the sample's HOME rank, and ranks meet at device-side barriers (no host involvement per wave).
+ * The home rank of image row y is (y / rows_per_block) % nranks: it alone accumulates that row, so fb ends up holding
+ * this rank's ROWS of the final image (not a partial sum) — describe the same blocks to spraygpu_image_set_rows and
+ * spraygpu_image_flush moves them to the root / host.  Same image, statistics and sample numbering as
+ * spraygpu_trace_tile_insitu.  One rank per GPU; every GPU must be able to map its peers (NVLink or PCIe P2P). */
+SPRAYGPU_API int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
+                                                const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
+                                                int rows_per_block, spraygpu_stats* stats);
 /* HdrImage::composite (image.h:167-181): fb = sum over ranks, valid on `root` (in place, device pointer). */
 SPRAYGPU_API int spraygpu_image_reduce(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, size_t npixels, int root);
 /* Image-partition composite for DISJOINT row bands (rank r rendered rows [row_begin[r], row_begin[r+1])):
@@ -297,7 +309,8 @@ SPRAYGPU_API int spraygpu_image_destroy(spraygpu_image img);                 /* 
 SPRAYGPU_API float* spraygpu_image_device(spraygpu_image img);               /* this rank's render target (device, w*h float4) */
 SPRAYGPU_API float* spraygpu_image_host(spraygpu_image img);                 /* HdrImage::buf: pinned host pixels */
 SPRAYGPU_API float* spraygpu_image_root(spraygpu_image img);                 /* the root's composite as mapped in THIS process (device) */
-/* Which rows this rank renders: blocks [row_begin[b], row_begin[b+1]) with owner[b] == rank (owner NULL: all mine).
+/* Which rows this rank renders: blocks [row_begin[b], row_begin[b+1]) with owner[b] == rank (owner NULL: all mine;
+ * owner[b] == -1: rendered by nobody on this communicator).
  * Replaces the rank's stripe of ImageScheduleTileList (src/render/tile.cc:317-391). */
 SPRAYGPU_API int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_begin /* nblocks + 1 */,
                                          const int32_t* owner /* nblocks or NULL */);

@@ -211,8 +211,10 @@ int spraygpu_device_create(int cuda_device, spraygpu_device* out) {
   d->sm_count = prop.multiProcessorCount;
   SG_CUDA(cudaMalloc(&d->d_domains, sizeof(DomainEntry) * SPRAYGPU_MAX_DOMAINS));
   SG_CUDA(cudaMalloc(&d->d_tlas, sizeof(TlasNode) * SPRAY_TLAS_MAX_NODES));
-  SG_CUDA(cudaMalloc(&d->d_counters, sizeof(unsigned long long) * 8));
-  SG_CUDA(cudaMemset(d->d_counters, 0, sizeof(unsigned long long) * 8));
+  // 8 render counters + 8 words of scratch that is NOT touched by render launches (set_mesh's max-index reduction
+  // runs in the middle of an out-of-core frame, between two counted launches)
+  SG_CUDA(cudaMalloc(&d->d_counters, sizeof(unsigned long long) * 16));
+  SG_CUDA(cudaMemset(d->d_counters, 0, sizeof(unsigned long long) * 16));
   SG_CUDA(cudaMallocHost(&d->pinned, 4096));
   d->pinned_bytes = 4096;
   SG_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
@@ -330,8 +332,8 @@ int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, c
     cudaFree(s->d_rgb); s->d_rgb = nullptr; s->cap_rgb = 0;
   }
   // every index must address a vertex (the reference trusts the PLY, ply_loader.cc:243-256; a GPU build would turn a
-  // bad index into out-of-bounds device writes).  d_counters[7] is free outside a render launch.
-  uint32_t* d_max = (uint32_t*)(d->d_counters + 7);
+  // bad index into out-of-bounds device writes).  d_counters[8] is scratch no render launch uses.
+  uint32_t* d_max = (uint32_t*)(d->d_counters + 8);
   int vrc = launch_max_index(d, s->d_faces, 3 * nf, d_max);
   if (vrc) return vrc;
   uint32_t* h_max = (uint32_t*)d->pinned;

@@ -83,7 +83,11 @@ struct Comm {
   Device* dev = nullptr;
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  // state of the peer-memory in-situ path (insitu2.cu), released by spraygpu_comm_destroy
+  void* p2p = nullptr;
+  void (*p2p_free)(Comm*, void*) = nullptr;
 };
+void** comm_p2p_slot(Comm* c, void (***free_fn)(Comm*, void*)) { *free_fn = &c->p2p_free; return &c->p2p; }
 
 // ------------------------------------------------------------------------------------------------
 // Peer-mapped device buffers (CUDA IPC over NVLink / NVSwitch P2P): every rank allocates `bytes`, the 64-byte IPC
@@ -211,6 +215,7 @@ int spraygpu_comm_destroy(spraygpu_comm comm) {
   Comm* c = (Comm*)comm;
   cudaSetDevice(c->dev->cuda_device);
   cudaStreamSynchronize(c->dev->stream);
+  if (c->p2p && c->p2p_free) { c->p2p_free(c, c->p2p); c->p2p = nullptr; }   // collective (host barrier inside)
   if (c->comm && nccl()) g_nccl.CommDestroy(c->comm);
   delete c;
   return SPRAYGPU_OK;

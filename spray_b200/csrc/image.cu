@@ -218,7 +218,7 @@ int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_
   for (int b = 0; b < nblocks; ++b) {
     SG_CHECK(row_begin[b] >= 0 && row_begin[b] <= row_begin[b + 1] && row_begin[b + 1] <= im->h, SPRAYGPU_ERR_ARG,
              "image_set_rows: block %d = rows [%d, %d) of %d", b, row_begin[b], row_begin[b + 1], im->h);
-    if (owner) SG_CHECK(owner[b] >= 0 && owner[b] < im->nranks, SPRAYGPU_ERR_ARG, "image_set_rows: block %d owner %d", b, owner[b]);
+    if (owner) SG_CHECK(owner[b] >= -1 && owner[b] < im->nranks, SPRAYGPU_ERR_ARG, "image_set_rows: block %d owner %d", b, owner[b]);
     if (owner && owner[b] != im->rank) continue;
     const int rows = row_begin[b + 1] - row_begin[b];
     if (rows <= 0) continue;

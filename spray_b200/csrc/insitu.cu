@@ -242,6 +242,7 @@ extern "C" int spraygpu_trace_tile_insitu(spraygpu_device dev_h, spraygpu_comm c
     insitu_init_wave_kernel<<<grid_for(3 * n, 256), 256, 0, st>>>(w, n);
     dev->launches++;
     const size_t dsmem = dom_smem_bytes(dev->ndomains, dev->tlas_n, 0);
+    SG_DYN_SMEM(insitu_shadow_kernel, dsmem);
     for (int depth = 0; depth < shade->bounces; ++depth) {
       P.depth = depth;
       rc = launch_intersect_domains(dev, rays, n, keys, nullptr, 0);                       // 1

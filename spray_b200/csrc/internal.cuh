@@ -31,6 +31,15 @@ void set_error(const char* fmt, ...);
     }                                        \
   } while (0)
 
+// Kernels that stage the domain table + top-level tree in dynamic shared memory need the opt-in above 48 KB
+// (hundreds of domains with a deep top-level tree); refuse what no B200 CTA can hold.
+#define SG_DYN_SMEM(kern, bytes)                                                                                     \
+  do {                                                                                                               \
+    const size_t b__ = (bytes);                                                                                      \
+    SG_CHECK(b__ <= 227u * 1024u, SPRAYGPU_ERR_LIMIT, "%s: %zu B of shared memory for the domain table (limit 227 KB)", #kern, b__); \
+    if (b__ > 48u * 1024u) SG_CUDA(cudaFuncSetAttribute((const void*)(kern), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b__)); \
+  } while (0)
+
 // device-visible per-domain record (96 B)
 struct DomainEntry {
   float box[6];           // world AABB as given by the scene description

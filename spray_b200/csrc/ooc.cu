@@ -368,6 +368,7 @@ extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_cam
           dev->launches++;
         }
         if (have_sh) {
+          SG_DYN_SMEM(ooc_shadow_kernel, dom_smem_bytes(nd, dev->tlas_n, 0));
           ooc_shadow_kernel<<<ooc_grid(total, 128), 128, dom_smem_bytes(nd, dev->tlas_n, 0), st>>>(
               dev->d_domains, nd, dev->d_tlas, dev->tlas_n, rays, sdir, n, total, occ);
           dev->launches++;

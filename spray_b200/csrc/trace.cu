@@ -634,6 +634,7 @@ static CameraDev to_camdev(const spraygpu_camera* c) {
 int launch_domain_lists(Device* dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts, int32_t* ids,
                         float* tmins) {
   if (!n) return SPRAYGPU_OK;
+  SG_DYN_SMEM(domain_lists_kernel, dom_smem_bytes(dev->ndomains, dev->tlas_n, 4));
   domain_lists_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 4), dev->stream>>>(
       dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, cap, counts, ids, tmins);
   dev->launches++;
@@ -657,6 +658,7 @@ int launch_occluded_scene(Scene* sc, const spraygpu_ray* rays, size_t n, uint8_t
 }
 int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint64_t* keys, float* uv, int merge) {
   if (!n) return SPRAYGPU_OK;
+  SG_DYN_SMEM(intersect_domains_kernel, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0));
   intersect_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0), dev->stream>>>(
       dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, keys, uv, merge);
   dev->launches++;
@@ -665,6 +667,7 @@ int launch_intersect_domains(Device* dev, const spraygpu_ray* rays, size_t n, ui
 }
 int launch_occluded_domains(Device* dev, const spraygpu_ray* rays, size_t n, uint8_t* occ, int merge) {
   if (!n) return SPRAYGPU_OK;
+  SG_DYN_SMEM(occluded_domains_kernel, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0));
   occluded_domains_kernel<<<grid_for(n, 128), 128, dom_smem_bytes(dev->ndomains, dev->tlas_n, 0), dev->stream>>>(
       dev->d_domains, dev->ndomains, dev->d_tlas, dev->tlas_n, rays, n, occ, merge);
   dev->launches++;

@@ -134,45 +134,96 @@ class ImagePartitionRenderer:
 
 
 class InsituRenderer:
-    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, round_robin=False):
+    """Domain partition (the reference's in-situ tracers): rank r holds the domains spraygpu_partition_domains gives it
+    and every rank walks every blocking tile.
+
+    mode "p2p" (default): spraygpu_trace_tile_insitu_p2p — keys / hit attributes / occlusion bytes cross NVLink inside
+    the kernels, each rank accumulates its HOME rows (interleaved blocks of `rows_per_block` image rows) and the sparse
+    image flush moves them to the root composite / the shared pinned host image.
+    mode "nccl": spraygpu_trace_tile_insitu — five dense NCCL all-reduces per wave, partial images summed with
+    spraygpu_image_reduce (round 1's path, kept for the A/B)."""
+
+    def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, round_robin=False, mode="p2p", rows_per_block=8,
+                 shm_name=None, max_tile_samples=None):
         import torch
         self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
+        self.mode, self.rpb = mode, int(rows_per_block)
         wb = np.stack([d["bounds"] for d in scene["domains"]])
         self.domain_to_rank = capi.partition_domains(wb, scenes.scene_bounds(scene), world, round_robin)
         self.owned = [i for i, r in enumerate(self.domain_to_rank) if r == rank]
         dev.load_scene(scene, owned=self.owned)
-        self.tiles = band_tiles(W, (0, H), shade.pixel_samples)   # every rank walks every blocking tile
-        self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-        self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
+        if max_tile_samples is None:
+            max_tile_samples = (4 << 20) if mode == "p2p" else (1 << 20)   # p2p: fewer, larger waves = fewer peer barriers
+        self.tiles = band_tiles(W, (0, H), shade.pixel_samples, max_tile_samples)   # every rank walks every blocking tile
+        if mode == "p2p":
+            self.image = capi.Image(dev, comm, W, H, shm_name)
+            begin = list(range(0, H, self.rpb)) + [H]
+            self.image.set_rows(begin, [b % world for b in range(len(begin) - 1)])
+            self.fb = self.image.device
+            self.fb_host = None
+        else:
+            self.image = None
+            self.fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+            self.fb_host = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
+
+    def _trace(self, stats=False):
+        tot = {}
+        for t in self.tiles:
+            if self.mode == "p2p":
+                st = self.comm.trace_tile_insitu_p2p(self.cam, self.shade, t, self.fb, self.rpb, stats=stats)
+            else:
+                st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=stats)
+            if stats:
+                for k, v in st.as_dict().items():
+                    tot[k] = tot.get(k, 0) + v            # already summed over ranks by the library
+        return tot
 
     def frame_device(self):
-        self.fb.zero_()
-        for t in self.tiles:
-            self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb)
-        self.comm.image_reduce(self.fb, self.W * self.H, 0)
+        if self.mode == "p2p":
+            self._trace()
+            self.image.flush(to_root=True, to_host=False, clear=True)
+        else:
+            self.fb.zero_()
+            self._trace()
+            self.comm.image_reduce(self.fb, self.W * self.H, 0)
 
     def frame_host(self):
-        self.frame_device()
-        if self.rank == 0:
-            self.fb_host.copy_(self.fb, non_blocking=True)
+        if self.mode == "p2p":
+            self._trace()
+            self.image.flush(to_root=False, to_host=True, clear=True)
+        else:
+            self.frame_device()
+            if self.rank == 0:
+                self.fb_host.copy_(self.fb, non_blocking=True)
         self.dev.synchronize()
 
     def count_rays(self):
-        tot = {k: 0 for k, _ in capi.Stats._fields_}
+        if self.mode == "p2p":
+            tot = self._trace(stats=True)
+            self.image.flush(to_root=True, to_host=False, clear=True)     # leave the render target cleared
+            return tot
         self.fb.zero_()
-        for t in self.tiles:
-            st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=True)   # summed over ranks by the library
-            for k, v in st.as_dict().items():
-                tot[k] = tot.get(k, 0) + v
-        return tot
+        return self._trace(stats=True)
 
     def composite_image(self):
-        """rank 0: the composited frame after frame_device() (numpy)."""
+        """rank 0: the composited frame after frame_device() (numpy); call on every rank."""
         self.dev.synchronize()
+        if self.mode == "p2p":
+            self.image.barrier()                       # every rank's flush has landed in the root composite
+            return self.image.read_device("root") if self.rank == 0 else None
         return self.fb.cpu().numpy()
 
+    def host_image(self):
+        self.dev.synchronize()
+        if self.mode == "p2p":
+            self.image.barrier()
+            return self.image.host
+        return self.fb_host.numpy() if self.fb_host is not None else None
+
     def close(self):
-        pass
+        if self.image is not None:
+            self.image.close()
+            self.image = None
 
 
 def _rmse(a, b):
@@ -187,6 +238,12 @@ def single_gpu_frame(dev, cam, shade, W, H):
     st = dev.trace_frame(cam, shade, tiles, fb, stats=True).as_dict()
     dev.synchronize()
     return fb.cpu().numpy(), st
+
+
+INSITU_LABEL = ("in-situ domain partition x%d (Morton): each GPU owns %d of %d domains; hit keys merged by 64-bit system-scope "
+                "atomicMin into every GPU's key array over NVLink (CUDA IPC), hit attributes and occlusion bytes by peer stores, "
+                "device-side barriers, no NCCL per wave; each GPU accumulates its home rows (blocks of %d rows) and flushes them "
+                "to rank 0 / the shared pinned host image")
 
 
 def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, workload, metric, unit):
@@ -244,25 +301,39 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         d2h = None
         r.close()
     else:
-        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm)
+        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, shm_name=shm)
         st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
         pc = insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream)
-        par_label = ("in-situ domain partition x%d (Morton), NCCL min-all-reduce on 64-bit hit keys + max-all-reduce on occlusion, NCCL image reduce" % world)
-        fp = None
+        r.frame_host()
+        host = r.host_image()
+        if rank == 0:
+            pc["host_image_equals_composite"] = bool(np.array_equal(host, pc.pop("_composite")))
+        fp = _sum_over_ranks(dict(zip(("root", "host"), r.image.flushed_pixels())))
+        par_label = INSITU_LABEL % (world, len(r.owned), len(sc["domains"]), r.rpb)
+        r.close()
     insitu_extra = None
     if args.partition == "both" and mode == "image":
         dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
         comm2 = bootstrap_comm(dev2, rank, world)
-        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2)
-        st2 = r2.count_rays()
         timer2 = type(timer)(timer.stream, timer.flush, dev2, world)
+        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, shm_name=shm + "_i")
+        st2 = r2.count_rays()
         ms2, l2 = timer2(r2.frame_device, max(args.steps // 2, 3), 3)
+        ms2h, _ = timer2(r2.frame_host, max(args.steps // 2, 3), 2)
         pc2 = insitu_parity_check(r2, sc, cam, sh, W, H, rank, local_rank, stream)
+        if rank == 0:
+            pc2.pop("_composite", None)
         r2n = st2["radiance_rays"] + st2["shadow_rays"]
         insitu_extra = {"value": r2n / (ms2 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2, "gpu_launches": int(l2),
-                        "parallelism": "in-situ domain partition x%d (Morton): each GPU owns %d of %d domains" % (world, len(r2.owned), len(sc["domains"])),
+                        "e2e": {"value": r2n / (ms2h * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2h},
+                        "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb),
                         "parity_check": pc2}
-        r2.close(); comm2.close(); dev2.close()
+        r2.close()
+        # A/B: round 1's exchange (dense NCCL all-reduces per wave) on the same communicator
+        r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl")
+        ms3, l3 = timer2(r3.frame_device, 3, 2)
+        insitu_extra["nccl_allreduce_variant"] = {"value": r2n / (ms3 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms3, "gpu_launches": int(l3)}
+        r3.close(); comm2.close(); dev2.close()
     if rank == 0:
         line = {"metric": metric, "value": rays / (ms_dev * 1e-3) / 1e6, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong",
@@ -301,12 +372,15 @@ def insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream):
     if rank == 0:
         full = capi.Device(local_rank, stream=stream.cuda_stream)
         full.load_scene(sc)
-        ref, st1 = single_gpu_frame(full, cam, sh, W, H)
+        sh_i = capi.Shade.from_buffer_copy(sh)
+        sh_i.eye_seed = capi.EYE_SEED_INSITU           # the in-situ tile always jitters with RandomSampler_init(pixid, s)
+        ref, st1 = single_gpu_frame(full, cam, sh_i, W, H)
         kf = torch.zeros(n, dtype=torch.int64, device="cuda")
         full.intersect_domains(rays, n, kf, None)
         full.synchronize()
         pc = {"against": "the same frame on ONE GPU holding every domain (fused kernel)", "rmse": _rmse(img, ref),
-              "max_abs": float(np.abs(img[..., :3] - ref[..., :3]).max()), "keys_equal": bool(torch.equal(keys, kf))}
+              "max_abs": float(np.abs(img[..., :3] - ref[..., :3]).max()), "keys_equal": bool(torch.equal(keys, kf)),
+              "bit_identical": bool(np.array_equal(img, ref)), "_composite": img}
         full.close()
     dist.barrier()
     return pc

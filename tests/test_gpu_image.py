@@ -49,7 +49,7 @@ def test_image_flush_to_host_is_exact_and_sparse():
     cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
     _frame(dev, sc, cd, kw, img.device)
     want = img.read_device("device")
-    img.set_rows([0, 32, 64, 96, 128, 160], [0, 1, 0, 1, 0])            # "rank 0 of 2": blocks 0, 2, 4
+    img.set_rows([0, 32, 64, 96, 128, 160], [0, -1, 0, -1, 0])          # blocks 1 and 3 belong to nobody here (-1)
     img.flush(to_host=True, clear=True)
     dev.synchronize()
     mine = np.zeros(H, bool); mine[0:32] = mine[64:96] = mine[128:160] = True

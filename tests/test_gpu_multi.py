@@ -21,9 +21,10 @@ def _rmse(a, b):
     return float(np.sqrt(np.mean((a[..., :3].astype(np.float64) - b[..., :3].astype(np.float64)) ** 2)))
 
 
+@pytest.mark.parametrize("p2p", [False, True])
 @pytest.mark.parametrize("kw", [dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=2),
                                 dict(shader=1, bounces=2, pixel_samples=1, ao_samples=3)])
-def test_insitu_single_rank_equals_fused(kw):
+def test_insitu_single_rank_equals_fused(kw, p2p):
     import torch
     sc = scenes.wavelets64(16)
     if kw.get("shader", 0) == 0:
@@ -36,7 +37,8 @@ def test_insitu_single_rank_equals_fused(kw):
     pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
     cd = scenes.camera_frame(pos + np.array([25, 15, 5], np.float32), lookat, up, 75.0, W, W)
     cam = capi.make_camera(cd)
-    sh = capi.make_shade(lights=sc["lights"], **dict(dict(ao_samples=2), **kw), **scenes.WAVELETS64_BLINN)
+    # the in-situ tile always jitters with RandomSampler_init(pixid, s): give the fused kernel the same seed
+    sh = capi.make_shade(lights=sc["lights"], eye_seed=capi.EYE_SEED_INSITU, **dict(dict(ao_samples=2), **kw), **scenes.WAVELETS64_BLINN)
     dev = capi.Device(0)
     dev.load_scene(sc)
     comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
@@ -46,7 +48,8 @@ def test_insitu_single_rank_equals_fused(kw):
     ta, tb = {}, {}
     for t in tiles:
         for fb, tot, fn in ((fb_a, ta, lambda: dev.trace_tile(cam, sh, t, fb_a, stats=True)),
-                            (fb_b, tb, lambda: comm.trace_tile_insitu(cam, sh, t, fb_b, stats=True))):
+                            (fb_b, tb, (lambda: comm.trace_tile_insitu_p2p(cam, sh, t, fb_b, 8, stats=True)) if p2p else
+                                 (lambda: comm.trace_tile_insitu(cam, sh, t, fb_b, stats=True)))):
             for k, v in fn().as_dict().items():
                 tot[k] = tot.get(k, 0) + v
     dev.synchronize()
@@ -96,6 +99,15 @@ def test_insitu_single_rank_vs_oracle(oracle, spp, bounces):
     assert tot["radiance_rays"] == st_o.radiance_rays and tot["shadow_rays"] == st_o.shadow_rays
     assert fb_o[..., :3].max() > 0.1
     assert _rmse(fb.cpu().numpy(), fb_o) <= 1e-4
+    # the peer-memory variant (insitu2.cu): same image and counts
+    fb2 = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    tot2 = {}
+    for t in tiles:
+        for k, v in comm.trace_tile_insitu_p2p(cam, sh, t, fb2, 4, stats=True).as_dict().items():
+            tot2[k] = tot2.get(k, 0) + v
+    dev.synchronize()
+    assert tot2["radiance_rays"] == st_o.radiance_rays and tot2["shadow_rays"] == st_o.shadow_rays and tot2["hits"] == tot["hits"]
+    assert _rmse(fb2.cpu().numpy(), fb_o) <= 1e-4
     # the fused kernel follows shade.eye_seed (bench.py's C5 at one GPU)
     sh1 = capi.make_shade(lights=sc["lights"], eye_seed=capi.EYE_SEED_INSITU, **kw)
     fb1 = np.zeros((H, W, 4), np.float32)
