@@ -36,6 +36,10 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
       timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extra-workloads --workload $wl > $out/ncu_plain_$wl.log 2>&1 &&
       ncu --set full --clock-control none --import-source on -k regex:render_tile -c 3 -o $out/prof_$wl python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extra-workloads --workload $wl > $out/ncu_$wl.log 2>&1
       ls -la $out/prof_$wl.ncu-rep ;;
+    insitu1)  # one-rank wavefront in-situ breakdown: plain run, then the ncu launch list of the same command
+      timeout 600 python tools/insitu_one.py $arg 3 > $out/insitu1_$arg.log 2>&1 &&
+      ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/insitu1_${arg}_launches.csv python tools/insitu_one.py $arg 1 > $out/insitu1_${arg}_ncu.log 2>&1
+      tail -3 $out/insitu1_$arg.log ;;
     smoke)
       timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; tail -2 $out/smoke.log ;;
     multi)   # multi:<nproc>:<script and args>
