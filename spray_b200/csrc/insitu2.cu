@@ -63,9 +63,9 @@ struct PeerPtrs { char* base[P2P_MAX_RANKS]; };
 // ---- device-side barrier ------------------------------------------------------------------------------------------
 // Called by EVERY thread at the end of a kernel whose peer stores must be visible before the peers go on.
 __device__ __forceinline__ void grid_signal_peers(unsigned int* done, const PeerPtrs& P, int nranks, int me) {
-  __threadfence_system();                  // this thread's peer stores / atomics are performed system-wide
-  __syncthreads();
+  __syncthreads();                         // the CTA's peer stores / atomics happen-before thread 0's fence ...
   if (threadIdx.x == 0) {
+    __threadfence_system();                // ... which is cumulative: they are performed system-wide before the signal
     const unsigned int total = gridDim.x * gridDim.y;
     if (atomicAdd(done, 1u) == total - 1u) {
       *done = 0u;                          // ready for the next signalling kernel (stream order)
