@@ -34,7 +34,7 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
     ncu)
       wl=$arg
       timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extra-workloads --workload $wl > $out/ncu_plain_$wl.log 2>&1 &&
-      ncu --set full --clock-control none --import-source on -k regex:render_tile -c 3 -o $out/prof_$wl python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extra-workloads --workload $wl > $out/ncu_$wl.log 2>&1
+      ncu --set full --clock-control none --import-source on -k regex:render_tile --launch-skip 4 -c 2 -o $out/prof_$wl python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extra-workloads --workload $wl > $out/ncu_$wl.log 2>&1
       ls -la $out/prof_$wl.ncu-rep ;;
     insitu1)  # one-rank wavefront in-situ breakdown: plain run, then the ncu launch list of the same command
       timeout 600 python tools/insitu_one.py $arg 3 > $out/insitu1_$arg.log 2>&1 &&
@@ -44,6 +44,7 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
       timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; tail -2 $out/smoke.log ;;
     multi)   # multi:<nproc>:<script and args>
       np_=${arg%%:*}; cmd=${arg#*:}
-      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $np_ --master-addr 127.0.0.1 --master-port 29533 $cmd > $out/multi_$(echo "$cmd" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60).log 2>&1; echo "multi $cmd rc $?"; tail -4 $out/multi_*.log | tail -8 ;;
+      lg=$out/multi_n${np_}_$(echo "$cmd" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60)
+      timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $np_ --master-addr 127.0.0.1 --master-port 29533 $cmd > $lg.log 2> $lg.err; echo "multi $np_ $cmd rc $?"; tail -c 1500 $lg.log; tail -3 $lg.err ;;
   esac
 done
