@@ -281,6 +281,22 @@ SPRAYGPU_API int spraygpu_trace_tile_insitu(spraygpu_device dev, spraygpu_comm c
 SPRAYGPU_API int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
                                                 const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
                                                 int rows_per_block, spraygpu_stats* stats);
+/* The in-situ blocking tile with TRUE RAY FORWARDING — replaces insitu::MultiThreadTracer's send / receive loop
+ * (src/insitu/insitu_multithread_tracer.inl:135-195, :313-442), insitu::Comm's per-destination MsgHeader + Ray[]
+ * messages (src/insitu/insitu_comm.inl:51-92) and the WorkStats termination count (src/insitu/insitu_work_stats.cc:34-85).
+ * Every sample has a HOME rank (image row y -> (y / rows_per_block) % nranks, as in spraygpu_trace_tile_insitu_p2p): the
+ * home rank alone generates, shades and accumulates it.  A ray is appended — 32 bytes, from inside the kernel that
+ * produced it, over NVLink / NVSwitch peer memory — to the inbox of every rank that owns a domain the ray ENTERS (exact
+ * slab test against all domain boxes); owners trace their inbox against their own domains, merge closest hits into the
+ * home rank's key array with a 64-bit system-scope atomicMin, store occlusions as single bytes and hit attributes as
+ * 16-byte records to the home rank.  Device-side barriers only; the number of waves is `bounces` (+ 1 for the trailing
+ * shadow rays).  domain_owner[i] = rank that holds domain i (spraygpu_partition_domains); a rank must have exactly its
+ * own domains resident.  fb receives this rank's HOME rows (describe them to spraygpu_image_set_rows, flush with
+ * spraygpu_image_flush).  Same image, statistics and sample numbering as spraygpu_trace_tile_insitu(_p2p). */
+SPRAYGPU_API int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
+                                                const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
+                                                int rows_per_block, const int32_t* domain_owner /* ndomains */,
+                                                spraygpu_stats* stats);
 /* HdrImage::composite (image.h:167-181): fb = sum over ranks, valid on `root` (in place, device pointer). */
 SPRAYGPU_API int spraygpu_image_reduce(spraygpu_device dev, spraygpu_comm comm, float* fb_rgba, size_t npixels, int root);
 /* Image-partition composite for DISJOINT row bands (rank r rendered rows [row_begin[r], row_begin[r+1])):

@@ -117,6 +117,7 @@ _PROTOS = {
     "spraygpu_partition_domains": (C.c_int, [C.c_int, _vp, _vp, C.c_int, C.c_int, _vp, _vp]),
     "spraygpu_trace_tile_insitu": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.POINTER(Stats)]),
     "spraygpu_trace_tile_insitu_p2p": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.c_int, C.POINTER(Stats)]),
+    "spraygpu_trace_tile_insitu_fwd": (C.c_int, [_vp, _vp, C.POINTER(Camera), C.POINTER(Shade), Tile, _vp, C.c_int, _vp, C.POINTER(Stats)]),
     "spraygpu_image_reduce": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
     "spraygpu_image_gather_rows": (C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int]),
     "spraygpu_image_gather_blocks": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, _vp, _vp, C.c_int]),
@@ -433,6 +434,15 @@ class Comm:
         st = Stats() if stats else None
         _check(lib().spraygpu_trace_tile_insitu_p2p(self.dev.h, self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb),
                                                     int(rows_per_block), C.byref(st) if st is not None else None))
+        return st
+
+    def trace_tile_insitu_fwd(self, cam, shade, tile, fb, rows_per_block, domain_owner, stats=False):
+        """The in-situ tile with ray forwarding (insitu3.cu): rays travel to the owners of the domains they enter, every
+        sample is shaded on its home rank; fb receives this rank's HOME rows of the final image."""
+        st = Stats() if stats else None
+        own = np.ascontiguousarray(domain_owner, np.int32)
+        _check(lib().spraygpu_trace_tile_insitu_fwd(self.dev.h, self.h, C.byref(cam), C.byref(shade), Tile(*tile), _ptr(fb),
+                                                    int(rows_per_block), own.ctypes.data, C.byref(st) if st is not None else None))
         return st
 
     def image_reduce(self, fb, npixels, root=0):

@@ -84,10 +84,11 @@ struct Comm {
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
   // state of the peer-memory in-situ path (insitu2.cu), released by spraygpu_comm_destroy
-  void* p2p = nullptr;
-  void (*p2p_free)(Comm*, void*) = nullptr;
+  // and of the ray-forwarding path (insitu3.cu): slot 0 / slot 1
+  void* p2p[2] = {nullptr, nullptr};
+  void (*p2p_free[2])(Comm*, void*) = {nullptr, nullptr};
 };
-void** comm_p2p_slot(Comm* c, void (***free_fn)(Comm*, void*)) { *free_fn = &c->p2p_free; return &c->p2p; }
+void** comm_p2p_slot(Comm* c, void (***free_fn)(Comm*, void*), int which) { *free_fn = &c->p2p_free[which]; return &c->p2p[which]; }
 
 // ------------------------------------------------------------------------------------------------
 // Peer-mapped device buffers (CUDA IPC over NVLink / NVSwitch P2P): every rank allocates `bytes`, the 64-byte IPC
@@ -215,7 +216,8 @@ int spraygpu_comm_destroy(spraygpu_comm comm) {
   Comm* c = (Comm*)comm;
   cudaSetDevice(c->dev->cuda_device);
   cudaStreamSynchronize(c->dev->stream);
-  if (c->p2p && c->p2p_free) { c->p2p_free(c, c->p2p); c->p2p = nullptr; }   // collective (host barrier inside)
+  for (int k = 0; k < 2; ++k)
+    if (c->p2p[k] && c->p2p_free[k]) { c->p2p_free[k](c, c->p2p[k]); c->p2p[k] = nullptr; }   // collective (host barrier inside)
   if (c->comm && nccl()) g_nccl.CommDestroy(c->comm);
   delete c;
   return SPRAYGPU_OK;

@@ -675,40 +675,50 @@ SPRAY_HD void collapse_select(int b, const int* bl, const int* br, const int* bf
 // [plane(1), plane(254)] and can be widened.  Guarantee kept here and relied on by node8_hits:
 //   plane(qlo) + 2^e/128 <= child.lo   and   plane(qhi) - 2^e/128 >= child.hi   (FP32-evaluated)
 // which absorbs the <= 2^-9-step rounding of the folded slab offset and the ulp of (p - o) * idir.
+// starting exponent of one axis: 2^e > ext / 253, and the step stays well above the ulp of the coordinates (or
+// p = nlo - step would round away)
+SPRAY_HD int quant_exp_init(float nlo, float nhi) {
+  const float ext = nhi - nlo;
+  int e;
+  if (!(ext > 0.0f)) e = -126;
+  else {
+    float f = frexpf(ext / 253.0f, &e);  // ext/253 = f * 2^e, f in [0.5,1)  =>  2^e > ext/253
+    (void)f;
+  }
+  {
+    const float m = fmaxf(fabsf(nlo), fabsf(nhi));
+    int em = -126;
+    if (m > 0.0f) { (void)frexpf(m, &em); em -= 22; }  // 2^em >= 2 ulp(m)
+    if (e < em) e = em;
+  }
+  if (e < -100) e = -100;
+  if (e > 100) e = 100;
+  return e;
+}
+// one child interval [clo, chi] on the grid p + q * scale: widest-safe bytes, false when the margin cannot be kept
+SPRAY_HD bool quant_child(float clo, float chi, float p, float scale, uint32_t* qlo, uint32_t* qhi) {
+  const float margin = 0.0078125f;  // 2^-7 step
+  int li = (int)fminf(fmaxf(floorf((clo - p) / scale), 0.f), 255.f);
+  int hi = (int)fminf(fmaxf(ceilf((chi - p) / scale), 0.f), 255.f);
+  while (li > 0 && p + ((float)li + margin) * scale > clo) --li;
+  while (hi < 255 && p + ((float)hi - margin) * scale < chi) ++hi;
+  *qlo = (uint32_t)li; *qhi = (uint32_t)hi;
+  return !(p + ((float)li + margin) * scale > clo || p + ((float)hi - margin) * scale < chi);
+}
+
 SPRAY_HD void encode_node8(const float* nlo, const float* nhi, const CollapseOut& c, uint32_t child_base,
                            uint32_t tri_base, u4* q) {
   uint32_t ebits[3]; float porg[3];
   uint32_t qlo[3][8], qhi[3][8];
-  const float margin = 0.0078125f;  // 2^-7 step
   for (int a = 0; a < 3; ++a) {
-    const float ext = nhi[a] - nlo[a];
-    int e;
-    if (!(ext > 0.0f)) e = -126;
-    else {
-      float f = frexpf(ext / 253.0f, &e);  // ext/253 = f * 2^e, f in [0.5,1)  =>  2^e > ext/253
-      (void)f;
-    }
-    // the step must stay well above the ulp of the coordinates, or p = nlo - step would round away
-    {
-      const float m = fmaxf(fabsf(nlo[a]), fabsf(nhi[a]));
-      int em = -126;
-      if (m > 0.0f) { (void)frexpf(m, &em); em -= 22; }  // 2^em >= 2 ulp(m)
-      if (e < em) e = em;
-    }
-    if (e < -100) e = -100;
-    if (e > 100) e = 100;
+    int e = quant_exp_init(nlo[a], nhi[a]);
     for (;; ++e) {
       const float scale = u2f((uint32_t)(e + 127) << 23);
       const float p = nlo[a] - scale;
       bool ok = true;
       for (int s = 0; s < 8 && ok; ++s) {
         if (c.meta[s] == 0) { qlo[a][s] = 255; qhi[a][s] = 0; continue; }
-        int li = (int)fminf(fmaxf(floorf((c.lo[s][a] - p) / scale), 0.f), 255.f);
-        int hi = (int)fminf(fmaxf(ceilf((c.hi[s][a] - p) / scale), 0.f), 255.f);
-        while (li > 0 && p + ((float)li + margin) * scale > c.lo[s][a]) --li;
-        while (hi < 255 && p + ((float)hi - margin) * scale < c.hi[s][a]) ++hi;
-        if (p + ((float)li + margin) * scale > c.lo[s][a] || p + ((float)hi - margin) * scale < c.hi[s][a]) ok = false;
-        qlo[a][s] = (uint32_t)li; qhi[a][s] = (uint32_t)hi;
+        ok = quant_child(c.lo[s][a], c.hi[s][a], p, scale, &qlo[a][s], &qhi[a][s]);
       }
       if (ok || e >= 120) { ebits[a] = (uint32_t)(e + 127); porg[a] = p; break; }
     }

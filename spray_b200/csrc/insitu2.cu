@@ -25,21 +25,9 @@
 #include "internal.cuh"
 #include "traverse.cuh"
 #include "shade.cuh"
+#include "peer.cuh"
 
 namespace spraygpu {
-
-struct Comm;
-int comm_shared_alloc(Comm* c, size_t bytes, void** local, std::vector<void*>* mapped, int only_rank);
-void comm_shared_free(Comm* c, void* local, std::vector<void*>* mapped);
-int comm_host_barrier(Comm* c);
-int comm_allreduce_u64_sum(Comm* c, unsigned long long* p, size_t n);
-int comm_rank(const Comm* c);
-int comm_size(const Comm* c);
-Device* comm_device(const Comm* c);
-void** comm_p2p_slot(Comm* c, void (***free_fn)(Comm*, void*));
-
-#define P2P_MAX_RANKS 16
-#define P2P_FLAG_BYTES 256
 
 struct P2PState {
   size_t cap_n = 0;            // samples the buffers hold
@@ -60,39 +48,6 @@ struct P2PState {
   unsigned int* h_err = nullptr;           // mapped pinned: set when a barrier wait timed out
   unsigned int* h_err_dev = nullptr;
 };
-
-struct PeerPtrs { char* base[P2P_MAX_RANKS]; };
-
-// ---- device-side barrier ------------------------------------------------------------------------------------------
-// Called by EVERY thread at the end of a kernel whose peer stores must be visible before the peers go on.
-__device__ __forceinline__ void grid_signal_peers(unsigned int* done, const PeerPtrs& P, int nranks, int me) {
-  __syncthreads();                         // the CTA's peer stores / atomics happen-before thread 0's fence ...
-  if (threadIdx.x == 0) {
-    __threadfence_system();                // ... which is cumulative: they are performed system-wide before the signal
-    const unsigned int total = gridDim.x * gridDim.y;
-    if (atomicAdd(done, 1u) == total - 1u) {
-      *done = 0u;                          // ready for the next signalling kernel (stream order)
-      __threadfence_system();
-      for (int r = 0; r < nranks; ++r)
-        if (r != me) atomicAdd_system((unsigned long long*)P.base[r], 1ull);
-    }
-  }
-}
-__global__ void p2p_signal_kernel(PeerPtrs P, int nranks, int me) {
-  __threadfence_system();
-  for (int r = 0; r < nranks; ++r)
-    if (r != me) atomicAdd_system((unsigned long long*)P.base[r], 1ull);
-}
-// one thread: wait until every peer has signalled `target` barriers; ~4 s timeout instead of a hung GPU
-__global__ void p2p_wait_kernel(volatile unsigned long long* flag, unsigned long long target, unsigned int* err) {
-  if (*(volatile unsigned int*)err) return;      // an earlier barrier already gave up: do not wait 4 s again
-  const long long t0 = clock64();
-  while (*flag < target) {
-    if (clock64() - t0 > 8000000000ll) { *err = 1u; break; }
-    __nanosleep(200);
-  }
-  __threadfence_system();
-}
 
 }  // namespace spraygpu
 
@@ -134,17 +89,6 @@ __device__ __forceinline__ uint32_t p2p_pixid(const P2PWave& P, size_t i, int* r
 }
 __device__ __forceinline__ int p2p_home(const P2PWave& P, int row) { return (row / P.rows_per_block) % P.nranks; }
 __device__ __forceinline__ uint32_t p2p_src_count(const P2PWave& P) { return P.src ? *P.src_n : (uint32_t)P.n; }
-// full-warp call: one atomic per warp, returns this lane's slot (valid where pred)
-__device__ __forceinline__ uint32_t warp_append(unsigned int* counter, bool pred) {
-  const uint32_t b = __ballot_sync(0xffffffffu, pred);
-  if (!b) return 0u;
-  const int lane = threadIdx.x & 31, leader = __ffs(b) - 1;
-  uint32_t base = 0;
-  if (lane == leader) base = atomicAdd(counter, (unsigned int)__popc(b));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  return base + __popc(b & ((1u << lane) - 1u));
-}
-
 __global__ void __launch_bounds__(256) p2p_fill_kernel(float* __restrict__ w, size_t n, float v) {
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i < n) w[i] = v;
@@ -475,7 +419,7 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
              "trace_tile_insitu_p2p: glass domains (two secondary rays per hit) are not supported on the in-situ path; "
              "the reference CHECK-fails on them too (insitu_shader_pt.h)");
   void (**free_slot)(Comm*, void*) = nullptr;
-  void** slot = comm_p2p_slot(comm, &free_slot);
+  void** slot = comm_p2p_slot(comm, &free_slot, 0);
   if (!*slot) { *slot = new P2PState(); *free_slot = p2p_destroy; }
   P2PState* S = (P2PState*)*slot;
   SG_CHECK(!S->h_err || *S->h_err == 0u, SPRAYGPU_ERR_STATE, "trace_tile_insitu_p2p: an earlier peer barrier timed out (a rank died or the ranks' call sequences differ)");

@@ -149,6 +149,7 @@ inline int grow_buffer(T** p, size_t* cap, size_t bytes) {
 int build_scene(Scene* sc);   // build.cu
 int launch_max_index(Device* dev, const uint32_t* d_idx, size_t n, uint32_t* d_out);   // build.cu
 int upload_domain_table(Device* dev);
+CameraDev to_camdev(const spraygpu_camera* c);   // trace.cu
 
 // trace.cu launchers
 int launch_domain_lists(Device* dev, const spraygpu_ray* rays, size_t n, int cap, int32_t* counts, int32_t* ids,

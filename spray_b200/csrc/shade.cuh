@@ -151,4 +151,25 @@ __device__ __forceinline__ void fb_add(float* fb, uint32_t pixid, float scale, v
   atomicAdd(px + 2, mul_rn(scale, Lr.z));
 }
 
+// tile = the rectangle being rendered; (pw, px, py) place it inside the BLOCKING tile that numbers the samples
+// (samid = index within the blocking tile, ooc_tracer.inl:84-172): pw = blocking tile width, (px, py) = offset of
+// `tile` inside it.  A rank that renders only some rows of a blocking tile (multi-GPU image partition) still seeds
+// every sample exactly as the one-rank frame does.
+__device__ __forceinline__ void eye_sample(const CameraDev& cam, spraygpu_tile tile, int pw, int px, int py, int spp, int eye_seed,
+                                           uint32_t x0, uint32_t y0, uint32_t sidx, uint32_t* samid, uint32_t* pixid, vec3* dir) {
+  const uint32_t bufid = (uint32_t)spp * ((y0 + (uint32_t)py) * (uint32_t)pw + x0 + (uint32_t)px) + sidx;
+  const int x = tile.x + (int)x0, y = tile.y + (int)y0;
+  float fx = (float)x, fy = (float)y;
+  if (spp > 1) {
+    // ooc::Tracer::genMultiEyes seeds with bufid (ooc_tracer.inl:151-155); insitu::genMultiSampleEyeRays with
+    // (pixid, s) (insitu_ray.h:161-165)
+    uint32_t s = eye_seed == SPRAYGPU_EYE_SEED_INSITU ? rng_init2((uint32_t)(y * cam.image_w + x), sidx) : rng_init1(bufid);
+    fx = add_rn((float)x, rng_float(s));
+    fy = add_rn((float)y, rng_float(s));
+  }
+  *dir = camera_dir(cam, fx, fy);
+  *samid = bufid;
+  *pixid = (uint32_t)(y * cam.image_w + x);
+}
+
 }  // namespace spraygpu

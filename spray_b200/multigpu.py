@@ -153,9 +153,9 @@ class InsituRenderer:
         self.owned = [i for i, r in enumerate(self.domain_to_rank) if r == rank]
         dev.load_scene(scene, owned=self.owned)
         if max_tile_samples is None:
-            max_tile_samples = (4 << 20) if mode == "p2p" else (1 << 20)   # p2p: fewer, larger waves = fewer peer barriers
+            max_tile_samples = (4 << 20) if mode in ("p2p", "fwd") else (1 << 20)   # p2p / fwd: fewer, larger waves = fewer peer barriers
         self.tiles = band_tiles(W, (0, H), shade.pixel_samples, max_tile_samples)   # every rank walks every blocking tile
-        if mode == "p2p":
+        if mode in ("p2p", "fwd"):
             self.image = capi.Image(dev, comm, W, H, shm_name)
             begin = list(range(0, H, self.rpb)) + [H]
             self.image.set_rows(begin, [b % world for b in range(len(begin) - 1)])
@@ -171,6 +171,8 @@ class InsituRenderer:
         for t in self.tiles:
             if self.mode == "p2p":
                 st = self.comm.trace_tile_insitu_p2p(self.cam, self.shade, t, self.fb, self.rpb, stats=stats)
+            elif self.mode == "fwd":
+                st = self.comm.trace_tile_insitu_fwd(self.cam, self.shade, t, self.fb, self.rpb, self.domain_to_rank, stats=stats)
             else:
                 st = self.comm.trace_tile_insitu(self.cam, self.shade, t, self.fb, stats=stats)
             if stats:
@@ -179,7 +181,7 @@ class InsituRenderer:
         return tot
 
     def frame_device(self):
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "fwd"):
             self._trace()
             self.image.flush(to_root=True, to_host=False, clear=True)
         else:
@@ -188,7 +190,7 @@ class InsituRenderer:
             self.comm.image_reduce(self.fb, self.W * self.H, 0)
 
     def frame_host(self):
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "fwd"):
             self._trace()
             self.image.flush(to_root=False, to_host=True, clear=True)
         else:
@@ -198,7 +200,7 @@ class InsituRenderer:
         self.dev.synchronize()
 
     def count_rays(self):
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "fwd"):
             tot = self._trace(stats=True)
             self.image.flush(to_root=True, to_host=False, clear=True)     # leave the render target cleared
             return tot
@@ -208,14 +210,14 @@ class InsituRenderer:
     def composite_image(self):
         """rank 0: the composited frame after frame_device() (numpy); call on every rank."""
         self.dev.synchronize()
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "fwd"):
             self.image.barrier()                       # every rank's flush has landed in the root composite
             return self.image.read_device("root") if self.rank == 0 else None
         return self.fb.cpu().numpy()
 
     def host_image(self):
         self.dev.synchronize()
-        if self.mode == "p2p":
+        if self.mode in ("p2p", "fwd"):
             self.image.barrier()
             return self.image.host
         return self.fb_host.numpy() if self.fb_host is not None else None
@@ -230,11 +232,14 @@ def _rmse(a, b):
     return float(np.sqrt(np.mean((np.asarray(a, np.float64)[..., :3] - np.asarray(b, np.float64)[..., :3]) ** 2)))
 
 
-def single_gpu_frame(dev, cam, shade, W, H):
-    """The whole frame on THIS GPU alone through the fused kernel (the parity_check reference); all domains must be resident."""
+def single_gpu_frame(dev, cam, shade, W, H, tiles=None):
+    """The whole frame on THIS GPU alone through the fused kernel (the parity_check reference); all domains must be resident.
+    `tiles`: the blocking tiles the compared renderer used (sample ids, and with them the bounce / area-light random
+    streams, are tile-relative: src/ooc/ooc_tracer.inl:84-172); default = the one-rank frame's."""
     import torch
     fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-    tiles = scenes.image_schedule_tiles(W, H, shade.pixel_samples, 1, 0)
+    if tiles is None:
+        tiles = scenes.image_schedule_tiles(W, H, shade.pixel_samples, 1, 0)
     st = dev.trace_frame(cam, shade, tiles, fb, stats=True).as_dict()
     dev.synchronize()
     return fb.cpu().numpy(), st
@@ -244,6 +249,11 @@ INSITU_LABEL = ("in-situ domain partition x%d (Morton): each GPU owns %d of %d d
                 "atomicMin into every GPU's key array over NVLink (CUDA IPC), hit attributes and occlusion bytes by peer stores, "
                 "device-side barriers, no NCCL per wave; each GPU accumulates its home rows (blocks of %d rows) and flushes them "
                 "to rank 0 / the shared pinned host image")
+
+
+FWD_LABEL = ("in-situ domain partition x%d with ray forwarding: each GPU owns %d of %d domains; a ray is appended (32 B, peer store over "
+             "NVLink) to the inbox of every GPU that owns a domain it enters, owners trace their inbox and atomicMin the packed key into "
+             "the sample's home GPU, every sample is generated / shaded / accumulated on its home GPU only (blocks of %d rows)")
 
 
 def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, workload, metric, unit):
@@ -329,6 +339,20 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
                         "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb),
                         "parity_check": pc2}
         r2.close()
+        # the ray-forwarding variant (insitu3.cu) on the same communicator, same parity check
+        r4 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="fwd", shm_name=shm + "_f")
+        st4 = r4.count_rays()
+        ms4, l4 = timer2(r4.frame_device, max(args.steps // 2, 3), 3)
+        ms4h, _ = timer2(r4.frame_host, max(args.steps // 2, 3), 2)
+        pc4 = insitu_parity_check(r4, sc, cam, sh, W, H, rank, local_rank, stream)
+        if rank == 0:
+            pc4.pop("_composite", None)
+            pc4["ray_counts_equal_dense_variant"] = all(st4[k] == st2[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))
+        insitu_extra["ray_forwarding"] = {"value": r2n / (ms4 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms4, "gpu_launches": int(l4),
+                                          "e2e": {"value": r2n / (ms4h * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms4h},
+                                          "parallelism": FWD_LABEL % (world, len(r4.owned), len(sc["domains"]), r4.rpb),
+                                          "parity_check": pc4}
+        r4.close()
         # A/B: round 1's exchange (dense NCCL all-reduces per wave) on the same communicator
         r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl")
         ms3, l3 = timer2(r3.frame_device, 3, 2)
@@ -374,7 +398,7 @@ def insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream):
         full.load_scene(sc)
         sh_i = capi.Shade.from_buffer_copy(sh)
         sh_i.eye_seed = capi.EYE_SEED_INSITU           # the in-situ tile always jitters with RandomSampler_init(pixid, s)
-        ref, st1 = single_gpu_frame(full, cam, sh_i, W, H)
+        ref, st1 = single_gpu_frame(full, cam, sh_i, W, H, tiles=r.tiles)
         kf = torch.zeros(n, dtype=torch.int64, device="cuda")
         full.intersect_domains(rays, n, kf, None)
         full.synchronize()

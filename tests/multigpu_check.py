@@ -53,6 +53,20 @@ def main():
             if rank == 0:
                 imgs_insitu.append((a, b.copy()))
             r1.image.barrier()
+        # ray forwarding (insitu3.cu): rays travel to the owners of the domains they enter, shading on the home rank
+        r1f = multigpu.InsituRenderer(d1, sc, cam, sh, W, H, rank, world, c1, mode="fwd", shm_name="spraygpu_checkf_%d_%d" % (os.getppid(), case),
+                                      rows_per_block=8 if case == 0 else 5, max_tile_samples=(1 << 16) if case == 0 else None)
+        st1f = r1f.count_rays()
+        imgs_fwd = []
+        for frame in range(3):
+            r1f.frame_device()
+            a = r1f.composite_image()
+            r1f.frame_host()
+            b = r1f.host_image()
+            if rank == 0:
+                imgs_fwd.append((a, b.copy()))
+            r1f.image.barrier()
+        r1f.close()
         r1n = multigpu.InsituRenderer(d1, sc, cam, sh, W, H, rank, world, c1, mode="nccl")
         st1n = r1n.count_rays()
         r1n.frame_device()
@@ -94,20 +108,23 @@ def main():
             ko, _ = osc.intersect(rays.cpu().numpy())
             e_insitu = max(max(rmse(a, ref_insitu), rmse(b, ref_insitu)) for a, b in imgs_insitu)
             e_insitu = max(e_insitu, rmse(img_insitu_nccl, ref_insitu))
-            e_insitu_o = rmse(imgs_insitu[-1][0], fb_oi)
+            e_insitu = max(e_insitu, max(max(rmse(a, ref_insitu), rmse(b, ref_insitu)) for a, b in imgs_fwd))
+            e_insitu_o = max(rmse(imgs_insitu[-1][0], fb_oi), rmse(imgs_fwd[-1][0], fb_oi))
             # one add per pixel (1 spp, 1 light, 1 bounce) is order-free -> bit-identical; otherwise float atomics reorder
             one_add = kw["bounces"] == 1 and kw["pixel_samples"] == 1
             same = (lambda a, b: bool(np.array_equal(a, b))) if one_add else (lambda a, b: rmse(a, b) <= 1e-7)
             insitu_same = all(same(a, b) for a, b in imgs_insitu) and all(same(a, imgs_insitu[0][0]) for a, _ in imgs_insitu) \
-                and (not one_add or bool(np.array_equal(imgs_insitu[0][0], ref_insitu)))
+                and (not one_add or bool(np.array_equal(imgs_insitu[0][0], ref_insitu))) \
+                and all(same(a, b) for a, b in imgs_fwd) and all(same(a, imgs_insitu[0][0]) for a, _ in imgs_fwd)
             e_img = max(rmse(a, ref) for a, _ in imgs)
             e_img_o = rmse(imgs[-1][0], fb_o)
             host_ok = all(np.array_equal(a, b) for a, b in imgs)
             bit = kw["bounces"] > 1 or kw["pixel_samples"] > 1 or all(np.array_equal(a, ref) for a, _ in imgs)
             same_keys = bool(torch.equal(keys, keys_full)) and bool(np.array_equal(keys.cpu().numpy().view(np.uint64), ko))
-            same_stats = all(st1[k] == st1n[k] == tot_i[k] == getattr(st_oi, k) for k in ("eye_rays", "radiance_rays", "shadow_rays")) and \
+            same_stats = all(st1[k] == st1f[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits")) and \
+                all(st1[k] == st1n[k] == tot_i[k] == getattr(st_oi, k) for k in ("eye_rays", "radiance_rays", "shadow_rays")) and \
                 all(st2[k] == tot[k] == getattr(st_o, k) for k in ("eye_rays", "radiance_rays", "shadow_rays"))
-            print("multigpu_check %s world=%d: insitu (p2p x3 frames + nccl) rmse %.3g (oracle %.3g) frames identical/host==composite %s | image-partition rmse %.3g (oracle %.3g) bit-identical %s "
+            print("multigpu_check %s world=%d: insitu (p2p + fwd x3 frames, nccl) rmse %.3g (oracle %.3g) frames identical/host==composite %s | image-partition rmse %.3g (oracle %.3g) bit-identical %s "
                   "host==composite %s | keys equal (GPU + oracle) %s | stats equal %s (%s)"
                   % (kw, world, e_insitu, e_insitu_o, insitu_same, e_img, e_img_o, bit, host_ok, same_keys, same_stats,
                      {k: st2[k] for k in ("radiance_rays", "shadow_rays", "hits")}))

@@ -21,7 +21,7 @@ def _rmse(a, b):
     return float(np.sqrt(np.mean((a[..., :3].astype(np.float64) - b[..., :3].astype(np.float64)) ** 2)))
 
 
-@pytest.mark.parametrize("p2p", [False, True])
+@pytest.mark.parametrize("p2p", [False, True, "fwd"])
 @pytest.mark.parametrize("kw", [dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=2),
                                 dict(shader=1, bounces=2, pixel_samples=1, ao_samples=3)])
 def test_insitu_single_rank_equals_fused(kw, p2p):
@@ -48,7 +48,8 @@ def test_insitu_single_rank_equals_fused(kw, p2p):
     ta, tb = {}, {}
     for t in tiles:
         for fb, tot, fn in ((fb_a, ta, lambda: dev.trace_tile(cam, sh, t, fb_a, stats=True)),
-                            (fb_b, tb, (lambda: comm.trace_tile_insitu_p2p(cam, sh, t, fb_b, 8, stats=True)) if p2p else
+                            (fb_b, tb, (lambda: comm.trace_tile_insitu_fwd(cam, sh, t, fb_b, 8, [0] * 16, stats=True)) if p2p == "fwd" else
+                                 (lambda: comm.trace_tile_insitu_p2p(cam, sh, t, fb_b, 8, stats=True)) if p2p else
                                  (lambda: comm.trace_tile_insitu(cam, sh, t, fb_b, stats=True)))):
             for k, v in fn().as_dict().items():
                 tot[k] = tot.get(k, 0) + v
@@ -108,6 +109,15 @@ def test_insitu_single_rank_vs_oracle(oracle, spp, bounces):
     dev.synchronize()
     assert tot2["radiance_rays"] == st_o.radiance_rays and tot2["shadow_rays"] == st_o.shadow_rays and tot2["hits"] == tot["hits"]
     assert _rmse(fb2.cpu().numpy(), fb_o) <= 1e-4
+    # the ray-forwarding variant (insitu3.cu): same image and counts
+    fb3 = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    tot3 = {}
+    for t in tiles:
+        for k, v in comm.trace_tile_insitu_fwd(cam, sh, t, fb3, 4, [0] * len(sc["domains"]), stats=True).as_dict().items():
+            tot3[k] = tot3.get(k, 0) + v
+    dev.synchronize()
+    assert tot3["radiance_rays"] == st_o.radiance_rays and tot3["shadow_rays"] == st_o.shadow_rays and tot3["hits"] == tot["hits"]
+    assert _rmse(fb3.cpu().numpy(), fb_o) <= 1e-4
     # the fused kernel follows shade.eye_seed (bench.py's C5 at one GPU)
     sh1 = capi.make_shade(lights=sc["lights"], eye_seed=capi.EYE_SEED_INSITU, **kw)
     fb1 = np.zeros((H, W, 4), np.float32)
