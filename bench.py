@@ -71,6 +71,17 @@ def workload(name, device_scene=True):
             shade = dict(shader=0, bounces=1, pixel_samples=1, ao_samples=1, **scenes.WAVELETS64_BLINN)
             label = ("C4 (reduced): 64-domain triangle soup, %d tris/domain, out-of-core with a %s-block device LRU, 2048x2048, bounces 1"
                      % (tris, os.environ.get("SPRAY_C4_CAP", "16")))
+    elif name == "c4":
+        # 512 domains (8 x 8 x 8 cells of extent 20), 2^23 triangles each = 4.29 G triangles: sharded over the GPUs of one box
+        # (in-situ partition, 64 domains per GPU at 8 GPUs), meshes generated on the owning GPU right before their commit
+        tris = int(os.environ.get("SPRAY_C4_TRIS", str(1 << 23)))
+        g = int(os.environ.get("SPRAY_C4_GRID", "8"))
+        sc = scenes.soup_scene_device((g, g, g), tris, lazy=True)
+        W = H = 2048
+        e = 20.0 * g
+        cd = scenes.camera_frame((1.19 * e, 1.12 * e, 1.06 * e), (0.5 * e, 0.5 * e, 0.5 * e), (0, 1, 0), 90.0, W, H)
+        shade = dict(shader=0, bounces=1, pixel_samples=1, ao_samples=1, **scenes.WAVELETS64_BLINN)
+        label = "C4: synthetic %d-domain triangle soup (device-generated), %d tris/domain = %.2f G triangles, 2048x2048, bounces 1" % (g ** 3, tris, g ** 3 * tris / 1e9)
     elif name == "c5":
         # in-situ configuration: 8 wavelet domains per GPU (8 / 16 / 32 / 64 domains at 1 / 2 / 4 / 8 GPUs), 4096^2 x 4 spp,
         # multi-sample eye rays jittered with the in-situ seed (insitu_ray.h:161-165)

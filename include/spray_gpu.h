@@ -146,6 +146,16 @@ SPRAYGPU_API int spraygpu_scene_set_transform(spraygpu_scene scene, const float*
 /* transform -> per-vertex normals (TriMeshBuffer::computeNormals, trimesh_buffer.cc:267-326, bit-exact:
  * same per-vertex summation order) -> LBVH -> 8-wide compressed BVH -> attribute pack.  = rtcCommit. */
 SPRAYGPU_API int spraygpu_scene_commit(spraygpu_scene scene);
+/* Parity dump of the acceleration structure (Embree's is opaque; here the tests compare it node for node with the CPU
+ * emulation of the same builder): num_nodes x 80-byte compressed 8-wide nodes and num_faces x 48-byte triangle records
+ * in leaf order.  Either pointer may be NULL. */
+SPRAYGPU_API int spraygpu_scene_get_bvh(spraygpu_scene scene, void* nodes, void* tris);
+/* The same build, ENQUEUED only: the whole pipeline (sort, hierarchy, collapse, records) runs on the device without a
+ * host round trip, so the caller can upload the next domain's mesh while this one builds (the reference serialises
+ * PLY load and rtcCommit of every cache miss behind a barrier, src/ooc/ooc_pcontext.h:145-154).  The scene may be
+ * bound (spraygpu_domain_bind) right away; node count, depth check and bounds are read back the first time they are
+ * needed (spraygpu_scene_get_info, or the next trace call over the domain table, which fails if the build did). */
+SPRAYGPU_API int spraygpu_scene_commit_async(spraygpu_scene scene);
 SPRAYGPU_API int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_info* out);
 SPRAYGPU_API int spraygpu_scene_get_normals(spraygpu_scene scene, float* out_nv3);      /* [h|d] */
 SPRAYGPU_API int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out_nv3);     /* world space, [h|d] */

@@ -91,6 +91,8 @@ _PROTOS = {
     "spraygpu_scene_set_mesh": (C.c_int, [_vp, _vp, C.c_size_t, _vp, C.c_size_t, _vp]),
     "spraygpu_scene_set_transform": (C.c_int, [_vp, _vp]),
     "spraygpu_scene_commit": (C.c_int, [_vp]),
+    "spraygpu_scene_commit_async": (C.c_int, [_vp]),
+    "spraygpu_scene_get_bvh": (C.c_int, [_vp, _vp, _vp]),
     "spraygpu_scene_get_info": (C.c_int, [_vp, C.POINTER(SceneInfo)]),
     "spraygpu_scene_get_normals": (C.c_int, [_vp, _vp]),
     "spraygpu_scene_get_vertices": (C.c_int, [_vp, _vp]),
@@ -271,14 +273,20 @@ class Device:
         for i, d in enumerate(doms):
             if i not in owned:
                 continue
-            if d.get("verts") is None:
+            verts, faces, rgb = d.get("verts"), d.get("faces"), d.get("rgb")
+            if verts is None and d.get("gen") is not None:
+                from . import scenes as _scenes            # lazily generated on the device (scenes.soup_scene_device(lazy=True))
+                seed, ntris, lo, hi = d["gen"]
+                verts, faces, rgb = _scenes.soup_domain_device(seed, ntris, np.asarray(lo).tolist(), np.asarray(hi).tolist())
+            if verts is None:
                 raise SprayGpuError("load_scene: domain %d is owned but carries no mesh" % i)
             s = self.new_scene()
-            s.set_mesh(d["verts"], d["faces"], d.get("rgb"))
+            s.set_mesh(verts, faces, rgb)
             s.set_transform(d.get("transform"))
-            s.commit()
+            s.commit(wait=False)                           # the builds queue up on the device; the first trace waits
             self.bind(i, s)
             out[i] = s
+            del verts, faces, rgb
         return out
 
     # ---- batched queries (numpy host arrays or torch device tensors)
@@ -544,8 +552,17 @@ class Scene:
             m = np.ascontiguousarray(m, np.float32).reshape(16)
             _check(lib().spraygpu_scene_set_transform(self.h, m.ctypes.data))
 
-    def commit(self):
-        _check(lib().spraygpu_scene_commit(self.h))
+    def commit(self, wait=True):
+        """rtcCommit: build the BVH8.  wait=False only enqueues the build (spraygpu_scene_commit_async)."""
+        _check(lib().spraygpu_scene_commit(self.h) if wait else lib().spraygpu_scene_commit_async(self.h))
+
+    def bvh(self):
+        """(nodes [num_nodes, 20] uint32, tris [num_faces, 12] float32): parity dump of the committed BVH8."""
+        inf = self.info()
+        nodes = np.zeros((inf.num_nodes, 20), np.uint32)
+        tris = np.zeros((inf.num_faces, 12), np.float32)
+        _check(lib().spraygpu_scene_get_bvh(self.h, nodes.ctypes.data, tris.ctypes.data))
+        return nodes, tris
 
     def info(self):
         inf = SceneInfo()

@@ -7,9 +7,13 @@
 //   -> triangle boxes + centroid bounds -> 30-bit Morton keys -> LSD radix sort
 //   -> Karras LBVH -> bottom-up refit -> level-synchronous collapse into 80-byte 8-wide nodes
 //   -> triangle records (48 B, leaf order) + attribute records (48 B, primID order)
+#include <cooperative_groups.h>
+
 #include <algorithm>
 
 #include "internal.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace spraygpu {
 
@@ -17,17 +21,23 @@ namespace spraygpu {
 // LSD radix sort, 8 bits per pass, stable, key+value (uint32).  Tile = 256 threads x 16 keys.
 // ------------------------------------------------------------------------------------------------
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = 16;                      // keys per thread of a full-size tile
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+// A tile is worked off in rounds of 256 keys with block-wide barriers between them, so a SMALL input sorted with
+// full-size tiles is pure latency (ncu r04f: 17 us per scatter pass for the 5 480-triangle wavelet domain, two CTAs on
+// the whole GPU).  Small inputs get fewer keys per thread, i.e. more CTAs with fewer rounds each.
+static inline int rs_items_for(int n, int sm_count) {
+  const int want = (n + RS_THREADS * 2 * sm_count - 1) / (RS_THREADS * 2 * sm_count);
+  return want < 1 ? 1 : (want > RS_ITEMS ? RS_ITEMS : want);
+}
 
 __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, int n, int shift,
-                                                             uint32_t* __restrict__ hist, int nblocks) {
+                                                             uint32_t* __restrict__ hist, int nblocks, int items) {
   __shared__ uint32_t h[256];
   h[threadIdx.x] = 0;
   __syncthreads();
-  const int base = blockIdx.x * RS_TILE;
-#pragma unroll
-  for (int r = 0; r < RS_ITEMS; ++r) {
+  const int base = blockIdx.x * RS_THREADS * items;
+  for (int r = 0; r < items; ++r) {
     int i = base + r * RS_THREADS + threadIdx.x;
     if (i < n) atomicAdd(&h[(keys[i] >> shift) & 0xffu], 1u);
   }
@@ -105,7 +115,7 @@ __global__ void __launch_bounds__(1024) rs_scan_sums_kernel(uint32_t* __restrict
 __global__ void __launch_bounds__(RS_THREADS)
     rs_scatter_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint32_t* __restrict__ kout,
                       uint32_t* __restrict__ vout, int n, int shift, const uint32_t* __restrict__ hist, int nblocks,
-                      const uint32_t* __restrict__ sums) {
+                      const uint32_t* __restrict__ sums, int items) {
   __shared__ uint32_t digit_base[256];
   __shared__ uint32_t warp_cnt[RS_THREADS / 32][256];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -113,8 +123,8 @@ __global__ void __launch_bounds__(RS_THREADS)
     const int idx = tid * nblocks + blockIdx.x;
     digit_base[tid] = hist[idx] + sums[idx / SC_CHUNK];
   }
-  const int base = blockIdx.x * RS_TILE;
-  for (int r = 0; r < RS_ITEMS; ++r) {
+  const int base = blockIdx.x * RS_THREADS * items;
+  for (int r = 0; r < items; ++r) {
 #pragma unroll
     for (int w = 0; w < RS_THREADS / 32; ++w) warp_cnt[w][tid] = 0;
     __syncthreads();
@@ -145,20 +155,21 @@ __global__ void __launch_bounds__(RS_THREADS)
 }
 
 // sorts (keys, vals) of length n on `bits` low key bits; result ends in (*k, *v) (pointers may swap)
-static int radix_sort(Device* dev, uint32_t** k, uint32_t** v, uint32_t** k2, uint32_t** v2, uint32_t* hist, int n,
-                      int bits) {
+static int radix_sort(Device* dev, cudaStream_t st, uint32_t** k, uint32_t** v, uint32_t** k2, uint32_t** v2, uint32_t* hist,
+                      int n, int bits) {
   if (n <= 1) return SPRAYGPU_OK;
-  const int nblocks = (n + RS_TILE - 1) / RS_TILE;
+  const int items = rs_items_for(n, dev->sm_count);
+  const int nblocks = (n + RS_THREADS * items - 1) / (RS_THREADS * items);
   const int passes = (bits + 7) / 8;
   const int total = 256 * nblocks, nchunks = (total + SC_CHUNK - 1) / SC_CHUNK;
   SG_CHECK(nchunks <= 1024, SPRAYGPU_ERR_LIMIT, "radix sort: %d keys exceed the two-level scan (max %d)", n, 1024 * SC_CHUNK / 256 * RS_TILE);
   uint32_t* sums = hist + (size_t)256 * nblocks;   // 1024 chunk totals live behind the counters
   for (int p = 0; p < passes; ++p) {
     const int shift = 8 * p;
-    rs_hist_kernel<<<nblocks, RS_THREADS, 0, dev->stream>>>(*k, n, shift, hist, nblocks);
-    rs_scan_chunks_kernel<<<nchunks, 1024, 0, dev->stream>>>(hist, total, sums);
-    rs_scan_sums_kernel<<<1, 1024, 0, dev->stream>>>(sums, nchunks);
-    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, dev->stream>>>(*k, *v, *k2, *v2, n, shift, hist, nblocks, sums);
+    rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(*k, n, shift, hist, nblocks, items);
+    rs_scan_chunks_kernel<<<nchunks, 1024, 0, st>>>(hist, total, sums);
+    rs_scan_sums_kernel<<<1, 1024, 0, st>>>(sums, nchunks);
+    rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(*k, *v, *k2, *v2, n, shift, hist, nblocks, sums, items);
     dev->launches += 4;
     std::swap(*k, *k2);
     std::swap(*v, *v2);
@@ -318,9 +329,11 @@ __global__ void lbvh_kernel(const uint32_t* __restrict__ keys, int n, int* __res
   if (i == 0) parent[0] = -1;
 }
 
+// also leaves, per internal node, the 16-byte record the collapse walks: (left, right, leaf count, half-area bits)
 __global__ void refit_kernel(const int* __restrict__ parent, const int* __restrict__ bl, const int* __restrict__ br,
+                             const int* __restrict__ bfirst, const int* __restrict__ blast,
                              const float* __restrict__ llo, const float* __restrict__ lhi, float* blo, float* bhi,
-                             int* flags, int n) {
+                             int4* __restrict__ info, int* flags, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int p = parent[n - 1 + i];
@@ -340,6 +353,7 @@ __global__ void refit_kernel(const int* __restrict__ parent, const int* __restri
     }
 #pragma unroll
     for (int a = 0; a < 3; ++a) { blo[3 * (size_t)p + a] = lo[a]; bhi[3 * (size_t)p + a] = hi[a]; }
+    info[p] = make_int4(cs[0], cs[1], blast[p] - bfirst[p] + 1, __float_as_int(box_half_area(lo, hi)));
     p = parent[p];
   }
 }
@@ -356,30 +370,221 @@ __device__ __forceinline__ void write_tri(const float* __restrict__ verts, const
   out[2] = make_float4(e2.x, e2.y, e2.z, 0.0f);
 }
 
-// one thread = one 8-wide node of the current level
-__global__ void __launch_bounds__(128)
-    collapse_kernel(int begin, int end, int* __restrict__ queue, unsigned int* __restrict__ counters,
-                    const int* __restrict__ bl, const int* __restrict__ br, const int* __restrict__ bfirst,
-                    const int* __restrict__ blast, const float* __restrict__ blo, const float* __restrict__ bhi,
-                    const float* __restrict__ llo, const float* __restrict__ lhi,
-                    const uint32_t* __restrict__ sorted, const float* __restrict__ verts,
-                    const uint32_t* __restrict__ faces, uint4* __restrict__ nodes, float4* __restrict__ tris) {
-  int j = begin + blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= end) return;
-  const int b = queue[j];
-  CollapseOut co;
-  collapse_select(b, bl, br, bfirst, blast, blo, bhi, llo, lhi, &co);
-  const uint32_t child_base = co.n_inner ? atomicAdd(&counters[0], (unsigned)co.n_inner) : 0u;
-  const uint32_t tri_base = co.n_tris ? atomicAdd(&counters[1], (unsigned)co.n_tris) : 0u;
-  for (int r = 0; r < co.n_inner; ++r) queue[child_base + r] = co.inner_ref[r];
-  u4 q[5];
-  encode_node8(blo + 3 * (size_t)b, bhi + 3 * (size_t)b, co, child_base, tri_base, q);
+// ------------------------------------------------------------------------------------------------
+// Collapse: binary LBVH -> 80-byte 8-wide nodes, ONE persistent cooperative launch.
+//
+// Round 1 ran one kernel per BVH8 level with one heavy thread per node (collapse_select + encode_node8: ~1 KB of
+// local arrays) and a counter read-back + cudaStreamSynchronize between levels: 51 % of a 1 Mi-triangle commit and
+// ~55 us per level even for a level of ONE node (profiles/r03a_build_1Mi_launches.csv).  Here EIGHT LANES share a
+// node — lane k holds child k of the node being assembled, everything lives in registers, the greedy choices
+// (open the largest child; give the best (child, octant) pair its slot) are 8-lane shuffle arg-max reductions — and
+// the levels are separated by grid-wide barriers inside the kernel, so a commit never talks to the host.  The
+// arithmetic is collapse_select's / encode_node8's (core.cuh, what tests/hostemu runs on the CPU), with the same
+// tie rules (lowest child index, then lowest slot), so the tree is the same tree.
+// ------------------------------------------------------------------------------------------------
+struct CollapseArgs {
+  int n;
+  int* queue;                    // queue[j] = binary root of 8-wide node j
+  unsigned int* counters;        // [0] nodes allocated, [1] triangles emitted, [2] levels, [3] nodes (final), [4] overflow
+  const int4* info;              // refit_kernel's record per internal node
+  const int* bfirst;
+  const float *blo, *bhi, *llo, *lhi;
+  const uint32_t* sorted;        // sorted position -> primID
+  uint4* nodes;
+  uint32_t node_cap;
+  uint32_t* tri_prim;            // leaf-order slot -> primID (tri records are written by tri_records_kernel)
+};
+
+__device__ __forceinline__ float g8_max(unsigned m, float v) {
+  v = fmaxf(v, __shfl_xor_sync(m, v, 1, 8)); v = fmaxf(v, __shfl_xor_sync(m, v, 2, 8)); return fmaxf(v, __shfl_xor_sync(m, v, 4, 8));
+}
+__device__ __forceinline__ float g8_min(unsigned m, float v) {
+  v = fminf(v, __shfl_xor_sync(m, v, 1, 8)); v = fminf(v, __shfl_xor_sync(m, v, 2, 8)); return fminf(v, __shfl_xor_sync(m, v, 4, 8));
+}
+__device__ __forceinline__ uint32_t g8_pack(unsigned m, uint32_t byte, int l8) {   // lanes 0-3: slots 0..3, lanes 4-7: slots 4..7
+  uint32_t w = byte << (8 * (l8 & 3));
+  w |= __shfl_xor_sync(m, w, 1, 8);
+  w |= __shfl_xor_sync(m, w, 2, 8);
+  return w;
+}
+
+__device__ __forceinline__ void collapse_node8(const CollapseArgs& A, int j, unsigned gmask, int gshift, int l8) {
+  const int b = A.queue[j];
+  const int4 rb = A.info[b];
+  int ref = 0, cnt = 0, cl = 0, cr = 0;
+  float area = 0.f;
+  auto load_child = [&](int c) {
+    ref = c;
+    if (c < 0) { cnt = 1; area = 0.f; cl = cr = 0; }
+    else { const int4 ci = A.info[c]; cl = ci.x; cr = ci.y; cnt = ci.z; area = __int_as_float(ci.w); }
+  };
+  int nc = 2;
+  if (l8 == 0) load_child(rb.x);
+  else if (l8 == 1) load_child(rb.y);
+  // phase 0: open the largest child that is not a leaf yet; phase 1 (SPRAY_SPLIT_LEAVES): spare slots split leaves
+  for (int phase = 0; phase < (SPRAY_SPLIT_LEAVES ? 2 : 1); ++phase) {
+    while (nc < 8) {
+      const bool cand = l8 < nc && ref >= 0 && (phase == 0 ? cnt > SPRAY_LEAF_MAX : cnt <= SPRAY_LEAF_MAX) && area > -1.0f;
+      const float key = cand ? area : -2.0f;
+      const float m = g8_max(gmask, key);
+      const unsigned bal = (__ballot_sync(gmask, cand && key == m) >> gshift) & 0xffu;
+      if (!bal) break;
+      const int best = __ffs((int)bal) - 1;
+      const int L = __shfl_sync(gmask, cl, best, 8), R = __shfl_sync(gmask, cr, best, 8);
+      if (l8 == best) load_child(L);
+      else if (l8 == nc) load_child(R);
+      ++nc;
+    }
+  }
+  // child boxes, the box around them (for the octant costs only: the node's own box is the binary node's)
+  const bool used = l8 < nc;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  if (used) {
+    const float* pl = ref < 0 ? A.llo + 3 * (size_t)(~ref) : A.blo + 3 * (size_t)ref;
+    const float* ph = ref < 0 ? A.lhi + 3 * (size_t)(~ref) : A.bhi + 3 * (size_t)ref;
 #pragma unroll
-  for (int k = 0; k < 5; ++k) nodes[5 * (size_t)j + k] = make_uint4(q[k].x, q[k].y, q[k].z, q[k].w);
-  uint32_t off = 0;
-  for (int l = 0; l < co.n_leaf; ++l)
-    for (int k = 0; k < co.tri_count[l]; ++k, ++off)
-      write_tri(verts, faces, sorted[co.tri_first[l] + k], tris + 3 * (size_t)(tri_base + off));
+    for (int a = 0; a < 3; ++a) { lo[a] = pl[a]; hi[a] = ph[a]; }
+  }
+  float cost[8];
+  {
+    float cen[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const float nlo = g8_min(gmask, lo[a]), nhi = g8_max(gmask, hi[a]);
+      cen[a] = 0.5f * (lo[a] + hi[a]) - 0.5f * (nlo + nhi);
+    }
+#pragma unroll
+    for (int s = 0; s < 8; ++s)
+      cost[s] = ((s & 1) ? cen[0] : -cen[0]) + ((s & 2) ? cen[1] : -cen[1]) + ((s & 4) ? cen[2] : -cen[2]);
+  }
+  // greedy octant slots: the best remaining (child, slot) pair first; ties -> lowest child, then lowest slot
+  int myslot = -1;
+  unsigned freeslots = 0xffu;
+  for (int it = 0; it < nc; ++it) {
+    float bc = -INFINITY;
+    int bs = -1;
+    if (used && myslot < 0) {
+#pragma unroll
+      for (int s = 0; s < 8; ++s)
+        if (((freeslots >> s) & 1u) && cost[s] > bc) { bc = cost[s]; bs = s; }
+    }
+    const float m = g8_max(gmask, bs >= 0 ? bc : -INFINITY);
+    const unsigned bal = (__ballot_sync(gmask, bs >= 0 && bc == m) >> gshift) & 0xffu;
+    int bk, bsel;
+    if (bal) {
+      bk = __ffs((int)bal) - 1;
+      bsel = __shfl_sync(gmask, bs, bk, 8);
+    } else {
+      // NaN / -inf costs never win a comparison: first unplaced child -> first free slot (collapse_select's fallback)
+      const unsigned un = (__ballot_sync(gmask, used && myslot < 0) >> gshift) & 0xffu;
+      bk = __ffs((int)un) - 1;
+      bsel = __ffs((int)freeslots) - 1;
+    }
+    if (l8 == bk) myslot = bsel;
+    freeslots &= ~(1u << bsel);
+  }
+  // from here on lane s IS slot s
+  int src = -1;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int ms = __shfl_sync(gmask, myslot, k, 8);
+    if (ms == l8) src = k;
+  }
+  const bool has = src >= 0;
+  const int sl = has ? src : 0;
+  const int sref = __shfl_sync(gmask, ref, sl, 8), scnt = __shfl_sync(gmask, cnt, sl, 8);
+  float slo[3], shi[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) { slo[a] = __shfl_sync(gmask, lo[a], sl, 8); shi[a] = __shfl_sync(gmask, hi[a], sl, 8); }
+  const bool inner = has && sref >= 0 && scnt > SPRAY_LEAF_MAX;
+  const bool leaf = has && !inner;
+  const unsigned ib = (__ballot_sync(gmask, inner) >> gshift) & 0xffu;
+  const int n_inner = __popc(ib), inner_idx = __popc(ib & ((1u << l8) - 1u));
+  const int c = leaf ? scnt : 0;
+  int incl = c;
+#pragma unroll
+  for (int off = 1; off < 8; off <<= 1) {
+    const int t = __shfl_up_sync(gmask, incl, off, 8);
+    if (l8 >= off) incl += t;
+  }
+  const int excl = incl - c, n_tris = __shfl_sync(gmask, incl, 7, 8);
+  uint32_t meta = 0;
+  if (inner) meta = (1u << 5) | (24u + (uint32_t)l8);
+  else if (leaf) meta = ((c == 1 ? 1u : (c == 2 ? 3u : 7u)) << 5) | (uint32_t)excl;
+  uint32_t child_base = 0, tri_base = 0;
+  if (l8 == 0) {
+    if (n_inner) child_base = atomicAdd(&A.counters[0], (unsigned)n_inner);
+    if (n_tris) tri_base = atomicAdd(&A.counters[1], (unsigned)n_tris);
+  }
+  child_base = __shfl_sync(gmask, child_base, 0, 8);
+  tri_base = __shfl_sync(gmask, tri_base, 0, 8);
+  const bool fits = child_base + (uint32_t)n_inner <= A.node_cap && tri_base + (uint32_t)n_tris <= (uint32_t)A.n;
+  if (!fits) { if (l8 == 0) A.counters[4] = 1u; }
+  else if (inner) A.queue[child_base + inner_idx] = sref;
+  else if (leaf) {
+    const int first = sref < 0 ? ~sref : A.bfirst[sref];
+    for (int k = 0; k < c; ++k) A.tri_prim[tri_base + excl + k] = A.sorted[first + k];
+  }
+  // quantise against the binary node's box: per axis the smallest exponent every child fits with its margin
+  const float* nbl = A.blo + 3 * (size_t)b;
+  const float* nbh = A.bhi + 3 * (size_t)b;
+  uint32_t ql[3], qh[3], ebits[3];
+  float porg[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float nlo = nbl[a], nhi = nbh[a];
+    int e = quant_exp_init(nlo, nhi);
+    for (;; ++e) {
+      const float scale = u2f((uint32_t)(e + 127) << 23);
+      const float p = nlo - scale;
+      bool ok = true;
+      uint32_t l = 255u, h = 0u;
+      if (has) ok = quant_child(slo[a], shi[a], p, scale, &l, &h);
+      const bool allok = ((__ballot_sync(gmask, !ok) >> gshift) & 0xffu) == 0u;
+      if (allok || e >= 120) { ql[a] = l; qh[a] = h; ebits[a] = (uint32_t)(e + 127); porg[a] = p; break; }
+    }
+  }
+  uint32_t w[7];
+  w[0] = g8_pack(gmask, meta, l8);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) { w[1 + a] = g8_pack(gmask, ql[a], l8); w[4 + a] = g8_pack(gmask, qh[a], l8); }
+  uint32_t wh[7];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) wh[k] = __shfl_sync(gmask, w[k], 4, 8);
+  if (l8 == 0 && (uint32_t)j < A.node_cap) {
+    uint4* out = A.nodes + 5 * (size_t)j;
+    out[0] = make_uint4(f2u(porg[0]), f2u(porg[1]), f2u(porg[2]), ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | (ib << 24));
+    out[1] = make_uint4(child_base, tri_base, w[0], wh[0]);
+    out[2] = make_uint4(w[1], wh[1], w[2], wh[2]);
+    out[3] = make_uint4(w[3], wh[3], w[4], wh[4]);
+    out[4] = make_uint4(w[5], wh[5], w[6], wh[6]);
+  }
+}
+
+__global__ void __launch_bounds__(256) collapse_coop_kernel(CollapseArgs A) {
+  cg::grid_group grid = cg::this_grid();
+  const int l8 = threadIdx.x & 7;
+  const int gshift = threadIdx.x & 24;
+  const unsigned gmask = 0xffu << gshift;
+  const size_t ngroups = (size_t)gridDim.x * (blockDim.x >> 3);
+  const size_t gid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  unsigned int begin = 0, end = 1, levels = 0;
+  while (begin < end) {
+    ++levels;
+    for (size_t j = begin + gid; j < end; j += ngroups) collapse_node8(A, (int)j, gmask, gshift, l8);
+    grid.sync();
+    begin = end;
+    end = min(*(volatile unsigned int*)&A.counters[0], A.node_cap);
+    if (levels > 4096u) break;     // cannot happen (every level adds nodes or ends); keeps a corrupted tree from hanging the GPU
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { A.counters[2] = levels; A.counters[3] = end; }
+}
+
+// 48-byte triangle records in BVH leaf order from the leaf-order primID list
+__global__ void tri_records_kernel(const float* __restrict__ verts, const uint32_t* __restrict__ faces,
+                                   const uint32_t* __restrict__ tri_prim, int n, float4* __restrict__ tris) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) write_tri(verts, faces, tri_prim[i], tris + 3 * (size_t)i);
 }
 
 // n == 1: a root with a single one-triangle leaf
@@ -426,9 +631,9 @@ __global__ void __launch_bounds__(256) max_index_kernel(const uint32_t* __restri
 }
 
 int launch_max_index(Device* dev, const uint32_t* d_idx, size_t n, uint32_t* d_out) {
-  SG_CUDA(cudaMemsetAsync(d_out, 0, sizeof(uint32_t), dev->stream));
+  SG_CUDA(cudaMemsetAsync(d_out, 0, sizeof(uint32_t), upload_stream(dev)));
   const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)dev->sm_count * 8);
-  max_index_kernel<<<grid, 256, 0, dev->stream>>>(d_idx, n, d_out);
+  max_index_kernel<<<grid, 256, 0, upload_stream(dev)>>>(d_idx, n, d_out);
   dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
@@ -457,19 +662,36 @@ struct Carver {
 
 static inline int grid_for(size_t n, int threads) { return (int)((n + threads - 1) / threads); }
 
+// one thread: the collapse's counters and root entry, the bounds accumulators (no host-staged copies in a commit)
+__global__ void build_init_kernel(uint32_t* bounds, unsigned int* counters, int* queue, unsigned int single) {
+  for (int a = 0; a < 3; ++a) {
+    bounds[a] = bounds[6 + a] = 0xFFFFFFFFu;   // min slots
+    bounds[3 + a] = bounds[9 + a] = 0u;        // max slots
+  }
+  counters[0] = 1u; counters[1] = single; counters[2] = 1u; counters[3] = 1u; counters[4] = 0u;   // single: n == 1, no collapse
+  queue[0] = 0;
+}
+
+// Enqueues the whole build on the device's build stream and returns: no host round trip.  The few words the host
+// wants back (node count, BVH8 depth, overflow flag, geometry bounds) land in the scene's pinned result record;
+// scene_finalize() waits for them the first time somebody needs them.
 int build_scene(Scene* sc) {
   Device* dev = sc->dev;
-  cudaStream_t st = dev->stream;
+  cudaStream_t st = build_stream(dev);
   const size_t nv = sc->nv, nf = sc->nf;
   SG_CHECK(nf >= 1 && nv >= 1, SPRAYGPU_ERR_STATE, "commit: empty mesh (nv=%zu nf=%zu)", nv, nf);
   SG_CHECK(nf <= SPRAYGPU_MAX_PRIMS, SPRAYGPU_ERR_LIMIT, "commit: %zu faces exceed the 23-bit primID field", nf);
   const int n = (int)nf;
   const int npairs = 3 * n;
+  if (sc->pending) { int frc = scene_finalize(sc); if (frc) return frc; }
 
-  cudaEvent_t ev0, ev1;
-  SG_CUDA(cudaEventCreate(&ev0));
-  SG_CUDA(cudaEventCreate(&ev1));
-  SG_CUDA(cudaEventRecord(ev0, st));
+  if (!sc->ev0) {
+    SG_CUDA(cudaEventCreate(&sc->ev0));
+    SG_CUDA(cudaEventCreate(&sc->ev1));
+    SG_CUDA(cudaMallocHost((void**)&sc->h_result, sizeof(uint32_t) * 32));
+  }
+  if (sc->ev_upload) SG_CUDA(cudaStreamWaitEvent(st, sc->ev_upload, 0));   // the mesh may have come in on another stream
+  SG_CUDA(cudaEventRecord(sc->ev0, st));
 
   // ---- persistent outputs
   int grc;
@@ -480,26 +702,32 @@ int build_scene(Scene* sc) {
   if ((grc = grow_buffer(&sc->d_normals, &sc->cap_normals, sizeof(float) * 3 * nv))) return grc;
   if ((grc = grow_buffer(&sc->d_tris, &sc->cap_tris, sizeof(float4) * 3 * nf))) return grc;
   if ((grc = grow_buffer(&sc->d_attr, &sc->cap_attr, sizeof(float4) * 3 * nf))) return grc;
+  // every 8-wide node but the root covers >= 4 triangles and a full node with k inner children has 8 - k leaf
+  // children: N(c) <= (c - 1) / 3 nodes for c >= 4 triangles (induction over the collapse); measured 0.13-0.18 n
+  const uint32_t node_cap = (uint32_t)(n / 3 + 2);
+  if ((grc = grow_buffer(&sc->d_nodes, &sc->cap_nodes, sizeof(uint4) * 5 * (size_t)node_cap))) return grc;
+  sc->node_cap = node_cap;
 
   // ---- scratch carve (two passes: size, then pointers)
-  const int nblocks_max = (npairs + RS_TILE - 1) / RS_TILE;
-  uint32_t *kA, *kB, *vA, *vB, *hist, *vstart, *vend, *bounds;
+  const int items_min = std::min(rs_items_for(npairs, dev->sm_count), rs_items_for(n, dev->sm_count));
+  const int nblocks_max = (npairs + RS_THREADS * items_min - 1) / (RS_THREADS * items_min);
+  uint32_t *kA, *kB, *vA, *vB, *hist, *vstart, *vend, *bounds, *tri_prim;
   unsigned int* counters;
   float *tlo, *thi, *llo, *lhi, *blo, *bhi;
   int *bl, *br, *bfirst, *blast, *parent, *flags, *queue;
-  uint4* tmp_nodes;
+  int4* info;
   auto carve = [&](Carver& c) {
     kA = c.take<uint32_t>(npairs); kB = c.take<uint32_t>(npairs);
     vA = c.take<uint32_t>(npairs); vB = c.take<uint32_t>(npairs);
     hist = c.take<uint32_t>((size_t)256 * nblocks_max + 1024);
     vstart = c.take<uint32_t>(nv); vend = c.take<uint32_t>(nv);
-    bounds = c.take<uint32_t>(12); counters = c.take<unsigned int>(4);
+    bounds = c.take<uint32_t>(12); counters = c.take<unsigned int>(8);
     tlo = c.take<float>(3 * nf); thi = c.take<float>(3 * nf);
     llo = c.take<float>(3 * nf); lhi = c.take<float>(3 * nf);
     blo = c.take<float>(3 * nf); bhi = c.take<float>(3 * nf);
     bl = c.take<int>(nf); br = c.take<int>(nf); bfirst = c.take<int>(nf); blast = c.take<int>(nf);
-    parent = c.take<int>(2 * nf); flags = c.take<int>(nf); queue = c.take<int>(nf);
-    tmp_nodes = c.take<uint4>(5 * nf);
+    parent = c.take<int>(2 * nf); flags = c.take<int>(nf); queue = c.take<int>(node_cap);
+    info = c.take<int4>(nf); tri_prim = c.take<uint32_t>(nf);
   };
   Carver sizer{nullptr};
   carve(sizer);
@@ -509,6 +737,8 @@ int build_scene(Scene* sc) {
   carve(carver);
 
   const int T = 256;
+  build_init_kernel<<<1, 1, 0, st>>>(bounds, counters, queue, n == 1 ? 1u : 0u);
+  dev->launches++;
   // ---- transform
   if (sc->has_xf) {
     Mat4 M; memcpy(M.m, sc->xf, sizeof(M.m));
@@ -519,7 +749,7 @@ int build_scene(Scene* sc) {
   pairs_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, kA, vA, npairs);
   dev->launches++;
   int vbits = 1; while (((size_t)1 << vbits) < nv) ++vbits;
-  rc = radix_sort(dev, &kA, &vA, &kB, &vB, hist, npairs, vbits);
+  rc = radix_sort(dev, st, &kA, &vA, &kB, &vB, hist, npairs, vbits);
   if (rc) return rc;
   SG_CUDA(cudaMemsetAsync(vstart, 0, sizeof(uint32_t) * nv, st));
   SG_CUDA(cudaMemsetAsync(vend, 0, sizeof(uint32_t) * nv, st));
@@ -529,84 +759,77 @@ int build_scene(Scene* sc) {
   dev->launches += 3;
 
   // ---- triangle boxes, Morton keys, sort
-  {
-    uint32_t hb[12];
-    for (int a = 0; a < 3; ++a) {
-      hb[a] = hb[6 + a] = 0xFFFFFFFFu;  // min slots
-      hb[3 + a] = hb[9 + a] = 0u;       // max slots
-    }
-    SG_CUDA(cudaMemcpyAsync(bounds, hb, sizeof(hb), cudaMemcpyHostToDevice, st));
-    // hb is on the stack: the copy from pageable memory is staged before the call returns
-  }
   tri_bounds_kernel<<<std::min(grid_for(nf, 256), dev->sm_count * 8), 256, 0, st>>>(sc->d_verts, sc->d_faces, n, tlo, thi, bounds);
   dev->launches++;
   if (n == 1) {
-    if ((grc = grow_buffer(&sc->d_nodes, &sc->cap_nodes, sizeof(uint4) * 5))) return grc;
     single_tri_kernel<<<1, 1, 0, st>>>(sc->d_verts, sc->d_faces, tlo, thi, sc->d_nodes, sc->d_tris);
     dev->launches++;
-    sc->n_nodes = 1;
-    sc->bvh_depth = 1;
   } else {
     morton_kernel<<<grid_for(nf, T), T, 0, st>>>(tlo, thi, n, bounds, kA, vA);
     dev->launches++;
-    rc = radix_sort(dev, &kA, &vA, &kB, &vB, hist, n, 30);
+    rc = radix_sort(dev, st, &kA, &vA, &kB, &vB, hist, n, 30);
     if (rc) return rc;
     leaf_boxes_kernel<<<grid_for(nf, T), T, 0, st>>>(vA, tlo, thi, n, llo, lhi);
     lbvh_kernel<<<grid_for(nf, T), T, 0, st>>>(kA, n, bl, br, bfirst, blast, parent);
     SG_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nf, st));
-    refit_kernel<<<grid_for(nf, T), T, 0, st>>>(parent, bl, br, llo, lhi, blo, bhi, flags, n);
+    refit_kernel<<<grid_for(nf, T), T, 0, st>>>(parent, bl, br, bfirst, blast, llo, lhi, blo, bhi, info, flags, n);
     dev->launches += 3;
-    // ---- collapse, level by level.  queue[j] = binary node of 8-wide node j; counters[0] = nodes
-    // allocated so far, counters[1] = triangles emitted so far.
-    {
-      unsigned int hc[4] = {1u, 0u, 0u, 0u};
-      int root = 0;
-      SG_CUDA(cudaMemcpyAsync(counters, hc, sizeof(hc), cudaMemcpyHostToDevice, st));
-      SG_CUDA(cudaMemcpyAsync(queue, &root, sizeof(int), cudaMemcpyHostToDevice, st));
-      int begin = 0, end = 1, levels = 0;
-      while (begin < end) {
-        ++levels;
-        collapse_kernel<<<grid_for(end - begin, 128), 128, 0, st>>>(begin, end, queue, counters, bl, br, bfirst,
-                                                                    blast, blo, bhi, llo, lhi, vA, sc->d_verts,
-                                                                    sc->d_faces, tmp_nodes, sc->d_tris);
-        dev->launches++;
-        unsigned int got[2];
-        SG_CUDA(cudaMemcpyAsync(got, counters, sizeof(got), cudaMemcpyDeviceToHost, st));
-        SG_CUDA(cudaStreamSynchronize(st));
-        begin = end;
-        end = (int)got[0];
-        SG_CHECK(end <= n, SPRAYGPU_ERR_STATE, "collapse: node count %d exceeds bound %d", end, n);
-      }
-      sc->n_nodes = (uint32_t)end;
-      sc->bvh_depth = (uint32_t)levels;
-      // the traversal stack holds one entry per BVH8 level (core.cuh, SPRAY_STACK_SIZE): refuse deeper trees here
-      // instead of dropping subtrees at trace time
-      SG_CHECK(levels <= SPRAY_STACK_SIZE, SPRAYGPU_ERR_LIMIT, "commit: BVH8 depth %d exceeds the traversal stack (%d)", levels,
-               SPRAY_STACK_SIZE);
+    // ---- collapse: one cooperative launch walks the levels (queue[j] = binary root of 8-wide node j)
+    if (dev->collapse_blocks_per_sm == 0) {
+      int bps = 0;
+      SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, collapse_coop_kernel, 256, 0));
+      SG_CHECK(bps > 0, SPRAYGPU_ERR_LIMIT, "commit: the collapse kernel does not fit an SM");
+      dev->collapse_blocks_per_sm = bps;
     }
-    if ((grc = grow_buffer(&sc->d_nodes, &sc->cap_nodes, sizeof(uint4) * 5 * (size_t)sc->n_nodes))) return grc;
-    SG_CUDA(cudaMemcpyAsync(sc->d_nodes, tmp_nodes, sizeof(uint4) * 5 * (size_t)sc->n_nodes,
-                            cudaMemcpyDeviceToDevice, st));
+    CollapseArgs A;
+    A.n = n; A.queue = queue; A.counters = counters; A.info = info; A.bfirst = bfirst;
+    A.blo = blo; A.bhi = bhi; A.llo = llo; A.lhi = lhi; A.sorted = vA; A.nodes = sc->d_nodes; A.node_cap = node_cap;
+    A.tri_prim = tri_prim;
+    // a level is at most node_cap nodes wide, 32 nodes per 256-thread CTA
+    const int grid = std::max(1, std::min(dev->collapse_blocks_per_sm * dev->sm_count, (int)((node_cap + 31) / 32)));
+    void* args[] = {(void*)&A};
+    SG_CUDA(cudaLaunchCooperativeKernel((const void*)collapse_coop_kernel, dim3(grid), dim3(256), args, 0, st));
+    tri_records_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_verts, sc->d_faces, tri_prim, n, sc->d_tris);
+    dev->launches += 2;
   }
-  // ---- geometry bounds back to the host
-  {
-    uint32_t hb[12];
-    SG_CUDA(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
-    SG_CUDA(cudaEventRecord(ev1, st));
-    SG_CUDA(cudaStreamSynchronize(st));
-    for (int a = 0; a < 6; ++a) {
-      uint32_t s = hb[6 + a];
-      uint32_t u = (s & 0x80000000u) ? (s & 0x7fffffffu) : ~s;
-      memcpy(&sc->bounds[a], &u, 4);
-    }
+  // ---- results: 8 counter words + 12 bounds words into the scene's pinned record
+  SG_CUDA(cudaMemcpyAsync(sc->h_result, counters, sizeof(uint32_t) * 8, cudaMemcpyDeviceToHost, st));
+  SG_CUDA(cudaMemcpyAsync(sc->h_result + 8, bounds, sizeof(uint32_t) * 12, cudaMemcpyDeviceToHost, st));
+  SG_CUDA(cudaEventRecord(sc->ev1, st));
+  SG_CUDA(cudaGetLastError());
+  sc->pending = true;
+  sc->committed = true;
+  return SPRAYGPU_OK;
+}
+
+// waits for an enqueued build and takes its results; the checks a commit owes its caller happen here
+int scene_finalize(Scene* sc) {
+  if (!sc->pending) return SPRAYGPU_OK;
+  SG_CUDA(cudaEventSynchronize(sc->ev1));
+  sc->pending = false;
+  const uint32_t* h = sc->h_result;
+  sc->n_nodes = h[3];
+  sc->bvh_depth = h[2];
+  for (int a = 0; a < 6; ++a) {
+    const uint32_t s = h[8 + 6 + a];
+    const uint32_t u = (s & 0x80000000u) ? (s & 0x7fffffffu) : ~s;
+    memcpy(&sc->bounds[a], &u, 4);
   }
   float ms = 0.f;
-  cudaEventElapsedTime(&ms, ev0, ev1);
+  cudaEventElapsedTime(&ms, sc->ev0, sc->ev1);
   sc->build_ms = ms;
-  cudaEventDestroy(ev0);
-  cudaEventDestroy(ev1);
-  SG_CUDA(cudaGetLastError());
-  sc->committed = true;
+  if (h[4] != 0u || h[1] != (uint32_t)sc->nf || sc->n_nodes > sc->node_cap) {
+    sc->committed = false;
+    set_error("commit: the collapse overflowed its buffers (%u nodes of %u, %u of %zu triangles)", h[0], sc->node_cap, h[1], sc->nf);
+    return SPRAYGPU_ERR_STATE;
+  }
+  // the traversal stack holds one entry per BVH8 level (core.cuh, SPRAY_STACK_SIZE): refuse deeper trees here
+  // instead of dropping subtrees at trace time
+  if (sc->bvh_depth > (uint32_t)SPRAY_STACK_SIZE) {
+    sc->committed = false;
+    set_error("commit: BVH8 depth %u exceeds the traversal stack (%d)", sc->bvh_depth, SPRAY_STACK_SIZE);
+    return SPRAYGPU_ERR_LIMIT;
+  }
   return SPRAYGPU_OK;
 }
 

@@ -146,6 +146,13 @@ static int tlas_build(Device* dev, int* ids, int n, int depth, int* max_depth) {
 }
 
 int upload_domain_table(Device* dev) {
+  // every kernel that reads the table comes through here: builds that were only enqueued (spraygpu_scene_commit_async)
+  // are waited for and checked now
+  for (int i = 0; i < dev->ndomains; ++i)
+    if (dev->bound[i] && dev->bound[i]->pending) {
+      int frc = scene_finalize(dev->bound[i]);
+      if (frc) return frc;
+    }
   if (!dev->table_dirty) return SPRAYGPU_OK;
   SG_CHECK(dev->ndomains > 0, SPRAYGPU_ERR_STATE, "no domain table: call spraygpu_domains_set first");
   {
@@ -218,6 +225,8 @@ int spraygpu_device_create(int cuda_device, spraygpu_device* out) {
   SG_CUDA(cudaMallocHost(&d->pinned, 4096));
   d->pinned_bytes = 4096;
   SG_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+  SG_CUDA(cudaStreamCreateWithFlags(&d->load_stream, cudaStreamNonBlocking));
+  SG_CUDA(cudaStreamCreateWithFlags(&d->upload_stream, cudaStreamNonBlocking));
   for (int i = 0; i < 2; ++i) {
     SG_CUDA(cudaEventCreateWithFlags(&d->ev_render[i], cudaEventDisableTiming));
     SG_CUDA(cudaEventCreateWithFlags(&d->ev_copy[i], cudaEventDisableTiming));
@@ -232,6 +241,8 @@ int spraygpu_device_destroy(spraygpu_device dev) {
   cudaSetDevice(d->cuda_device);
   cudaStreamSynchronize(d->stream);
   if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); cudaStreamDestroy(d->copy_stream); }
+  if (d->load_stream) { cudaStreamSynchronize(d->load_stream); cudaStreamDestroy(d->load_stream); }
+  if (d->upload_stream) { cudaStreamSynchronize(d->upload_stream); cudaStreamDestroy(d->upload_stream); }
   for (int i = 0; i < 2; ++i) {
     if (d->ev_render[i]) cudaEventDestroy(d->ev_render[i]);
     if (d->ev_copy[i]) cudaEventDestroy(d->ev_copy[i]);
@@ -294,6 +305,11 @@ int spraygpu_scene_destroy(spraygpu_scene scene) {
   Device* d = s->dev;
   cudaSetDevice(d->cuda_device);
   cudaStreamSynchronize(d->stream);
+  if (d->load_stream) cudaStreamSynchronize(d->load_stream);
+  s->pending = false;
+  if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }
+  if (s->ev_upload) cudaEventDestroy(s->ev_upload);
+  if (s->h_result) cudaFreeHost(s->h_result);
   for (int i = 0; i < d->ndomains; ++i)
     if (d->bound[i] == s) {
       d->bound[i] = nullptr;
@@ -316,18 +332,23 @@ int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, c
   Scene* s = SCN(scene);
   Device* d = s->dev;
   SG_CUDA(cudaSetDevice(d->cuda_device));
-  SG_CUDA(cudaStreamSynchronize(d->stream));
+  // The block's buffers are about to be overwritten.  Normally nothing may still read them: wait for the device's
+  // stream.  While the out-of-core tile prefetches (ooc.cu) the upload goes to the load stream, which that tile has
+  // ordered behind the last trace that used this block.
+  cudaStream_t st = upload_stream(d);
+  if (!d->loading_async) SG_CUDA(cudaStreamSynchronize(d->stream));
+  if (s->pending) { SG_CUDA(cudaEventSynchronize(s->ev1)); s->pending = false; }
   // a re-used cache block keeps its allocations when the new mesh fits (grow_buffer)
   s->committed = false; s->n_nodes = 0; s->d_verts = nullptr;
   s->nv = nv; s->nf = nf;
   int grc;
   if ((grc = grow_buffer(&s->d_verts_obj, &s->cap_verts_obj, sizeof(float) * 3 * nv))) return grc;
   if ((grc = grow_buffer(&s->d_faces, &s->cap_faces, sizeof(uint32_t) * 3 * nf))) return grc;
-  SG_CUDA(cudaMemcpyAsync(s->d_verts_obj, xyz, sizeof(float) * 3 * nv, cudaMemcpyDefault, d->stream));
-  SG_CUDA(cudaMemcpyAsync(s->d_faces, idx, sizeof(uint32_t) * 3 * nf, cudaMemcpyDefault, d->stream));
+  SG_CUDA(cudaMemcpyAsync(s->d_verts_obj, xyz, sizeof(float) * 3 * nv, cudaMemcpyDefault, st));
+  SG_CUDA(cudaMemcpyAsync(s->d_faces, idx, sizeof(uint32_t) * 3 * nf, cudaMemcpyDefault, st));
   if (rgb) {
     if ((grc = grow_buffer(&s->d_rgb, &s->cap_rgb, sizeof(uint32_t) * nv))) return grc;
-    SG_CUDA(cudaMemcpyAsync(s->d_rgb, rgb, sizeof(uint32_t) * nv, cudaMemcpyDefault, d->stream));
+    SG_CUDA(cudaMemcpyAsync(s->d_rgb, rgb, sizeof(uint32_t) * nv, cudaMemcpyDefault, st));
   } else if (s->d_rgb) {
     cudaFree(s->d_rgb); s->d_rgb = nullptr; s->cap_rgb = 0;
   }
@@ -337,8 +358,10 @@ int spraygpu_scene_set_mesh(spraygpu_scene scene, const float* xyz, size_t nv, c
   int vrc = launch_max_index(d, s->d_faces, 3 * nf, d_max);
   if (vrc) return vrc;
   uint32_t* h_max = (uint32_t*)d->pinned;
-  SG_CUDA(cudaMemcpyAsync(h_max, d_max, sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
-  SG_CUDA(cudaStreamSynchronize(d->stream));  // host arrays may be freed after return
+  SG_CUDA(cudaMemcpyAsync(h_max, d_max, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  if (!s->ev_upload) SG_CUDA(cudaEventCreateWithFlags(&s->ev_upload, cudaEventDisableTiming));
+  SG_CUDA(cudaEventRecord(s->ev_upload, st));
+  SG_CUDA(cudaStreamSynchronize(st));  // host arrays may be freed after return
   if ((size_t)*h_max >= nv) {
     const uint32_t bad = *h_max;
     s->nv = s->nf = 0;   // the mesh is unusable: commit reports "empty mesh"
@@ -364,7 +387,26 @@ int spraygpu_scene_commit(spraygpu_scene scene) {
   SG_CUDA(cudaSetDevice(s->dev->cuda_device));
   int rc = build_scene(s);
   if (rc) return rc;
+  // inside the out-of-core tile's prefetch (ooc.cu) a commit is enqueue-only: the tile waits for the group's builds
+  // before it traces the group, and meanwhile the next domain's mesh crosses PCIe
+  if (!s->dev->loading_async) {
+    rc = scene_finalize(s);
+    if (rc) return rc;
+  }
   // refresh table entries that point at this scene
+  Device* d = s->dev;
+  for (int i = 0; i < d->ndomains; ++i)
+    if (d->bound[i] == s) spraygpu_domain_bind((spraygpu_device)d, i, scene);
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_scene_commit_async(spraygpu_scene scene) {
+  SG_CHECK(scene, SPRAYGPU_ERR_ARG, "commit_async: scene is NULL");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->d_verts_obj && s->d_faces, SPRAYGPU_ERR_STATE, "commit_async: no mesh set");
+  SG_CUDA(cudaSetDevice(s->dev->cuda_device));
+  int rc = build_scene(s);
+  if (rc) return rc;
   Device* d = s->dev;
   for (int i = 0; i < d->ndomains; ++i)
     if (d->bound[i] == s) spraygpu_domain_bind((spraygpu_device)d, i, scene);
@@ -375,6 +417,7 @@ int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_info* out) {
   SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_info: NULL argument");
   Scene* s = SCN(scene);
   SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_info: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
   out->num_vertices = s->nv; out->num_faces = s->nf; out->num_nodes = s->n_nodes;
   out->node_bytes = (uint64_t)s->n_nodes * 80; out->tri_bytes = (uint64_t)s->nf * 48; out->attr_bytes = (uint64_t)s->nf * 48;
   memcpy(out->bounds, s->bounds, sizeof(out->bounds));
@@ -392,12 +435,24 @@ int spraygpu_scene_get_normals(spraygpu_scene scene, float* out) {
   SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_normals: NULL argument");
   Scene* s = SCN(scene);
   SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_normals: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
   return copy_out(s->dev, out, s->d_normals, sizeof(float) * 3 * s->nv);
+}
+int spraygpu_scene_get_bvh(spraygpu_scene scene, void* nodes, void* tris) {
+  SG_CHECK(scene, SPRAYGPU_ERR_ARG, "get_bvh: scene is NULL");
+  Scene* s = SCN(scene);
+  SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_bvh: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
+  int rc = SPRAYGPU_OK;
+  if (nodes) rc = copy_out(s->dev, nodes, s->d_nodes, (size_t)s->n_nodes * 80);
+  if (!rc && tris) rc = copy_out(s->dev, tris, s->d_tris, s->nf * 48);
+  return rc;
 }
 int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out) {
   SG_CHECK(scene && out, SPRAYGPU_ERR_ARG, "get_vertices: NULL argument");
   Scene* s = SCN(scene);
   SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "get_vertices: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
   return copy_out(s->dev, out, s->d_verts, sizeof(float) * 3 * s->nv);
 }
 
@@ -406,6 +461,7 @@ int spraygpu_intersect(spraygpu_scene scene, int domain_id, const spraygpu_ray* 
   SG_CHECK(scene && (n == 0 || (rays && keys)), SPRAYGPU_ERR_ARG, "intersect: NULL argument");
   Scene* s = SCN(scene);
   SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "intersect: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
   SG_CHECK(domain_id >= 0 && domain_id < SPRAYGPU_MAX_DOMAINS, SPRAYGPU_ERR_ARG, "intersect: bad domain id %d", domain_id);
   if (!n) return SPRAYGPU_OK;
   SG_CUDA(cudaSetDevice(s->dev->cuda_device));
@@ -425,6 +481,7 @@ int spraygpu_occluded(spraygpu_scene scene, const spraygpu_ray* rays, size_t n, 
   SG_CHECK(scene && (n == 0 || (rays && occ)), SPRAYGPU_ERR_ARG, "occluded: NULL argument");
   Scene* s = SCN(scene);
   SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "occluded: scene not committed");
+  { int frc = scene_finalize(s); if (frc) return frc; }
   if (!n) return SPRAYGPU_OK;
   SG_CUDA(cudaSetDevice(s->dev->cuda_device));
   Stager st(s->dev);
@@ -464,6 +521,10 @@ int spraygpu_domain_bind(spraygpu_device dev, int id, spraygpu_scene scene) {
   SG_CHECK(id >= 0 && id < d->ndomains, SPRAYGPU_ERR_ARG, "domain_bind: bad domain id %d (table has %d)", id, d->ndomains);
   DomainEntry& e = d->h_domains[id];
   Scene* s = SCN(scene);
+  // out-of-core prefetch (ooc.cu): a kernel is reading this domain right now; refusing the eviction here keeps the
+  // cache from overwriting its block (the cache is smaller than the max_resident the tile was given)
+  SG_CHECK(!(d->loading_async && (size_t)id < d->tracing.size() && d->tracing[(size_t)id] && d->bound[id] != s), SPRAYGPU_ERR_STATE,
+           "domain_bind: domain %d is being traced and cannot be evicted now (cache smaller than max_resident?)", id);
   if (s) {
     SG_CHECK(s->committed, SPRAYGPU_ERR_STATE, "domain_bind: scene not committed");
     SG_CHECK(s->dev == d, SPRAYGPU_ERR_ARG, "domain_bind: scene belongs to another device");

@@ -462,6 +462,7 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
       S->grid_trace = b1 * dev->sm_count; S->grid_shade = b3 * dev->sm_count; S->grid_smem = dsmem;
     }
     const int grid_lin = dev->sm_count * 8;
+    PhaseTimer T(st);
     rc = launch_eye_rays(dev, cam, tile, shade->pixel_samples, SPRAYGPU_EYE_SEED_INSITU, S->rays[0]);   // insitu_ray.h:103-182
     if (rc) return rc;
     p2p_fill_kernel<<<p2p_grid(3 * n, 256), 256, 0, st>>>(S->w[0], 3 * n, 1.0f);
@@ -469,7 +470,9 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
     SG_CUDA(cudaMemsetAsync(mine + S->o_keys[0], 0xFF, n * 8, st));
     p2p_signal_kernel<<<1, 1, 0, st>>>(P.peers, nranks, me);       // everyone's first key array is reset
     dev->launches++;
+    T.mark("eye+init");
     barrier_wait();
+    T.mark("bar");
     int cur = 0;
     for (int depth = 0; depth < shade->bounces; ++depth) {
       const int kb = depth & 1;
@@ -480,20 +483,28 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
       if (npasses) SG_CUDA(cudaMemsetAsync(mine + S->o_occ, 0, n * (size_t)npasses, st));
       p2p_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, kb);
       p2p_trace_kernel<<<S->grid_trace, P2P_THREADS, smem_trace, st>>>(P, S->rays[cur]);      // K1
+      T.mark("trace");
       barrier_wait();
+      T.mark("bar");
       p2p_capture_kernel<<<grid_lin, 128, 0, st>>>(P, S->rays[cur]);                           // K2
+      T.mark("capture");
       barrier_wait();
+      T.mark("bar");
       p2p_shade_kernel<<<S->grid_shade, P2P_THREADS, smem_shade, st>>>(P, S->rays[cur], S->w[cur], S->rays[cur ^ 1], S->w[cur ^ 1],
                                                                        S->list[kb ^ 1], S->d_ctl + CTL_LIVE0 + (kb ^ 1), S->ret,
                                                                        dev->d_counters);      // K3
+      T.mark("shade");
       barrier_wait();
+      T.mark("bar");
       if (npasses) {
         p2p_retire_kernel<<<grid_lin, 256, 0, st>>>(P, S->ret, fb);                            // K4
         dev->launches++;
+        T.mark("retire");
       }
       dev->launches += 4;
       cur ^= 1;
     }
+    T.report("insitu_p2p", me);
     SG_CUDA(cudaGetLastError());
   }
   if (stats) {

@@ -115,30 +115,45 @@ __device__ __forceinline__ RouteTab load_route_smem(const float* __restrict__ ro
 }
 
 // ranks that own a domain this ray enters: the reference's exact slab test (aabb.h:139-169) with tnear = 1e-3, the same
-// test the owner's traversal applies before it opens the domain (TlasSource), so nothing is sent in vain and nothing missed
-__device__ __forceinline__ uint32_t route_mask(const float* __restrict__ boxes, const RouteTab& R, int nranks, vec3 o, vec3 d) {
+// test the owner's traversal applies before it opens the domain (TlasSource), so nothing is sent in vain and nothing
+// missed.  *primary = the rank that owns the NEAREST entered domain (smallest entry distance; ties -> lowest rank): it
+// traces first, the others trace afterwards against the hit it found (insitu::Isector::isectWithoutFarDomain,
+// src/insitu/insitu_isector.h:165-224: "all but ... nearer than the known hit t").
+__device__ __forceinline__ uint32_t route_mask(const float* __restrict__ boxes, const RouteTab& R, int nranks, vec3 o, vec3 d, int* primary) {
   const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
   const float ix = div_rn(1.0f, d.x), iy = div_rn(1.0f, d.y), iz = div_rn(1.0f, d.z);
   uint32_t mask = 0;
+  float best = INFINITY;
+  int prim = -1;
   for (int rk = 0; rk < nranks; ++rk) {
     const int b = R.begin[rk], e = R.begin[rk + 1];
     if (b == e) continue;
     const float* rb = R.rank_box + 6 * rk;
     float t;
     if (!tlas_box_hit(rb[0], rb[1], rb[2], rb[3], rb[4], rb[5], r, &t)) continue;   // conservative
+    float near = INFINITY;
+    bool any = false;
     for (int k = b; k < e; ++k) {
       float tmin;
-      if (domain_slab_inv(boxes + 6 * R.perm[k], o, ix, iy, iz, SPRAY_RAY_EPS, INFINITY, &tmin)) { mask |= 1u << rk; break; }
+      if (domain_slab_inv(boxes + 6 * R.perm[k], o, ix, iy, iz, SPRAY_RAY_EPS, INFINITY, &tmin)) { any = true; near = fminf(near, tmin); }
+    }
+    if (any) {
+      mask |= 1u << rk;
+      if (prim < 0 || near < best) { best = near; prim = rk; }
     }
   }
+  *primary = prim;
   return mask;
 }
 
 // ALL 32 lanes call.  Appends this lane's ray to the inbox of every rank in `mask` (insitu::Comm::send): one system-scope
 // atomicAdd per (warp, destination), two 16-byte peer stores per record.
-//   record = { ox, oy, oz, sample | dx, dy, dz, meta },  meta = home rank | kind << 8 (0 radiance, 1 shadow) | pass << 16
-__device__ __forceinline__ void fwd_push(const FwdWave& P, size_t o_inbox, int which, uint32_t mask, vec3 o, vec3 d, uint32_t sample,
-                                         uint32_t meta) {
+//   record = { ox, oy, oz, sample | dx, dy, dz, meta },
+//   meta = home rank | kind << 8 (0 radiance, 1 shadow) | secondary << 9 (not the owner of the nearest domain) | pass << 16
+#define FWD_META_SHADOW (1u << 8)
+#define FWD_META_SECONDARY (1u << 9)
+__device__ __forceinline__ void fwd_push(const FwdWave& P, size_t o_inbox, int which, uint32_t mask, int primary, vec3 o, vec3 d,
+                                         uint32_t sample, uint32_t meta) {
   const int lane = threadIdx.x & 31;
   uint32_t all = __reduce_or_sync(0xffffffffu, mask);
   while (all) {
@@ -155,7 +170,7 @@ __device__ __forceinline__ void fwd_push(const FwdWave& P, size_t o_inbox, int w
       if (slot < P.inbox_cap) {
         uint4* rec = (uint4*)(P.peers.base[rk] + o_inbox) + 2 * (size_t)slot;
         rec[0] = make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), sample);
-        rec[1] = make_uint4(__float_as_uint(d.x), __float_as_uint(d.y), __float_as_uint(d.z), meta);
+        rec[1] = make_uint4(__float_as_uint(d.x), __float_as_uint(d.y), __float_as_uint(d.z), meta | (rk == primary ? 0u : FWD_META_SECONDARY));
       } else {
         P.ctl[FC_OVERFLOW] = 1u;
       }
@@ -193,6 +208,7 @@ __global__ void __launch_bounds__(FWD_THREADS) fwd_route0_kernel(FwdWave P, spra
     }
     if (!__any_sync(0xffffffffu, go)) continue;
     uint32_t mask = 0;
+    int primary = -1;
     if (go) {
       const uint32_t sidx = (uint32_t)(i % (size_t)P.spp), pix = (uint32_t)(i / (size_t)P.spp);
       uint32_t samid, pixid;
@@ -201,45 +217,81 @@ __global__ void __launch_bounds__(FWD_THREADS) fwd_route0_kernel(FwdWave P, spra
       float4* out = reinterpret_cast<float4*>(rays + i);
       out[0] = make_float4(o.x, o.y, o.z, SPRAY_RAY_EPS);
       out[1] = make_float4(d.x, d.y, d.z, INFINITY);
-      mask = route_mask(boxes, R, P.nranks, o, d);
+      mask = route_mask(boxes, R, P.nranks, o, d, &primary);
     }
-    fwd_push(P, P.o_inbox_next, P.inbox_next, mask, o, d, (uint32_t)i, (uint32_t)P.me);
+    fwd_push(P, P.o_inbox_next, P.inbox_next, mask, primary, o, d, (uint32_t)i, (uint32_t)P.me);
   }
   grid_signal_peers(P.ctl + FC_DONE, P.peers, P.nranks, P.me);
 }
 
-// F2: trace MY inbox against MY domains (insitu::TContext::processRays for received rays).  Persistent CTAs; every
-// record enters at least one of my domains, so all lanes of a full chunk work.
+// F2: trace MY inbox against MY domains (insitu::TContext::processRays for received rays), in two passes separated by a
+// barrier.  Pass 0: the records for which I own the NEAREST entered domain.  Pass 1: the others — by then the home
+// rank's key / occlusion byte holds what the nearest owner found, so a radiance ray is traced only in front of that
+// hit (tbound) and an already occluded shadow ray not at all.  In an opaque scene most rays end in the first domain
+// they enter: without the second pass every other owner along the ray walks its BVHs for nothing (measured at 2 GPUs
+// on C3: the speculative single pass cost 2x the single-GPU traversal work).  Persistent CTAs; the records of a pass
+// are compacted through a per-warp index queue so that the traversal runs with full warps.
 __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
-    fwd_serve_kernel(FwdWave P, uint32_t* __restrict__ cand_idx, unsigned long long* __restrict__ cand_key) {
+    fwd_serve_kernel(FwdWave P, int pass, uint32_t* __restrict__ cand_idx, unsigned long long* __restrict__ cand_key) {
   extern __shared__ float smem[];
   const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
+  uint32_t* q = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, P.tlas_n, 0) + 15) & ~(size_t)15)) + (size_t)(threadIdx.x >> 5) * FWD_QCAP;
   const int lane = threadIdx.x & 31;
   const uint32_t nrec = min(((const unsigned int*)(P.peers.base[P.me] + FWD_CTR_OFFSET))[P.inbox_cur], P.inbox_cap);
   const uint4* inbox = (const uint4*)(P.peers.base[P.me] + P.o_inbox_cur);
+  unsigned int* work = P.ctl + (pass ? FC_WORK_ROUTE : FC_WORK_SERVE);   // the route counter is idle during a wave's F2
+  int count = 0;
+  bool more = true;
   for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(P.ctl + FC_WORK_SERVE, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= nrec) break;
-    const uint32_t k = base + lane;
-    const bool act = k < nrec;
-    uint4 a = make_uint4(0, 0, 0, 0), b = make_uint4(0, 0, __float_as_uint(1.0f), 0);
-    if (act) { a = inbox[2 * (size_t)k]; b = inbox[2 * (size_t)k + 1]; }
+    if (count < 32 && more) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(work, 32u);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (base >= nrec) { more = false; continue; }
+      const uint32_t k = base + lane;
+      bool go = false;
+      if (k < nrec) {
+        const uint32_t meta = inbox[2 * (size_t)k + 1].w;
+        go = (int)((meta >> 9) & 1u) == pass;
+        if (go && pass && (meta & FWD_META_SHADOW)) {
+          // VBuf::occluded: somebody nearer already blocked it
+          const uint32_t sample = inbox[2 * (size_t)k].w;
+          go = ((const volatile uint8_t*)(P.peers.base[meta & 0xffu] + P.o_occ))[(size_t)(meta >> 16) * P.n + sample] == 0;
+        }
+      }
+      const uint32_t bm = __ballot_sync(0xffffffffu, go);
+      if (go) q[count + __popc(bm & ((1u << lane) - 1u))] = k;
+      count += __popc(bm);
+      __syncwarp();
+      continue;
+    }
+    if (count == 0) break;
+    const int nq = count < 32 ? count : 32;
+    count -= nq;
+    const bool act = lane < nq;
+    const uint32_t k = q[count + (act ? lane : 0)];
+    __syncwarp();
+    const uint4 a = inbox[2 * (size_t)k], b = inbox[2 * (size_t)k + 1];
     const vec3 o = mk3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
     const vec3 d = mk3(__uint_as_float(b.x), __uint_as_float(b.y), __uint_as_float(b.z));
-    const uint32_t sample = a.w, home = b.w & 0xffu, pass = b.w >> 16;
-    const bool shadow = (b.w >> 8) & 1u;
+    const uint32_t sample = a.w, home = b.w & 0xffu, lpass = b.w >> 16;
+    const bool shadow = (b.w & FWD_META_SHADOW) != 0u;
+    unsigned long long* hkey = (unsigned long long*)(P.peers.base[home] + P.o_keys) + sample;
+    float tbound = INFINITY;
+    if (act && pass && !shadow) {
+      const unsigned long long known = *(const volatile unsigned long long*)hkey;
+      if (known != SPRAY_KEY_MISS) tbound = key_t(known);                                 // VBuf::correct: only nearer hits matter
+    }
     SceneHit h;
-    const bool hit = scene_trace_warp<false>(P.table, D, act, o, d, shadow, h, nullptr);
+    const bool hit = scene_trace_warp<false>(P.table, D, act, o, d, shadow, h, nullptr, tbound);
     bool candidate = false;
     unsigned long long key = 0;
     if (act && hit) {
       if (shadow) {
-        ((uint8_t*)(P.peers.base[home] + P.o_occ))[(size_t)pass * P.n + sample] = 1;     // VBuf::setObuf on the home rank
+        ((uint8_t*)(P.peers.base[home] + P.o_occ))[(size_t)lpass * P.n + sample] = 1;    // VBuf::setObuf on the home rank
       } else {
         key = make_key(h.t, h.dom, h.prim);
-        const unsigned long long old = atomicMin_system((unsigned long long*)(P.peers.base[home] + P.o_keys) + sample, key);
+        const unsigned long long old = atomicMin_system(hkey, key);
         candidate = key < old;                                                            // VBuf::updateTbufOut
       }
     }
@@ -367,6 +419,7 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
     {
       const uint32_t slot = warp_append(next_n, bounce);
       uint32_t mask = 0;
+      int primary = -1;
       if (bounce) {
         next_list[slot] = i;
         spraygpu_ray nx;
@@ -375,9 +428,9 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
         store_ray(rays_next + i, nx);
         w_next[3 * (size_t)i] = bw.x; w_next[3 * (size_t)i + 1] = bw.y; w_next[3 * (size_t)i + 2] = bw.z;
         keys_next[i] = SPRAY_KEY_MISS;                          // VBuf::resetTbufOut for the samples that go on
-        mask = route_mask(boxes, R, P.nranks, c.pos, bd);
+        mask = route_mask(boxes, R, P.nranks, c.pos, bd, &primary);
       }
-      fwd_push(P, P.o_inbox_next, P.inbox_next, mask, c.pos, bd, i, (uint32_t)P.me);
+      fwd_push(P, P.o_inbox_next, P.inbox_next, mask, primary, c.pos, bd, i, (uint32_t)P.me);
     }
     uint32_t ls = rng_init1(samid * (uint32_t)next_depth);     // light_sampler (insitu_shader_pt.h:115)
     int l = 0, k = 0;
@@ -388,12 +441,13 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
       if (more) emit = shade_light_pass<true>(P.shade, pt, nl, c, Lin, pixid, l, k, ls, &wi, &Lr, &more);
       const size_t j = (size_t)p * P.n + i;
       uint32_t mask = 0;
+      int primary = -1;
       if (emit) {
         ++n_shadow;
         occ[j] = 0;
-        mask = route_mask(boxes, R, P.nranks, c.pos, wi);
+        mask = route_mask(boxes, R, P.nranks, c.pos, wi, &primary);
       }
-      fwd_push(P, P.o_inbox_next, P.inbox_next, mask, c.pos, wi, i, (uint32_t)P.me | (1u << 8) | ((uint32_t)p << 16));
+      fwd_push(P, P.o_inbox_next, P.inbox_next, mask, primary, c.pos, wi, i, (uint32_t)P.me | FWD_META_SHADOW | ((uint32_t)p << 16));
       const uint32_t slot = warp_append(P.ctl + FC_RET, emit);
       if (emit) ret[slot] = make_uint4((uint32_t)j, __float_as_uint(Lr.x), __float_as_uint(Lr.y), __float_as_uint(Lr.z));
     }
@@ -592,17 +646,19 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     const size_t dsmem = (dom_smem_bytes(nd, dev->tlas_n, 0) + 15) & ~(size_t)15;
     const size_t smem_route = sizeof(float) * (6 * (size_t)nd + route_words(nranks, nd));
     const size_t smem_shade = smem_route + sizeof(uint32_t) * FWD_QCAP * (FWD_THREADS / 32);
+    const size_t smem_serve = dsmem + sizeof(uint32_t) * FWD_QCAP * (FWD_THREADS / 32);
     if (S->grid_smem != dsmem + smem_shade) {
-      SG_DYN_SMEM(fwd_serve_kernel, dsmem);
+      SG_DYN_SMEM(fwd_serve_kernel, smem_serve);
       SG_DYN_SMEM(fwd_shade_kernel, smem_shade);
       SG_DYN_SMEM(fwd_route0_kernel, smem_route);
       int b2 = 0, b4 = 0;
-      SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, fwd_serve_kernel, FWD_THREADS, dsmem));
+      SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, fwd_serve_kernel, FWD_THREADS, smem_serve));
       SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b4, fwd_shade_kernel, FWD_THREADS, smem_shade));
       SG_CHECK(b2 > 0 && b4 > 0, SPRAYGPU_ERR_LIMIT, "trace_tile_insitu_fwd: the wave kernels do not fit an SM (%zu B shared)", dsmem);
       S->grid_serve = b2 * dev->sm_count; S->grid_shade = b4 * dev->sm_count; S->grid_smem = dsmem + smem_shade;
     }
     const int grid_lin = dev->sm_count * 8;
+    PhaseTimer T(st);
     // ---- tile start: my wave-0 keys reset, both inboxes empty, then everyone meets
     SG_CUDA(cudaMemsetAsync(mine + S->o_keys[0], 0xFF, n * 8, st));
     fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, my_ctr, 3, 0);
@@ -610,13 +666,16 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     p2p_signal_kernel<<<1, 1, 0, st>>>(P.peers, nranks, me);
     dev->launches += 3;
     barrier_wait();
+    T.mark("init+bar");
     // ---- F1: eye rays into inbox 0
     P.depth = 0; P.src = nullptr; P.src_n = S->d_ctl + FC_LIVE0;
     P.inbox_next = 0; P.o_inbox_next = S->o_inbox[0]; P.inbox_cur = 1; P.o_inbox_cur = S->o_inbox[1];
     P.o_keys = S->o_keys[0]; P.o_keys_next = S->o_keys[1];
     fwd_route0_kernel<<<grid_lin, FWD_THREADS, smem_route, st>>>(P, S->rays[0]);
     dev->launches++;
+    T.mark("route0");
     barrier_wait();
+    T.mark("bar");
     int cur = 0;
     const int nwaves = shade->bounces + (npasses ? 1 : 0);     // the last one serves the trailing shadow rays only
     for (int depth = 0; depth < nwaves; ++depth) {
@@ -629,25 +688,40 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
       P.src_n = S->d_ctl + FC_LIVE0 + kb;
       // nobody appends to the next inbox before the barrier that follows F3 of this wave
       fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, my_ctr, 1 << (kb ^ 1), kb ^ 1);
-      fwd_serve_kernel<<<S->grid_serve, FWD_THREADS, dsmem, st>>>(P, S->cand_idx, S->cand_key);                 // F2
+      fwd_serve_kernel<<<S->grid_serve, FWD_THREADS, smem_serve, st>>>(P, 0, S->cand_idx, S->cand_key);       // F2, nearest owners
       dev->launches += 2;
+      T.mark("serve");
       barrier_wait();
+      T.mark("bar");
+      if (nranks > 1) {
+        fwd_serve_kernel<<<S->grid_serve, FWD_THREADS, smem_serve, st>>>(P, 1, S->cand_idx, S->cand_key);     // F2, the others, bounded
+        dev->launches++;
+        T.mark("serve2");
+        barrier_wait();
+        T.mark("bar");
+      }
       if (depth > 0 && npasses) {
         fwd_retire_kernel<<<grid_lin, 256, 0, st>>>(P, S->ret, fb);                                              // F5 (wave depth - 1)
         fwd_zero_ret_kernel<<<1, 1, 0, st>>>(S->d_ctl);
         dev->launches += 2;
+        T.mark("retire");
       }
       if (!shading) break;
       fwd_capture_kernel<<<grid_lin, 128, 0, st>>>(P, S->cand_idx, S->cand_key);                                // F3
       dev->launches++;
+      T.mark("capture");
       barrier_wait();
+      T.mark("bar");
       fwd_shade_kernel<<<S->grid_shade, FWD_THREADS, smem_shade, st>>>(P, S->rays[cur], S->w[cur], S->rays[cur ^ 1], S->w[cur ^ 1],
                                                                        S->list[kb ^ 1], S->d_ctl + FC_LIVE0 + (kb ^ 1), S->ret,
                                                                        dev->d_counters);                        // F4
       dev->launches++;
+      T.mark("shade");
       barrier_wait();
+      T.mark("bar");
       cur ^= 1;
     }
+    T.report("insitu_fwd", me);
     SG_CUDA(cudaGetLastError());
   }
   if (stats) {

@@ -101,6 +101,13 @@ struct Device {
   std::vector<TlasNode> h_tlas;    // built in upload_domain_table
   TlasNode* d_tlas = nullptr;
   int tlas_n = 0;                  // 0: no resident domain
+  // acceleration-structure builds and mesh uploads go to `load_stream` while `loading_async` is set (the out-of-core
+  // tile prefetches the next domain group while the current one is traced, ooc.cu); otherwise to `stream`
+  cudaStream_t load_stream = nullptr;     // builds of prefetched domains
+  cudaStream_t upload_stream = nullptr;   // their mesh uploads: domain k + 1 crosses PCIe while domain k builds
+  bool loading_async = false;
+  std::vector<uint8_t> tracing;           // domains of the group being traced while the next one loads: must not be evicted
+  int collapse_blocks_per_sm = 0;  // occupancy of the cooperative collapse kernel (queried once)
   unsigned long long* d_counters = nullptr;  // [0] work counter, [1..] stats
   uint64_t launches = 0;           // kernels launched by this library (bench "gpu_launches")
   // last render-kernel configuration (function attribute + occupancy are queried once per kernel / smem size)
@@ -133,7 +140,15 @@ struct Scene {
   float4* d_attr = nullptr;
   float bounds[6];
   double build_ms = 0.0;
+  // an enqueued build whose results have not been read back yet (build_scene / scene_finalize)
+  bool pending = false;
+  uint32_t node_cap = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev_upload = nullptr; // set_mesh's copies (recorded on the stream they went to)
+  uint32_t* h_result = nullptr;    // pinned: 8 counter words + 12 bounds words
 };
+inline cudaStream_t build_stream(const Device* d) { return d->loading_async && d->load_stream ? d->load_stream : d->stream; }
+inline cudaStream_t upload_stream(const Device* d) { return d->loading_async && d->upload_stream ? d->upload_stream : d->stream; }
 
 int ensure_scratch(Scratch& s, size_t bytes);
 // make *p hold at least `bytes` (re-using the allocation when it is large enough and not more than 2x too large)
@@ -146,7 +161,8 @@ inline int grow_buffer(T** p, size_t* cap, size_t bytes) {
   *cap = bytes;
   return SPRAYGPU_OK;
 }
-int build_scene(Scene* sc);   // build.cu
+int build_scene(Scene* sc);     // build.cu: enqueue the build (no host wait)
+int scene_finalize(Scene* sc);  // build.cu: wait for it, read node count / depth / bounds, run the commit's checks
 int launch_max_index(Device* dev, const uint32_t* d_idx, size_t n, uint32_t* d_out);   // build.cu
 int upload_domain_table(Device* dev);
 CameraDev to_camdev(const spraygpu_camera* c);   // trace.cu

@@ -21,6 +21,8 @@
 //        shadow rays and the bounce ray -> wave s+1                                        ooc_shade_kernel
 // so a frame costs (bounces + 1) sweeps over the entered domains, the same count as the reference's rounds.
 // The result is independent of the grouping: closest hit = lexicographic min of (t, domain, prim).
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -240,6 +242,8 @@ __global__ void __launch_bounds__(256)
 using namespace spraygpu;
 
 static inline int ooc_grid(size_t n, int t) { return (int)((n + t - 1) / t); }
+// SPRAY_OOC_PREFETCH=0: the serial schedule of round 1 (A/B knob)
+static inline bool ooc_prefetch_disabled() { const char* e = getenv("SPRAY_OOC_PREFETCH"); return e && *e == '0'; }
 
 extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_camera* cam, const spraygpu_shade* shade,
                                        spraygpu_tile tile, float* fb, int max_resident, spraygpu_load_fn load, void* user,
@@ -339,27 +343,49 @@ extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_cam
       std::stable_partition(order.begin(), order.end(), [&](const std::pair<unsigned int, int>& a) {
         return dev->h_domains[(size_t)a.second].resident != 0;
       });
-      // 3. groups
-      for (size_t g0 = 0; g0 < order.size() && rc == SPRAYGPU_OK; g0 += (size_t)max_resident) {
-        const size_t g1 = std::min(order.size(), g0 + (size_t)max_resident);
-        dev->active.assign((size_t)nd, 0);
-        for (size_t g = g0; g < g1; ++g) {
-          const int id = order[g].second;
-          const int lrc = load(user, id);
-          if (lrc) { set_error("trace_tile_ooc: load callback failed for domain %d (rc %d)", id, lrc); rc = SPRAYGPU_ERR_STATE; break; }
-          dev->active[(size_t)id] = 1;
+      // 3. groups.  With room for two groups in the cache (max_resident >= 2) the NEXT group is loaded — mesh upload on
+      // the upload stream, BVH build on the load stream — while the CURRENT one is traced on the device's stream; the
+      // reference serialises Scene::load behind a barrier (ooc_pcontext.h:145-154).  An LRU cache of max_resident
+      // blocks then evicts only domains of groups that were traced two steps ago: the load streams wait for that
+      // trace's event before they overwrite a block.
+      const bool prefetch = max_resident >= 2 && dev->load_stream && dev->upload_stream && !ooc_prefetch_disabled();
+      const size_t gsz = prefetch ? (size_t)max_resident / 2 : (size_t)max_resident;
+      const size_t ngroups = (order.size() + gsz - 1) / gsz;
+      std::vector<cudaEvent_t> ev_trace(ngroups, nullptr);
+      auto load_group = [&](size_t g) -> int {
+        const size_t g0 = g * gsz, g1 = std::min(order.size(), g0 + gsz);
+        if (prefetch) {
+          // blocks evicted now were last read by the trace of group g - 2 at the latest
+          if (g >= 2) {
+            if (cudaStreamWaitEvent(dev->upload_stream, ev_trace[g - 2], 0) != cudaSuccess ||
+                cudaStreamWaitEvent(dev->load_stream, ev_trace[g - 2], 0) != cudaSuccess) { set_error("trace_tile_ooc: cudaStreamWaitEvent failed"); return SPRAYGPU_ERR_CUDA; }
+          }
+          dev->loading_async = true;
         }
-        if (rc) break;
-        for (size_t g = g0; g < g1; ++g)
-          if (!dev->h_domains[(size_t)order[g].second].resident) {
+        int lrc2 = SPRAYGPU_OK;
+        for (size_t g_ = g0; g_ < g1; ++g_) {
+          const int id = order[g_].second;
+          const int lrc = load(user, id);
+          if (lrc) { set_error("trace_tile_ooc: load callback failed for domain %d (rc %d)", id, lrc); lrc2 = SPRAYGPU_ERR_STATE; break; }
+        }
+        dev->loading_async = false;
+        return lrc2;
+      };
+      if (ngroups) rc = load_group(0);
+      for (size_t g = 0; g < ngroups && rc == SPRAYGPU_OK; ++g) {
+        const size_t g0 = g * gsz, g1 = std::min(order.size(), g0 + gsz);
+        dev->active.assign((size_t)nd, 0);
+        for (size_t g_ = g0; g_ < g1; ++g_) dev->active[(size_t)order[g_].second] = 1;
+        for (size_t g_ = g0; g_ < g1; ++g_)
+          if (!dev->h_domains[(size_t)order[g_].second].resident) {
             set_error("trace_tile_ooc: domain %d is not resident after its group was loaded (cache smaller than max_resident = %d?)",
-                      order[g].second, max_resident);
+                      order[g_].second, max_resident);
             rc = SPRAYGPU_ERR_STATE;
             break;
           }
         if (rc) break;
         dev->table_dirty = true;
-        rc = upload_domain_table(dev);
+        rc = upload_domain_table(dev);       // waits for the group's enqueued builds (scene_finalize), then uploads
         if (rc) break;
         if (have_rad) {
           rc = launch_intersect_domains(dev, rays, n, keys, nullptr, 1);
@@ -373,7 +399,20 @@ extern "C" int spraygpu_trace_tile_ooc(spraygpu_device dev_h, const spraygpu_cam
               dev->d_domains, nd, dev->d_tlas, dev->tlas_n, rays, sdir, n, total, occ);
           dev->launches++;
         }
+        if (prefetch) {
+          if (cudaEventCreateWithFlags(&ev_trace[g], cudaEventDisableTiming) != cudaSuccess || cudaEventRecord(ev_trace[g], st) != cudaSuccess) {
+            set_error("trace_tile_ooc: cudaEventRecord failed"); rc = SPRAYGPU_ERR_CUDA; break;
+          }
+          // the cache must hold the group being traced AND the one being loaded: spraygpu_domain_bind refuses to
+          // unbind (evict) a domain of the current group while the next one loads
+          dev->tracing = dev->active;
+          if (g + 1 < ngroups) rc = load_group(g + 1);       // overlaps the trace just enqueued
+          dev->tracing.clear();
+        } else if (g + 1 < ngroups) {
+          rc = load_group(g + 1);                             // set_mesh waits for the device's stream: serial
+        }
       }
+      for (cudaEvent_t e : ev_trace) if (e) cudaEventDestroy(e);
       dev->active.clear();
       dev->table_dirty = true;
       if (rc) break;

@@ -2,6 +2,10 @@
 // arrays; insitu3.cu: ray forwarding).  Every rank maps every other rank's region (CUDA IPC over NVLink / NVSwitch,
 // comm_shared_alloc in comm.cu); offset 0 of a region is its barrier counter.
 #pragma once
+#include <stdlib.h>
+
+#include <string>
+#include <utility>
 #include <vector>
 
 #include "internal.cuh"
@@ -64,5 +68,33 @@ __device__ __forceinline__ uint32_t warp_append(unsigned int* counter, bool pred
   base = __shfl_sync(0xffffffffu, base, leader);
   return base + __popc(b & ((1u << lane) - 1u));
 }
+
+// SPRAY_INSITU_TIMING=1: CUDA events between the phases of a tile, printed per rank at the end of the call (a
+// development aid: it synchronises the stream, so timed benchmark runs leave it off)
+struct PhaseTimer {
+  bool on = false;
+  cudaStream_t st = nullptr;
+  std::vector<std::pair<const char*, cudaEvent_t>> ev;
+  explicit PhaseTimer(cudaStream_t s) : st(s) { const char* e = getenv("SPRAY_INSITU_TIMING"); on = e && *e == '1'; mark("start"); }
+  void mark(const char* name) {
+    if (!on) return;
+    cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st);
+    ev.push_back(std::make_pair(name, e));
+  }
+  void report(const char* what, int rank) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    std::string line = std::string(what) + " rank " + std::to_string(rank) + ":";
+    for (size_t i = 1; i < ev.size(); ++i) {
+      float ms = 0.f; cudaEventElapsedTime(&ms, ev[i - 1].second, ev[i].second);
+      char buf[64]; snprintf(buf, sizeof(buf), " %s %.0f", ev[i].first, ms * 1e3f);
+      line += buf;
+    }
+    float tot = 0.f; cudaEventElapsedTime(&tot, ev.front().second, ev.back().second);
+    fprintf(stderr, "%s | total %.0f us\n", line.c_str(), tot * 1e3f);
+    for (auto& e : ev) cudaEventDestroy(e.second);
+    ev.clear();
+  }
+};
 
 }  // namespace spraygpu

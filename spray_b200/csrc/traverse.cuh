@@ -663,12 +663,15 @@ struct LaneTrav {
 
 // Call with ALL 32 lanes of the warp (act = this lane carries a ray).  Returns: any == false -> out.t < inf;
 // any == true -> occluded.
+// tbound: a hit is only wanted if (t, domain, prim) is lexicographically below (tbound, ~0, ~0) — the t of a hit already
+// known elsewhere (another GPU's domains, ray forwarding); everything behind it is culled like a local best hit.
 template <bool COUNT, typename Source>
 __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const RayCtx& r, const bool any, SceneHit& out,
-                                           uint32_t* cnt /*[3]: domain tests, nodes, tris*/) {
+                                           uint32_t* cnt /*[3]: domain tests, nodes, tris*/, const float tbound = INFINITY) {
   LaneStack stack;
   LaneTrav T(stack);
   T.begin(act);
+  T.out.t = tbound;
 #if SPRAY_COOP_TRI
   __shared__ CoopScratch coop_scratch[SPRAY_MAX_CTA_WARPS];
   CoopScratch& S = coop_scratch[threadIdx.x >> 5];
@@ -683,18 +686,19 @@ __device__ __forceinline__ bool trace_warp(Source& src, const bool act, const Ra
 #endif
   }
   out = T.out;
-  return any ? T.found : (out.t < INFINITY);
+  return any ? T.found : (out.prim != 0xFFFFFFFFu);
 }
 
 // closest / any hit over the ray's entered resident domains; all 32 lanes call.
 template <bool COUNT>
 __device__ __forceinline__ bool scene_trace_warp(const DomainEntry* __restrict__ table, const DomSmem& D, const bool act,
-                                                 vec3 o, vec3 d, const bool any, SceneHit& out, uint32_t* cnt) {
+                                                 vec3 o, vec3 d, const bool any, SceneHit& out, uint32_t* cnt,
+                                                 const float tbound = INFINITY) {
   const RayCtx r = make_ray_ctx(o, d, SPRAY_RAY_EPS);
   TlasStack tstack;
   TlasSource src(table, D, tstack);
   src.reset(act);
-  return trace_warp<COUNT>(src, act, r, any, out, cnt);
+  return trace_warp<COUNT>(src, act, r, any, out, cnt, tbound);
 }
 
 }  // namespace spraygpu

@@ -264,8 +264,8 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
     cam = capi.make_camera(cd)
     sh = capi.make_shade(lights=sc["lights"], **shade)
     mode = "image" if args.partition == "both" else args.partition
-    if args.workload == "c5" and "SPRAY_PARTITION" not in os.environ and "--partition" not in " ".join(os.sys.argv):
-        mode = "insitu"                                   # C5 is the reference's in-situ configuration
+    if args.workload in ("c4", "c5") and "SPRAY_PARTITION" not in os.environ and "--partition" not in " ".join(os.sys.argv):
+        mode = "insitu"                                   # C4 (sharded scene) / C5 are the reference's in-situ configurations
     comm = bootstrap_comm(dev, rank, world)
     shm = "spraygpu_img_%s_%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
     line = None
@@ -311,16 +311,57 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         d2h = None
         r.close()
     else:
-        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, shm_name=shm)
+        # in-situ headline (C4 / C5, or --partition insitu): SPRAY_INSITU_MODE picks the variant, the other one is measured beside it
+        imode = os.environ.get("SPRAY_INSITU_MODE", "fwd")
+        rr = os.environ.get("SPRAY_INSITU_RR", "0") == "1"
+        fits_one_gpu = args.workload != "c4" or int(os.environ.get("SPRAY_C4_TRIS", str(1 << 23))) * len(sc["domains"]) <= (1 << 26)
+        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=imode, shm_name=shm, round_robin=rr)
+        build_ms = float(sum(s_.info().build_ms for s_ in dev.scenes if s_.h))
+        build_tris = int(sum(s_.info().num_faces for s_ in dev.scenes if s_.h))
         st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
-        pc = insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream)
+        r.frame_device()
+        comp = r.composite_image()
+        if fits_one_gpu:
+            pc = insitu_parity_check(r, sc, cam, sh, W, H, rank, local_rank, stream)
+        else:
+            pc = {"against": None} if rank == 0 else None
         r.frame_host()
         host = r.host_image()
         if rank == 0:
-            pc["host_image_equals_composite"] = bool(np.array_equal(host, pc.pop("_composite")))
+            pc["host_image_equals_composite"] = bool(np.array_equal(host, comp))
+            pc.pop("_composite", None)
         fp = _sum_over_ranks(dict(zip(("root", "host"), r.image.flushed_pixels())))
-        par_label = INSITU_LABEL % (world, len(r.owned), len(sc["domains"]), r.rpb)
-        r.close()
+        owned_n, rpb = len(r.owned), r.rpb
+        # the other variant on the same device / scene (the domains stay loaded): cross-check of two independent exchanges
+        omode = "p2p" if imode == "fwd" else "fwd"
+        r.image.close(); r.image = None
+        r_o = InsituRenderer.__new__(InsituRenderer)
+        r_o.__dict__.update(r.__dict__)
+        r_o.mode = omode
+        r_o.image = capi.Image(dev, comm, W, H, shm + "_o")
+        begin = list(range(0, H, r_o.rpb)) + [H]
+        r_o.image.set_rows(begin, [b_ % world for b_ in range(len(begin) - 1)])
+        r_o.fb = r_o.image.device
+        st_o = r_o.count_rays()
+        ms_o, l_o = timer(r_o.frame_device, max(args.steps // 2, 3), 3)
+        r_o.frame_device()
+        comp_o = r_o.composite_image()
+        other = None
+        if rank == 0:
+            other = {"mode": omode, "value": rays / (ms_o * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms_o, "gpu_launches": int(l_o),
+                     "image_rmse_vs_headline_variant": _rmse(comp_o, comp), "image_bit_identical": bool(np.array_equal(comp_o, comp)),
+                     "ray_counts_equal": all(st_o[k] == st[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))}
+            if not fits_one_gpu:
+                pc = {"against": "the scene does not fit one GPU: cross-check of the two in-situ exchanges (ray forwarding vs dense peer-memory waves), "
+                                 "each parity-tested against the single-GPU frame and the oracle at sizes that fit (tests/multigpu_check.py)",
+                      "rmse": other["image_rmse_vs_headline_variant"], "bit_identical": other["image_bit_identical"],
+                      "keys_equal": other["ray_counts_equal"], "host_image_equals_composite": pc.get("host_image_equals_composite")}
+        r_o.image.close(); r_o.image = None
+        par_label = (FWD_LABEL if imode == "fwd" else INSITU_LABEL) % (world, owned_n, len(sc["domains"]), rpb)
+        if rr:
+            par_label += "; domains dealt round-robin over the Morton order (data_partition.h:139-155)"
+        insitu_headline = {"other_variant": other, "build": {"triangles_this_gpu": build_tris, "commit_device_ms_this_gpu": build_ms,
+                                                               "mtris_per_s": build_tris / max(build_ms, 1e-9) / 1e3}}
     insitu_extra = None
     if args.partition == "both" and mode == "image":
         dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
@@ -374,6 +415,8 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
             line["e2e"]["d2h_note"] = "sparse flush: only pixels that are or were non-zero are stored to the host image (full frame = %d B)" % (W * H * 16)
         if insitu_extra:
             line["insitu"] = insitu_extra
+        if mode != "image":
+            line["insitu_detail"] = insitu_headline
     comm.close()
     return line
 

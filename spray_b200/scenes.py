@@ -164,9 +164,12 @@ def soup_domain_device(seed, ntris, cell_lo, cell_hi, device="cuda"):
 
 
 def soup_scene_device(grid=(4, 4, 4), tris_per_domain=1 << 20, cell=20.0, mtl=(MTL_DIFFUSE, (1.0, 1.0, 1.0)), seed0=0,
-                      only=None):
+                      only=None, lazy=False):
     """soup_scene with device-resident meshes: domains carry `verts/faces/rgb` as CUDA tensors (or None for the
-    domains not in `only` — another rank's share); capi.Device.load_scene uploads nothing for them."""
+    domains not in `only` — another rank's share); capi.Device.load_scene uploads nothing for them.
+    lazy: no tensors at all, only the `gen` recipe — load_scene generates each owned domain right before its commit and
+    drops the tensors afterwards (C4: 64 x 8 Mi triangles per GPU would otherwise hold 32 GB of raw meshes beside the
+    committed scenes)."""
     doms = []
     gx, gy, gz = grid
     for i in range(gx * gy * gz):
@@ -174,7 +177,7 @@ def soup_scene_device(grid=(4, 4, 4), tris_per_domain=1 << 20, cell=20.0, mtl=(M
         lo = np.array([ix * cell, iy * cell, iz * cell], np.float32)
         hi = lo + f32(cell)
         d = dict(transform=None, bounds=np.concatenate([lo, hi]).astype(np.float32), mtl=mtl, gen=(seed0 + i, tris_per_domain, lo, hi))
-        if only is None or i in only:
+        if not lazy and (only is None or i in only):
             d["verts"], d["faces"], d["rgb"] = soup_domain_device(seed0 + i, tris_per_domain, lo.tolist(), hi.tolist())
         doms.append(d)
     return dict(domains=doms, lights=[(LIGHT_POINT, (0.0, 500.0, 1000.0), (1.0, 1.0, 1.0))])

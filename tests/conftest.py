@@ -39,6 +39,7 @@ def _load_hostemu(soname, flags):
     E.emu_destroy.argtypes = [C.c_void_p]
     E.emu_num_nodes.restype = C.c_size_t
     E.emu_num_nodes.argtypes = [C.c_void_p]
+    E.emu_get_bvh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     E.emu_depth.restype = C.c_int
     E.emu_depth.argtypes = [C.c_void_p]
     E.emu_intersect.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -235,6 +235,10 @@ EmuScene* emu_build(const float* verts, size_t nv, const uint32_t* faces, size_t
 void emu_destroy(EmuScene* s) { delete s; }
 int emu_depth(const EmuScene* s) { return s->depth; }
 size_t emu_num_nodes(const EmuScene* s) { return s->nodes.size() / 5; }
+void emu_get_bvh(const EmuScene* s, void* nodes, void* tris) {
+  memcpy(nodes, s->nodes.data(), s->nodes.size() * sizeof(u4));
+  memcpy(tris, s->tris.data(), s->tris.size() * sizeof(float));
+}
 
 // rays: 8 floats each (ox,oy,oz,tmin,dx,dy,dz,tmax)
 void emu_intersect(EmuScene* s, uint32_t domain, const float* rays, size_t n, uint64_t* keys, float* uv,

@@ -42,9 +42,11 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
       tail -3 $out/insitu1_$arg.log ;;
     smoke)
       timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; tail -2 $out/smoke.log ;;
+    env)     # env:NAME=VALUE  (exported for the following steps)
+      export "$arg" ;;
     multi)   # multi:<nproc>:<script and args>
       np_=${arg%%:*}; cmd=${arg#*:}
-      lg=$out/multi_n${np_}_$(echo "$cmd" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60)
+      lg=$out/multi_n${np_}_$(echo "$cmd" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60)${SPRAY_INSITU_RR:+_rr$SPRAY_INSITU_RR}
       timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $np_ --master-addr 127.0.0.1 --master-port 29533 $cmd > $lg.log 2> $lg.err; echo "multi $np_ $cmd rc $?"; tail -c 1500 $lg.log; tail -3 $lg.err ;;
   esac
 done
