@@ -155,14 +155,11 @@ def measured_peak_hbm():
 
 
 def lib_hash():
-    """sha256 of the libspraygpu.so this process loads: profiles/ncu_counters.json is keyed by it, so counters of
-    another build are never printed beside this one's timings."""
+    """Build id of the libspraygpu.so this process loads (capi.build_id: sha256 of its SOURCES — nvcc's output is not
+    bit-reproducible): profiles/ncu_counters.json is keyed by it, so counters of another build are never printed
+    beside this one's timings."""
     from spray_b200 import capi
-    h = hashlib.sha256()
-    with open(capi.LIB_PATH, "rb") as f:
-        for blk in iter(lambda: f.read(1 << 20), b""):
-            h.update(blk)
-    return h.hexdigest()
+    return capi.build_id()
 
 
 def ncu_counters(workload_name):
@@ -431,7 +428,7 @@ def main():
                        "rays_per_frame": int(r["rays"]), "eye_rays": int(st["eye_rays"]), "shadow_rays": int(st["shadow_rays"]),
                        "hits": int(st["hits"]),
                        "parallelism": "1 GPU, all domains resident", "build_s_all_domains": r["build_s"],
-                       "lib_sha256": lib_hash()[:16]},
+                       "lib_build_id": lib_hash()[:16]},
             "clocks": clocks, "gpu_launches": int(r["launches"]),
             "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"],

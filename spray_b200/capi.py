@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # SPRAYGPU_LIB selects an experimental build variant of the SAME sources (tools/variants.sh)
 LIB_PATH = os.environ.get("SPRAYGPU_LIB") or os.path.join(_HERE, "libspraygpu.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "spray_gpu.h")
+CSRC_DIR = os.path.join(_HERE, "csrc")
 
 KEY_MISS = 0xFFFFFFFFFFFFFFFF
 MAX_LIGHTS = 8
@@ -155,6 +156,27 @@ def lib():
         fn.restype, fn.argtypes = res, args
     _lib = L
     return L
+
+
+def build_id():
+    """Identifies the library build for profiles/ncu_counters.json: sha256 over the SOURCES libspraygpu.so is made from
+    (csrc/*.cu, *.cuh, Makefile, include/spray_gpu.h).  nvcc's output is not bit-reproducible (two clean builds of the
+    same tree differ), so a hash of the binary would stop matching as soon as anybody rebuilds.  A variant library
+    loaded through SPRAYGPU_LIB (other -D flags, same sources) is identified by its own bytes instead."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    if os.environ.get("SPRAYGPU_LIB"):
+        with open(LIB_PATH, "rb") as f:
+            h.update(f.read())
+        return "variant-" + h.hexdigest()
+    files = sorted(glob.glob(os.path.join(CSRC_DIR, "*.cu")) + glob.glob(os.path.join(CSRC_DIR, "*.cuh")) +
+                   [os.path.join(CSRC_DIR, "Makefile"), HEADER_PATH])
+    for fn in files:
+        h.update(os.path.basename(fn).encode())
+        with open(fn, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
 
 
 def declared_symbols():

@@ -38,7 +38,7 @@ namespace spraygpu {
 struct FwdState {
   size_t cap_n = 0;
   int cap_passes = 0;
-  size_t inbox_cap = 0;        // records per inbox
+  size_t seg_cap = 0;          // records per (source rank) segment of an inbox
   void* local = nullptr;       // the peer-mapped region of THIS rank
   std::vector<void*> mapped;
   size_t o_inbox[2] = {0, 0}, o_keys[2] = {0, 0}, o_cap = 0, o_occ = 0;
@@ -59,8 +59,14 @@ struct FwdState {
 };
 
 // control words (rank-local device memory)
-enum { FC_DONE = 0, FC_WORK_ROUTE, FC_WORK_SERVE, FC_WORK_SHADE, FC_RET, FC_CAND, FC_LIVE0, FC_LIVE1, FC_OVERFLOW, FC_WORDS = 12 };
-// words at P2P_FLAG_BYTES/2 of a region: the two inbox counters (peers add to them)
+// FC_PUSH0 / FC_PUSH1: records THIS rank has appended to inbox 0 / 1 of every destination (16 words each).  A
+// destination's inbox is cut into one segment per SOURCE rank, so slots are handed out by a LOCAL atomic — the first
+// version took them from a counter in the destination's memory: one NVLink round trip (~2-3 us) per (warp,
+// destination), and route0 / shade were bound by exactly that latency (130 / 123 us for 0.5 M rays at 8 GPUs).
+enum { FC_DONE = 0, FC_WORK_ROUTE, FC_WORK_SERVE, FC_WORK_SHADE, FC_RET, FC_CAND, FC_LIVE0, FC_LIVE1, FC_OVERFLOW, FC_PUSH0 = 16,
+       FC_PUSH1 = 32, FC_WORDS = 48 };
+// words at P2P_FLAG_BYTES/2 of a region: records per source segment of inbox 0 (16 words) and inbox 1 (16 words), written
+// by the sources when they have finished appending (fwd_publish_kernel)
 #define FWD_CTR_OFFSET 128
 #define FWD_THREADS 128
 #define FWD_MINBLOCKS 4
@@ -90,7 +96,7 @@ struct FwdWave {
   int nranks, me, rows_per_block;
   size_t o_inbox_cur, o_inbox_next, o_keys, o_keys_next, o_cap, o_occ;
   int inbox_cur, inbox_next;   // which counter word
-  uint32_t inbox_cap;
+  uint32_t seg_cap;
   PeerPtrs peers;
   unsigned int* ctl;
   const uint32_t* src;         // wave > 0: the live home samples
@@ -163,12 +169,12 @@ __device__ __forceinline__ void fwd_push(const FwdWave& P, size_t o_inbox, int w
     const uint32_t b = __ballot_sync(0xffffffffu, go);
     const int leader = __ffs((int)b) - 1;
     uint32_t base = 0;
-    if (lane == leader) base = atomicAdd_system((unsigned int*)(P.peers.base[rk] + FWD_CTR_OFFSET) + which, (unsigned int)__popc(b));
+    if (lane == leader) base = atomicAdd(P.ctl + (which ? FC_PUSH1 : FC_PUSH0) + rk, (unsigned int)__popc(b));
     base = __shfl_sync(0xffffffffu, base, leader);
     if (go) {
       const uint32_t slot = base + __popc(b & ((1u << lane) - 1u));
-      if (slot < P.inbox_cap) {
-        uint4* rec = (uint4*)(P.peers.base[rk] + o_inbox) + 2 * (size_t)slot;
+      if (slot < P.seg_cap) {
+        uint4* rec = (uint4*)(P.peers.base[rk] + o_inbox) + 2 * ((size_t)P.me * P.seg_cap + slot);
         rec[0] = make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), sample);
         rec[1] = make_uint4(__float_as_uint(d.x), __float_as_uint(d.y), __float_as_uint(d.z), meta | (rk == primary ? 0u : FWD_META_SECONDARY));
       } else {
@@ -178,11 +184,30 @@ __device__ __forceinline__ void fwd_push(const FwdWave& P, size_t o_inbox, int w
   }
 }
 
-__global__ void fwd_reset_kernel(unsigned int* ctl, unsigned int* inbox_ctr, int zero_inbox /*bit 0 / bit 1*/, int zero_live /*-1: none*/) {
+__global__ void fwd_reset_kernel(unsigned int* ctl, int zero_push /*bit 0 / bit 1*/, int zero_live /*-1: none*/) {
   ctl[FC_WORK_ROUTE] = 0u; ctl[FC_WORK_SERVE] = 0u; ctl[FC_WORK_SHADE] = 0u; ctl[FC_CAND] = 0u;
-  if (zero_inbox & 1) inbox_ctr[0] = 0u;
-  if (zero_inbox & 2) inbox_ctr[1] = 0u;
+  for (int r = 0; r < P2P_MAX_RANKS; ++r) {
+    if (zero_push & 1) ctl[FC_PUSH0 + r] = 0u;
+    if (zero_push & 2) ctl[FC_PUSH1 + r] = 0u;
+  }
   if (zero_live >= 0) ctl[FC_LIVE0 + zero_live] = 0u;
+}
+// one thread, after a kernel that appended records: tell every destination how many records my segment of its inbox
+// `which` holds, then signal the barrier (the appending kernel has completed: its peer stores are performed)
+__global__ void fwd_publish_kernel(PeerPtrs P, int nranks, int me, const unsigned int* ctl, int which, uint32_t seg_cap) {
+  for (int r = 0; r < nranks; ++r) {
+    const unsigned int c = ctl[(which ? FC_PUSH1 : FC_PUSH0) + r];
+    ((unsigned int*)(P.base[r] + FWD_CTR_OFFSET))[which * P2P_MAX_RANKS + me] = c < seg_cap ? c : seg_cap;
+  }
+  __threadfence_system();
+  for (int r = 0; r < nranks; ++r)
+    if (r != me) atomicAdd_system((unsigned long long*)P.base[r], 1ull);
+}
+// record index k of the concatenated segments -> physical record index (segment * seg_cap + offset)
+__device__ __forceinline__ uint32_t fwd_phys(const uint32_t* seg_end, int nranks, uint32_t seg_cap, uint32_t k) {
+  int sgm = 0;
+  while (sgm < nranks - 1 && k >= seg_end[sgm]) ++sgm;
+  return (uint32_t)sgm * seg_cap + (k - (sgm ? seg_end[sgm - 1] : 0u));
 }
 __global__ void fwd_zero_ret_kernel(unsigned int* ctl) { ctl[FC_RET] = 0u; }
 
@@ -221,7 +246,6 @@ __global__ void __launch_bounds__(FWD_THREADS) fwd_route0_kernel(FwdWave P, spra
     }
     fwd_push(P, P.o_inbox_next, P.inbox_next, mask, primary, o, d, (uint32_t)i, (uint32_t)P.me);
   }
-  grid_signal_peers(P.ctl + FC_DONE, P.peers, P.nranks, P.me);
 }
 
 // F2: trace MY inbox against MY domains (insitu::TContext::processRays for received rays), in two passes separated by a
@@ -237,7 +261,13 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
   const DomSmem D = load_domain_smem(P.table, P.nd, P.tlas, P.tlas_n, smem);
   uint32_t* q = (uint32_t*)((char*)smem + ((dom_smem_bytes(P.nd, P.tlas_n, 0) + 15) & ~(size_t)15)) + (size_t)(threadIdx.x >> 5) * FWD_QCAP;
   const int lane = threadIdx.x & 31;
-  const uint32_t nrec = min(((const unsigned int*)(P.peers.base[P.me] + FWD_CTR_OFFSET))[P.inbox_cur], P.inbox_cap);
+  uint32_t seg_end[P2P_MAX_RANKS];
+  uint32_t nrec = 0;
+#pragma unroll
+  for (int r = 0; r < P2P_MAX_RANKS; ++r) {
+    if (r < P.nranks) nrec += ((const unsigned int*)(P.peers.base[P.me] + FWD_CTR_OFFSET))[P.inbox_cur * P2P_MAX_RANKS + r];
+    seg_end[r] = nrec;
+  }
   const uint4* inbox = (const uint4*)(P.peers.base[P.me] + P.o_inbox_cur);
   unsigned int* work = P.ctl + (pass ? FC_WORK_ROUTE : FC_WORK_SERVE);   // the route counter is idle during a wave's F2
   int count = 0;
@@ -248,9 +278,10 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
       if (lane == 0) base = atomicAdd(work, 32u);
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= nrec) { more = false; continue; }
-      const uint32_t k = base + lane;
+      uint32_t k = base + lane;
       bool go = false;
       if (k < nrec) {
+        k = fwd_phys(seg_end, P.nranks, P.seg_cap, k);
         const uint32_t meta = inbox[2 * (size_t)k + 1].w;
         go = (int)((meta >> 9) & 1u) == pass;
         if (go && pass && (meta & FWD_META_SHADOW)) {
@@ -461,7 +492,6 @@ __global__ void __launch_bounds__(FWD_THREADS, FWD_MINBLOCKS)
     for (int off = 16; off; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
     if (lane == 0 && x) atomicAdd(counters + slots[qq], x);
   }
-  grid_signal_peers(P.ctl + FC_DONE, P.peers, P.nranks, P.me);
 }
 
 // F5: TContext::retireShadows -> HdrImage::add (all entries are this rank's home samples)
@@ -508,7 +538,7 @@ static void fwd_destroy(Comm* c, void* p) {
 }
 
 // collective: every rank calls with the same (n, npasses)
-static int fwd_ensure(Comm* c, FwdState* S, size_t n, int npasses) {
+static int fwd_ensure(Comm* c, FwdState* S, size_t n, int npasses, size_t need_seg) {
   Device* dev = comm_device(c);
   if (!S->d_ctl) {
     SG_CUDA(cudaMalloc((void**)&S->d_ctl, sizeof(unsigned int) * FC_WORDS));
@@ -518,7 +548,7 @@ static int fwd_ensure(Comm* c, FwdState* S, size_t n, int npasses) {
     *S->h_err = 0u;
     SG_CUDA(cudaHostGetDevicePointer((void**)&S->h_err_dev, S->h_err, 0));
   }
-  if (n <= S->cap_n && npasses <= S->cap_passes) return SPRAYGPU_OK;
+  if (n <= S->cap_n && npasses <= S->cap_passes && need_seg <= S->seg_cap) return SPRAYGPU_OK;
   SG_CUDA(cudaStreamSynchronize(dev->stream));
   if (S->local) {
     int rc = comm_host_barrier(c);
@@ -530,10 +560,11 @@ static int fwd_ensure(Comm* c, FwdState* S, size_t n, int npasses) {
   const size_t cn = std::max(n, S->cap_n);
   const int cp = std::max(npasses, std::max(S->cap_passes, 1));
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
-  // worst case: every sample of the tile sends its radiance ray and all its shadow rays to this rank
-  S->inbox_cap = cn * (size_t)(1 + cp);
+  // worst case: every home sample of a source rank sends its radiance ray and all its shadow rays to this rank
+  S->seg_cap = std::max(need_seg, S->seg_cap);
+  const size_t inbox_cap = S->seg_cap * (size_t)comm_size(c);
   size_t off = P2P_FLAG_BYTES;
-  for (int k = 0; k < 2; ++k) { S->o_inbox[k] = off; off += al(S->inbox_cap * 32); }
+  for (int k = 0; k < 2; ++k) { S->o_inbox[k] = off; off += al(inbox_cap * 32); }
   for (int k = 0; k < 2; ++k) { S->o_keys[k] = off; off += al(cn * 8); }
   S->o_cap = off; off += al(cn * 16);
   S->o_occ = off; off += al(cn * (size_t)cp);
@@ -546,8 +577,8 @@ static int fwd_ensure(Comm* c, FwdState* S, size_t n, int npasses) {
     SG_CUDA(cudaMalloc((void**)&S->list[k], cn * sizeof(uint32_t)));
   }
   SG_CUDA(cudaMalloc((void**)&S->ret, cn * sizeof(uint4) * (size_t)cp));
-  SG_CUDA(cudaMalloc((void**)&S->cand_idx, S->inbox_cap * sizeof(uint32_t)));
-  SG_CUDA(cudaMalloc((void**)&S->cand_key, S->inbox_cap * sizeof(unsigned long long)));
+  SG_CUDA(cudaMalloc((void**)&S->cand_idx, inbox_cap * sizeof(uint32_t)));
+  SG_CUDA(cudaMalloc((void**)&S->cand_key, inbox_cap * sizeof(unsigned long long)));
   S->cap_n = cn; S->cap_passes = cp;
   return comm_host_barrier(c);
 }
@@ -605,7 +636,12 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     SG_CHECK(n * (size_t)(npasses + 1) < ((size_t)1 << 32), SPRAYGPU_ERR_LIMIT,
              "trace_tile_insitu_fwd: %zu samples x %d light passes do not fit 32-bit record indices; use smaller blocking tiles", n, npasses);
     SG_CHECK(npasses < 65536, SPRAYGPU_ERR_LIMIT, "trace_tile_insitu_fwd: %d light passes", npasses);
-    rc = fwd_ensure(comm, S, n, npasses);
+    // a rank is home to at most ceil(h / (rows_per_block * nranks)) row blocks of the tile
+    const size_t home_rows = (size_t)((tile.h + rows_per_block * nranks - 1) / (rows_per_block * nranks) + 1) * rows_per_block;
+    const size_t need_seg = std::min(home_rows, (size_t)tile.h) * tile.w * shade->pixel_samples * (size_t)(1 + npasses);
+    SG_CHECK(need_seg * (size_t)nranks < ((size_t)1 << 32), SPRAYGPU_ERR_LIMIT,
+             "trace_tile_insitu_fwd: %zu inbox records do not fit 32-bit record indices; use smaller blocking tiles", need_seg * (size_t)nranks);
+    rc = fwd_ensure(comm, S, n, npasses, need_seg);
     if (rc) return rc;
     // routing table: domains grouped by owner, one box per rank
     {
@@ -634,10 +670,9 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     P.table = dev->d_domains; P.nd = nd; P.tlas = dev->d_tlas; P.tlas_n = dev->tlas_n; P.route = S->d_route;
     P.shade = *shade; P.tile = tile; P.cam = to_camdev(cam); P.image_w = cam->image_w; P.spp = shade->pixel_samples;
     P.npasses = npasses; P.n = n; P.nranks = nranks; P.me = me; P.rows_per_block = rows_per_block;
-    P.o_cap = S->o_cap; P.o_occ = S->o_occ; P.ctl = S->d_ctl; P.inbox_cap = (uint32_t)S->inbox_cap;
+    P.o_cap = S->o_cap; P.o_occ = S->o_occ; P.ctl = S->d_ctl; P.seg_cap = (uint32_t)S->seg_cap;
     for (int r = 0; r < P2P_MAX_RANKS; ++r) P.peers.base[r] = r < nranks ? (char*)S->mapped[(size_t)r] : nullptr;
     char* mine = (char*)S->local;
-    unsigned int* my_ctr = (unsigned int*)(mine + FWD_CTR_OFFSET);
     auto barrier_wait = [&]() {
       ++S->seq;
       p2p_wait_kernel<<<1, 1, 0, st>>>((volatile unsigned long long*)mine, S->seq * (unsigned long long)(nranks - 1), S->h_err_dev);
@@ -661,7 +696,7 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     PhaseTimer T(st);
     // ---- tile start: my wave-0 keys reset, both inboxes empty, then everyone meets
     SG_CUDA(cudaMemsetAsync(mine + S->o_keys[0], 0xFF, n * 8, st));
-    fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, my_ctr, 3, 0);
+    fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, 3, 0);
     fwd_zero_ret_kernel<<<1, 1, 0, st>>>(S->d_ctl);
     p2p_signal_kernel<<<1, 1, 0, st>>>(P.peers, nranks, me);
     dev->launches += 3;
@@ -672,7 +707,8 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
     P.inbox_next = 0; P.o_inbox_next = S->o_inbox[0]; P.inbox_cur = 1; P.o_inbox_cur = S->o_inbox[1];
     P.o_keys = S->o_keys[0]; P.o_keys_next = S->o_keys[1];
     fwd_route0_kernel<<<grid_lin, FWD_THREADS, smem_route, st>>>(P, S->rays[0]);
-    dev->launches++;
+    fwd_publish_kernel<<<1, 1, 0, st>>>(P.peers, nranks, me, S->d_ctl, 0, P.seg_cap);
+    dev->launches += 2;
     T.mark("route0");
     barrier_wait();
     T.mark("bar");
@@ -687,7 +723,7 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
       P.src = depth ? S->list[kb] : nullptr;
       P.src_n = S->d_ctl + FC_LIVE0 + kb;
       // nobody appends to the next inbox before the barrier that follows F3 of this wave
-      fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, my_ctr, 1 << (kb ^ 1), kb ^ 1);
+      fwd_reset_kernel<<<1, 1, 0, st>>>(S->d_ctl, 1 << (kb ^ 1), kb ^ 1);
       fwd_serve_kernel<<<S->grid_serve, FWD_THREADS, smem_serve, st>>>(P, 0, S->cand_idx, S->cand_key);       // F2, nearest owners
       dev->launches += 2;
       T.mark("serve");
@@ -715,7 +751,8 @@ extern "C" int spraygpu_trace_tile_insitu_fwd(spraygpu_device dev_h, spraygpu_co
       fwd_shade_kernel<<<S->grid_shade, FWD_THREADS, smem_shade, st>>>(P, S->rays[cur], S->w[cur], S->rays[cur ^ 1], S->w[cur ^ 1],
                                                                        S->list[kb ^ 1], S->d_ctl + FC_LIVE0 + (kb ^ 1), S->ret,
                                                                        dev->d_counters);                        // F4
-      dev->launches++;
+      fwd_publish_kernel<<<1, 1, 0, st>>>(P.peers, nranks, me, S->d_ctl, kb ^ 1, P.seg_cap);
+      dev->launches += 2;
       T.mark("shade");
       barrier_wait();
       T.mark("bar");

@@ -312,8 +312,8 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         r.close()
     else:
         # in-situ headline (C4 / C5, or --partition insitu): SPRAY_INSITU_MODE picks the variant, the other one is measured beside it
-        imode = os.environ.get("SPRAY_INSITU_MODE", "fwd")
-        rr = os.environ.get("SPRAY_INSITU_RR", "0") == "1"
+        imode = os.environ.get("SPRAY_INSITU_MODE", "p2p")
+        rr = os.environ.get("SPRAY_INSITU_RR", "1") == "1"
         fits_one_gpu = args.workload != "c4" or int(os.environ.get("SPRAY_C4_TRIS", str(1 << 23))) * len(sc["domains"]) <= (1 << 26)
         r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=imode, shm_name=shm, round_robin=rr)
         build_ms = float(sum(s_.info().build_ms for s_ in dev.scenes if s_.h))
@@ -367,7 +367,8 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
         comm2 = bootstrap_comm(dev2, rank, world)
         timer2 = type(timer)(timer.stream, timer.flush, dev2, world)
-        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, shm_name=shm + "_i")
+        rr = os.environ.get("SPRAY_INSITU_RR", "1") == "1"    # domains dealt round-robin over the Morton order (data_partition.h:139-155)
+        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, shm_name=shm + "_i", round_robin=rr)
         st2 = r2.count_rays()
         ms2, l2 = timer2(r2.frame_device, max(args.steps // 2, 3), 3)
         ms2h, _ = timer2(r2.frame_host, max(args.steps // 2, 3), 2)
@@ -377,11 +378,12 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         r2n = st2["radiance_rays"] + st2["shadow_rays"]
         insitu_extra = {"value": r2n / (ms2 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2, "gpu_launches": int(l2),
                         "e2e": {"value": r2n / (ms2h * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2h},
-                        "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb),
+                        "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb) +
+                                       ("; domains dealt round-robin over the Morton order (data_partition.h:139-155)" if rr else ""),
                         "parity_check": pc2}
         r2.close()
         # the ray-forwarding variant (insitu3.cu) on the same communicator, same parity check
-        r4 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="fwd", shm_name=shm + "_f")
+        r4 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="fwd", shm_name=shm + "_f", round_robin=rr)
         st4 = r4.count_rays()
         ms4, l4 = timer2(r4.frame_device, max(args.steps // 2, 3), 3)
         ms4h, _ = timer2(r4.frame_host, max(args.steps // 2, 3), 2)
@@ -395,7 +397,7 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
                                           "parity_check": pc4}
         r4.close()
         # A/B: round 1's exchange (dense NCCL all-reduces per wave) on the same communicator
-        r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl")
+        r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl", round_robin=rr)
         ms3, l3 = timer2(r3.frame_device, 3, 2)
         insitu_extra["nccl_allreduce_variant"] = {"value": r2n / (ms3 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms3, "gpu_launches": int(l3)}
         r3.close(); comm2.close(); dev2.close()

@@ -89,6 +89,48 @@ def _worker(rank, world, port, q):
         dist.all_reduce(tm)
         ok_owner = int(tm.item()) == int(hit.sum())
 
+        # ---- in-situ with ray forwarding (insitu3.cu's protocol): a sample lives on its HOME rank (interleaved row blocks);
+        # its ray is sent to every rank that owns an entered domain, flagged primary for the owner of the NEAREST one;
+        # pass 0 traces the primary records, pass 1 the others and keeps only what beats the known key; the home rank's
+        # key array ends up with the single-rank closest hit and every hit has exactly one attribute writer
+        rpb = 4
+        home = ((np.arange(n) // W) // rpb) % world                  # pixel row -> home rank (1 spp, whole-image tile)
+        first = ids[np.arange(n), 0]                                  # nearest entered domain (DomainList::sort order)
+        outbox = [[] for _ in range(world)]
+        for i in np.nonzero(home == rank)[0]:
+            if counts[i] == 0:
+                continue
+            owners = set(int(d2r[d]) for d in ids[i, :counts[i]])
+            for r in owners:
+                outbox[r].append((int(i), int(d2r[first[i]]) == r))
+        gathered_boxes = [None] * world
+        dist.all_gather_object(gathered_boxes, outbox)
+        inbox = [rec for src in gathered_boxes for rec in src[rank]]           # what every home rank sent to ME
+        dom_keys = {d: _keys_to_i64(osc.intersect_domain(d, rays)[0]) for d in owned}
+        for d in owned:
+            dom_keys[d][~entered[:, d]] = I64_MAX
+        home_keys = torch.full((n,), I64_MAX, dtype=torch.int64)
+        writers = torch.zeros(n, dtype=torch.int64)
+        for want_primary in (True, False):
+            mine_k = np.full(n, I64_MAX, np.int64)
+            known = home_keys.numpy().copy()                                     # after the barrier: pass 0's result
+            for (i, primary) in inbox:
+                if primary != want_primary:
+                    continue
+                k = min(int(dom_keys[d][i]) for d in owned)
+                if k < known[i]:                                                 # tbound: only hits below the known key
+                    mine_k[i] = k
+            t = torch.from_numpy(np.minimum(mine_k, home_keys.numpy()))
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)                             # = atomicMin_system into the home arrays
+            home_keys = t
+        final = home_keys.numpy()
+        for (i, primary) in inbox:                                               # F3: candidates whose key survived
+            if final[i] != I64_MAX and min(int(dom_keys[d][i]) for d in owned) == final[i]:
+                writers[i] += 1
+        dist.all_reduce(writers)
+        ok_fwd = bool(np.array_equal(final, _keys_to_i64(k_full))) and bool(np.array_equal(writers.numpy() == 1, final != I64_MAX))
+        ok_keys = ok_keys and ok_fwd
+
         # ---- image partition: row bands, each rank renders its band, rank 0 gathers
         bands = multigpu.row_bands(H, world)
         tiles = multigpu.band_tiles(W, bands[rank:rank + 2], 1, max_samples=W * 8)

@@ -40,6 +40,9 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
       timeout 600 python tools/insitu_one.py $arg 3 > $out/insitu1_$arg.log 2>&1 &&
       ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:p2p_|insitu_|eye_rays|intersect_domains|image_flush' -c 600 --csv --log-file $out/insitu1_${arg}_launches.csv python tools/insitu_one.py $arg 1 > $out/insitu1_${arg}_ncu.log 2>&1
       tail -3 $out/insitu1_$arg.log ;;
+    py)      # py:<script and args>  (one GPU)
+      lg=$out/py_$(echo "$arg" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60)
+      timeout 900 python $arg > $lg.log 2> $lg.err; echo "py $arg rc $?"; tail -8 $lg.log ;;
     smoke)
       timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; tail -2 $out/smoke.log ;;
     env)     # env:NAME=VALUE  (exported for the following steps)

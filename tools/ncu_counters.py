@@ -4,8 +4,9 @@
     ncu -i gpurun_out/prof_c2.ncu-rep --page raw --csv > gpurun_out/prof_c2_raw.csv      (here, no GPU needed)
     tools/ncu_counters.py <workload> <raw.csv> <lib.so that was profiled> [source note]
 
-Writes / updates profiles/ncu_counters.json:  { sha256(lib.so): { workload: {counters...} } }.  bench.py looks its
-own library's hash up in that file and prints `traffic: null` when there is no capture of that exact build, so a
+Writes / updates profiles/ncu_counters.json:  { build id: { workload: {counters...} } }, build id = capi.build_id() =
+sha256 of the sources the library is built from (run this on the SAME tree that was profiled).  bench.py looks its
+own build id up in that file and prints `traffic: null` when there is no capture of that exact build, so a
 profile can never be quoted beside another build's timings (the traffic constant was two kernel
 revisions stale).  Values are per LAUNCH (one launch = one frame); the kernel row with the longest duration is used."""
 import csv
@@ -74,7 +75,9 @@ def main():
         ent["l2_bytes"] = ent["l2_sectors"] * 32.0
     if "ncu_duration_ns" in ent:
         ent["ncu_duration_ms"] = ent.pop("ncu_duration_ns") / 1e6
-    h = hashlib.sha256(open(lib, "rb").read()).hexdigest()
+    sys.path.insert(0, ROOT)
+    from spray_b200 import capi
+    h = capi.build_id()        # sha256 of the library's sources (the binary is not bit-reproducible); `lib` is kept for the log
     db = {}
     if os.path.exists(OUT):
         db = json.load(open(OUT))
