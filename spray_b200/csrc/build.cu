@@ -3,7 +3,7 @@
 // per-vertex normals (:267-326).
 //
 // Pipeline (all on dev->stream, no host round trips except one 8-byte counter read per BVH8 level):
-//   transform -> (vertex,face) pair sort -> deterministic per-vertex normal sums
+//   transform -> per-vertex face lists (counting scatter) sorted per vertex -> deterministic per-vertex normal sums
 //   -> triangle boxes + centroid bounds -> 30-bit Morton keys -> LSD radix sort
 //   -> Karras LBVH -> bottom-up refit -> level-synchronous collapse into 80-byte 8-wide nodes
 //   -> triangle records (48 B, leaf order) + attribute records (48 B, primID order)
@@ -195,46 +195,131 @@ __global__ void transform_kernel(const float* __restrict__ vin, float* __restric
   vout[3 * i + 2] = add_rn(add_rn(mul_rn(m[2], x), mul_rn(m[6], y)), add_rn(mul_rn(m[10], z), mul_rn(m[14], 1.0f)));
 }
 
-__global__ void pairs_kernel(const uint32_t* __restrict__ faces, uint32_t* __restrict__ keys,
-                             uint32_t* __restrict__ vals, int npairs) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= npairs) return;
-  keys[i] = faces[i];
-  vals[i] = (uint32_t)i / 3u;
+// ------------------------------------------------------------------------------------------------
+// Per-vertex normals WITHOUT the (vertex, face) pair sort (round 2).  The reference adds the face normals to a vertex
+// in increasing face order (trimesh_buffer.cc:267-326) and the float sum depends on that order, so each vertex needs
+// its incident faces SORTED — but only within the vertex.  Round 1 radix-sorted all 3 n pairs by vertex (3 passes over
+// 3 Mi pairs for a 1 Mi-triangle domain: ~280 us of a 1.06 ms commit).  Here: count the valence, hand every vertex a
+// segment (block scan + one atomic per 1024 vertices: segments need no particular order), scatter the face ids with
+// per-vertex atomics (arbitrary order), and let the summing thread sort its own short list (valence <= 32: insertion
+// sort in local memory; heavier vertices — the apex of a fan — go to a list worked off by one CTA each with an
+// all-ascending bitonic network in place).  Same faces, same order, bit-identical sums.
+// ------------------------------------------------------------------------------------------------
+#define NRM_LIGHT_MAX 32
+__global__ void vcount_kernel(const uint32_t* __restrict__ faces, int npairs, uint32_t* __restrict__ vcnt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < npairs) atomicAdd(&vcnt[faces[i]], 1u);
 }
-
-__global__ void segments_kernel(const uint32_t* __restrict__ skeys, int npairs, uint32_t* __restrict__ vstart,
-                                uint32_t* __restrict__ vend) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= npairs) return;
-  uint32_t k = skeys[i];
-  if (i == 0 || skeys[i - 1] != k) vstart[k] = (uint32_t)i;
-  if (i == npairs - 1 || skeys[i + 1] != k) vend[k] = (uint32_t)i + 1u;
+__global__ void __launch_bounds__(1024) valloc_kernel(const uint32_t* __restrict__ vcnt, size_t nv, uint32_t* __restrict__ vstart,
+                                                      unsigned int* __restrict__ cursor) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t base_s;
+  const size_t v = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const uint32_t c = v < nv ? vcnt[v] : 0u;
+  uint32_t inc = c;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, inc, off);
+    if (lane >= off) inc += o;
+  }
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t w = wsum[lane];
+    uint32_t wi = w;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, wi, off);
+      if (lane >= off) wi += o;
+    }
+    wsum[lane] = wi - w;
+    if (lane == 31) base_s = wi ? atomicAdd(cursor, wi) : 0u;
+  }
+  __syncthreads();
+  if (v < nv) vstart[v] = base_s + wsum[warp] + inc - c;
 }
-
-// TriMeshBuffer::computeNormals, trimesh_buffer.cc:267-326.  The reference adds face normals to a
-// vertex in increasing face order; the stable sort preserved that order, so each vertex's float sum is
-// bit-identical to the serial loop.
-__global__ void normals_kernel(const float* __restrict__ verts, const uint32_t* __restrict__ faces,
-                               const uint32_t* __restrict__ sfaces, const uint32_t* __restrict__ vstart,
-                               const uint32_t* __restrict__ vend, float* __restrict__ normals, size_t nv) {
-  size_t v = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+__global__ void vfill_kernel(const uint32_t* __restrict__ faces, int npairs, const uint32_t* __restrict__ vstart,
+                             uint32_t* __restrict__ vfill, uint32_t* __restrict__ vlist) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npairs) return;
+  const uint32_t v = faces[i];
+  vlist[vstart[v] + atomicAdd(&vfill[v], 1u)] = (uint32_t)i / 3u;
+}
+__device__ __forceinline__ void face_normal(const float* __restrict__ verts, const uint32_t* __restrict__ faces, uint32_t f, float* fx,
+                                            float* fy, float* fz) {
+  const uint32_t i0 = faces[3 * (size_t)f], i1 = faces[3 * (size_t)f + 1], i2 = faces[3 * (size_t)f + 2];
+  const vec3 v0 = mk3(verts[3 * (size_t)i0], verts[3 * (size_t)i0 + 1], verts[3 * (size_t)i0 + 2]);
+  const vec3 v1 = mk3(verts[3 * (size_t)i1], verts[3 * (size_t)i1 + 1], verts[3 * (size_t)i1 + 2]);
+  const vec3 v2 = mk3(verts[3 * (size_t)i2], verts[3 * (size_t)i2 + 1], verts[3 * (size_t)i2 + 2]);
+  const vec3 u = gsub(v1, v0), w = gsub(v2, v0);
+  *fx = sub_rn(mul_rn(u.y, w.z), mul_rn(u.z, w.y));
+  *fy = sub_rn(mul_rn(u.z, w.x), mul_rn(u.x, w.z));
+  *fz = sub_rn(mul_rn(u.x, w.y), mul_rn(u.y, w.x));
+}
+__global__ void normals_light_kernel(const float* __restrict__ verts, const uint32_t* __restrict__ faces,
+                                     const uint32_t* __restrict__ vlist, const uint32_t* __restrict__ vstart,
+                                     const uint32_t* __restrict__ vcnt, float* __restrict__ normals, size_t nv,
+                                     uint32_t* __restrict__ heavy, unsigned int* __restrict__ heavy_n) {
+  const size_t v = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (v >= nv) return;
+  const uint32_t d = vcnt[v], b = vstart[v];
+  if (d > NRM_LIGHT_MAX) { heavy[atomicAdd(heavy_n, 1u)] = (uint32_t)v; return; }
+  uint32_t fl[NRM_LIGHT_MAX];
+  for (uint32_t k = 0; k < d; ++k) {           // insertion sort while loading
+    const uint32_t f = vlist[b + k];
+    uint32_t j = k;
+    while (j > 0 && fl[j - 1] > f) { fl[j] = fl[j - 1]; --j; }
+    fl[j] = f;
+  }
   float nx = 0.0f, ny = 0.0f, nz = 0.0f;
-  const uint32_t b = vstart[v], e = vend[v];
-  for (uint32_t i = b; i < e; ++i) {
-    const uint32_t f = sfaces[i];
-    const uint32_t i0 = faces[3 * (size_t)f], i1 = faces[3 * (size_t)f + 1], i2 = faces[3 * (size_t)f + 2];
-    vec3 v0 = mk3(verts[3 * (size_t)i0], verts[3 * (size_t)i0 + 1], verts[3 * (size_t)i0 + 2]);
-    vec3 v1 = mk3(verts[3 * (size_t)i1], verts[3 * (size_t)i1 + 1], verts[3 * (size_t)i1 + 2]);
-    vec3 v2 = mk3(verts[3 * (size_t)i2], verts[3 * (size_t)i2 + 1], verts[3 * (size_t)i2 + 2]);
-    vec3 u = gsub(v1, v0), w = gsub(v2, v0);
-    float fx = sub_rn(mul_rn(u.y, w.z), mul_rn(u.z, w.y));
-    float fy = sub_rn(mul_rn(u.z, w.x), mul_rn(u.x, w.z));
-    float fz = sub_rn(mul_rn(u.x, w.y), mul_rn(u.y, w.x));
+  for (uint32_t k = 0; k < d; ++k) {
+    float fx, fy, fz;
+    face_normal(verts, faces, fl[k], &fx, &fy, &fz);
     nx = add_rn(nx, fx); ny = add_rn(ny, fy); nz = add_rn(nz, fz);
   }
   normals[3 * v] = nx; normals[3 * v + 1] = ny; normals[3 * v + 2] = nz;
+}
+// one CTA per heavy vertex: sort its face list in place (bitonic network with every comparator ascending, so the virtual
+// +inf padding up to the next power of two never moves), then sum in order — face normals in parallel per 256-entry
+// chunk, the additions by one thread (the order IS the result)
+__global__ void __launch_bounds__(256) normals_heavy_kernel(const float* __restrict__ verts, const uint32_t* __restrict__ faces,
+                                                            uint32_t* __restrict__ vlist, const uint32_t* __restrict__ vstart,
+                                                            const uint32_t* __restrict__ vcnt, float* __restrict__ normals,
+                                                            const uint32_t* __restrict__ heavy, const unsigned int* __restrict__ heavy_n) {
+  __shared__ float fn[256][3];
+  const unsigned int nh = *heavy_n;
+  for (unsigned int h = blockIdx.x; h < nh; h += gridDim.x) {
+    const uint32_t v = heavy[h], d = vcnt[v];
+    uint32_t* a = vlist + vstart[v];
+    uint32_t P = 1;
+    while (P < d) P <<= 1;
+    for (uint32_t k = 2; k <= P; k <<= 1) {
+      for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+        for (uint32_t i = threadIdx.x; i < d; i += blockDim.x) {
+          const uint32_t l = (j == (k >> 1)) ? (i ^ (k - 1)) : (i ^ j);
+          if (l > i && l < d) {
+            const uint32_t x = a[i], y = a[l];
+            if (x > y) { a[i] = y; a[l] = x; }
+          }
+        }
+        __syncthreads();
+      }
+    }
+    float nx = 0.0f, ny = 0.0f, nz = 0.0f;
+    for (uint32_t c0 = 0; c0 < d; c0 += 256) {
+      const uint32_t k = c0 + threadIdx.x;
+      if (k < d) face_normal(verts, faces, a[k], &fn[threadIdx.x][0], &fn[threadIdx.x][1], &fn[threadIdx.x][2]);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        const uint32_t m = min(256u, d - c0);
+        for (uint32_t q = 0; q < m; ++q) { nx = add_rn(nx, fn[q][0]); ny = add_rn(ny, fn[q][1]); nz = add_rn(nz, fn[q][2]); }
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) { normals[3 * (size_t)v] = nx; normals[3 * (size_t)v + 1] = ny; normals[3 * (size_t)v + 2] = nz; }
+    __syncthreads();
+  }
 }
 
 __device__ __forceinline__ void atomic_min_f(uint32_t* a, float v) { atomicMin(a, float_sortable(v)); }
@@ -622,7 +707,7 @@ __global__ void fill_u32_kernel(uint32_t* p, uint32_t v, size_t n) {
 }
 
 // largest vertex index of the face list (spraygpu_scene_set_mesh validates it against nv: an out-of-range index of
-// a malformed / truncated PLY would otherwise become out-of-bounds device WRITES in segments_kernel at commit)
+// a malformed / truncated PLY would otherwise become out-of-bounds device WRITES in vcount_kernel at commit)
 __global__ void __launch_bounds__(256) max_index_kernel(const uint32_t* __restrict__ idx, size_t n, uint32_t* __restrict__ out) {
   uint32_t m = 0u;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) m = max(m, idx[i]);
@@ -711,7 +796,7 @@ int build_scene(Scene* sc) {
   // ---- scratch carve (two passes: size, then pointers)
   const int items_min = std::min(rs_items_for(npairs, dev->sm_count), rs_items_for(n, dev->sm_count));
   const int nblocks_max = (npairs + RS_THREADS * items_min - 1) / (RS_THREADS * items_min);
-  uint32_t *kA, *kB, *vA, *vB, *hist, *vstart, *vend, *bounds, *tri_prim;
+  uint32_t *kA, *kB, *vA, *vB, *hist, *vstart, *vend, *vcnt_buf, *bounds, *tri_prim;
   unsigned int* counters;
   float *tlo, *thi, *llo, *lhi, *blo, *bhi;
   int *bl, *br, *bfirst, *blast, *parent, *flags, *queue;
@@ -720,7 +805,7 @@ int build_scene(Scene* sc) {
     kA = c.take<uint32_t>(npairs); kB = c.take<uint32_t>(npairs);
     vA = c.take<uint32_t>(npairs); vB = c.take<uint32_t>(npairs);
     hist = c.take<uint32_t>((size_t)256 * nblocks_max + 1024);
-    vstart = c.take<uint32_t>(nv); vend = c.take<uint32_t>(nv);
+    vstart = c.take<uint32_t>(nv); vend = c.take<uint32_t>(nv); vcnt_buf = c.take<uint32_t>(nv);
     bounds = c.take<uint32_t>(12); counters = c.take<unsigned int>(8);
     tlo = c.take<float>(3 * nf); thi = c.take<float>(3 * nf);
     llo = c.take<float>(3 * nf); lhi = c.take<float>(3 * nf);
@@ -745,18 +830,24 @@ int build_scene(Scene* sc) {
     transform_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts_obj, sc->d_verts, nv, M);
     dev->launches++;
   }
-  // ---- normals (deterministic order)
-  pairs_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, kA, vA, npairs);
-  dev->launches++;
-  int vbits = 1; while (((size_t)1 << vbits) < nv) ++vbits;
-  rc = radix_sort(dev, st, &kA, &vA, &kB, &vB, hist, npairs, vbits);
-  if (rc) return rc;
-  SG_CUDA(cudaMemsetAsync(vstart, 0, sizeof(uint32_t) * nv, st));
-  SG_CUDA(cudaMemsetAsync(vend, 0, sizeof(uint32_t) * nv, st));
-  segments_kernel<<<grid_for(npairs, T), T, 0, st>>>(kA, npairs, vstart, vend);
-  normals_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts, sc->d_faces, vA, vstart, vend, sc->d_normals, nv);
-  attr_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_faces, sc->d_normals, sc->d_rgb, n, sc->d_attr);
-  dev->launches += 3;
+  // ---- normals: valence count -> segments -> face lists -> per-vertex sorted sums (no global sort)
+  SG_CUDA(cudaMemsetAsync(vend, 0, sizeof(uint32_t) * nv, st));        // vend = per-vertex fill cursor
+  SG_CUDA(cudaMemsetAsync(vcnt_buf, 0, sizeof(uint32_t) * nv, st));    // valence
+  SG_CUDA(cudaMemsetAsync(counters + 5, 0, sizeof(unsigned int) * 2, st));   // [5] segment cursor, [6] heavy vertices
+  {
+    uint32_t* vcnt = vcnt_buf;
+    uint32_t* vlist = kA;                 // npairs face ids, grouped by vertex
+    uint32_t* heavy = vB;                 // vertices with more than NRM_LIGHT_MAX faces (at most npairs / 33)
+    vcount_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vcnt);
+    valloc_kernel<<<grid_for(nv, 1024), 1024, 0, st>>>(vcnt, nv, vstart, counters + 5);
+    vfill_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vstart, vend, vlist);
+    normals_light_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, nv, heavy,
+                                                        counters + 6);
+    normals_heavy_kernel<<<std::min(dev->sm_count * 4, npairs / (NRM_LIGHT_MAX + 1) + 1), 256, 0, st>>>(
+        sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, heavy, counters + 6);
+    attr_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_faces, sc->d_normals, sc->d_rgb, n, sc->d_attr);
+    dev->launches += 6;
+  }
 
   // ---- triangle boxes, Morton keys, sort
   tri_bounds_kernel<<<std::min(grid_for(nf, 256), dev->sm_count * 8), 256, 0, st>>>(sc->d_verts, sc->d_faces, n, tlo, thi, bounds);

@@ -80,6 +80,24 @@ def rects_of_blocks(block_begin, block_owner, rank, blocking_tiles):
     return rects, parents
 
 
+def scatter_partition(world_bounds, scene_bounds, nranks):
+    """View-independent spreading of the domains over the ranks (NOT in the reference; an experiment for the in-situ load
+    imbalance): the reference's partitions follow the Morton order — contiguous runs put all
+    camera-facing domains on few ranks, and dealing round-robin over the Morton order is, on a 2^k grid, the parity
+    partition (one rank owns every all-odd cell).  Here the Morton-sorted domains are dealt in the order of a fixed
+    multiplicative hash of their Morton rank, nd / nranks each."""
+    d2r, codes = capi.partition_domains(world_bounds, scene_bounds, 1, False, return_codes=True)
+    order = np.argsort(codes, kind="stable")
+    nd = len(order)
+    h = (np.arange(nd, dtype=np.uint64) * np.uint64(2654435761) + np.uint64(40503)) % np.uint64(1 << 32)
+    h = ((h >> np.uint64(13)) ^ h) * np.uint64(0x5bd1e995) % np.uint64(1 << 32)
+    deal = np.argsort(h, kind="stable")                   # position in the deal of Morton rank j
+    out = np.zeros(nd, np.int32)
+    for pos, j in enumerate(deal):
+        out[order[j]] = pos % nranks
+    return out
+
+
 def bootstrap_comm(dev, rank, world):
     """Create the library's NCCL communicator; the unique id travels over torch.distributed."""
     import torch.distributed as dist
@@ -150,6 +168,8 @@ class InsituRenderer:
         self.mode, self.rpb = mode, int(rows_per_block)
         wb = np.stack([d["bounds"] for d in scene["domains"]])
         self.domain_to_rank = capi.partition_domains(wb, scenes.scene_bounds(scene), world, round_robin)
+        if os.environ.get("SPRAY_INSITU_PART", "") == "scatter" and world > 1:
+            self.domain_to_rank = scatter_partition(wb, scenes.scene_bounds(scene), world)
         self.owned = [i for i, r in enumerate(self.domain_to_rank) if r == rank]
         dev.load_scene(scene, owned=self.owned)
         if max_tile_samples is None:

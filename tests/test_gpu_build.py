@@ -117,3 +117,47 @@ def test_commit_async_then_trace(oracle):
     dev.intersect_domains(rays, len(rays), keys, None)
     assert np.array_equal(keys, ko)
     dev.close()
+
+
+def test_normals_of_high_valence_vertices_bit_exact(oracle):
+    """computeNormals (trimesh_buffer.cc:267-326) sums a vertex's face normals in increasing face order.  The commit
+    gathers each vertex's faces with atomics (arbitrary order) and sorts them per vertex: in local memory up to 32
+    faces, with a block-wide bitonic network beyond — a fan whose hub has 5 000 faces, rims of 32 / 33 / 100 faces, a
+    face that names the same vertex twice."""
+    rng = np.random.default_rng(12)
+    verts = [np.zeros(3, np.float32)]
+    faces = []
+
+    def fan(hub, nfaces, centre, radius):
+        base = len(verts)
+        ang = np.sort(rng.uniform(0, 2 * np.pi, nfaces + 1))
+        for a in ang:
+            verts.append(np.asarray(centre, np.float32) + np.float32(radius) * np.array([np.cos(a), np.sin(a), rng.uniform(-0.2, 0.2)], np.float32))
+        for k in range(nfaces):
+            faces.append((hub, base + k, base + k + 1))
+
+    fan(0, 5000, (0, 0, 0), 7.0)
+    for nf_, c in ((32, (20, 0, 0)), (33, (0, 20, 0)), (100, (20, 20, 0)), (1, (40, 0, 0))):
+        verts.append(np.asarray(c, np.float32) + np.float32(0.5))
+        fan(len(verts) - 1, nf_, c, 3.0)
+    faces.append((0, 0, 5))                                  # degenerate: the hub twice
+    v = np.asarray(verts, np.float32)
+    f = np.asarray(faces, np.uint32)
+    perm = rng.permutation(len(f))                           # face order = summation order: shuffle it
+    f = np.ascontiguousarray(f[perm])
+    lo, hi = v.min(0) - 1, v.max(0) + 1
+    dom = dict(verts=v, faces=f, rgb=None, transform=None, bounds=np.concatenate([lo, hi]).astype(np.float32))
+    osc = oracle.Scene([dom])
+    dev = capi.Device(0)
+    dev.set_domains([dom["bounds"]], [(0, (1, 1, 1))])
+    s = dev.new_scene()
+    s.set_mesh(v, f, None)
+    for _ in range(2):                                       # twice: the atomics order the lists differently each time
+        s.commit()
+        assert np.array_equal(s.normals(), osc.normals(0))
+    dev.bind(0, s)
+    rays = random_rays(5000, lo, hi, seed=4)
+    keys = np.zeros(len(rays), np.uint64)
+    dev.intersect_domains(rays, len(rays), keys, None)
+    assert np.array_equal(keys, osc.intersect(rays)[0])
+    dev.close()
