@@ -131,6 +131,8 @@ _PROTOS = {
     "spraygpu_image_root": (_vp, [_vp]),
     "spraygpu_image_set_rows": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "spraygpu_image_flush": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "spraygpu_image_flush_async": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "spraygpu_image_wait": (C.c_int, [_vp]),
     "spraygpu_image_flushed_pixels": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "spraygpu_image_barrier": (C.c_int, [_vp]),
     "spraygpu_image_read": (C.c_int, [_vp, C.c_int, _vp]),
@@ -518,6 +520,16 @@ class Image:
 
     def flush(self, to_root=False, to_host=False, clear=True):
         _check(lib().spraygpu_image_flush(self.h_, int(to_root), int(to_host), int(clear)))
+
+    def flush_async(self, to_root=False, to_host=False):
+        """Flush + clear on the image's own stream, overlapped with the next frame; `device` switches to the other target."""
+        _check(lib().spraygpu_image_flush_async(self.h_, int(to_root), int(to_host)))
+        self.device = lib().spraygpu_image_device(self.h_)
+        if self.comm is None or self.comm.nranks == 1:
+            self.root = lib().spraygpu_image_root(self.h_)
+
+    def wait(self):
+        _check(lib().spraygpu_image_wait(self.h_))
 
     def flushed_pixels(self):
         a, b = C.c_uint64(), C.c_uint64()

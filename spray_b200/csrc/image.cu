@@ -40,7 +40,14 @@ struct Image {
   Device* dev = nullptr;
   Comm* comm = nullptr;
   int w = 0, h = 0, rank = 0, nranks = 1, root = 0;
-  float4* d_target = nullptr;          // this rank's render target
+  float4* d_target = nullptr;          // this rank's CURRENT render target (= d_targets[cur])
+  // spraygpu_image_flush_async: two targets — frame k is flushed (and cleared) on `flush_stream` while frame k + 1 is
+  // traced into the other one on the device's stream
+  float4* d_targets[2] = {nullptr, nullptr};
+  int cur = 0;
+  cudaStream_t flush_stream = nullptr;
+  cudaEvent_t ev_trace = nullptr, ev_flush[2] = {nullptr, nullptr};
+  bool flushed_once[2] = {false, false};
   float4* d_root_local = nullptr;      // root: the composite image (peer-mapped into every rank); others: nullptr
   std::vector<void*> root_mapped;      // [nranks] mappings of every rank's shared buffer; [root] is the composite
   float4* h_image = nullptr;           // pinned host image (private cudaHostAlloc, or shared memory + cudaHostRegister)
@@ -125,6 +132,7 @@ int spraygpu_image_create(spraygpu_device dev_h, spraygpu_comm comm_h, int image
         cudaMalloc((void**)&im->d_prev_host, words * 4) != cudaSuccess || cudaMalloc((void**)&im->d_flushed, 16) != cudaSuccess) {
       set_error("image_create: device allocation failed: %s", cudaGetErrorString(cudaGetLastError())); rc = SPRAYGPU_ERR_CUDA; break;
     }
+    im->d_targets[0] = im->d_target;
     cudaMemsetAsync(im->d_target, 0, im->bytes, dev->stream);
     cudaMemsetAsync(im->d_prev_root, 0, words * 4, dev->stream);
     cudaMemsetAsync(im->d_prev_host, 0, words * 4, dev->stream);
@@ -185,6 +193,7 @@ int spraygpu_image_destroy(spraygpu_image img) {
     comm_host_barrier(im->comm);       // nobody is still storing through a mapping that is about to go away
     comm_shared_free(im->comm, im->d_root_local, &im->root_mapped);
   }
+  if (im->flush_stream) cudaStreamSynchronize(im->flush_stream);
   if (im->h_image) {
     if (!im->shm_name.empty()) {
       cudaHostUnregister(im->h_image);
@@ -192,7 +201,12 @@ int spraygpu_image_destroy(spraygpu_image img) {
       if (im->shm_owner) shm_unlink(im->shm_name.c_str());
     } else cudaFreeHost(im->h_image);
   }
-  if (im->d_target) cudaFree(im->d_target);
+  if (im->flush_stream) { cudaStreamSynchronize(im->flush_stream); cudaStreamDestroy(im->flush_stream); }
+  if (im->ev_trace) cudaEventDestroy(im->ev_trace);
+  for (int k = 0; k < 2; ++k) {
+    if (im->ev_flush[k]) cudaEventDestroy(im->ev_flush[k]);
+    if (im->d_targets[k]) cudaFree(im->d_targets[k]);
+  }
   if (im->d_prev_root) cudaFree(im->d_prev_root);
   if (im->d_prev_host) cudaFree(im->d_prev_host);
   if (im->d_flushed) cudaFree(im->d_flushed);
@@ -236,11 +250,7 @@ int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_
   return SPRAYGPU_OK;
 }
 
-int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear) {
-  SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_flush: img is NULL");
-  Image* im = (Image*)img;
-  if (!im->nmy) return SPRAYGPU_OK;
-  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+static int image_launch_flush(Image* im, float4* target, int to_root, int to_host, int clear, cudaStream_t st, int threads) {
   float4* root = nullptr;
   if (to_root && im->nranks > 1) root = (float4*)im->root_mapped[(size_t)im->root];
   float4* host = to_host ? im->h_image_dev : nullptr;
@@ -249,10 +259,61 @@ int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear
   // ~2 warps of work per 256-thread block pass; enough blocks to cover the SMs, a grid-stride loop does the rest
   int gx = (int)std::min<size_t>((max_pix + 1023) / 1024, (size_t)std::max(1, im->dev->sm_count * 8 / std::max(im->nmy, 1)));
   if (gx < 1) gx = 1;
-  image_flush_kernel<<<dim3((unsigned)gx, (unsigned)im->nmy), 256, 0, im->dev->stream>>>(
-      im->d_target, root, host, im->d_prev_root, im->d_prev_host, im->d_blocks, im->w, clear, im->d_flushed);
+  image_flush_kernel<<<dim3((unsigned)gx, (unsigned)im->nmy), threads, 0, st>>>(
+      target, root, host, im->d_prev_root, im->d_prev_host, im->d_blocks, im->w, clear, im->d_flushed);
   im->dev->launches++;
   SG_CUDA(cudaGetLastError());
+  return SPRAYGPU_OK;
+}
+
+int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear) {
+  SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_flush: img is NULL");
+  Image* im = (Image*)img;
+  if (!im->nmy) return SPRAYGPU_OK;
+  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));   // the bitmaps are shared with pending async flushes
+  return image_launch_flush(im, im->d_target, to_root, to_host, clear, im->dev->stream, 256);
+}
+
+// Frame-level double buffering: the flush of the frame just traced runs on its own (high-priority) stream with
+// 128-thread CTAs of 30 registers — they fit beside the five resident CTAs of the persistent render kernel on every
+// SM — so its PCIe / NVLink stores overlap the NEXT frame's trace, which goes to the other render target.  The target
+// is always cleared (it is traced into again two frames later).
+int spraygpu_image_flush_async(spraygpu_image img, int to_root, int to_host) {
+  SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_flush_async: img is NULL");
+  Image* im = (Image*)img;
+  Device* dev = im->dev;
+  SG_CUDA(cudaSetDevice(dev->cuda_device));
+  if (!im->flush_stream) {
+    int lo = 0, hi = 0;
+    SG_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    SG_CUDA(cudaStreamCreateWithPriority(&im->flush_stream, cudaStreamNonBlocking, hi));
+    SG_CUDA(cudaEventCreateWithFlags(&im->ev_trace, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k) SG_CUDA(cudaEventCreateWithFlags(&im->ev_flush[k], cudaEventDisableTiming));
+    SG_CUDA(cudaMalloc((void**)&im->d_targets[1], im->bytes));
+    SG_CUDA(cudaMemsetAsync(im->d_targets[1], 0, im->bytes, dev->stream));
+  }
+  SG_CUDA(cudaEventRecord(im->ev_trace, dev->stream));
+  SG_CUDA(cudaStreamWaitEvent(im->flush_stream, im->ev_trace, 0));
+  if (im->nmy) {
+    int rc = image_launch_flush(im, im->d_targets[im->cur], to_root, to_host, 1, im->flush_stream, 128);
+    if (rc) return rc;
+  }
+  SG_CUDA(cudaEventRecord(im->ev_flush[im->cur], im->flush_stream));
+  im->flushed_once[im->cur] = true;
+  im->cur ^= 1;
+  im->d_target = im->d_targets[im->cur];
+  // the next frame is traced into the other target: its own flush (two frames ago) must have cleared it
+  if (im->flushed_once[im->cur]) SG_CUDA(cudaStreamWaitEvent(dev->stream, im->ev_flush[im->cur], 0));
+  return SPRAYGPU_OK;
+}
+
+// host wait: every flush issued so far has landed (the host image holds the last flushed frame)
+int spraygpu_image_wait(spraygpu_image img) {
+  SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_wait: img is NULL");
+  Image* im = (Image*)img;
+  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
   return SPRAYGPU_OK;
 }
 
@@ -260,6 +321,7 @@ int spraygpu_image_flushed_pixels(spraygpu_image img, uint64_t* to_root, uint64_
   SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_flushed_pixels: img is NULL");
   Image* im = (Image*)img;
   SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
   unsigned long long h[2] = {0, 0};
   SG_CUDA(cudaMemcpyAsync(h, im->d_flushed, sizeof(h), cudaMemcpyDeviceToHost, im->dev->stream));
   SG_CUDA(cudaStreamSynchronize(im->dev->stream));
@@ -284,6 +346,7 @@ int spraygpu_image_barrier(spraygpu_image img) {
   Image* im = (Image*)img;
   SG_CUDA(cudaSetDevice(im->dev->cuda_device));
   SG_CUDA(cudaStreamSynchronize(im->dev->stream));
+  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
   if (im->comm) return comm_host_barrier(im->comm);
   return SPRAYGPU_OK;
 }

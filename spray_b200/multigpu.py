@@ -141,6 +141,12 @@ class ImagePartitionRenderer:
         self.image.flush(to_root=False, to_host=True, clear=True)
         self.dev.synchronize()
 
+    def frame_host_async(self):
+        """frame_host without the per-frame synchronize: this frame's rows are stored into the host image on the image's
+        own stream while the next frame is traced into the second render target (spraygpu_image_flush_async)."""
+        self.dev.trace_frame_rects(self.cam, self.shade, self.rects, self.parents, self.image.device)
+        self.image.flush_async(to_host=True)
+
     def count_rays(self):
         """Deterministic per-frame ray counts, summed over the ranks (one extra frame with stats)."""
         st = self._trace(stats=True).as_dict()
@@ -305,6 +311,12 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
     if mode == "image":
         r = ImagePartitionRenderer(dev, sc, cam, sh, W, H, rank, world, comm, shm_name=shm)
         st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
+        # pipelined e2e: frame k's rows cross PCIe while frame k + 1 is traced (one bracket around all frames, L2 fills inside)
+        ms_e2e_sync = ms_e2e
+        ms_e2e_pipe = timer.pipelined(r.frame_host_async, r.image.wait, max(args.steps, 5), 3)
+        r.image.wait()
+        e2e_pipelined = ms_e2e_pipe <= ms_e2e
+        ms_e2e = min(ms_e2e, ms_e2e_pipe)
         # ---- parity_check (outside the timed region): one more frame on all ranks, then rank 0 renders the whole
         # frame alone and compares with its composite; the host image of the e2e path must equal the composite too
         r.image.barrier()
@@ -432,9 +444,14 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
                         "d2h_bytes_per_step": int(W * H * 16)}}
         if fp is not None:
             # the flush is sparse: pixels that are (or were) non-zero; report what actually crossed PCIe per e2e frame
-            e2e_frames = max(args.steps // 2, 3) + 2 + 1
+            e2e_frames = max(args.steps // 2, 3) + 2 + 1 + ((max(args.steps, 5) + 3) if mode == "image" else 0)
             line["e2e"]["d2h_bytes_per_step"] = int(fp["host"] * 16 // e2e_frames)
             line["e2e"]["d2h_note"] = "sparse flush: only pixels that are or were non-zero are stored to the host image (full frame = %d B)" % (W * H * 16)
+        if mode == "image":
+            line["e2e"]["mode"] = ("pipelined frames (spraygpu_image_flush_async: frame k's rows cross PCIe while frame k + 1 is traced; one "
+                                   "bracket around all frames, L2 fills and the final host wait inside)" if e2e_pipelined else "one frame at a time")
+            line["e2e"]["per_frame_sync"] = {"value": rays / (ms_e2e_sync * 1e-3) / 1e6, "ms_per_step": ms_e2e_sync}
+            line["e2e"]["pipelined_ms_per_step_incl_l2_fill"] = ms_e2e_pipe
         if insitu_extra:
             line["insitu"] = insitu_extra
         if mode != "image":

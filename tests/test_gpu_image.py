@@ -61,6 +61,48 @@ def test_image_flush_to_host_is_exact_and_sparse():
     img.close(); dev.close()
 
 
+def test_image_flush_async_pipelines_frames_exactly():
+    """spraygpu_image_flush_async: frame k is flushed (and its target cleared) on the image's own stream while frame
+    k + 1 is traced into the second render target.  Frames from different cameras, several rounds through both
+    targets: after spraygpu_image_wait the host image is exactly the last frame, and both targets end up cleared."""
+    sc = scenes.wavelets64(8)
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    W, H = 256, 160
+    kw = dict(bounces=1, pixel_samples=1, **scenes.WAVELETS64_BLINN)
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    shifts = ([0, 0, 0], [25, 10, 0], [-40, -5, 30], [10, -20, 5], [0, 0, 0], [-15, 25, -10], [5, 5, 5])
+    # references: each frame on its own, synchronously
+    ref_img = capi.Image(dev, None, W, H)
+    want = []
+    for sft in shifts:
+        cd = scenes.camera_frame(pos + np.array(sft, np.float32), lookat, up, 90.0, W, H)
+        _frame(dev, sc, cd, kw, ref_img.device)
+        want.append(ref_img.read_device("device"))
+        ref_img.flush(clear=True)
+    assert not np.array_equal(want[0], want[1])
+    img = capi.Image(dev, None, W, H)
+    targets = set()
+    for k, sft in enumerate(shifts):
+        cd = scenes.camera_frame(pos + np.array(sft, np.float32), lookat, up, 90.0, W, H)
+        targets.add(int(img.device))
+        _frame(dev, sc, cd, kw, img.device)
+        img.flush_async(to_host=True)                # returns at once; the next frame goes to the other target
+        if k in (2, 5, 6):                           # look at some frames, let the others stream through
+            img.wait()
+            assert np.array_equal(img.host, want[k]), k
+    assert len(targets) == 2
+    img.wait(); dev.synchronize()
+    assert not img.read_device("device").any()       # the current target was cleared by its own flush two frames ago
+    # mixing in a synchronous flush afterwards still works on the current target
+    cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+    _frame(dev, sc, cd, kw, img.device)
+    img.flush(to_host=True, clear=True)
+    dev.synchronize()
+    assert np.array_equal(img.host, want[0])
+    img.close(); ref_img.close(); dev.close()
+
+
 def test_trace_frame_rects_equals_whole_tiles(oracle):
     """Rectangles of blocking tiles keep their blocking tile's sample ids: any cut of the frame into rectangles gives the
     image of the uncut frame (bit-identical at 1 spp / 1 bounce, same ray counts and RMSE <= 1e-4 vs the oracle at
