@@ -311,8 +311,9 @@ def single_gpu(name, dev, stream, timer, steps, warmup, with_e2e=True):
         out["ms_e2e"], _ = timer(step_e2e, n_e2e, 2)
         _, pix = img.flushed_pixels()
 
-        # the same frames back to back, frame k's flush (spraygpu_image_flush_async, its own stream, second render target)
-        # overlapping frame k + 1's trace; one bracket around all of them, L2 fills and the final host wait inside
+        # the same frames back to back, frame k's PCIe stores (spraygpu_image_flush_async: compact list, a few CTAs on the
+        # image's own stream) overlapping frame k + 1's trace; one bracket around all of them, L2 fills and the final host
+        # wait inside
         def step_pipe():
             dev.trace_frame(cam, sh, tiles, img.device)
             img.flush_async(to_host=True)
@@ -467,9 +468,9 @@ def main():
             "clocks": clocks, "gpu_launches": int(r["launches"]),
             "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"],
-                    "mode": "pipelined frames: spraygpu_image_flush_async stores frame k into the pinned host image on its own stream while "
-                            "frame k + 1 is traced into the second render target; one event bracket around all frames, the L2 fills "
-                            "between frames and the final host wait INSIDE it" if r["ms_e2e_pipe"] <= r["ms_e2e"] else "one frame at a time",
+                    "mode": "pipelined frames: spraygpu_image_flush_async compacts frame k's pixels on the device and a few CTAs on the image's "
+                            "own stream store them into the pinned host image while frame k + 1 is traced; one event bracket around all "
+                            "frames, the L2 fills between frames and the final host wait INSIDE it" if r["ms_e2e_pipe"] <= r["ms_e2e"] else "one frame at a time",
                     "per_frame_sync": {"value": e2e_sync_v, "ms_per_step": r["ms_e2e"],
                                        "note": "trace, flush, host synchronize per frame (no overlap between frames); L2 fill outside the events"},
                     "pipelined_ms_per_step_incl_l2_fill": r["ms_e2e_pipe"],

@@ -343,11 +343,11 @@ SPRAYGPU_API int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const 
 /* HdrImage::composite (to_root) and/or the download into HdrImage::buf (to_host) for this rank's rows, then
  * image.clear() of the render target (clear).  Enqueued on the device's stream. */
 SPRAYGPU_API int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear);
-/* The same flush, OVERLAPPED with the next frame: it runs on its own stream (small CTAs that fit beside the persistent
- * render kernel's), the render target is always cleared, and spraygpu_image_device() switches to a second target, so
- * the caller's next spraygpu_trace_frame(..., spraygpu_image_device(img), ...) starts at once; the library orders the
- * re-use of a target behind its flush.  spraygpu_image_wait: host wait until every flush issued so far has landed
- * (renderFilm's loop, src/render/spray_renderer.inl:355-372, with composite() of frame k hidden behind trace() of k + 1). */
+/* The same flush (target always cleared), with the PCIe half OVERLAPPED with the next frame: on the device's stream the
+ * render target is scanned, root-bound pixels are pushed over NVLink, host-bound pixels are compacted into a device list;
+ * a few small CTAs on the image's own stream then stream that list into the pinned host image while the caller's next
+ * spraygpu_trace_frame runs.  spraygpu_image_wait: host wait until every flush issued so far has landed (renderFilm's
+ * loop, src/render/spray_renderer.inl:355-372, with composite() of frame k hidden behind trace() of frame k + 1). */
 SPRAYGPU_API int spraygpu_image_flush_async(spraygpu_image img, int to_root, int to_host);
 SPRAYGPU_API int spraygpu_image_wait(spraygpu_image img);
 /* cumulative pixels (16 B each) stored to the root composite / the host image by this rank's flushes */

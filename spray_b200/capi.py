@@ -522,11 +522,9 @@ class Image:
         _check(lib().spraygpu_image_flush(self.h_, int(to_root), int(to_host), int(clear)))
 
     def flush_async(self, to_root=False, to_host=False):
-        """Flush + clear on the image's own stream, overlapped with the next frame; `device` switches to the other target."""
+        """Flush + clear with the PCIe stores overlapped with the next frame (compaction on the device's stream, a few
+        CTAs on the image's own stream store the list into the host image)."""
         _check(lib().spraygpu_image_flush_async(self.h_, int(to_root), int(to_host)))
-        self.device = lib().spraygpu_image_device(self.h_)
-        if self.comm is None or self.comm.nranks == 1:
-            self.root = lib().spraygpu_image_root(self.h_)
 
     def wait(self):
         _check(lib().spraygpu_image_wait(self.h_))

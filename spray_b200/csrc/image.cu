@@ -40,14 +40,16 @@ struct Image {
   Device* dev = nullptr;
   Comm* comm = nullptr;
   int w = 0, h = 0, rank = 0, nranks = 1, root = 0;
-  float4* d_target = nullptr;          // this rank's CURRENT render target (= d_targets[cur])
-  // spraygpu_image_flush_async: two targets — frame k is flushed (and cleared) on `flush_stream` while frame k + 1 is
-  // traced into the other one on the device's stream
-  float4* d_targets[2] = {nullptr, nullptr};
+  float4* d_target = nullptr;          // this rank's render target
+  // spraygpu_image_flush_async: the host-bound pixels of frame k are COMPACTED on the device's stream (index + value
+  // lists, double-buffered) and stored into the host image by a few CTAs on `flush_stream` while frame k + 1 is traced
+  uint32_t* d_list_idx[2] = {nullptr, nullptr};
+  float4* d_list_val[2] = {nullptr, nullptr};
+  unsigned int* d_list_n = nullptr;    // [2] entries in each list
   int cur = 0;
   cudaStream_t flush_stream = nullptr;
-  cudaEvent_t ev_trace = nullptr, ev_flush[2] = {nullptr, nullptr};
-  bool flushed_once[2] = {false, false};
+  cudaEvent_t ev_compact = nullptr, ev_store[2] = {nullptr, nullptr};
+  bool stored_once[2] = {false, false};
   float4* d_root_local = nullptr;      // root: the composite image (peer-mapped into every rank); others: nullptr
   std::vector<void*> root_mapped;      // [nranks] mappings of every rank's shared buffer; [root] is the composite
   float4* h_image = nullptr;           // pinned host image (private cudaHostAlloc, or shared memory + cudaHostRegister)
@@ -64,46 +66,96 @@ struct Image {
   unsigned long long* d_flushed = nullptr;   // [0] pixels stored to root, [1] pixels stored to host (cumulative)
 };
 
-// One warp handles 32 consecutive pixels of a row block; the two "what the destination holds" bitmaps are read and
-// written one word per warp.
-__global__ void __launch_bounds__(256)
+// One warp handles FLUSH_GROUPS x 32 consecutive pixels of a row block per iteration: the loads of all groups are issued
+// before any is used, so a warp keeps FLUSH_GROUPS x 512 B in flight.  That matters for the overlapped flush
+// (spraygpu_image_flush_async), whose CTAs squeeze in beside the persistent render kernel — 3 warps per SM: with one
+// group per iteration the scan of a 64 MB target was latency-bound at 0.8 ms (r04p), longer than the frame it was
+// meant to hide behind.  The two "what the destination holds" bitmaps are read and written one word per group.
+#define FLUSH_GROUPS 4
+__global__ void __launch_bounds__(256, 4)
     image_flush_kernel(float4* __restrict__ target, float4* __restrict__ root, float4* __restrict__ host, uint32_t* __restrict__ prev_root,
                        uint32_t* __restrict__ prev_host, const int2* __restrict__ blocks, int image_w, int clear,
-                       unsigned long long* __restrict__ flushed) {
+                       unsigned long long* __restrict__ flushed, uint32_t* __restrict__ list_idx, float4* __restrict__ list_val,
+                       unsigned int* __restrict__ list_n) {
+  // list_idx != NULL: the host-bound pixels are appended to (list_idx, list_val) instead of being stored to `host`
+  // (image_store_kernel does that later); `host` then only says that the host image is a destination
   const int2 blk = blocks[blockIdx.y];
   const size_t npix = (size_t)blk.y * image_w;
   const size_t base = (size_t)blk.x * image_w;            // first pixel of the block: a multiple of 32 (image_w % 32 == 0)
   const int lane = threadIdx.x & 31;
-  for (size_t p0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) & ~(size_t)31; p0 < npix; p0 += (size_t)gridDim.x * blockDim.x) {
-    const size_t p = p0 + lane;
-    const bool in = p < npix;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (in) v = target[base + p];
-    const bool nz = in && (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f);
-    const uint32_t nzm = __ballot_sync(0xffffffffu, nz);
-    const size_t word = (base + p0) >> 5;                 // one bitmap word per 32-pixel group of the image
-    if (root) {
-      uint32_t pm = 0u;
-      if (lane == 0) pm = prev_root[word];
-      pm = __shfl_sync(0xffffffffu, pm, 0);
-      if (in && ((nzm | pm) >> lane & 1u)) root[base + p] = v;
-      if (lane == 0) {
-        if (pm != nzm) prev_root[word] = nzm;
-        if (flushed && (nzm | pm)) atomicAdd(flushed + 0, (unsigned long long)__popc(nzm | pm));
-      }
+  const size_t warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  unsigned long long n_root = 0, n_host = 0;
+  for (size_t p0 = warp * (32 * FLUSH_GROUPS); p0 < npix; p0 += warps * (32 * FLUSH_GROUPS)) {
+    float4 v[FLUSH_GROUPS];
+    uint32_t pr = 0u, ph = 0u;                              // lane g holds group g's bitmap words
+    const size_t word0 = (base + p0) >> 5;
+    if (lane < FLUSH_GROUPS && p0 + 32 * (size_t)lane < npix) {
+      if (root) pr = prev_root[word0 + lane];
+      if (host) ph = prev_host[word0 + lane];
     }
-    if (host) {
-      uint32_t pm = 0u;
-      if (lane == 0) pm = prev_host[word];
-      pm = __shfl_sync(0xffffffffu, pm, 0);
-      if (in && ((nzm | pm) >> lane & 1u)) host[base + p] = v;
-      if (lane == 0) {
-        if (pm != nzm) prev_host[word] = nzm;
-        if (flushed && (nzm | pm)) atomicAdd(flushed + 1, (unsigned long long)__popc(nzm | pm));
-      }
+#pragma unroll
+    for (int g = 0; g < FLUSH_GROUPS; ++g) {
+      const size_t p = p0 + 32 * (size_t)g + lane;
+      v[g] = p < npix ? target[base + p] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (clear && nz) target[base + p] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int g = 0; g < FLUSH_GROUPS; ++g) {
+      const size_t p = p0 + 32 * (size_t)g + lane;
+      const bool in = p < npix;
+      const bool nz = in && (v[g].x != 0.0f || v[g].y != 0.0f || v[g].z != 0.0f || v[g].w != 0.0f);
+      const uint32_t nzm = __ballot_sync(0xffffffffu, nz);
+      if (root) {
+        const uint32_t pm = __shfl_sync(0xffffffffu, pr, g);
+        if (in && ((nzm | pm) >> lane & 1u)) root[base + p] = v[g];
+        if (lane == 0 && (nzm | pm)) {
+          if (pm != nzm) prev_root[word0 + g] = nzm;
+          n_root += (unsigned long long)__popc(nzm | pm);
+        }
+      }
+      if (host) {
+        const uint32_t pm = __shfl_sync(0xffffffffu, ph, g);
+        const uint32_t m = nzm | pm;
+        if (list_idx) {
+          uint32_t slot = 0;
+          if (lane == 0 && m) slot = atomicAdd(list_n, (unsigned int)__popc(m));
+          slot = __shfl_sync(0xffffffffu, slot, 0);
+          if (in && (m >> lane & 1u)) {
+            const uint32_t e = slot + __popc(m & ((1u << lane) - 1u));
+            list_idx[e] = (uint32_t)(base + p);
+            list_val[e] = v[g];
+          }
+        } else if (in && (m >> lane & 1u)) host[base + p] = v[g];
+        if (lane == 0 && m) {
+          if (pm != nzm) prev_host[word0 + g] = nzm;
+          n_host += (unsigned long long)__popc(m);
+        }
+      }
+      if (clear && nz) target[base + p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
+  if (flushed && lane == 0) {
+    if (n_root) atomicAdd(flushed + 0, n_root);
+    if (n_host) atomicAdd(flushed + 1, n_host);
+  }
+}
+
+// The PCIe half of spraygpu_image_flush_async: a FEW CTAs stream the compact list into the pinned host image while the
+// next frame is traced.  Measured (tools/pipe_probe.py, r04r): when every SM carries a CTA that issues zero-copy stores
+// to system memory, the persistent render kernel beside it slows from 0.66 to 0.84 ms — PCIe back-pressure blocks the
+// SM's path to L2 for everybody on that SM — so the stores must come from few SMs, and the scan of the 64 MB target
+// (which needs all of them to be fast) is done separately, without stores, on the device's stream.
+__global__ void __launch_bounds__(64) image_store_kernel(const uint32_t* __restrict__ list_idx, const float4* __restrict__ list_val,
+                                                         const unsigned int* __restrict__ list_n, float4* __restrict__ host) {
+  const unsigned int n = *list_n;
+  const unsigned int stride = gridDim.x * blockDim.x;
+  unsigned int e = blockIdx.x * blockDim.x + threadIdx.x;
+  for (; e + 3 * stride < n; e += 4 * stride) {          // four independent 20-byte fetches in flight per lane
+    const uint32_t i0 = list_idx[e], i1 = list_idx[e + stride], i2 = list_idx[e + 2 * stride], i3 = list_idx[e + 3 * stride];
+    const float4 v0 = list_val[e], v1 = list_val[e + stride], v2 = list_val[e + 2 * stride], v3 = list_val[e + 3 * stride];
+    host[i0] = v0; host[i1] = v1; host[i2] = v2; host[i3] = v3;
+  }
+  for (; e < n; e += stride) host[list_idx[e]] = list_val[e];
 }
 
 }  // namespace spraygpu
@@ -132,7 +184,6 @@ int spraygpu_image_create(spraygpu_device dev_h, spraygpu_comm comm_h, int image
         cudaMalloc((void**)&im->d_prev_host, words * 4) != cudaSuccess || cudaMalloc((void**)&im->d_flushed, 16) != cudaSuccess) {
       set_error("image_create: device allocation failed: %s", cudaGetErrorString(cudaGetLastError())); rc = SPRAYGPU_ERR_CUDA; break;
     }
-    im->d_targets[0] = im->d_target;
     cudaMemsetAsync(im->d_target, 0, im->bytes, dev->stream);
     cudaMemsetAsync(im->d_prev_root, 0, words * 4, dev->stream);
     cudaMemsetAsync(im->d_prev_host, 0, words * 4, dev->stream);
@@ -202,11 +253,14 @@ int spraygpu_image_destroy(spraygpu_image img) {
     } else cudaFreeHost(im->h_image);
   }
   if (im->flush_stream) { cudaStreamSynchronize(im->flush_stream); cudaStreamDestroy(im->flush_stream); }
-  if (im->ev_trace) cudaEventDestroy(im->ev_trace);
+  if (im->ev_compact) cudaEventDestroy(im->ev_compact);
   for (int k = 0; k < 2; ++k) {
-    if (im->ev_flush[k]) cudaEventDestroy(im->ev_flush[k]);
-    if (im->d_targets[k]) cudaFree(im->d_targets[k]);
+    if (im->ev_store[k]) cudaEventDestroy(im->ev_store[k]);
+    if (im->d_list_idx[k]) cudaFree(im->d_list_idx[k]);
+    if (im->d_list_val[k]) cudaFree(im->d_list_val[k]);
   }
+  if (im->d_list_n) cudaFree(im->d_list_n);
+  if (im->d_target) cudaFree(im->d_target);
   if (im->d_prev_root) cudaFree(im->d_prev_root);
   if (im->d_prev_host) cudaFree(im->d_prev_host);
   if (im->d_flushed) cudaFree(im->d_flushed);
@@ -250,17 +304,21 @@ int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_
   return SPRAYGPU_OK;
 }
 
-static int image_launch_flush(Image* im, float4* target, int to_root, int to_host, int clear, cudaStream_t st, int threads) {
+static int image_launch_flush(Image* im, int to_root, int to_host, int clear, cudaStream_t st, int list /* -1: store directly */) {
   float4* root = nullptr;
   if (to_root && im->nranks > 1) root = (float4*)im->root_mapped[(size_t)im->root];
   float4* host = to_host ? im->h_image_dev : nullptr;
   if (!root && !host && !clear) return SPRAYGPU_OK;
   const size_t max_pix = (size_t)im->max_rows * im->w;
-  // ~2 warps of work per 256-thread block pass; enough blocks to cover the SMs, a grid-stride loop does the rest
-  int gx = (int)std::min<size_t>((max_pix + 1023) / 1024, (size_t)std::max(1, im->dev->sm_count * 8 / std::max(im->nmy, 1)));
+  const int threads = 256;
+  // enough blocks to cover the SMs, a grid-stride loop does the rest
+  int gx = (int)std::min<size_t>((max_pix + (size_t)threads * FLUSH_GROUPS - 1) / ((size_t)threads * FLUSH_GROUPS),
+                                 (size_t)std::max(1, im->dev->sm_count * 8 / std::max(im->nmy, 1)));
   if (gx < 1) gx = 1;
+  const bool use_list = list >= 0 && host;
   image_flush_kernel<<<dim3((unsigned)gx, (unsigned)im->nmy), threads, 0, st>>>(
-      target, root, host, im->d_prev_root, im->d_prev_host, im->d_blocks, im->w, clear, im->d_flushed);
+      im->d_target, root, host, im->d_prev_root, im->d_prev_host, im->d_blocks, im->w, clear, im->d_flushed,
+      use_list ? im->d_list_idx[list] : nullptr, use_list ? im->d_list_val[list] : nullptr, use_list ? im->d_list_n + list : nullptr);
   im->dev->launches++;
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
@@ -271,40 +329,50 @@ int spraygpu_image_flush(spraygpu_image img, int to_root, int to_host, int clear
   Image* im = (Image*)img;
   if (!im->nmy) return SPRAYGPU_OK;
   SG_CUDA(cudaSetDevice(im->dev->cuda_device));
-  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));   // the bitmaps are shared with pending async flushes
-  return image_launch_flush(im, im->d_target, to_root, to_host, clear, im->dev->stream, 256);
+  // a synchronous flush to the host must not overtake stores of earlier asynchronous ones
+  if (im->flush_stream && to_host) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
+  return image_launch_flush(im, to_root, to_host, clear, im->dev->stream, -1);
 }
 
-// Frame-level double buffering: the flush of the frame just traced runs on its own (high-priority) stream with
-// 128-thread CTAs of 30 registers — they fit beside the five resident CTAs of the persistent render kernel on every
-// SM — so its PCIe / NVLink stores overlap the NEXT frame's trace, which goes to the other render target.  The target
-// is always cleared (it is traced into again two frames later).
+// The flush OVERLAPPED with the next frame.  On the device's stream, right behind the trace: scan the render target,
+// push the root-bound pixels over NVLink as before, APPEND the host-bound pixels (index + value) to a compact device
+// list and clear the target — no system-memory store, ~25 us for a 64 MB target.  On the image's own stream: a few
+// small CTAs (they fit into the registers the persistent render kernel leaves free) stream that list into the pinned
+// host image while the next frame is traced.  Two lists alternate; a list is re-used only after its stores are done.
 int spraygpu_image_flush_async(spraygpu_image img, int to_root, int to_host) {
   SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_flush_async: img is NULL");
   Image* im = (Image*)img;
   Device* dev = im->dev;
   SG_CUDA(cudaSetDevice(dev->cuda_device));
+  if (!to_host) return spraygpu_image_flush(img, to_root, 0, 1);
   if (!im->flush_stream) {
-    int lo = 0, hi = 0;
-    SG_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    SG_CUDA(cudaStreamCreateWithPriority(&im->flush_stream, cudaStreamNonBlocking, hi));
-    SG_CUDA(cudaEventCreateWithFlags(&im->ev_trace, cudaEventDisableTiming));
-    for (int k = 0; k < 2; ++k) SG_CUDA(cudaEventCreateWithFlags(&im->ev_flush[k], cudaEventDisableTiming));
-    SG_CUDA(cudaMalloc((void**)&im->d_targets[1], im->bytes));
-    SG_CUDA(cudaMemsetAsync(im->d_targets[1], 0, im->bytes, dev->stream));
+    int least = 0, greatest = 0;
+    SG_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    SG_CUDA(cudaStreamCreateWithPriority(&im->flush_stream, cudaStreamNonBlocking, greatest));
+    SG_CUDA(cudaEventCreateWithFlags(&im->ev_compact, cudaEventDisableTiming));
+    const size_t npix = (size_t)im->w * im->h;
+    for (int k = 0; k < 2; ++k) {
+      SG_CUDA(cudaEventCreateWithFlags(&im->ev_store[k], cudaEventDisableTiming));
+      SG_CUDA(cudaMalloc((void**)&im->d_list_idx[k], npix * sizeof(uint32_t)));
+      SG_CUDA(cudaMalloc((void**)&im->d_list_val[k], npix * sizeof(float4)));
+    }
+    SG_CUDA(cudaMalloc((void**)&im->d_list_n, sizeof(unsigned int) * 2));
   }
-  SG_CUDA(cudaEventRecord(im->ev_trace, dev->stream));
-  SG_CUDA(cudaStreamWaitEvent(im->flush_stream, im->ev_trace, 0));
+  const int k = im->cur;
+  if (im->stored_once[k]) SG_CUDA(cudaStreamWaitEvent(dev->stream, im->ev_store[k], 0));   // list k is free again
+  SG_CUDA(cudaMemsetAsync(im->d_list_n + k, 0, sizeof(unsigned int), dev->stream));
   if (im->nmy) {
-    int rc = image_launch_flush(im, im->d_targets[im->cur], to_root, to_host, 1, im->flush_stream, 128);
+    int rc = image_launch_flush(im, to_root, 1, 1, dev->stream, k);
     if (rc) return rc;
   }
-  SG_CUDA(cudaEventRecord(im->ev_flush[im->cur], im->flush_stream));
-  im->flushed_once[im->cur] = true;
+  SG_CUDA(cudaEventRecord(im->ev_compact, dev->stream));
+  SG_CUDA(cudaStreamWaitEvent(im->flush_stream, im->ev_compact, 0));
+  image_store_kernel<<<16, 64, 0, im->flush_stream>>>(im->d_list_idx[k], im->d_list_val[k], im->d_list_n + k, im->h_image_dev);
+  dev->launches++;
+  SG_CUDA(cudaGetLastError());
+  SG_CUDA(cudaEventRecord(im->ev_store[k], im->flush_stream));
+  im->stored_once[k] = true;
   im->cur ^= 1;
-  im->d_target = im->d_targets[im->cur];
-  // the next frame is traced into the other target: its own flush (two frames ago) must have cleared it
-  if (im->flushed_once[im->cur]) SG_CUDA(cudaStreamWaitEvent(dev->stream, im->ev_flush[im->cur], 0));
   return SPRAYGPU_OK;
 }
 
@@ -313,6 +381,7 @@ int spraygpu_image_wait(spraygpu_image img) {
   SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_wait: img is NULL");
   Image* im = (Image*)img;
   SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  SG_CUDA(cudaStreamSynchronize(im->dev->stream));
   if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
   return SPRAYGPU_OK;
 }

@@ -142,8 +142,8 @@ class ImagePartitionRenderer:
         self.dev.synchronize()
 
     def frame_host_async(self):
-        """frame_host without the per-frame synchronize: this frame's rows are stored into the host image on the image's
-        own stream while the next frame is traced into the second render target (spraygpu_image_flush_async)."""
+        """frame_host without the per-frame synchronize: this frame's rows are compacted on the device and stored into the
+        host image on the image's own stream while the next frame is traced (spraygpu_image_flush_async)."""
         self.dev.trace_frame_rects(self.cam, self.shade, self.rects, self.parents, self.image.device)
         self.image.flush_async(to_host=True)
 

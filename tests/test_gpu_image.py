@@ -62,9 +62,10 @@ def test_image_flush_to_host_is_exact_and_sparse():
 
 
 def test_image_flush_async_pipelines_frames_exactly():
-    """spraygpu_image_flush_async: frame k is flushed (and its target cleared) on the image's own stream while frame
-    k + 1 is traced into the second render target.  Frames from different cameras, several rounds through both
-    targets: after spraygpu_image_wait the host image is exactly the last frame, and both targets end up cleared."""
+    """spraygpu_image_flush_async: frame k's host-bound pixels are compacted on the device's stream (target cleared) and
+    streamed into the host image by a few CTAs on the image's own stream while frame k + 1 is traced.  Frames from
+    different cameras, several rounds through both lists: after spraygpu_image_wait the host image is exactly the last
+    frame, and the target is left cleared."""
     sc = scenes.wavelets64(8)
     dev = capi.Device(0)
     dev.load_scene(sc)
@@ -82,18 +83,15 @@ def test_image_flush_async_pipelines_frames_exactly():
         ref_img.flush(clear=True)
     assert not np.array_equal(want[0], want[1])
     img = capi.Image(dev, None, W, H)
-    targets = set()
     for k, sft in enumerate(shifts):
         cd = scenes.camera_frame(pos + np.array(sft, np.float32), lookat, up, 90.0, W, H)
-        targets.add(int(img.device))
         _frame(dev, sc, cd, kw, img.device)
-        img.flush_async(to_host=True)                # returns at once; the next frame goes to the other target
+        img.flush_async(to_host=True)                # returns at once; the stores overlap the next frame
         if k in (2, 5, 6):                           # look at some frames, let the others stream through
             img.wait()
             assert np.array_equal(img.host, want[k]), k
-    assert len(targets) == 2
     img.wait(); dev.synchronize()
-    assert not img.read_device("device").any()       # the current target was cleared by its own flush two frames ago
+    assert not img.read_device("device").any()       # cleared by the compaction pass
     # mixing in a synchronous flush afterwards still works on the current target
     cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
     _frame(dev, sc, cd, kw, img.device)
