@@ -274,7 +274,8 @@ SPRAYGPU_API int spraygpu_partition_domains(int ndomains, const float* world_aab
  * (insitu::VBuf::compositeTbuf); the rank owning the winning domain shades; shadow directions travel by
  * an all-reduce, occlusion by ncclAllReduce(max) on one byte per ray (compositeObuf); the owner adds the
  * radiance into ITS frame buffer.  fb therefore holds this rank's partial image: sum the ranks with
- * spraygpu_image_reduce.  fb must be a device pointer.  stats (may be NULL) are summed over ranks.
+ * spraygpu_image_reduce.  fb must be a device pointer.  stats (may be NULL) are summed over ranks with a collective:
+ * pass NULL on every rank or non-NULL on every rank (the same holds for the _p2p and _fwd variants below).
  * insitu::{SingleThread,MultiThread}Tracer::trace (src/insitu/insitu_singlethread_tracer.inl:381-466). */
 SPRAYGPU_API int spraygpu_trace_tile_insitu(spraygpu_device dev, spraygpu_comm comm, const spraygpu_camera* cam,
                                             const spraygpu_shade* shade, spraygpu_tile tile, float* fb_rgba,
