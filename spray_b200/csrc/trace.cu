@@ -180,6 +180,11 @@ __global__ void __launch_bounds__(256)
 // (ooc_tcontext.inl:29-135), ShaderPt / ShaderAo (ooc_shader_pt.h:94-227, ooc_shader_ao.h:92-197).
 // ------------------------------------------------------------------------------------------------
 #define SPRAY_MAX_FRAME_TILES 32
+// 8x4 pixel blocks a warp claims per atomicAdd on the frame's work counter (A/B knob: a same-address atomic costs ~2 ns
+// of L2 time and a 2048^2 frame is 131 K blocks)
+#ifndef SPRAY_CLAIM_BLOCKS
+#define SPRAY_CLAIM_BLOCKS 1
+#endif
 struct RenderParams {
   const DomainEntry* table;
   int nd;
@@ -308,14 +313,22 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
   uint32_t n_eye = 0, n_rad = 0, n_shadow = 0, n_hit = 0;
   int count = 0;      // rays in this warp's queue (warp-uniform)
   bool more = true;   // the tile still has unclaimed sample slots
+  uint32_t claim_next = 0, claim_end = 0;   // this warp's claimed slot range
 
   for (;;) {
     if (count < 32 && more) {
       // ---------------- refill: one 8x4 pixel block of eye rays (ooc_tracer.inl:84-172) ----------------
-      unsigned long long base = 0;
-      if (lane == 0) base = atomicAdd(P.counters, 32ull);
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (base >= P.total_slots) { more = false; continue; }
+      // the warp claims SPRAY_CLAIM_BLOCKS blocks per atomic on the frame's work counter and walks them one at a time
+      if (claim_next >= claim_end) {
+        unsigned long long b = 0;
+        if (lane == 0) b = atomicAdd(P.counters, (unsigned long long)(32 * SPRAY_CLAIM_BLOCKS));
+        b = __shfl_sync(0xffffffffu, b, 0);
+        if (b >= P.total_slots) { more = false; continue; }
+        claim_next = (uint32_t)b;
+        claim_end = (uint32_t)(b + 32 * SPRAY_CLAIM_BLOCKS < P.total_slots ? b + 32 * SPRAY_CLAIM_BLOCKS : P.total_slots);
+      }
+      const unsigned long long base = claim_next;
+      claim_next += 32u;
       uint32_t local;
       const int ti = tile_of_slot(P, (uint32_t)base, &local);
       const spraygpu_tile tile = P.tiles[ti];

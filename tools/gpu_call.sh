@@ -40,6 +40,10 @@ print('$v [$ba]', 'Mrays/s %.0f'%d['value'], 'ms %.3f'%d['ms_per_step'], 'frac %
       timeout 600 python tools/insitu_one.py $arg 3 > $out/insitu1_$arg.log 2>&1 &&
       ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:p2p_|insitu_|eye_rays|intersect_domains|image_flush' -c 600 --csv --log-file $out/insitu1_${arg}_launches.csv python tools/insitu_one.py $arg 1 > $out/insitu1_${arg}_ncu.log 2>&1
       tail -3 $out/insitu1_$arg.log ;;
+    fwd1)    # one-rank ray-forwarding tile under ncu: launch list with durations
+      timeout 600 python tools/insitu_one.py $arg 3 fwd > $out/fwd1_$arg.log 2>&1 &&
+      ncu --metrics gpu__time_duration.sum --clock-control none -k 'regex:fwd_|p2p_' -c 400 --csv --log-file $out/fwd1_${arg}_launches.csv python tools/insitu_one.py $arg 1 fwd > $out/fwd1_${arg}_ncu.log 2>&1
+      tail -3 $out/fwd1_$arg.log ;;
     py)      # py:<script and args>  (one GPU)
       lg=$out/py_$(echo "$arg" | tr -c 'a-zA-Z0-9' '_' | cut -c1-60)
       timeout 900 python $arg > $lg.log 2> $lg.err; echo "py $arg rc $?"; tail -8 $lg.log ;;

@@ -22,7 +22,7 @@ def main():
     sh = capi.make_shade(lights=sc["lights"], **shade)
     dev = capi.Device(0, stream=stream.cuda_stream)
     comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
-    for mode in ("p2p", "nccl"):
+    for mode in (sys.argv[3].split(",") if len(sys.argv) > 3 else ("p2p", "nccl")):
         r = multigpu.InsituRenderer(dev, sc, cam, sh, W, H, 0, 1, comm, mode=mode)
         st = r.count_rays()
         rays = st["radiance_rays"] + st["shadow_rays"]
