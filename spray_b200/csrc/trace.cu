@@ -182,6 +182,9 @@ __global__ void __launch_bounds__(256)
 #define SPRAY_MAX_FRAME_TILES 32
 // 8x4 pixel blocks a warp claims per atomicAdd on the frame's work counter (A/B knob: a same-address atomic costs ~2 ns
 // of L2 time and a 2048^2 frame is 131 K blocks)
+#ifndef SPRAY_BLOCK_SWIZZLE_DEFAULT
+#define SPRAY_BLOCK_SWIZZLE_DEFAULT 0
+#endif
 #ifndef SPRAY_CLAIM_BLOCKS
 #define SPRAY_CLAIM_BLOCKS 1
 #endif
@@ -205,9 +208,21 @@ struct RenderParams {
   uint16_t parent_dx[SPRAY_MAX_FRAME_TILES], parent_dy[SPRAY_MAX_FRAME_TILES];
   uint32_t slot_end[SPRAY_MAX_FRAME_TILES];        // exclusive prefix end of tile t's slots (32 * pixel blocks * spp)
   uint32_t blocks_per_row[SPRAY_MAX_FRAME_TILES];
+  // block enumeration inside a tile: 0 = row-major; else super-tiles of 2^(swz & 15) x 2^(swz >> 4) pixel blocks, row-major
+  // inside a super-tile and across super-tiles (blocks_per_row is then padded to whole super-tiles): the warps that
+  // are active at the same time cover a compact patch of the image instead of a band as wide as the tile
+  uint8_t swz[SPRAY_MAX_FRAME_TILES];
   uint32_t total_slots;
   int qcap;                      // GENERAL variant: ray-queue entries per warp (the lean variant's is a constant)
 };
+
+__device__ __forceinline__ void block_xy(uint32_t blk, uint32_t bpr, uint32_t swz, uint32_t* bx, uint32_t* by) {
+  if (swz == 0u) { *bx = blk % bpr; *by = blk / bpr; return; }
+  const uint32_t lw = swz & 15u, lh = swz >> 4, per = 1u << (lw + lh);
+  const uint32_t st = blk / per, in = blk & (per - 1u), stpr = bpr >> lw;      // bpr is a multiple of 2^lw here
+  *bx = ((st % stpr) << lw) + (in & ((1u << lw) - 1u));
+  *by = ((st / stpr) << lh) + (in >> lw);
+}
 
 // slot base (multiple of 32) -> its tile, the slot index inside the tile
 __device__ __forceinline__ int tile_of_slot(const RenderParams& P, uint32_t base, uint32_t* local) {
@@ -336,8 +351,10 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
       const uint32_t slot = local + lane;
       const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
       const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-      const uint32_t x0 = (blk % bpr) * 8u + (within & 7u);
-      const uint32_t y0 = (blk / bpr) * 4u + (within >> 3);
+      uint32_t bx, by;
+      block_xy(blk, bpr, P.swz[ti], &bx, &by);
+      const uint32_t x0 = bx * 8u + (within & 7u);
+      const uint32_t y0 = by * 4u + (within >> 3);
       const bool has_ray = x0 < (uint32_t)tile.w && y0 < (uint32_t)tile.h;
       uint32_t samid = 0, pixid = 0;
       vec3 dir = mk3(0.f, 0.f, 1.f);
@@ -549,8 +566,10 @@ __global__ void __launch_bounds__(SPRAY_RENDER_THREADS, SPRAY_RENDER_MINBLOCKS) 
           const uint32_t slot = local + lane;
           const uint32_t pix_slot = slot / (uint32_t)spp, sidx = slot % (uint32_t)spp;
           const uint32_t blk = pix_slot >> 5, within = pix_slot & 31u;
-          const uint32_t x0 = (blk % bpr) * 8u + (within & 7u);
-          const uint32_t y0 = (blk / bpr) * 4u + (within >> 3);
+          uint32_t bx, by;
+          block_xy(blk, bpr, P.swz[ti], &bx, &by);
+          const uint32_t x0 = bx * 8u + (within & 7u);
+          const uint32_t y0 = by * 4u + (within >> 3);
           const bool has_ray = x0 < (uint32_t)tile.w && y0 < (uint32_t)tile.h;
           uint32_t esam = 0, epix = 0;
           vec3 dir = mk3(0.f, 0.f, 1.f);
@@ -691,6 +710,13 @@ int launch_render_tile(Device* dev, const spraygpu_camera* cam, const spraygpu_s
 // up to SPRAY_MAX_FRAME_TILES tiles in ONE persistent launch; reset_counters = false keeps accumulating the
 // statistics of a frame that needs several launches
 // parents == nullptr: every tile is a whole blocking tile; else tiles[t] is a sub-rectangle of the blocking tile parents[t]
+// SPRAY_BLOCK_SWIZZLE=k (A/B knob, read once): enumerate a tile's pixel blocks in super-tiles of 2^k x 2^(k+1) blocks
+static int swizzle_log2() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SPRAY_BLOCK_SWIZZLE"); v = e ? atoi(e) : SPRAY_BLOCK_SWIZZLE_DEFAULT; if (v < 0 || v > 7) v = 0; }
+  return v;
+}
+
 int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_shade* shade, const spraygpu_tile* tiles,
                         const spraygpu_tile* parents, int ntiles, float* fb, bool counted, bool reset_counters) {
   SG_CHECK(ntiles >= 0 && ntiles <= SPRAY_MAX_FRAME_TILES, SPRAYGPU_ERR_LIMIT, "%d tiles in one launch (max %d)", ntiles, SPRAY_MAX_FRAME_TILES);
@@ -702,12 +728,22 @@ int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_
   P.ntiles = 0;
   for (int t = 0; t < ntiles; ++t) {
     const spraygpu_tile tile = tiles[t];
-    const uint32_t bpr = (uint32_t)((tile.w + 7) / 8);
-    const uint64_t ts = (uint64_t)bpr * (uint64_t)((tile.h + 3) / 4) * 32ull * (uint64_t)shade->pixel_samples;
+    uint32_t bpr = (uint32_t)((tile.w + 7) / 8), brows = (uint32_t)((tile.h + 3) / 4);
+    uint8_t swz = 0;
+    if (swizzle_log2() > 0 && bpr && brows) {
+      // super-tiles of up to 2^k x 2^(k+1) blocks (8 x 4 pixels each: 64 x 64 pixels at k = 3), shrunk to the tile
+      uint32_t lw = (uint32_t)swizzle_log2(), lh = lw + 1;
+      while (lw > 0 && (1u << lw) > bpr) --lw;
+      while (lh > 0 && (1u << lh) > brows) --lh;
+      swz = (uint8_t)(lw | (lh << 4));
+      bpr = ((bpr + (1u << lw) - 1) >> lw) << lw;
+      brows = ((brows + (1u << lh) - 1) >> lh) << lh;
+    }
+    const uint64_t ts = (uint64_t)bpr * (uint64_t)brows * 32ull * (uint64_t)shade->pixel_samples;
     if (!ts) continue;
     slots += ts;
     SG_CHECK(slots < 0xFFFFFFFFull, SPRAYGPU_ERR_LIMIT, "tiles too large: %llu sample slots", (unsigned long long)slots);
-    P.tiles[P.ntiles] = tile; P.blocks_per_row[P.ntiles] = bpr; P.slot_end[P.ntiles] = (uint32_t)slots;
+    P.tiles[P.ntiles] = tile; P.blocks_per_row[P.ntiles] = bpr; P.slot_end[P.ntiles] = (uint32_t)slots; P.swz[P.ntiles] = swz;
     P.parent_w[P.ntiles] = tile.w; P.parent_dx[P.ntiles] = 0; P.parent_dy[P.ntiles] = 0;
     if (parents) {
       const spraygpu_tile par = parents[t];
@@ -720,7 +756,7 @@ int launch_render_tiles(Device* dev, const spraygpu_camera* cam, const spraygpu_
     ++P.ntiles;
   }
   for (int t = P.ntiles; t < SPRAY_MAX_FRAME_TILES; ++t) {
-    P.tiles[t] = spraygpu_tile{0, 0, 0, 0}; P.blocks_per_row[t] = 1; P.slot_end[t] = (uint32_t)slots;
+    P.tiles[t] = spraygpu_tile{0, 0, 0, 0}; P.blocks_per_row[t] = 1; P.slot_end[t] = (uint32_t)slots; P.swz[t] = 0;
     P.parent_w[t] = 0; P.parent_dx[t] = 0; P.parent_dy[t] = 0;
   }
   P.total_slots = (uint32_t)slots;
