@@ -8,6 +8,7 @@
 //   -> Karras LBVH -> bottom-up refit -> level-synchronous collapse into 80-byte 8-wide nodes
 //   -> triangle records (48 B, leaf order) + attribute records (48 B, primID order)
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -747,6 +748,13 @@ struct Carver {
 
 static inline int grid_for(size_t n, int threads) { return (int)((n + threads - 1) / threads); }
 
+// SPRAY_BUILD_GRAPHS=0 disables the CUDA-graph replay of repeated commits (A/B knob)
+static bool build_graphs_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SPRAY_BUILD_GRAPHS"); v = (e && *e == '0') ? 0 : 1; }
+  return v == 1;
+}
+
 // one thread: the collapse's counters and root entry, the bounds accumulators (no host-staged copies in a commit)
 __global__ void build_init_kernel(uint32_t* bounds, unsigned int* counters, int* queue, unsigned int single) {
   for (int a = 0; a < 3; ++a) {
@@ -763,8 +771,21 @@ __global__ void build_init_kernel(uint32_t* bounds, unsigned int* counters, int*
 int build_scene(Scene* sc) {
   Device* dev = sc->dev;
   cudaStream_t st = build_stream(dev);
+  Scratch* scratch = &dev->scratch;
   const size_t nv = sc->nv, nf = sc->nf;
   SG_CHECK(nf >= 1 && nv >= 1, SPRAYGPU_ERR_STATE, "commit: empty mesh (nv=%zu nf=%zu)", nv, nf);
+  if (nf <= SPRAY_POOL_MAX_TRIS && !dev->loading_async) {
+    // small domain: one of the pool streams (round robin), ordered behind everything already on the device's stream
+    // (a re-commit must not overwrite buffers a running trace still reads)
+    if (sc->pool_slot < 0) sc->pool_slot = (int)(dev->pool_rr++ % SPRAY_BUILD_POOL);   // sticky: the graph of a re-commit names the stream
+    const unsigned slot = (unsigned)sc->pool_slot;
+    if (!dev->pool_stream[slot]) SG_CUDA(cudaStreamCreateWithFlags(&dev->pool_stream[slot], cudaStreamNonBlocking));
+    if (!dev->pool_order) SG_CUDA(cudaEventCreateWithFlags(&dev->pool_order, cudaEventDisableTiming));
+    SG_CUDA(cudaEventRecord(dev->pool_order, dev->stream));
+    SG_CUDA(cudaStreamWaitEvent(dev->pool_stream[slot], dev->pool_order, 0));
+    st = dev->pool_stream[slot];
+    scratch = &dev->pool_scratch[slot];
+  }
   SG_CHECK(nf <= SPRAYGPU_MAX_PRIMS, SPRAYGPU_ERR_LIMIT, "commit: %zu faces exceed the 23-bit primID field", nf);
   const int n = (int)nf;
   const int npairs = 3 * n;
@@ -816,76 +837,121 @@ int build_scene(Scene* sc) {
   };
   Carver sizer{nullptr};
   carve(sizer);
-  int rc = ensure_scratch(dev->scratch, sizer.off + 256);
+  int rc = ensure_scratch(*scratch, sizer.off + 256);
   if (rc) return rc;
-  Carver carver{(char*)dev->scratch.ptr};
+  Carver carver{(char*)scratch->ptr};
   carve(carver);
 
-  const int T = 256;
-  build_init_kernel<<<1, 1, 0, st>>>(bounds, counters, queue, n == 1 ? 1u : 0u);
-  dev->launches++;
-  // ---- transform
-  if (sc->has_xf) {
-    Mat4 M; memcpy(M.m, sc->xf, sizeof(M.m));
-    transform_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts_obj, sc->d_verts, nv, M);
+  // Everything from here to the result copies is ~30 launches of fixed shape for a given (mesh size, buffers, stream):
+  // the second commit with the same shape captures them into a CUDA graph, later ones replay it with ONE launch.  A
+  // re-committed cache block (out-of-core LRU, the reference's rtcCommit on every miss) and the many small domains of
+  // a C2 / C5 scene are enqueue-bound otherwise: ~35 API calls = 0.14 ms of host time per commit (r04x).
+  auto enqueue = [&]() -> int {
+    const int T = 256;
+    build_init_kernel<<<1, 1, 0, st>>>(bounds, counters, queue, n == 1 ? 1u : 0u);
     dev->launches++;
-  }
-  // ---- normals: valence count -> segments -> face lists -> per-vertex sorted sums (no global sort)
-  SG_CUDA(cudaMemsetAsync(vend, 0, sizeof(uint32_t) * nv, st));        // vend = per-vertex fill cursor
-  SG_CUDA(cudaMemsetAsync(vcnt_buf, 0, sizeof(uint32_t) * nv, st));    // valence
-  SG_CUDA(cudaMemsetAsync(counters + 5, 0, sizeof(unsigned int) * 2, st));   // [5] segment cursor, [6] heavy vertices
-  {
-    uint32_t* vcnt = vcnt_buf;
-    uint32_t* vlist = kA;                 // npairs face ids, grouped by vertex
-    uint32_t* heavy = vB;                 // vertices with more than NRM_LIGHT_MAX faces (at most npairs / 33)
-    vcount_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vcnt);
-    valloc_kernel<<<grid_for(nv, 1024), 1024, 0, st>>>(vcnt, nv, vstart, counters + 5);
-    vfill_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vstart, vend, vlist);
-    normals_light_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, nv, heavy,
-                                                        counters + 6);
-    normals_heavy_kernel<<<std::min(dev->sm_count * 4, npairs / (NRM_LIGHT_MAX + 1) + 1), 256, 0, st>>>(
-        sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, heavy, counters + 6);
-    attr_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_faces, sc->d_normals, sc->d_rgb, n, sc->d_attr);
-    dev->launches += 6;
-  }
-
-  // ---- triangle boxes, Morton keys, sort
-  tri_bounds_kernel<<<std::min(grid_for(nf, 256), dev->sm_count * 8), 256, 0, st>>>(sc->d_verts, sc->d_faces, n, tlo, thi, bounds);
-  dev->launches++;
-  if (n == 1) {
-    single_tri_kernel<<<1, 1, 0, st>>>(sc->d_verts, sc->d_faces, tlo, thi, sc->d_nodes, sc->d_tris);
-    dev->launches++;
-  } else {
-    morton_kernel<<<grid_for(nf, T), T, 0, st>>>(tlo, thi, n, bounds, kA, vA);
-    dev->launches++;
-    rc = radix_sort(dev, st, &kA, &vA, &kB, &vB, hist, n, 30);
-    if (rc) return rc;
-    leaf_boxes_kernel<<<grid_for(nf, T), T, 0, st>>>(vA, tlo, thi, n, llo, lhi);
-    lbvh_kernel<<<grid_for(nf, T), T, 0, st>>>(kA, n, bl, br, bfirst, blast, parent);
-    SG_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nf, st));
-    refit_kernel<<<grid_for(nf, T), T, 0, st>>>(parent, bl, br, bfirst, blast, llo, lhi, blo, bhi, info, flags, n);
-    dev->launches += 3;
-    // ---- collapse: one cooperative launch walks the levels (queue[j] = binary root of 8-wide node j)
-    if (dev->collapse_blocks_per_sm == 0) {
-      int bps = 0;
-      SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, collapse_coop_kernel, 256, 0));
-      SG_CHECK(bps > 0, SPRAYGPU_ERR_LIMIT, "commit: the collapse kernel does not fit an SM");
-      dev->collapse_blocks_per_sm = bps;
+    // ---- transform
+    if (sc->has_xf) {
+      Mat4 M; memcpy(M.m, sc->xf, sizeof(M.m));
+      transform_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts_obj, sc->d_verts, nv, M);
+      dev->launches++;
     }
-    CollapseArgs A;
-    A.n = n; A.queue = queue; A.counters = counters; A.info = info; A.bfirst = bfirst;
-    A.blo = blo; A.bhi = bhi; A.llo = llo; A.lhi = lhi; A.sorted = vA; A.nodes = sc->d_nodes; A.node_cap = node_cap;
-    A.tri_prim = tri_prim;
-    // a level is at most node_cap nodes wide, 32 nodes per 256-thread CTA
-    const int grid = std::max(1, std::min(dev->collapse_blocks_per_sm * dev->sm_count, (int)((node_cap + 31) / 32)));
-    void* args[] = {(void*)&A};
-    SG_CUDA(cudaLaunchCooperativeKernel((const void*)collapse_coop_kernel, dim3(grid), dim3(256), args, 0, st));
-    tri_records_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_verts, sc->d_faces, tri_prim, n, sc->d_tris);
-    dev->launches += 2;
+    // ---- normals: valence count -> segments -> face lists -> per-vertex sorted sums (no global sort)
+    SG_CUDA(cudaMemsetAsync(vend, 0, sizeof(uint32_t) * nv, st));        // vend = per-vertex fill cursor
+    SG_CUDA(cudaMemsetAsync(vcnt_buf, 0, sizeof(uint32_t) * nv, st));    // valence
+    SG_CUDA(cudaMemsetAsync(counters + 5, 0, sizeof(unsigned int) * 2, st));   // [5] segment cursor, [6] heavy vertices
+    {
+      uint32_t* vcnt = vcnt_buf;
+      uint32_t* vlist = kA;                 // npairs face ids, grouped by vertex
+      uint32_t* heavy = vB;                 // vertices with more than NRM_LIGHT_MAX faces (at most npairs / 33)
+      vcount_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vcnt);
+      valloc_kernel<<<grid_for(nv, 1024), 1024, 0, st>>>(vcnt, nv, vstart, counters + 5);
+      vfill_kernel<<<grid_for(npairs, T), T, 0, st>>>(sc->d_faces, npairs, vstart, vend, vlist);
+      normals_light_kernel<<<grid_for(nv, T), T, 0, st>>>(sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, nv, heavy,
+                                                          counters + 6);
+      normals_heavy_kernel<<<std::min(dev->sm_count * 4, npairs / (NRM_LIGHT_MAX + 1) + 1), 256, 0, st>>>(
+          sc->d_verts, sc->d_faces, vlist, vstart, vcnt, sc->d_normals, heavy, counters + 6);
+      attr_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_faces, sc->d_normals, sc->d_rgb, n, sc->d_attr);
+      dev->launches += 6;
+    }
+
+    // ---- triangle boxes, Morton keys, sort
+    tri_bounds_kernel<<<std::min(grid_for(nf, 256), dev->sm_count * 8), 256, 0, st>>>(sc->d_verts, sc->d_faces, n, tlo, thi, bounds);
+    dev->launches++;
+    if (n == 1) {
+      single_tri_kernel<<<1, 1, 0, st>>>(sc->d_verts, sc->d_faces, tlo, thi, sc->d_nodes, sc->d_tris);
+      dev->launches++;
+    } else {
+      morton_kernel<<<grid_for(nf, T), T, 0, st>>>(tlo, thi, n, bounds, kA, vA);
+      dev->launches++;
+      rc = radix_sort(dev, st, &kA, &vA, &kB, &vB, hist, n, 30);
+      if (rc) return rc;
+      leaf_boxes_kernel<<<grid_for(nf, T), T, 0, st>>>(vA, tlo, thi, n, llo, lhi);
+      lbvh_kernel<<<grid_for(nf, T), T, 0, st>>>(kA, n, bl, br, bfirst, blast, parent);
+      SG_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nf, st));
+      refit_kernel<<<grid_for(nf, T), T, 0, st>>>(parent, bl, br, bfirst, blast, llo, lhi, blo, bhi, info, flags, n);
+      dev->launches += 3;
+      // ---- collapse: one cooperative launch walks the levels (queue[j] = binary root of 8-wide node j)
+      if (dev->collapse_blocks_per_sm == 0) {
+        int bps = 0;
+        SG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, collapse_coop_kernel, 256, 0));
+        SG_CHECK(bps > 0, SPRAYGPU_ERR_LIMIT, "commit: the collapse kernel does not fit an SM");
+        dev->collapse_blocks_per_sm = bps;
+      }
+      CollapseArgs A;
+      A.n = n; A.queue = queue; A.counters = counters; A.info = info; A.bfirst = bfirst;
+      A.blo = blo; A.bhi = bhi; A.llo = llo; A.lhi = lhi; A.sorted = vA; A.nodes = sc->d_nodes; A.node_cap = node_cap;
+      A.tri_prim = tri_prim;
+      // a level is at most node_cap nodes wide, 32 nodes per 256-thread CTA
+      const int grid = std::max(1, std::min(dev->collapse_blocks_per_sm * dev->sm_count, (int)((node_cap + 31) / 32)));
+      void* args[] = {(void*)&A};
+      SG_CUDA(cudaLaunchCooperativeKernel((const void*)collapse_coop_kernel, dim3(grid), dim3(256), args, 0, st));
+      tri_records_kernel<<<grid_for(nf, T), T, 0, st>>>(sc->d_verts, sc->d_faces, tri_prim, n, sc->d_tris);
+      dev->launches += 2;
+    }
+    // ---- results: 8 counter words + 12 bounds words into the scene's pinned record
+    SG_CUDA(cudaMemcpyAsync(sc->h_result, counters, sizeof(uint32_t) * 8, cudaMemcpyDeviceToHost, st));
+    SG_CUDA(cudaMemcpyAsync(sc->h_result + 8, bounds, sizeof(uint32_t) * 12, cudaMemcpyDeviceToHost, st));
+    return SPRAYGPU_OK;
+  };
+  uint64_t key = 1469598103934665603ull;
+  {
+    const void* ptrs[] = {sc->d_verts_obj, sc->d_faces, sc->d_rgb, sc->d_verts, sc->d_normals, sc->d_tris, sc->d_attr, sc->d_nodes,
+                          scratch->ptr, (const void*)st, sc->h_result};
+    auto mix = [&](const void* p, size_t nbytes) { const unsigned char* c = (const unsigned char*)p; for (size_t i = 0; i < nbytes; ++i) { key ^= c[i]; key *= 1099511628211ull; } };
+    mix(ptrs, sizeof(ptrs)); mix(&nv, sizeof(nv)); mix(&nf, sizeof(nf)); mix(&sc->has_xf, sizeof(sc->has_xf));
+    if (sc->has_xf) mix(sc->xf, sizeof(sc->xf));
   }
-  // ---- results: 8 counter words + 12 bounds words into the scene's pinned record
-  SG_CUDA(cudaMemcpyAsync(sc->h_result, counters, sizeof(uint32_t) * 8, cudaMemcpyDeviceToHost, st));
-  SG_CUDA(cudaMemcpyAsync(sc->h_result + 8, bounds, sizeof(uint32_t) * 12, cudaMemcpyDeviceToHost, st));
+  bool launched = false;
+  if (build_graphs_enabled() && !sc->graph_failed) {
+    if (sc->graph_exec && sc->graph_key == key) {
+      SG_CUDA(cudaGraphLaunch(sc->graph_exec, st));
+      dev->launches += sc->graph_launches;
+      launched = true;
+    } else if (sc->seen_key == key) {
+      if (sc->graph_exec) { cudaGraphExecDestroy(sc->graph_exec); sc->graph_exec = nullptr; }
+      if (cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+        const uint64_t l0 = dev->launches;
+        const int erc = enqueue();
+        cudaGraph_t g = nullptr;
+        const cudaError_t ce = cudaStreamEndCapture(st, &g);
+        if (erc == SPRAYGPU_OK && ce == cudaSuccess && g && cudaGraphInstantiate(&sc->graph_exec, g, 0) == cudaSuccess) {
+          sc->graph_key = key;
+          sc->graph_launches = (uint32_t)(dev->launches - l0);
+          SG_CUDA(cudaGraphLaunch(sc->graph_exec, st));
+          launched = true;
+        } else {
+          sc->graph_failed = true;        // whatever this driver cannot capture: plain launches from now on
+          sc->graph_exec = nullptr;
+          dev->launches = l0;
+          cudaGetLastError();
+        }
+        if (g) cudaGraphDestroy(g);
+      } else cudaGetLastError();
+    }
+  }
+  sc->seen_key = key;
+  if (!launched) { const int erc = enqueue(); if (erc) return erc; }
   SG_CUDA(cudaEventRecord(sc->ev1, st));
   SG_CUDA(cudaGetLastError());
   sc->pending = true;

@@ -243,6 +243,11 @@ int spraygpu_device_destroy(spraygpu_device dev) {
   if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); cudaStreamDestroy(d->copy_stream); }
   if (d->load_stream) { cudaStreamSynchronize(d->load_stream); cudaStreamDestroy(d->load_stream); }
   if (d->upload_stream) { cudaStreamSynchronize(d->upload_stream); cudaStreamDestroy(d->upload_stream); }
+  for (int k = 0; k < SPRAY_BUILD_POOL; ++k) {
+    if (d->pool_stream[k]) { cudaStreamSynchronize(d->pool_stream[k]); cudaStreamDestroy(d->pool_stream[k]); }
+    if (d->pool_scratch[k].ptr) cudaFree(d->pool_scratch[k].ptr);
+  }
+  if (d->pool_order) cudaEventDestroy(d->pool_order);
   for (int i = 0; i < 2; ++i) {
     if (d->ev_render[i]) cudaEventDestroy(d->ev_render[i]);
     if (d->ev_copy[i]) cudaEventDestroy(d->ev_copy[i]);
@@ -306,10 +311,12 @@ int spraygpu_scene_destroy(spraygpu_scene scene) {
   cudaSetDevice(d->cuda_device);
   cudaStreamSynchronize(d->stream);
   if (d->load_stream) cudaStreamSynchronize(d->load_stream);
+  if (s->pending && s->ev1) cudaEventSynchronize(s->ev1);     // a build on a pool stream
   s->pending = false;
   if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }
   if (s->ev_upload) cudaEventDestroy(s->ev_upload);
   if (s->h_result) cudaFreeHost(s->h_result);
+  if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
   for (int i = 0; i < d->ndomains; ++i)
     if (d->bound[i] == s) {
       d->bound[i] = nullptr;

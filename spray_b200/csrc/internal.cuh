@@ -108,6 +108,13 @@ struct Device {
   bool loading_async = false;
   std::vector<uint8_t> tracing;           // domains of the group being traced while the next one loads: must not be evicted
   int collapse_blocks_per_sm = 0;  // occupancy of the cooperative collapse kernel (queried once)
+  // small domains (<= SPRAY_POOL_MAX_TRIS triangles) build on a pool of streams, each with its own scratch: a 5 480-triangle
+  // commit is ~30 launches of near-empty kernels (0.25 ms of latency, the GPU idle), so enqueue-only commits of many small
+  // domains overlap each other instead of queueing on one stream (C2 / C5 scene load: 64 wavelet domains)
+  cudaStream_t pool_stream[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  Scratch pool_scratch[8];
+  cudaEvent_t pool_order = nullptr;
+  unsigned pool_rr = 0;
   unsigned long long* d_counters = nullptr;  // [0] work counter, [1..] stats
   uint64_t launches = 0;           // kernels launched by this library (bench "gpu_launches")
   // last render-kernel configuration (function attribute + occupancy are queried once per kernel / smem size)
@@ -146,7 +153,15 @@ struct Scene {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   cudaEvent_t ev_upload = nullptr; // set_mesh's copies (recorded on the stream they went to)
   uint32_t* h_result = nullptr;    // pinned: 8 counter words + 12 bounds words
+  // CUDA graph of the build's launches for the shape `graph_key` (captured on the second commit of that shape)
+  cudaGraphExec_t graph_exec = nullptr;
+  uint64_t graph_key = 0, seen_key = 0;
+  uint32_t graph_launches = 0;
+  bool graph_failed = false;
+  int pool_slot = -1;              // build-stream pool slot of a small domain (Device::pool_stream)
 };
+#define SPRAY_BUILD_POOL 8
+#define SPRAY_POOL_MAX_TRIS (1u << 16)
 inline cudaStream_t build_stream(const Device* d) { return d->loading_async && d->load_stream ? d->load_stream : d->stream; }
 inline cudaStream_t upload_stream(const Device* d) { return d->loading_async && d->upload_stream ? d->upload_stream : d->stream; }
 
