@@ -168,13 +168,13 @@ class InsituRenderer:
     spraygpu_image_reduce (round 1's path, kept for the A/B)."""
 
     def __init__(self, dev, scene, cam, shade, W, H, rank, world, comm, round_robin=False, mode="p2p", rows_per_block=8,
-                 shm_name=None, max_tile_samples=None):
+                 shm_name=None, max_tile_samples=None, scatter=False):
         import torch
         self.dev, self.cam, self.shade, self.W, self.H, self.rank, self.world, self.comm = dev, cam, shade, W, H, rank, world, comm
         self.mode, self.rpb = mode, int(rows_per_block)
         wb = np.stack([d["bounds"] for d in scene["domains"]])
         self.domain_to_rank = capi.partition_domains(wb, scenes.scene_bounds(scene), world, round_robin)
-        if os.environ.get("SPRAY_INSITU_PART", "") == "scatter" and world > 1:
+        if scatter and world > 1:
             self.domain_to_rank = scatter_partition(wb, scenes.scene_bounds(scene), world)
         self.owned = [i for i, r in enumerate(self.domain_to_rank) if r == rank]
         dev.load_scene(scene, owned=self.owned)
@@ -277,6 +277,19 @@ INSITU_LABEL = ("in-situ domain partition x%d (Morton): each GPU owns %d of %d d
                 "to rank 0 / the shared pinned host image")
 
 
+def insitu_deal():
+    """bench.py's domain -> rank deal for the in-situ modes: SPRAY_INSITU_PART = scatter (default) | rr | morton."""
+    part = os.environ.get("SPRAY_INSITU_PART", "")
+    if not part:
+        part = "rr" if os.environ.get("SPRAY_INSITU_RR", "") == "1" else ("morton" if os.environ.get("SPRAY_INSITU_RR", "") == "0" else "scatter")
+    label = {"morton": "",
+             "rr": "; domains dealt round-robin over the Morton order (data_partition.h:139-155)",
+             "scatter": "; domains dealt over the GPUs in the order of a hash of their Morton rank (a view-independent spread, NOT one of "
+                        "the reference's two partitions: contiguous Morton runs and round-robin put the camera-facing cells of a 4x4x4 grid "
+                        "on few GPUs; the image is the same under any deal)"}[part]
+    return dict(round_robin=part == "rr", scatter=part == "scatter"), label
+
+
 FWD_LABEL = ("in-situ domain partition x%d with ray forwarding: each GPU owns %d of %d domains; a ray is appended (32 B, peer store over "
              "NVLink) to the inbox of every GPU that owns a domain it enters, owners trace their inbox and atomicMin the packed key into "
              "the sample's home GPU, every sample is generated / shaded / accumulated on its home GPU only (blocks of %d rows)")
@@ -344,10 +357,12 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         r.close()
     else:
         # in-situ headline (C4 / C5, or --partition insitu): SPRAY_INSITU_MODE picks the variant, the other one is measured beside it
-        imode = os.environ.get("SPRAY_INSITU_MODE", "p2p")
-        rr = os.environ.get("SPRAY_INSITU_RR", "1") == "1"
+        # soups (opaque: the second, bounded serve pass removes most speculative work) do better with ray forwarding, the
+        # sparse wavelet scenes with the dense peer-memory exchange; the other variant is always measured beside the headline
+        imode = os.environ.get("SPRAY_INSITU_MODE", "fwd" if args.workload in ("c3", "c4") else "p2p")
+        deal_kw, deal_label = insitu_deal()
         fits_one_gpu = args.workload != "c4" or int(os.environ.get("SPRAY_C4_TRIS", str(1 << 23))) * len(sc["domains"]) <= (1 << 26)
-        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=imode, shm_name=shm, round_robin=rr)
+        r = InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=imode, shm_name=shm, **deal_kw)
         build_ms = float(sum(s_.info().build_ms for s_ in dev.scenes if s_.h))
         build_tris = int(sum(s_.info().num_faces for s_ in dev.scenes if s_.h))
         st, rays, ms_dev, launches, clocks, ms_e2e = measure(r, True)
@@ -390,8 +405,7 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
                       "keys_equal": other["ray_counts_equal"], "host_image_equals_composite": pc.get("host_image_equals_composite")}
         r_o.image.close(); r_o.image = None
         par_label = (FWD_LABEL if imode == "fwd" else INSITU_LABEL) % (world, owned_n, len(sc["domains"]), rpb)
-        if rr:
-            par_label += "; domains dealt round-robin over the Morton order (data_partition.h:139-155)"
+        par_label += deal_label
         insitu_headline = {"other_variant": other, "build": {"triangles_this_gpu": build_tris, "commit_device_ms_this_gpu": build_ms,
                                                                "mtris_per_s": build_tris / max(build_ms, 1e-9) / 1e3}}
     insitu_extra = None
@@ -399,8 +413,8 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         dev2 = capi.Device(local_rank, stream=stream.cuda_stream)
         comm2 = bootstrap_comm(dev2, rank, world)
         timer2 = type(timer)(timer.stream, timer.flush, dev2, world)
-        rr = os.environ.get("SPRAY_INSITU_RR", "1") == "1"    # domains dealt round-robin over the Morton order (data_partition.h:139-155)
-        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, shm_name=shm + "_i", round_robin=rr)
+        deal_kw, deal_label = insitu_deal()
+        r2 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, shm_name=shm + "_i", **deal_kw)
         st2 = r2.count_rays()
         ms2, l2 = timer2(r2.frame_device, max(args.steps // 2, 3), 3)
         ms2h, _ = timer2(r2.frame_host, max(args.steps // 2, 3), 2)
@@ -410,12 +424,11 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
         r2n = st2["radiance_rays"] + st2["shadow_rays"]
         insitu_extra = {"value": r2n / (ms2 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2, "gpu_launches": int(l2),
                         "e2e": {"value": r2n / (ms2h * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms2h},
-                        "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb) +
-                                       ("; domains dealt round-robin over the Morton order (data_partition.h:139-155)" if rr else ""),
+                        "parallelism": INSITU_LABEL % (world, len(r2.owned), len(sc["domains"]), r2.rpb) + deal_label,
                         "parity_check": pc2}
         r2.close()
         # the ray-forwarding variant (insitu3.cu) on the same communicator, same parity check
-        r4 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="fwd", shm_name=shm + "_f", round_robin=rr)
+        r4 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="fwd", shm_name=shm + "_f", **deal_kw)
         st4 = r4.count_rays()
         ms4, l4 = timer2(r4.frame_device, max(args.steps // 2, 3), 3)
         ms4h, _ = timer2(r4.frame_host, max(args.steps // 2, 3), 2)
@@ -425,11 +438,11 @@ def bench_multi(args, dev, stream, timer, sampler, rank, world, local_rank, work
             pc4["ray_counts_equal_dense_variant"] = all(st4[k] == st2[k] for k in ("eye_rays", "radiance_rays", "shadow_rays", "hits"))
         insitu_extra["ray_forwarding"] = {"value": r2n / (ms4 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms4, "gpu_launches": int(l4),
                                           "e2e": {"value": r2n / (ms4h * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms4h},
-                                          "parallelism": FWD_LABEL % (world, len(r4.owned), len(sc["domains"]), r4.rpb),
+                                          "parallelism": FWD_LABEL % (world, len(r4.owned), len(sc["domains"]), r4.rpb) + deal_label,
                                           "parity_check": pc4}
         r4.close()
         # A/B: round 1's exchange (dense NCCL all-reduces per wave) on the same communicator
-        r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl", round_robin=rr)
+        r3 = InsituRenderer(dev2, sc, cam, sh, W, H, rank, world, comm2, mode="nccl", **deal_kw)
         ms3, l3 = timer2(r3.frame_device, 3, 2)
         insitu_extra["nccl_allreduce_variant"] = {"value": r2n / (ms3 * 1e-3) / 1e6, "unit": unit, "ms_per_step": ms3, "gpu_launches": int(l3)}
         r3.close(); comm2.close(); dev2.close()

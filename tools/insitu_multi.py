@@ -24,7 +24,7 @@ def main():
     dev = capi.Device(local, stream=stream.cuda_stream)
     comm = multigpu.bootstrap_comm(dev, rank, world)
     for mode in modes:
-        r = multigpu.InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=mode, round_robin=os.environ.get("SPRAY_INSITU_RR", "0") == "1", shm_name="spraygpu_tm_%d_%s" % (os.getppid(), mode))
+        r = multigpu.InsituRenderer(dev, sc, cam, sh, W, H, rank, world, comm, mode=mode, round_robin=os.environ.get("SPRAY_INSITU_RR", "0") == "1", scatter=os.environ.get("SPRAY_INSITU_PART", "") == "scatter", shm_name="spraygpu_tm_%d_%s" % (os.getppid(), mode))
         st = r.count_rays()
         rays = st["radiance_rays"] + st["shadow_rays"]
         for _ in range(3):
