@@ -115,3 +115,37 @@ def test_ooc_rejects_bad_arguments_and_failing_loader():
     with pytest.raises(ZeroDivisionError):           # loader raises: surfaces in Python, not through the C frame
         dev.trace_tile_ooc(cam, sh, (0, 0, W, W), fb, 2, lambda i: 1 // 0)
     dev.close()
+
+
+def test_c4_shape_512_domains_fused_and_out_of_core(oracle):
+    """Config C4's SHAPE at test size: 8 x 8 x 8 = 512 domains (the limit of the key's 9 domain bits; the top-level tree
+    and the domain table need the > 48 KB shared-memory opt-in), 192 triangles each.  The fused kernel with everything
+    resident, and the out-of-core sweep behind a 16-block LRU (groups of 8, the next group prefetched while the current
+    one is traced; re-loaded blocks replay their build graph), against the oracle: ray counts equal, RMSE <= 1e-4,
+    the two GPU paths bit-identical at 1 spp."""
+    sc = scenes.soup_scene((8, 8, 8), 192)
+    assert len(sc["domains"]) == 512
+    W, H = 192, 128
+    e = 160.0
+    cd = scenes.camera_frame((1.19 * e, 1.12 * e, 1.06 * e), (0.5 * e, 0.5 * e, 0.5 * e), (0, 1, 0), 90.0, W, H)
+    kw = dict(bounces=2, pixel_samples=1, **scenes.WAVELETS64_BLINN)
+    tiles = scenes.image_schedule_tiles(W, H, 1, 1, 0)
+    fb_o, st_o = _oracle(oracle, sc, cd, kw, tiles)
+    assert fb_o[..., :3].max() > 0.05 and st_o.shadow_rays > 1000
+    # resident, fused
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    cam = capi.make_camera(cd)
+    sh = capi.make_shade(lights=sc["lights"], **kw)
+    fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    st = dev.trace_frame(cam, sh, tiles, fb, stats=True)
+    dev.synchronize()
+    fused = fb.cpu().numpy()
+    dev.close()
+    assert st.radiance_rays == st_o.radiance_rays and st.shadow_rays == st_o.shadow_rays
+    assert _rmse(fused, fb_o) <= RMSE_TOL
+    # out of core: 16 of 512 domains on the device
+    img, tot, cache = _render_ooc(sc, cd, kw, tiles, 16)
+    assert tot["radiance_rays"] == st_o.radiance_rays and tot["shadow_rays"] == st_o.shadow_rays
+    assert cache.misses > 100 and _rmse(img, fb_o) <= RMSE_TOL
+    assert _rmse(img, fused) <= 1e-7
