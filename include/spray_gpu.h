@@ -351,6 +351,8 @@ SPRAYGPU_API int spraygpu_image_flush(spraygpu_image img, int to_root, int to_ho
  * loop, src/render/spray_renderer.inl:355-372, with composite() of frame k hidden behind trace() of frame k + 1). */
 SPRAYGPU_API int spraygpu_image_flush_async(spraygpu_image img, int to_root, int to_host);
 SPRAYGPU_API int spraygpu_image_wait(spraygpu_image img);
+/* Device-side join (no host wait): work enqueued on the device's stream afterwards starts when every flush issued so far has landed. */
+SPRAYGPU_API int spraygpu_image_join(spraygpu_image img);
 /* cumulative pixels (16 B each) stored to the root composite / the host image by this rank's flushes */
 SPRAYGPU_API int spraygpu_image_flushed_pixels(spraygpu_image img, uint64_t* to_root, uint64_t* to_host);
 /* Plain full-size D2H copy of this rank's render target (which = 0) or of the root composite as mapped here

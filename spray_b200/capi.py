@@ -133,6 +133,7 @@ _PROTOS = {
     "spraygpu_image_flush": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "spraygpu_image_flush_async": (C.c_int, [_vp, C.c_int, C.c_int]),
     "spraygpu_image_wait": (C.c_int, [_vp]),
+    "spraygpu_image_join": (C.c_int, [_vp]),
     "spraygpu_image_flushed_pixels": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "spraygpu_image_barrier": (C.c_int, [_vp]),
     "spraygpu_image_read": (C.c_int, [_vp, C.c_int, _vp]),
@@ -528,6 +529,10 @@ class Image:
 
     def wait(self):
         _check(lib().spraygpu_image_wait(self.h_))
+
+    def join(self):
+        """The device stream waits for every pending flush (no host wait)."""
+        _check(lib().spraygpu_image_join(self.h_))
 
     def flushed_pixels(self):
         a, b = C.c_uint64(), C.c_uint64()

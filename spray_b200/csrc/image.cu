@@ -376,6 +376,17 @@ int spraygpu_image_flush_async(spraygpu_image img, int to_root, int to_host) {
   return SPRAYGPU_OK;
 }
 
+// device-side join: work enqueued on the device's stream after this call starts only when every flush issued so far has
+// landed (no host wait) — e.g. a kernel that reads the host image, or an event that closes a timed region
+int spraygpu_image_join(spraygpu_image img) {
+  SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_join: img is NULL");
+  Image* im = (Image*)img;
+  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  for (int k = 0; k < 2; ++k)
+    if (im->stored_once[k]) SG_CUDA(cudaStreamWaitEvent(im->dev->stream, im->ev_store[k], 0));
+  return SPRAYGPU_OK;
+}
+
 // host wait: every flush issued so far has landed (the host image holds the last flushed frame)
 int spraygpu_image_wait(spraygpu_image img) {
   SG_CHECK(img, SPRAYGPU_ERR_ARG, "image_wait: img is NULL");
