@@ -1,13 +1,15 @@
 #!/usr/bin/env python3
 """bench.py — headline benchmark of the per-domain ray-tracing hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4s|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|c3|c4s|c5|c4 (N > 1)]
                     [--partition image|insitu|both]
 
 A step = one frame of the hot path on the named workload: every blocking tile of the image goes through the
 fused persistent kernel (eye rays -> domain culling -> per-domain BVH8 closest hit -> shading -> shadow rays ->
 frame buffer).  `value` = (primary + shadow [+ bounce] rays resolved per frame) / device time, inputs resident in
-HBM; `e2e` = the same through the C ABI with a pinned HOST frame buffer (D2H inside the timed region).
+HBM; `e2e` = the same through the C ABI with a pinned HOST image (descriptors H2D, the frame's pixels D2H inside the
+timed region; frames pipelined: frame k's PCIe stores overlap frame k + 1's trace, the per-frame-synchronised figure is
+printed beside it).
 
 N > 1 (torchrun, one rank per GPU), `--partition`:
   image  (headline; the reference's `spray_ooc --partition image`): every rank holds all domains and renders an
