@@ -224,3 +224,26 @@ def test_rects_of_blocks_partition_the_frame_and_keep_blocking_tiles():
                 assert (px, py, pw, ph) in blocking
                 cover[y:y + h] += 1
         assert np.all(cover == 1)
+
+
+def test_scatter_partition_is_a_balanced_deterministic_deal():
+    """bench.py's in-situ deal (multigpu.scatter_partition; not a reference partition): every rank gets nd / N domains,
+    the deal is a pure function of the domain boxes, and on the 4 x 4 x 4 grid it spreads the camera-facing cells where
+    contiguous Morton runs and the round-robin deal leave one rank without any."""
+    from spray_b200 import capi, multigpu, scenes
+    sc = scenes.wavelets64()
+    wb = np.stack([d["bounds"] for d in sc["domains"]])
+    sb = scenes.scene_bounds(sc)
+    for world in (2, 4, 8):
+        a = multigpu.scatter_partition(wb, sb, world)
+        assert np.array_equal(a, multigpu.scatter_partition(wb, sb, world))
+        assert np.array_equal(np.bincount(a, minlength=world), np.full(world, len(wb) // world))
+    lo = wb[:, :3]
+    step = np.diff(np.unique(lo[:, 0]))[0]
+    idx = np.round((lo - lo.min(0)) / step).astype(int)
+    front = (idx == idx.max()).any(1)
+    rr = capi.partition_domains(wb, sb, 8, True)
+    sca = multigpu.scatter_partition(wb, sb, 8)
+    assert np.bincount(rr[front], minlength=8).min() == 0            # the parity partition starves the all-even rank
+    assert np.bincount(sca[front], minlength=8).min() >= 2
+    assert np.bincount(sca[front], minlength=8).max() <= np.bincount(rr[front], minlength=8).max()
