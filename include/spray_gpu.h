@@ -160,6 +160,28 @@ SPRAYGPU_API int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_in
 SPRAYGPU_API int spraygpu_scene_get_normals(spraygpu_scene scene, float* out_nv3);      /* [h|d] */
 SPRAYGPU_API int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out_nv3);     /* world space, [h|d] */
 
+/* Per-vertex normals WITHOUT any allocation.  No counterpart in the reference (Embree and the reference allocate
+ * freely on the host); it exists for hosts that cannot let a plug-in call cudaMalloc — typically the simulation an
+ * in-situ renderer lives in, which has given all of HBM to its own memory pool (a cudaMalloc would fail or eat into
+ * the solver's budget) and whose streams a cudaMalloc / cudaFree would stall with their device-wide synchronisation.
+ * Same kernels and bit-identical normals as spraygpu_scene_commit + spraygpu_scene_get_normals (no transform), but
+ * the work space (valences, face lists) is a fixed array inside the library image, not a grown scratch buffer:
+ *   - limits: nv <= SPRAYGPU_STATIC_MAX_VERTS, nf <= SPRAYGPU_STATIC_MAX_FACES, else SPRAYGPU_ERR_LIMIT; every GPU
+ *     that loads the library carries the array (about 4.6 MB) until the process exits;
+ *   - xyz (nv*3 floats), idx (nf*3 uint32) and normals (nv*3 floats, overwritten) are DEVICE pointers on the current
+ *     CUDA device — a host array would need a staging allocation and is refused with SPRAYGPU_ERR_ARG; needs no
+ *     spraygpu_device (creating one allocates); cuda_stream is the caller's cudaStream_t (NULL: default stream);
+ *   - face indices are validated like spraygpu_scene_set_mesh does: the call waits on the stream once for a 4-byte
+ *     read-back, then enqueues the normals kernels and returns without waiting for them;
+ *   - the first call on each GPU also looks up the array's device address; make that call (any small mesh will do)
+ *     during set-up, before any stream capture begins;
+ *   - all calls on a GPU share the one array: calls whose kernels could overlap (two streams, two threads) race —
+ *     serialise them. */
+#define SPRAYGPU_STATIC_MAX_VERTS (1u << 17)
+#define SPRAYGPU_STATIC_MAX_FACES (1u << 18)
+SPRAYGPU_API int spraygpu_compute_normals_static(const float* xyz, size_t nv, const uint32_t* idx, size_t nf, float* normals,
+                                                 void* cuda_stream);
+
 /* Scene::intersect on ONE domain = rtcIntersect + TriMeshBuffer::updateIntersection, batched
  * (src/render/scene.inl:190-199).  keys[i] carries domain_id in its domain field; uv may be NULL. [h|d] */
 SPRAYGPU_API int spraygpu_intersect(spraygpu_scene scene, int domain_id, const spraygpu_ray* rays, size_t n, spraygpu_key* keys,

@@ -97,6 +97,7 @@ _PROTOS = {
     "spraygpu_scene_get_info": (C.c_int, [_vp, C.POINTER(SceneInfo)]),
     "spraygpu_scene_get_normals": (C.c_int, [_vp, _vp]),
     "spraygpu_scene_get_vertices": (C.c_int, [_vp, _vp]),
+    "spraygpu_compute_normals_static": (C.c_int, [_vp, C.c_size_t, _vp, C.c_size_t, _vp, _vp]),
     "spraygpu_intersect": (C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp]),
     "spraygpu_occluded": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "spraygpu_domains_set": (C.c_int, [_vp, C.c_int, _vp, _vp]),
@@ -205,6 +206,21 @@ def _ptr(a):
         assert a.is_contiguous()
         return a.data_ptr()
     return a
+
+
+STATIC_MAX_VERTS = 1 << 17
+STATIC_MAX_FACES = 1 << 18
+
+
+def compute_normals_static(xyz, idx, normals, cuda_stream=None):
+    """spraygpu_compute_normals_static: per-vertex normals of a mesh that already lives on the GPU, written into
+    `normals`, with the library's built-in scratch array as work space — the call allocates nothing, for hosts (an
+    in-situ simulation that owns all of HBM) where a plug-in's cudaMalloc is not an option.  xyz / idx / normals are
+    CUDA tensors (or raw device addresses together with explicit counts via lib()); needs no Device."""
+    nv, nf = xyz.numel() // 3, idx.numel() // 3
+    assert xyz.element_size() == 4 and idx.element_size() == 4 and normals.numel() == 3 * nv
+    _check(lib().spraygpu_compute_normals_static(_ptr(xyz), nv, _ptr(idx), nf, _ptr(normals),
+                                                 _vp(cuda_stream) if cuda_stream else None))
 
 
 def make_camera(desc):

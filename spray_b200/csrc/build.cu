@@ -990,4 +990,114 @@ int scene_finalize(Scene* sc) {
   return SPRAYGPU_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// spraygpu_compute_normals_static — the per-vertex normals stage for hosts that must not allocate.
+//
+// SpRay's in-situ mode runs the renderer INSIDE a simulation.  Such a host has usually handed all of HBM to its own
+// pool at start-up, so a cudaMalloc from a plug-in either fails or takes memory the solver counted on; and cudaMalloc /
+// cudaFree synchronise the whole device, which stalls the solver's streams in the middle of a time step.  The regular
+// path (spraygpu_scene_commit) grows a scratch buffer with cudaMalloc.  This entry point runs the same five kernels
+// (vcount -> valloc -> vfill -> normals_light -> normals_heavy, unchanged) with their work space carved out of the
+// file-scope device array below instead: valence counts, segment starts, fill cursors, the per-vertex face lists and
+// the list of heavy vertices.  No cudaMalloc, cudaFree, event / stream creation or other allocating call is made.
+//
+// The array is part of the library image: every GPU that loads libspraygpu holds its ~4.6 MB until the process exits,
+// and all calls on one GPU share it.  Nothing is kept between calls on purpose — the counters, the valences and the fill
+// cursors are zeroed at the start of every call because the previous call's values are still there — but two calls whose
+// kernels overlap on the GPU (different streams, or different host threads) trample each other's lists.
+// ------------------------------------------------------------------------------------------------
+constexpr size_t NS_MAXV = SPRAYGPU_STATIC_MAX_VERTS, NS_MAXF = SPRAYGPU_STATIC_MAX_FACES;
+constexpr size_t ns_pad(size_t words) { return (words + 63) & ~(size_t)63; }      // every region starts 256-byte aligned
+constexpr size_t NS_VCNT = 0;                                   // [nv]  valence
+constexpr size_t NS_VSTART = NS_VCNT + ns_pad(NS_MAXV);         // [nv]  first slot of the vertex's face list
+constexpr size_t NS_VFILL = NS_VSTART + ns_pad(NS_MAXV);        // [nv]  fill cursor                         (starts at 0)
+constexpr size_t NS_VLIST = NS_VFILL + ns_pad(NS_MAXV);         // [3 nf] face ids grouped by vertex
+constexpr size_t NS_HEAVY = NS_VLIST + ns_pad(3 * NS_MAXF);     // vertices with > NRM_LIGHT_MAX faces: < 3 nf / 32
+constexpr size_t NS_CTR = NS_HEAVY + ns_pad(3 * NS_MAXF / NRM_LIGHT_MAX + 1);   // [0] segment cursor [1] heavy count [2] max index
+constexpr size_t NS_WORDS = NS_CTR + 64;
+static __device__ __align__(256) uint32_t g_normals_scratch[NS_WORDS];
+
+// In HOST code `g_normals_scratch` is only the host-side shadow of the symbol: handing it to a kernel would fault (or,
+// on a system where the GPU can reach host memory, quietly work on the wrong bytes).  The device address comes from
+// cudaGetSymbolAddress, per device (every GPU has its own copy), asked for with that device current.
+constexpr int NS_MAX_DEVICES = 64;
+static uint32_t* g_ns_addr[NS_MAX_DEVICES];
+static int g_ns_sms[NS_MAX_DEVICES];
+
+static int normals_static_setup(int device, uint32_t** base, int* sm_count) {
+  SG_CHECK(device >= 0 && device < NS_MAX_DEVICES, SPRAYGPU_ERR_LIMIT, "compute_normals_static: CUDA device %d (at most %d)",
+           device, NS_MAX_DEVICES);
+  uint32_t* p = __atomic_load_n(&g_ns_addr[device], __ATOMIC_ACQUIRE);
+  if (!p) {
+    // racing first calls resolve the same address twice: harmless
+    void* sym = nullptr;
+    SG_CUDA(cudaGetSymbolAddress(&sym, g_normals_scratch));
+    SG_CHECK(sym != nullptr, SPRAYGPU_ERR_CUDA, "compute_normals_static: no device address for the scratch array");
+    int sms = 0;
+    SG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    g_ns_sms[device] = sms > 0 ? sms : 148;
+    p = (uint32_t*)sym;
+    __atomic_store_n(&g_ns_addr[device], p, __ATOMIC_RELEASE);
+  }
+  *base = p;
+  *sm_count = g_ns_sms[device];
+  return SPRAYGPU_OK;
+}
+
+static int ns_device_pointer(const void* p, int device, const char* what) {
+  cudaPointerAttributes at;
+  SG_CUDA(cudaPointerGetAttributes(&at, p));
+  SG_CHECK((at.type == cudaMemoryTypeDevice && at.device == device) || at.type == cudaMemoryTypeManaged, SPRAYGPU_ERR_ARG,
+           "compute_normals_static: %s must be device memory of the current GPU (%d); host arrays would need a staging "
+           "allocation, which this entry point never makes", what, device);
+  return SPRAYGPU_OK;
+}
+
 }  // namespace spraygpu
+
+using namespace spraygpu;
+
+extern "C" int spraygpu_compute_normals_static(const float* xyz, size_t nv, const uint32_t* idx, size_t nf, float* normals,
+                                               void* cuda_stream) {
+  SG_CHECK(xyz && idx && normals && nv >= 1 && nf >= 1, SPRAYGPU_ERR_ARG, "compute_normals_static: bad argument (nv=%zu nf=%zu)", nv, nf);
+  SG_CHECK(nv <= NS_MAXV && nf <= NS_MAXF, SPRAYGPU_ERR_LIMIT,
+           "compute_normals_static: %zu vertices / %zu faces exceed the built-in scratch (at most %zu / %zu); use "
+           "spraygpu_scene_commit, which allocates",
+           nv, nf, NS_MAXV, NS_MAXF);
+  int device = -1;
+  SG_CUDA(cudaGetDevice(&device));
+  uint32_t* S = nullptr;
+  int sms = 148, rc;
+  if ((rc = normals_static_setup(device, &S, &sms))) return rc;   // first call per GPU: resolves the array's device address
+  if ((rc = ns_device_pointer(xyz, device, "xyz")) || (rc = ns_device_pointer(idx, device, "idx")) ||
+      (rc = ns_device_pointer(normals, device, "normals")))
+    return rc;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  uint32_t *vcnt = S + NS_VCNT, *vstart = S + NS_VSTART, *vfill = S + NS_VFILL, *vlist = S + NS_VLIST, *heavy = S + NS_HEAVY;
+  unsigned int* ctr = S + NS_CTR;
+  const int npairs = (int)(3 * nf), T = 256;
+
+  // what has to start at zero (the array still holds the previous call's values)
+  SG_CUDA(cudaMemsetAsync(ctr, 0, sizeof(uint32_t) * 4, st));
+  SG_CUDA(cudaMemsetAsync(vcnt, 0, sizeof(uint32_t) * nv, st));
+  SG_CUDA(cudaMemsetAsync(vfill, 0, sizeof(uint32_t) * nv, st));
+
+  // an index >= nv would become out-of-bounds writes into the scratch array: check before the scatter, as
+  // spraygpu_scene_set_mesh does (4 bytes come back to the host; the call waits for the stream here)
+  max_index_kernel<<<(int)std::min<size_t>(((size_t)npairs + 255) / 256, (size_t)sms * 8), 256, 0, st>>>(idx, (size_t)npairs, ctr + 2);
+  SG_CUDA(cudaGetLastError());
+  uint32_t h_max = 0;
+  SG_CUDA(cudaMemcpyAsync(&h_max, ctr + 2, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  SG_CUDA(cudaStreamSynchronize(st));
+  SG_CHECK((size_t)h_max < nv, SPRAYGPU_ERR_ARG, "compute_normals_static: face index %u out of range (nv = %zu)", h_max, nv);
+
+  vcount_kernel<<<grid_for((size_t)npairs, T), T, 0, st>>>(idx, npairs, vcnt);
+  valloc_kernel<<<grid_for(nv, 1024), 1024, 0, st>>>(vcnt, nv, vstart, ctr + 0);
+  vfill_kernel<<<grid_for((size_t)npairs, T), T, 0, st>>>(idx, npairs, vstart, vfill, vlist);
+  normals_light_kernel<<<grid_for(nv, T), T, 0, st>>>(xyz, idx, vlist, vstart, vcnt, normals, nv, heavy, ctr + 1);
+  normals_heavy_kernel<<<std::min(sms * 4, npairs / (NRM_LIGHT_MAX + 1) + 1), 256, 0, st>>>(xyz, idx, vlist, vstart, vcnt, normals,
+                                                                                          heavy, ctr + 1);
+  SG_CUDA(cudaGetLastError());
+  return SPRAYGPU_OK;
+}
