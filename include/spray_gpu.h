@@ -360,7 +360,12 @@ SPRAYGPU_API float* spraygpu_image_host(spraygpu_image img);                 /* 
 SPRAYGPU_API float* spraygpu_image_root(spraygpu_image img);                 /* the root's composite as mapped in THIS process (device) */
 /* Which rows this rank renders: blocks [row_begin[b], row_begin[b+1]) with owner[b] == rank (owner NULL: all mine;
  * owner[b] == -1: rendered by nobody on this communicator).
- * Replaces the rank's stripe of ImageScheduleTileList (src/render/tile.cc:317-391). */
+ * Replaces the rank's stripe of ImageScheduleTileList (src/render/tile.cc:317-391).
+ * May be called again later (re-balancing): rows this rank gives up are RELEASED — what its earlier flushes left
+ * non-zero in them at the root composite / the host image is zeroed there, after pending asynchronous flushes have
+ * landed — so the new owner starts from black.  Call it between a flush and the next trace (unflushed pixels of released
+ * rows stay in the render target).  Collective when the image was created with a comm (every rank calls it; ranks
+ * meet before anyone flushes under the new ownership). */
 SPRAYGPU_API int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_begin /* nblocks + 1 */,
                                          const int32_t* owner /* nblocks or NULL */);
 /* HdrImage::composite (to_root) and/or the download into HdrImage::buf (to_host) for this rank's rows, then

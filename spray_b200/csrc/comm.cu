@@ -99,36 +99,79 @@ void** comm_p2p_slot(Comm* c, void (***free_fn)(Comm*, void*), int which) { *fre
 // only_rank >= 0: map that rank's buffer only (the others stay nullptr)
 int comm_shared_alloc(Comm* c, size_t bytes, void** local, std::vector<void*>* mapped, int only_rank) {
   SG_CUDA(cudaSetDevice(c->dev->cuda_device));
+  *local = nullptr;
+  mapped->clear();
   void* p = nullptr;
+  char* d_h = nullptr;
   SG_CUDA(cudaMalloc(&p, bytes));
-  SG_CUDA(cudaMemsetAsync(p, 0, bytes, c->dev->stream));
-  mapped->assign((size_t)c->nranks, nullptr);
-  (*mapped)[(size_t)c->rank] = p;
-  *local = p;
-  if (c->nranks == 1) { SG_CUDA(cudaStreamSynchronize(c->dev->stream)); return SPRAYGPU_OK; }
+  // every error return below gives back what was taken so far (the caller sees *local == NULL and an empty `mapped`)
+  auto fail = [&](int code) {
+    for (int r = 0; r < (int)mapped->size(); ++r)
+      if (r != c->rank && (*mapped)[(size_t)r]) cudaIpcCloseMemHandle((*mapped)[(size_t)r]);
+    mapped->clear();
+    if (d_h) cudaFree(d_h);
+    cudaFree(p);
+    cudaGetLastError();
+    return code;
+  };
+#define SA_CUDA(call)                                                                                       \
+  do {                                                                                                      \
+    cudaError_t e__ = (call);                                                                               \
+    if (e__ != cudaSuccess) {                                                                               \
+      set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));                \
+      return fail(SPRAYGPU_ERR_CUDA);                                                                       \
+    }                                                                                                       \
+  } while (0)
+  SA_CUDA(cudaMemsetAsync(p, 0, bytes, c->dev->stream));
+  if (c->nranks == 1) {
+    SA_CUDA(cudaStreamSynchronize(c->dev->stream));
+    mapped->assign(1, p);
+    *local = p;
+    return SPRAYGPU_OK;
+  }
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   cudaIpcMemHandle_t mine;
-  SG_CUDA(cudaIpcGetMemHandle(&mine, p));
-  char* d_h = nullptr;
-  SG_CUDA(cudaMalloc((void**)&d_h, 64 * (size_t)c->nranks));
-  SG_CUDA(cudaMemcpyAsync(d_h + 64 * (size_t)c->rank, &mine, 64, cudaMemcpyHostToDevice, c->dev->stream));
-  SG_NCCL(g_nccl.AllGather(d_h + 64 * (size_t)c->rank, d_h, 64, ncclChar, c->comm, c->dev->stream));
+  SA_CUDA(cudaIpcGetMemHandle(&mine, p));
+  SA_CUDA(cudaMalloc((void**)&d_h, 64 * (size_t)c->nranks));
+  SA_CUDA(cudaMemcpyAsync(d_h + 64 * (size_t)c->rank, &mine, 64, cudaMemcpyHostToDevice, c->dev->stream));
+  {
+    ncclResult_t nr = g_nccl.AllGather(d_h + 64 * (size_t)c->rank, d_h, 64, ncclChar, c->comm, c->dev->stream);
+    if (nr != ncclSuccess) { set_error("comm_shared_alloc: ncclAllGather failed: %s", g_nccl.GetErrorString(nr)); return fail(SPRAYGPU_ERR_CUDA); }
+  }
   std::vector<cudaIpcMemHandle_t> all((size_t)c->nranks);
-  SG_CUDA(cudaMemcpyAsync(all.data(), d_h, 64 * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->dev->stream));
-  SG_CUDA(cudaStreamSynchronize(c->dev->stream));
+  SA_CUDA(cudaMemcpyAsync(all.data(), d_h, 64 * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->dev->stream));
+  SA_CUDA(cudaStreamSynchronize(c->dev->stream));
   cudaFree(d_h);
+  d_h = nullptr;
+  mapped->assign((size_t)c->nranks, nullptr);
   for (int r = 0; r < c->nranks; ++r) {
     if (r == c->rank || (only_rank >= 0 && r != only_rank)) continue;
     void* q = nullptr;
     cudaError_t e = cudaIpcOpenMemHandle(&q, all[(size_t)r], cudaIpcMemLazyEnablePeerAccess);
     if (e != cudaSuccess) {
       set_error("cudaIpcOpenMemHandle(rank %d) failed: %s (peer access over NVLink is required)", r, cudaGetErrorString(e));
-      cudaGetLastError();
-      return SPRAYGPU_ERR_CUDA;
+      return fail(SPRAYGPU_ERR_CUDA);
     }
     (*mapped)[(size_t)r] = q;
   }
+#undef SA_CUDA
+  (*mapped)[(size_t)c->rank] = p;
+  *local = p;
   return SPRAYGPU_OK;
+}
+// Collective agreement on a set-up step: returns 1 only if EVERY rank passed ok != 0 (min over ranks), so that all ranks
+// take the same branch afterwards — one rank bailing out alone would leave its peers in the next collective for ever.
+// Also a rendezvous (stream sync + all-reduce), like comm_host_barrier.  -1: the exchange itself failed.
+int comm_all_ok(Comm* c, int ok) {
+  if (c->nranks == 1) return ok ? 1 : 0;
+  if (cudaSetDevice(c->dev->cuda_device) != cudaSuccess) return -1;
+  unsigned long long v = ok ? 1ull : 0ull;
+  unsigned long long* d = c->dev->d_counters + 9;        // scratch word no kernel uses
+  if (cudaMemcpyAsync(d, &v, sizeof(v), cudaMemcpyHostToDevice, c->dev->stream) != cudaSuccess) return -1;
+  if (g_nccl.AllReduce(d, d, 1, ncclUint64, ncclMin, c->comm, c->dev->stream) != ncclSuccess) return -1;
+  if (cudaMemcpyAsync(&v, d, sizeof(v), cudaMemcpyDeviceToHost, c->dev->stream) != cudaSuccess) return -1;
+  if (cudaStreamSynchronize(c->dev->stream) != cudaSuccess) return -1;
+  return v ? 1 : 0;
 }
 // collective: every rank must have stopped using the peers' mappings (the caller synchronises ranks first)
 void comm_shared_free(Comm* c, void* local, std::vector<void*>* mapped) {

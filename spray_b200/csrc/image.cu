@@ -32,6 +32,7 @@ struct Comm;
 int comm_shared_alloc(Comm* c, size_t bytes, void** local, std::vector<void*>* mapped, int only_rank);
 void comm_shared_free(Comm* c, void* local, std::vector<void*>* mapped);
 int comm_host_barrier(Comm* c);
+int comm_all_ok(Comm* c, int ok);
 int comm_rank(const Comm* c);
 int comm_size(const Comm* c);
 Device* comm_device(const Comm* c);
@@ -58,7 +59,7 @@ struct Image {
   bool shm_owner = false;
   size_t bytes = 0;
   // rows this rank renders: blocks [row_begin[b], row_begin[b+1]) with owner[b] == rank
-  std::vector<int32_t> my_begin, my_rows;
+  std::vector<int2> my_blocks;         // host copy of d_blocks (set_rows compares the old and the new ownership)
   int2* d_blocks = nullptr;            // (first row, row count) of my blocks
   int nmy = 0, max_rows = 0;
   uint32_t* d_prev_root = nullptr;     // 1 bit / pixel: the root composite holds a non-zero value there
@@ -158,9 +159,34 @@ __global__ void __launch_bounds__(64) image_store_kernel(const uint32_t* __restr
   for (; e < n; e += stride) host[list_idx[e]] = list_val[e];
 }
 
+// Rows that LEAVE this rank (spraygpu_image_set_rows): the "what the destination holds" bits are per rank, so the new
+// owner knows nothing about the non-zero pixels this rank's flushes left at the destinations and would never overwrite
+// the ones it renders black.  The old owner therefore zeroes them there and forgets them.  One warp per bitmap word.
+__global__ void __launch_bounds__(256) image_release_kernel(float4* __restrict__ root, float4* __restrict__ host,
+                                                            uint32_t* __restrict__ prev_root, uint32_t* __restrict__ prev_host,
+                                                            const int2* __restrict__ ranges, int image_w) {
+  const int2 r = ranges[blockIdx.y];
+  const size_t word0 = ((size_t)r.x * image_w) >> 5, words = ((size_t)r.y * image_w) >> 5;
+  const int lane = threadIdx.x & 31;
+  const size_t warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (size_t w = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < words; w += warps) {
+    const uint32_t mr = root ? prev_root[word0 + w] : 0u, mh = host ? prev_host[word0 + w] : 0u;
+    if (mr >> lane & 1u) root[((word0 + w) << 5) + lane] = zero;
+    if (mh >> lane & 1u) host[((word0 + w) << 5) + lane] = zero;
+    __syncwarp();
+    if (lane == 0) {
+      if (mr) prev_root[word0 + w] = 0u;
+      if (mh) prev_host[word0 + w] = 0u;
+    }
+  }
+}
+
 }  // namespace spraygpu
 
 using namespace spraygpu;
+
+static int image_set_rows_impl(Image* im, int nblocks, const int32_t* row_begin, const int32_t* owner, bool collective);
 
 extern "C" {
 
@@ -188,12 +214,23 @@ int spraygpu_image_create(spraygpu_device dev_h, spraygpu_comm comm_h, int image
     cudaMemsetAsync(im->d_prev_root, 0, words * 4, dev->stream);
     cudaMemsetAsync(im->d_prev_host, 0, words * 4, dev->stream);
     cudaMemsetAsync(im->d_flushed, 0, 16, dev->stream);
+    // Collective set-up steps end in comm_all_ok(): a rank that failed keeps walking through the remaining rendezvous
+    // points instead of bailing out alone, and EVERY rank returns the error — a lone early return would leave the
+    // peers holding an image one rank does not have, hanging in the next collective.
     if (comm && im->nranks > 1) {
       // the composite lives on the root; the other ranks allocate a token buffer so that the exchange stays symmetric
       void* local = nullptr;
-      rc = comm_shared_alloc(comm, im->rank == im->root ? im->bytes : 256, &local, &im->root_mapped, im->root);
-      if (rc) break;
+      const int arc = comm_shared_alloc(comm, im->rank == im->root ? im->bytes : 256, &local, &im->root_mapped, im->root);
       im->d_root_local = (float4*)local;
+      const int all = comm_all_ok(comm, arc == SPRAYGPU_OK);
+      if (all != 1) {
+        if (arc == SPRAYGPU_OK) set_error("image_create: another rank could not set up the peer-mapped composite");
+        // everybody is here (comm_all_ok is a rendezvous): drop the mappings now, so that no rank's destroy waits at a
+        // barrier the rank that failed never reaches
+        comm_shared_free(comm, im->d_root_local, &im->root_mapped);
+        im->d_root_local = nullptr;
+        rc = arc ? arc : SPRAYGPU_ERR_STATE; break;
+      }
     }
     // host image
     if (shm_name && shm_name[0]) {
@@ -205,18 +242,37 @@ int spraygpu_image_create(spraygpu_device dev_h, spraygpu_comm comm_h, int image
         if (fd >= 0 && ftruncate(fd, (off_t)im->bytes) != 0) { close(fd); fd = -1; }
         im->shm_owner = fd >= 0;
       }
-      if (comm) { rc = comm_host_barrier(comm); if (rc) break; }       // the segment exists before anyone opens it
-      if (im->rank != im->root) fd = shm_open(im->shm_name.c_str(), O_RDWR, 0600);
-      if (fd < 0) { set_error("image_create: shm_open(%s) failed", im->shm_name.c_str()); rc = SPRAYGPU_ERR_STATE; break; }
-      void* p = mmap(nullptr, im->bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-      close(fd);
-      if (p == MAP_FAILED) { set_error("image_create: mmap of %s failed", im->shm_name.c_str()); rc = SPRAYGPU_ERR_STATE; break; }
-      if (im->rank == im->root) memset(p, 0, im->bytes);
-      im->h_image = (float4*)p;
-      if (cudaHostRegister(p, im->bytes, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) {
-        set_error("image_create: cudaHostRegister failed: %s", cudaGetErrorString(cudaGetLastError())); rc = SPRAYGPU_ERR_CUDA; break;
+      // the segment exists before anyone opens it — or nobody goes on
+      if (comm && comm_all_ok(comm, im->rank != im->root || fd >= 0) != 1) {
+        if (fd >= 0) close(fd);
+        set_error("image_create: the root could not create the shared-memory segment %s", im->shm_name.c_str());
+        rc = SPRAYGPU_ERR_STATE; break;
       }
-      if (comm) { rc = comm_host_barrier(comm); if (rc) break; }       // zero-filled before anyone flushes into it
+      int step = 0;       // 0 ok, else what failed on THIS rank
+      if (im->rank != im->root) fd = shm_open(im->shm_name.c_str(), O_RDWR, 0600);
+      if (fd < 0) step = 1;
+      void* p = MAP_FAILED;
+      if (!step) {
+        p = mmap(nullptr, im->bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        close(fd);
+        if (p == MAP_FAILED) step = 2;
+      }
+      if (!step) {
+        if (im->rank == im->root) memset(p, 0, im->bytes);
+        im->h_image = (float4*)p;
+        if (cudaHostRegister(p, im->bytes, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) {
+          cudaGetLastError();
+          munmap(p, im->bytes); im->h_image = nullptr;      // destroy must not unregister what was never registered
+          step = 3;
+        }
+      }
+      // zero-filled and mapped everywhere before anyone flushes into it
+      const int all = comm ? comm_all_ok(comm, step == 0) : (step == 0);
+      if (all != 1) {
+        static const char* what[] = {"another rank failed to map the shared host image", "shm_open failed", "mmap failed", "cudaHostRegister failed"};
+        set_error("image_create: %s (%s)", what[step], im->shm_name.c_str());
+        rc = step == 3 ? SPRAYGPU_ERR_CUDA : SPRAYGPU_ERR_STATE; break;
+      }
     } else {
       if (cudaHostAlloc((void**)&im->h_image, im->bytes, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) {
         set_error("image_create: cudaHostAlloc failed: %s", cudaGetErrorString(cudaGetLastError())); rc = SPRAYGPU_ERR_CUDA; break;
@@ -232,7 +288,7 @@ int spraygpu_image_create(spraygpu_device dev_h, spraygpu_comm comm_h, int image
   *out = (spraygpu_image)im;
   // default: one block = the whole image, rendered by this rank
   const int32_t rb[2] = {0, image_h};
-  return spraygpu_image_set_rows(*out, 1, rb, nullptr);
+  return image_set_rows_impl(im, 1, rb, nullptr, false);   // nothing flushed yet: nothing to hand over, no rendezvous
 }
 
 int spraygpu_image_destroy(spraygpu_image img) {
@@ -280,28 +336,7 @@ float* spraygpu_image_root(spraygpu_image img) {
 
 int spraygpu_image_set_rows(spraygpu_image img, int nblocks, const int32_t* row_begin, const int32_t* owner) {
   SG_CHECK(img && nblocks >= 0 && (row_begin || nblocks == 0), SPRAYGPU_ERR_ARG, "image_set_rows: bad argument");
-  Image* im = (Image*)img;
-  std::vector<int2> mine;
-  int max_rows = 0;
-  for (int b = 0; b < nblocks; ++b) {
-    SG_CHECK(row_begin[b] >= 0 && row_begin[b] <= row_begin[b + 1] && row_begin[b + 1] <= im->h, SPRAYGPU_ERR_ARG,
-             "image_set_rows: block %d = rows [%d, %d) of %d", b, row_begin[b], row_begin[b + 1], im->h);
-    if (owner) SG_CHECK(owner[b] >= -1 && owner[b] < im->nranks, SPRAYGPU_ERR_ARG, "image_set_rows: block %d owner %d", b, owner[b]);
-    if (owner && owner[b] != im->rank) continue;
-    const int rows = row_begin[b + 1] - row_begin[b];
-    if (rows <= 0) continue;
-    mine.push_back(make_int2(row_begin[b], rows));
-    max_rows = std::max(max_rows, rows);
-  }
-  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
-  SG_CUDA(cudaStreamSynchronize(im->dev->stream));
-  if (im->d_blocks) { cudaFree(im->d_blocks); im->d_blocks = nullptr; }
-  im->nmy = (int)mine.size(); im->max_rows = max_rows;
-  if (im->nmy) {
-    SG_CUDA(cudaMalloc((void**)&im->d_blocks, sizeof(int2) * mine.size()));
-    SG_CUDA(cudaMemcpy(im->d_blocks, mine.data(), sizeof(int2) * mine.size(), cudaMemcpyHostToDevice));
-  }
-  return SPRAYGPU_OK;
+  return image_set_rows_impl((Image*)img, nblocks, row_begin, owner, true);
 }
 
 static int image_launch_flush(Image* im, int to_root, int to_host, int clear, cudaStream_t st, int list /* -1: store directly */) {
@@ -432,3 +467,62 @@ int spraygpu_image_barrier(spraygpu_image img) {
 }
 
 }  // extern "C"
+
+// set_rows proper.  Rows this rank gives up are released first (image_release_kernel): pending asynchronous stores are
+// waited for, the pixels this rank left non-zero at the root composite / the host image are zeroed there, and — with a
+// communicator — all ranks meet, so that a new owner's first flush cannot be overtaken by the old owner's zeroes.
+static int image_set_rows_impl(Image* im, int nblocks, const int32_t* row_begin, const int32_t* owner, bool collective) {
+  std::vector<int2> mine;
+  int max_rows = 0;
+  for (int b = 0; b < nblocks; ++b) {
+    SG_CHECK(row_begin[b] >= 0 && row_begin[b] <= row_begin[b + 1] && row_begin[b + 1] <= im->h, SPRAYGPU_ERR_ARG,
+             "image_set_rows: block %d = rows [%d, %d) of %d", b, row_begin[b], row_begin[b + 1], im->h);
+    if (owner) SG_CHECK(owner[b] >= -1 && owner[b] < im->nranks, SPRAYGPU_ERR_ARG, "image_set_rows: block %d owner %d", b, owner[b]);
+    if (owner && owner[b] != im->rank) continue;
+    const int rows = row_begin[b + 1] - row_begin[b];
+    if (rows <= 0) continue;
+    mine.push_back(make_int2(row_begin[b], rows));
+    max_rows = std::max(max_rows, rows);
+  }
+  SG_CUDA(cudaSetDevice(im->dev->cuda_device));
+  SG_CUDA(cudaStreamSynchronize(im->dev->stream));
+  if (im->flush_stream) SG_CUDA(cudaStreamSynchronize(im->flush_stream));
+  // rows that were mine and are not any more
+  std::vector<int2> released;
+  if (!im->my_blocks.empty()) {
+    std::vector<char> keep((size_t)im->h, 0), had((size_t)im->h, 0);
+    for (const int2& b : mine) std::fill(keep.begin() + b.x, keep.begin() + b.x + b.y, 1);
+    for (const int2& b : im->my_blocks) std::fill(had.begin() + b.x, had.begin() + b.x + b.y, 1);
+    for (int y = 0; y < im->h;) {
+      if (!(had[(size_t)y] && !keep[(size_t)y])) { ++y; continue; }
+      int y1 = y;
+      while (y1 < im->h && had[(size_t)y1] && !keep[(size_t)y1]) ++y1;
+      released.push_back(make_int2(y, y1 - y));
+      y = y1;
+    }
+  }
+  if (!released.empty()) {
+    float4* root = im->nranks > 1 ? (float4*)im->root_mapped[(size_t)im->root] : nullptr;
+    int2* d_ranges = nullptr;
+    SG_CUDA(cudaMalloc((void**)&d_ranges, sizeof(int2) * released.size()));
+    cudaError_t e = cudaMemcpy(d_ranges, released.data(), sizeof(int2) * released.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+      image_release_kernel<<<dim3((unsigned)std::max(1, im->dev->sm_count * 4 / (int)released.size()), (unsigned)released.size()), 256, 0,
+                             im->dev->stream>>>(root, im->h_image_dev, im->d_prev_root, im->d_prev_host, d_ranges, im->w);
+      im->dev->launches++;
+      e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaStreamSynchronize(im->dev->stream);
+    }
+    cudaFree(d_ranges);
+    if (e != cudaSuccess) { set_error("image_set_rows: releasing rows failed: %s", cudaGetErrorString(e)); return SPRAYGPU_ERR_CUDA; }
+  }
+  if (collective && im->comm) { int rc = comm_host_barrier(im->comm); if (rc) return rc; }
+  if (im->d_blocks) { cudaFree(im->d_blocks); im->d_blocks = nullptr; }
+  im->nmy = (int)mine.size(); im->max_rows = max_rows;
+  im->my_blocks = mine;
+  if (im->nmy) {
+    SG_CUDA(cudaMalloc((void**)&im->d_blocks, sizeof(int2) * mine.size()));
+    SG_CUDA(cudaMemcpy(im->d_blocks, mine.data(), sizeof(int2) * mine.size(), cudaMemcpyHostToDevice));
+  }
+  return SPRAYGPU_OK;
+}

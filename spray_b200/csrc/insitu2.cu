@@ -422,7 +422,7 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
   void** slot = comm_p2p_slot(comm, &free_slot, 0);
   if (!*slot) { *slot = new P2PState(); *free_slot = p2p_destroy; }
   P2PState* S = (P2PState*)*slot;
-  SG_CHECK(!S->h_err || *S->h_err == 0u, SPRAYGPU_ERR_STATE, "trace_tile_insitu_p2p: an earlier peer barrier timed out (a rank died or the ranks' call sequences differ)");
+  { int erc = p2p_take_error(S->h_err, "trace_tile_insitu_p2p"); if (erc) return erc; }
   int rc = upload_domain_table(dev);
   if (rc) return rc;
   const size_t n = (size_t)tile.w * tile.h * shade->pixel_samples;
@@ -446,7 +446,7 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
     char* mine = (char*)S->local;
     auto barrier_wait = [&]() {
       ++S->seq;
-      p2p_wait_kernel<<<1, 1, 0, st>>>((volatile unsigned long long*)mine, S->seq * (unsigned long long)(nranks - 1), S->h_err_dev);
+      p2p_wait_kernel<<<1, 1, 0, st>>>((volatile unsigned long long*)mine, S->seq * (unsigned long long)(nranks - 1), S->h_err_dev, p2p_timeout_cycles());
       dev->launches++;
     };
     const size_t dsmem = (dom_smem_bytes(dev->ndomains, dev->tlas_n, 0) + 15) & ~(size_t)15;
@@ -514,7 +514,7 @@ extern "C" int spraygpu_trace_tile_insitu_p2p(spraygpu_device dev_h, spraygpu_co
     unsigned long long* h = (unsigned long long*)dev->pinned;
     SG_CUDA(cudaMemcpyAsync(h, dev->d_counters, sizeof(unsigned long long) * 8, cudaMemcpyDeviceToHost, st));
     SG_CUDA(cudaStreamSynchronize(st));
-    SG_CHECK(*S->h_err == 0u, SPRAYGPU_ERR_STATE, "trace_tile_insitu_p2p: a peer barrier timed out");
+    { int erc = p2p_take_error(S->h_err, "trace_tile_insitu_p2p"); if (erc) return erc; }
     stats->eye_rays = n; stats->radiance_rays = n + h[2]; stats->shadow_rays = h[3]; stats->domain_tests = 0;
     stats->nodes_visited = 0; stats->tris_tested = 0; stats->hits = h[7];
   }

@@ -47,15 +47,47 @@ static __global__ void p2p_signal_kernel(PeerPtrs P, int nranks, int me) {
   for (int r = 0; r < nranks; ++r)
     if (r != me) atomicAdd_system((unsigned long long*)P.base[r], 1ull);
 }
-// one thread: wait until every peer has signalled `target` barriers; ~4 s timeout instead of a hung GPU
-static __global__ void p2p_wait_kernel(volatile unsigned long long* flag, unsigned long long target, unsigned int* err) {
-  if (*(volatile unsigned int*)err) return;      // an earlier barrier already gave up: do not wait 4 s again
+// one thread: wait until every peer has signalled `target` barriers; gives up after `timeout` SM cycles (default ~4 s,
+// p2p_timeout_cycles) instead of hanging the GPU, and says so in bit 0 of the mapped error word
+#define P2P_ERR_TIMEOUT 1u
+#define P2P_ERR_OVERFLOW 2u
+static __global__ void p2p_wait_kernel(volatile unsigned long long* flag, unsigned long long target, unsigned int* err, long long timeout) {
+  if (*(volatile unsigned int*)err & P2P_ERR_TIMEOUT) return;      // an earlier barrier already gave up: do not wait again
   const long long t0 = clock64();
   while (*flag < target) {
-    if (clock64() - t0 > 8000000000ll) { *err = 1u; break; }
+    if (clock64() - t0 > timeout) { *err = *(volatile unsigned int*)err | P2P_ERR_TIMEOUT; break; }   // one thread, stream order: no atomic on mapped host memory
     __nanosleep(200);
   }
   __threadfence_system();
+}
+// SPRAY_PEER_TIMEOUT_S: seconds a rank waits for its peers at a device-side barrier (default 4).  Raise it when one
+// rank is legitimately late: under ncu / compute-sanitizer (kernels serialised and replayed), a long host-side step
+// between tiles on one rank, the first lazy module load.  Counted in SM cycles at a nominal 2 GHz.
+static inline long long p2p_timeout_cycles() {
+  static long long v = 0;
+  if (!v) {
+    const char* e = getenv("SPRAY_PEER_TIMEOUT_S");
+    double sec = e ? atof(e) : 4.0;
+    if (!(sec > 0.0)) sec = 4.0;
+    if (sec > 3600.0) sec = 3600.0;
+    v = (long long)(sec * 2.0e9);
+  }
+  return v;
+}
+// The mapped error word at the start of a tile call: report what the previous tile left there, ONCE, and clear it — the
+// communicator stays usable (a rank that was merely late has signalled by now; the barrier counters are cumulative).
+static inline int p2p_take_error(unsigned int* h_err, const char* who) {
+  if (!h_err || *h_err == 0u) return SPRAYGPU_OK;
+  const unsigned int e = *h_err;
+  *h_err = 0u;
+  if (e & P2P_ERR_TIMEOUT) {
+    set_error("%s: a peer barrier of the previous tile timed out (a rank died, the ranks' call sequences differ, or a rank was more "
+              "than SPRAY_PEER_TIMEOUT_S late); that tile's pixels are incomplete%s", who,
+              (e & P2P_ERR_OVERFLOW) ? "; an inbox also overflowed" : "");
+    return SPRAYGPU_ERR_STATE;
+  }
+  set_error("%s: an inbox overflowed in the previous tile (rays were dropped); use smaller blocking tiles", who);
+  return SPRAYGPU_ERR_LIMIT;
 }
 
 // full-warp call: one atomic per warp, returns this lane's slot (valid where pred)

@@ -141,3 +141,49 @@ def test_trace_frame_rects_equals_whole_tiles(oracle):
     with pytest.raises(capi.SprayGpuError):
         dev.trace_frame_rects(cam, sh, [(0, 0, W, 8)], [(0, 4, W, 8)], fb1)     # rectangle outside its blocking tile
     dev.close()
+
+
+def test_set_rows_releases_rows_after_a_non_black_frame():
+    """Re-partitioning AFTER pixels have been flushed: the bitmap of "what the destination holds" is per rank, so rows a
+    rank gives up must be zeroed at the destination by that rank (nobody else knows they are non-zero); rows it takes
+    back later are flushed from scratch.  Synchronous and asynchronous flushes."""
+    sc = scenes.wavelets64(8)
+    dev = capi.Device(0)
+    dev.load_scene(sc)
+    W, H = 256, 160
+    kw = dict(bounces=1, pixel_samples=1, **scenes.WAVELETS64_BLINN)
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cd = scenes.camera_frame(pos, lookat, up, 90.0, W, H)
+    for use_async in (False, True):
+        img = capi.Image(dev, None, W, H)
+
+        def flush():
+            if use_async:
+                img.flush_async(to_host=True)        # set_rows itself must wait for the pending stores
+            else:
+                img.flush(to_host=True, clear=True)
+                dev.synchronize()
+
+        _frame(dev, sc, cd, kw, img.device)
+        want = img.read_device("device")
+        assert want.any()
+        flush()
+        mine = np.zeros(H, bool); mine[0:32] = mine[64:96] = mine[128:160] = True
+        assert want[~mine].any()                                            # the rows given up are not black
+        img.set_rows([0, 32, 64, 96, 128, 160], [0, -1, 0, -1, 0])          # blocks 1 and 3 leave this rank
+        assert np.array_equal(img.host[mine], want[mine]) and not img.host[~mine].any()
+        # a different frame under the new ownership: only my rows arrive, the others stay black
+        cd2 = scenes.camera_frame(pos + np.array([25, 10, 0], np.float32), lookat, up, 90.0, W, H)
+        _frame(dev, sc, cd2, kw, img.device)
+        want2 = img.read_device("device")
+        flush(); img.wait()
+        assert np.array_equal(img.host[mine], want2[mine]) and not img.host[~mine].any()
+        # the rows come back: the leftovers of frame 2 in the target are flushed, black pixels included
+        img.set_rows([0, H], None)
+        flush(); img.wait()
+        assert np.array_equal(img.host[~mine], want2[~mine])
+        _frame(dev, sc, cd, kw, img.device)
+        flush(); img.wait()
+        assert np.array_equal(img.host, want)
+        img.close()
+    dev.close()

@@ -134,6 +134,44 @@ def test_insitu_single_rank_vs_oracle(oracle, spp, bounces):
     comm.close(); dev.close()
 
 
+def test_fwd_inbox_overflow_is_reported_once_and_cleared(monkeypatch):
+    """Ray forwarding: an inbox overflow (rays dropped) must surface even on the timed path, which passes stats = NULL —
+    the tile's last kernel mirrors it into the mapped error word, the NEXT call reports it once (SPRAYGPU_ERR_LIMIT)
+    and clears it, and the communicator works again afterwards.  SPRAY_FWD_SEG_CAP shrinks the segments for the test."""
+    import torch
+    sc = scenes.wavelets64(4)
+    dev = capi.Device(0); dev.load_scene(sc)
+    comm = capi.Comm(dev, 1, 0, capi.comm_unique_id())
+    W = H = 64
+    pos, lookat, up = scenes.default_camera_pose(scenes.scene_bounds(sc))
+    cam = capi.make_camera(scenes.camera_frame(pos, lookat, up, 90.0, W, H))
+    sh = capi.make_shade(lights=sc["lights"], bounces=1, pixel_samples=1, **scenes.WAVELETS64_BLINN)
+    owner = [0] * len(sc["domains"])
+    fb = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    good = comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner, stats=True).as_dict()
+    dev.synchronize()
+    want = fb.cpu().numpy().copy()
+    assert good["hits"] > 64
+    monkeypatch.setenv("SPRAY_FWD_SEG_CAP", "16")
+    fb.zero_()
+    comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner)                   # no stats: returns OK, rays were dropped
+    dev.synchronize()
+    monkeypatch.delenv("SPRAY_FWD_SEG_CAP")
+    with pytest.raises(capi.SprayGpuError, match="overflowed"):                        # ... and the next call says so
+        comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner)
+    fb.zero_()
+    again = comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner, stats=True).as_dict()   # reported once, then clean
+    dev.synchronize()
+    assert again == good and np.array_equal(fb.cpu().numpy(), want)
+    monkeypatch.setenv("SPRAY_FWD_SEG_CAP", "16")
+    with pytest.raises(capi.SprayGpuError, match="overflowed"):                        # with stats the same call reports it
+        comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner, stats=True)
+    monkeypatch.delenv("SPRAY_FWD_SEG_CAP")
+    fb.zero_()
+    assert comm.trace_tile_insitu_fwd(cam, sh, (0, 0, W, H), fb, 4, owner, stats=True).as_dict() == good
+    comm.close(); dev.close()
+
+
 def test_insitu_rejects_glass_and_host_fb():
     sc = scenes.wavelets64(2)
     sc["domains"][1]["mtl"] = (scenes.MTL_GLASS, (1.0, 1.5, 0))
