@@ -177,21 +177,27 @@ def ncu_counters(workload_name):
     return ent[workload_name], ent[workload_name].get("source", "profiles/ncu_counters.json")
 
 
-def run_cpu(sc, cd, shade, W, H, steps, warmup):
-    """Oracle (CPU restatement, OpenMP) on the WHOLE frame.  Returns (Mrays/s, seconds/step, rays, cores)."""
+def run_cpu(sc, cd, shade, W, H, steps, warmup, tiles=None, keep=None):
+    """Oracle (CPU restatement, OpenMP) on the WHOLE frame, cut into the same blocking tiles as the GPU arm (sample ids,
+    and with them the seeds, are tile-relative).  Returns (Mrays/s, seconds/step, rays, cores); with `keep` (a dict) the
+    last frame, its counters and the oracle scene are left in it for the parity check."""
     from oracle import pyoracle as O
+    from spray_b200 import scenes
     osc = O.Scene(sc["domains"])
     cam = O.camera_from_desc(cd)
-    sh, keep = O.make_shade(lights=sc["lights"], **shade)
-    tile = (0, 0, W, H)
+    sh, keep_alive = O.make_shade(lights=sc["lights"], **shade)
+    if tiles is None:
+        tiles = scenes.image_schedule_tiles(W, H, shade["pixel_samples"], 1, 0)
     times, rays = [], 0
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        fb, st = osc.render(cam, sh, [tile])
+        fb, st = osc.render(cam, sh, list(tiles))
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
             rays = st.radiance_rays + st.shadow_rays
+    if keep is not None:
+        keep.update(frame=fb, stats=st, scene=osc)
     sec = float(np.mean(times))
     return rays / sec / 1e6, sec, int(rays), O.lib().orc_num_threads()
 
@@ -229,38 +235,54 @@ class Timer:
             ms = float(t.item())
         return ms, launches
 
+    def fill_ms(self, reps=8):
+        """Device time of one L2 fill alone (the 256 MB store between timed iterations), CUDA events, mean of `reps`."""
+        import torch
+        self.barrier()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        for a, b in evs:
+            a.record(self.stream)
+            self.flush.fill_(1)
+            b.record(self.stream)
+        torch.cuda.synchronize()
+        return float(np.mean([a.elapsed_time(b) for a, b in evs]))
+
     def pipelined(self, step, join, finish, steps, warmup):
-        """K frames back to back whose read-back overlaps the next frame.  Per frame one event pair on the device stream
-        around `step` (trace + on-device compaction of the frame's pixels; the PCIe stores of the PREVIOUS frame run
-        inside that interval on the image's stream), the L2 fill between frames outside the events as in the device-timed
-        figure, plus the TAIL: `join` makes the device stream wait for the last frame's stores before the closing event.
-        ms per frame = (sum of the frame intervals + tail) / K: every byte of every frame is inside a timed interval."""
+        """K frames back to back whose read-back overlaps the next frame (`step` = trace + on-device compaction of the
+        frame's pixels; the PCIe stores of frame k run on the image's own stream while frame k + 1 is traced).
+
+        ONE event pair brackets the whole sequence: opened before frame 0's L2 fill, closed after `join` has made the
+        device stream wait for the last frame's stores.  The K fills inside it are taken out with a separately measured
+        fill time: ms per frame = (bracket - K * fill) / K.  The stores of frame k also progress while the fill before
+        frame k + 1 runs, so this can understate a pipeline whose stores are LONGER than its trace by at most one fill
+        per frame; `upper` = bracket / K (fills counted as frame time) is returned beside it and printed, and the
+        per-frame-synchronised figure stays in the line.  Returns (ms, upper_ms, fill_ms)."""
         import torch
         for _ in range(warmup):
             step()
         finish()
+        fill = self.fill_ms()
         self.barrier()
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        for a, b in evs:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        for _ in range(steps):
             self.flush.fill_(1)
-            a.record(self.stream)
             step()
-            b.record(self.stream)
         join()
-        tail = torch.cuda.Event(enable_timing=True)
-        tail.record(self.stream)
+        e1.record(self.stream)
         finish()
         self.barrier()
-        ms = (float(sum(a.elapsed_time(b) for a, b in evs)) + float(evs[-1][1].elapsed_time(tail))) / steps
+        total = float(e0.elapsed_time(e1))
+        ms, upper = (total - steps * fill) / steps, total / steps
         if self.world > 1:
             import torch.distributed as dist
-            t = torch.tensor([ms], device="cuda")
+            t = torch.tensor([ms, upper, fill], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+            ms, upper, fill = (float(x) for x in t.tolist())
+        return ms, upper, fill
 
 
-def single_gpu(name, dev, stream, timer, steps, warmup, with_e2e=True):
+def single_gpu(name, dev, stream, timer, steps, warmup, with_e2e=True, keep_frame=False):
     """One workload on one GPU through the fused kernel.  Returns the dict the JSON line is built from."""
     import torch
     from spray_b200 import capi, scenes
@@ -338,7 +360,7 @@ def single_gpu(name, dev, stream, timer, steps, warmup, with_e2e=True):
             dev.trace_frame(cam, sh, tiles, img.device)
             img.flush_async(to_host=True)
 
-        out["ms_e2e_pipe"] = timer.pipelined(step_pipe, img.join, img.wait, max(steps, 5), 3)
+        out["ms_e2e_pipe"], out["ms_e2e_pipe_upper"], out["ms_fill"] = timer.pipelined(step_pipe, img.join, img.wait, max(steps, 5), 3)
         img.wait()
         out["h2d"] = int(capi.C.sizeof(capi.Camera) + capi.C.sizeof(capi.Shade) + len(tiles) * 16)
         out["d2h"] = int(pix * 16 // (n_e2e + 2))
@@ -357,10 +379,46 @@ def single_gpu(name, dev, stream, timer, steps, warmup, with_e2e=True):
             dev.synchronize()
 
         out["ms_e2e_full"], _ = timer(step_full, 3, 1)
+    if keep_frame:
+        # parity material for the bench line (outside every timed region): the frame itself and the closest-hit keys of
+        # all its eye rays through the batched seam
+        fb_d.zero_()
+        dev.trace_frame(cam, sh, tiles, fb_d)
+        dev.synchronize()
+        out["frame"] = fb_d.cpu().numpy()
+        if shade["pixel_samples"] == 1:
+            n = W * H
+            rays_d = torch.zeros((n, 8), dtype=torch.float32, device="cuda")
+            dev.gen_eye_rays(cam, (0, 0, W, H), 1, rays_d)
+            keys_d = torch.zeros(n, dtype=torch.int64, device="cuda")
+            dev.intersect_domains(rays_d, n, keys_d, None)
+            dev.synchronize()
+            out["eye_rays_host"] = rays_d.cpu().numpy()
+            out["eye_keys"] = keys_d.cpu().numpy().view(np.uint64)
+            del rays_d, keys_d
     for s_ in list(scenes_by_id.values()):
         s_.close()
     dev.scenes = [s_ for s_ in dev.scenes if s_.h]
     return out
+
+
+def parity_check_of(r, kept):
+    """GPU frame of the benched workload against the oracle frame the cpu_baseline leg rendered anyway (same blocking
+    tiles): RMSE / max |diff| over RGB (north_star: RMSE <= 1e-4), equal ray counters, and — at 1 spp — the closest-hit
+    key of EVERY eye ray (stride 1) bit-equal to the oracle's."""
+    g, o = r["frame"], kept["frame"]
+    d = g[..., :3].astype(np.float64) - o[..., :3].astype(np.float64)
+    st_g, st_o = r["stats"], kept["stats"]
+    pc = {"against": "oracle O2 (CPU restatement), whole %dx%d frame" % (r["W"], r["H"]),
+          "rmse": float(np.sqrt(np.mean(d * d))), "max_abs": float(np.abs(d).max()), "tolerance_rmse": 1e-4,
+          "ray_counts_equal": bool(int(st_g["eye_rays"]) == int(st_o.eye_rays) and int(st_g["radiance_rays"]) == int(st_o.radiance_rays)
+                                   and int(st_g["shadow_rays"]) == int(st_o.shadow_rays))}
+    if "eye_keys" in r:
+        ko, _ = kept["scene"].intersect(r["eye_rays_host"])
+        pc["keys_equal_stride1"] = bool(np.array_equal(r["eye_keys"], ko))
+        pc["keys_compared"] = int(len(ko))
+    pc["ok"] = bool(pc["rmse"] <= 1e-4 and pc["ray_counts_equal"] and pc.get("keys_equal_stride1", True))
+    return pc
 
 
 def roofline_of(r, name, steps):
@@ -428,11 +486,18 @@ def main():
         if rank != 0:
             return
         sc, cd, shade, label, W, H = workload(args.workload, device_scene=False)
-        v, sec, rays, cores = run_cpu(sc, cd, shade, W, H, max(args.steps, 1), min(args.warmup, 1))
+        from spray_b200 import scenes as _scenes
+        tiles_ref = _scenes.image_schedule_tiles(W, H, shade["pixel_samples"], 1, 0)
+        kept_ref = {}
+        v, sec, rays, cores = run_cpu(sc, cd, shade, W, H, max(args.steps, 1), min(args.warmup, 1), tiles=tiles_ref, keep=kept_ref)
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic camera rays on the reference's example scene",
-                "config": {"workload": label, "rays_per_frame": rays},
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic camera rays on the reference's example scene",
+                # the same keys as the GPU arm's config (the driver compares the two dicts' keys)
+                "config": {"workload": label, "tiles_per_frame": len(tiles_ref), "l2_flush_between_steps": False,
+                           "rays_per_frame": rays, "eye_rays": int(kept_ref["stats"].eye_rays), "shadow_rays": int(kept_ref["stats"].shadow_rays),
+                           "hits": None, "parallelism": "%d host threads (OpenMP), all domains resident" % cores,
+                           "build_s_all_domains": None, "lib_build_id": None},
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                  "sample": "the whole %dx%d frame (%d rays/step); CPU restatement (oracle O2), NOT Embree" % (W, H, rays)},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -470,7 +535,7 @@ def main():
         return
 
     sampler.start()
-    r = single_gpu(args.workload, dev, stream, timer, args.steps, args.warmup)
+    r = single_gpu(args.workload, dev, stream, timer, args.steps, args.warmup, keep_frame=not args.no_cpu_baseline)
     clocks = sampler.stop()
     value = r["rays"] / (r["ms_dev"] * 1e-3) / 1e6
     e2e_sync_v = r["rays"] / (r["ms_e2e"] * 1e-3) / 1e6
@@ -478,7 +543,7 @@ def main():
     e2e_v = r["rays"] / (e2e_ms * 1e-3) / 1e6
     st = r["stats"]
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": r["ms_dev"], "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": r["ms_dev"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic camera rays on the reference's example scene (random-free)",
             "config": {"workload": r["label"], "tiles_per_frame": len(r["tiles"]), "l2_flush_between_steps": True,
                        "rays_per_frame": int(r["rays"]), "eye_rays": int(st["eye_rays"]), "shadow_rays": int(st["shadow_rays"]),
@@ -489,11 +554,13 @@ def main():
             "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"],
                     "mode": "pipelined frames: spraygpu_image_flush_async compacts frame k's pixels on the device and a few CTAs on the image's "
-                            "own stream store them into the pinned host image while frame k + 1 is traced; per-frame events on the device stream "
-                            "(L2 fill between frames outside them, as for `value`) + the tail until the last frame's stores have landed" if r["ms_e2e_pipe"] <= r["ms_e2e"] else "one frame at a time",
+                            "own stream store them into the pinned host image while frame k + 1 is traced; one event pair around all frames up to the "
+                            "moment the last frame's stores have landed, minus the separately timed L2 fills" if r["ms_e2e_pipe"] <= r["ms_e2e"] else "one frame at a time",
                     "per_frame_sync": {"value": e2e_sync_v, "ms_per_step": r["ms_e2e"],
                                        "note": "trace, flush, host synchronize per frame (no overlap between frames); L2 fill outside the events"},
                     "pipelined_ms_per_step": r["ms_e2e_pipe"],
+                    "pipelined_ms_per_step_upper": r["ms_e2e_pipe_upper"], "l2_fill_ms": r["ms_fill"],
+                    "pipelined_note": "upper = the same bracket with the L2 fills counted as frame time (frame k's stores also progress during the fill before frame k + 1)",
                     "d2h_note": "spraygpu_image_flush: pixels that are or were non-zero are stored into the pinned host image "
                                 "(full frame = %d B); host image == device frame: %s" % (r["W"] * r["H"] * 16, r["e2e_host_image_equals_device_frame"]),
                     "full_copy": {"value": r["rays"] / (r["ms_e2e_full"] * 1e-3) / 1e6, "ms_per_step": r["ms_e2e_full"],
@@ -526,9 +593,15 @@ def main():
     if not args.no_cpu_baseline:
         sc, cd, shade, label, W, H = workload(args.workload, device_scene=False) if args.workload != "c2" else (r["scene"], r["cd"], r["shade"], r["label"], r["W"], r["H"])
         nsteps = 3 if args.workload in ("c1", "c2") else 1
-        v, sec, crays, cores = run_cpu(sc, cd, shade, W, H, nsteps, 1 if nsteps > 1 else 0)
+        kept = {}
+        v, sec, crays, cores = run_cpu(sc, cd, shade, W, H, nsteps, 1 if nsteps > 1 else 0, tiles=r["tiles"], keep=kept)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": "the whole frame (%d rays), %d steps; CPU restatement (oracle O2), NOT Embree" % (crays, nsteps)}
+        if "frame" in r:
+            try:
+                line["parity_check"] = parity_check_of(r, kept)
+            except Exception as e:
+                line["parity_check"] = {"error": repr(e)[:300]}
     print(json.dumps(line))
     dev.close()
 

@@ -268,8 +268,10 @@ static void concentric_disk(float u1, float u2, float* dx, float* dy) {
     else { r = -sy; theta = 6.0f + sx / r; }
   }
   theta = (float)(theta * (M_PI / 4.f)); /* theta *= SPRAY_PI / 4.f  (double product, narrowed) */
-  *dx = r * cosf(theta);
-  *dy = r * sinf(theta);
+  /* cos / sin / pow: evaluated in double and rounded once, on BOTH sides (core.cuh cos_f64 / sin_f64 / pow_f64): equal to
+   * glibc's cosf / sinf / powf (what the reference calls) except where those are not correctly rounded */
+  *dx = r * (float)cos((double)theta);
+  *dy = r * (float)sin((double)theta);
 }
 static v3 local_to_world(v3 N, v3 v) {
   v3 dx0 = V(0, N.z, -N.y);
@@ -297,7 +299,7 @@ void orc_cosine_hemisphere(float u1, float u2, const float n[3], float wi[3], fl
 static v3 blinn_phong(float costheta, v3 kd, v3 ks, float shininess, v3 li, v3 wi, v3 n, v3 wo) {
   v3 half_hat = gnormalize(vadd(wi, wo));
   float n_dot_h = gclamp(gdot(n, half_hat), 0.0f, 1.0f);
-  v3 cs = vscale(ks, powf(n_dot_h, shininess));
+  v3 cs = vscale(ks, (float)pow((double)n_dot_h, (double)shininess));
   v3 cd = vscale(kd, costheta);
   return vmul(li, vadd(cd, cs));
 }

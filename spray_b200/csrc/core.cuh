@@ -757,6 +757,16 @@ SPRAY_HD vec3 unpack_color(uint32_t c) {
 // Sampling / BSDF pieces — reference src/render/sampler.h:49-128, sampler.cc:54-60,
 // reflection.h:126-214, light.h:41-89.
 // ---------------------------------------------------------------------------------------------
+// The three transcendentals of the shading path (cos / sin of the disk angle, the Blinn-Phong power).  The reference
+// calls glibc's cosf / sinf / powf (src/render/sampler.cc:54-60, src/render/reflection.h:202-214), which are correctly
+// rounded for all practical purposes; libdevice's float versions are 1-2 ulp off, and on a multi-bounce or AO path a few
+// ulp in a sample direction flips an occasional shadow / bounce decision (round 2: RMSE 1.4e-4 .. 2.7e-4 against the
+// CPU checker at 384^2).  Both sides — here and the CPU restatement the tests check against — evaluate in DOUBLE and round once to float:
+// the double results differ by an ulp of double at most, which changes the float in ~1 of 2^28 calls.  A few calls per
+// hit; the FP64 rate is irrelevant next to the traversal.
+SPRAY_HD float cos_f64(float x) { return (float)cos((double)x); }
+SPRAY_HD float sin_f64(float x) { return (float)sin((double)x); }
+SPRAY_HD float pow_f64(float x, float y) { return (float)pow((double)x, (double)y); }
 SPRAY_HD void concentric_disk(float u1, float u2, float* dx, float* dy) {
   float r, theta;
   float sx = sub_rn(mul_rn(2.0f, u1), 1.0f);
@@ -770,8 +780,8 @@ SPRAY_HD void concentric_disk(float u1, float u2, float* dx, float* dy) {
     else { r = -sy; theta = add_rn(6.0f, div_rn(sx, r)); }
   }
   theta = (float)((double)theta * (3.14159265358979323846 / 4.0)); // theta *= SPRAY_PI / 4.f (double)
-  *dx = mul_rn(r, cosf(theta));
-  *dy = mul_rn(r, sinf(theta));
+  *dx = mul_rn(r, cos_f64(theta));
+  *dy = mul_rn(r, sin_f64(theta));
 }
 SPRAY_HD vec3 local_to_world(vec3 N, vec3 v) {
   vec3 dx0 = mk3(0.f, N.z, -N.y);
@@ -793,7 +803,7 @@ SPRAY_HD void cosine_hemisphere(float u1, float u2, vec3 N, vec3* wi, float* pdf
 SPRAY_HD vec3 blinn_phong(float costheta, vec3 kd, vec3 ks, float shininess, vec3 li, vec3 wi, vec3 n, vec3 wo) {
   vec3 half_hat = gnormalize(gadd(wi, wo));
   float n_dot_h = gclamp(gdot(n, half_hat), 0.0f, 1.0f);
-  vec3 cs = gscale(ks, powf(n_dot_h, shininess));
+  vec3 cs = gscale(ks, pow_f64(n_dot_h, shininess));
   vec3 cd = gscale(kd, costheta);
   return gmul(li, gadd(cd, cs));
 }

@@ -129,10 +129,10 @@ def main():
                   "host==composite %s | keys equal (GPU + oracle) %s | stats equal %s (%s)"
                   % (kw, world, e_insitu, e_insitu_o, insitu_same, e_img, e_img_o, bit, host_ok, same_keys, same_stats,
                      {k: st2[k] for k in ("radiance_rays", "shadow_rays", "hits")}))
-            # GPU vs oracle: a few-ulp difference flips an occasional shadow / bounce decision at multi-bounce depth; each
-            # flipped sample moves one pixel by up to 1/spp, so the multi-bounce case gets 3e-4 (measured 1.4e-4 at 384^2);
+            # GPU vs oracle: north_star's bar (RMSE <= 1e-4) for every case, multi-bounce and AO included — cos / sin / pow
+            # are evaluated the same way on both sides since round 3 (core.cuh cos_f64 ...), so no decision flips;
             # GPU vs GPU (same arithmetic on 1 and N ranks) stays at 1e-6
-            tol_o = 1e-4 if one_add else 3e-4
+            tol_o = 1e-4
             ok = ok and e_insitu <= 1e-6 and e_img <= 1e-6 and e_insitu_o <= tol_o and e_img_o <= tol_o and bit and host_ok \
                 and insitu_same and same_keys and same_stats and ref[..., :3].max() > 0.1
         r2.close(); r1n.close(); r1.close()

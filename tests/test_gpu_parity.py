@@ -255,15 +255,19 @@ def test_render_c1(oracle, c1):
     d.close()
 
 
-@pytest.mark.parametrize("kw", [dict(bounces=1, pixel_samples=1), dict(bounces=3, pixel_samples=1),
-                                dict(bounces=2, pixel_samples=4),
-                                dict(shader=1, bounces=1, pixel_samples=1, ao_samples=4),
-                                dict(shader=1, bounces=2, pixel_samples=2, ao_samples=2)])
-def test_render_c2(oracle, dev_c2, c2, kw):
-    """Config C2 shape (wavelets64 camera/blinn): PT and AO shaders, bounces, multi-sampling."""
+@pytest.mark.parametrize("kw,W", [(dict(bounces=1, pixel_samples=1), 192), (dict(bounces=3, pixel_samples=1), 192),
+                                  (dict(bounces=2, pixel_samples=4), 192),
+                                  (dict(shader=1, bounces=1, pixel_samples=1, ao_samples=4), 192),
+                                  (dict(shader=1, bounces=2, pixel_samples=2, ao_samples=2), 192),
+                                  # the two cases round 2's 2-rank check missed the 1e-4 bar on (1.4e-4 / 2.7e-4 with
+                                  # libdevice's cosf / sinf / powf against glibc's), at that check's image size
+                                  (dict(bounces=3, pixel_samples=2), 384),
+                                  (dict(shader=1, bounces=2, pixel_samples=2, ao_samples=3), 384)])
+def test_render_c2(oracle, dev_c2, c2, kw, W):
+    """Config C2 shape (wavelets64 camera/blinn): PT and AO shaders, bounces, multi-sampling; RMSE <= 1e-4 (north_star's
+    tolerance) and equal ray counts in every case."""
     sc, osc = c2
     p = scenes.WAVELETS64_CAMERA
-    W = 192
     cd = _cam_desc(sc, W, W, (p["pos"], p["lookat"], p["up"]))
     spp = kw.get("pixel_samples", 1)
     tiles = scenes.image_schedule_tiles(W, W, spp, 1, 0, 1 << 14)
