@@ -160,6 +160,17 @@ SPRAYGPU_API int spraygpu_scene_get_info(spraygpu_scene scene, spraygpu_scene_in
 SPRAYGPU_API int spraygpu_scene_get_normals(spraygpu_scene scene, float* out_nv3);      /* [h|d] */
 SPRAYGPU_API int spraygpu_scene_get_vertices(spraygpu_scene scene, float* out_nv3);     /* world space, [h|d] */
 
+/* The benchmark's synthetic domains ("triangle soup, generated on device from a counter-based
+ * RNG ... reproducible on the CPU oracle from the same function"); stands in for PlyLoader::load of a mesh file
+ * (src/io/ply_loader.cc:179-324) when there is no file.  Triangle p of the soup is a pure function of (key, p):
+ * Philox-4x32-10 with key (key, 0) and counter (p, block, 0, 0); centre uniform in the cell [lo, hi], two edges of uniform
+ * direction and length U(0.5, 2) * h, vertices clipped to the cell; IEEE-exact float operations only, so the CPU
+ * restatement produces the same bits.  xyz: 9 * ntris floats, idx: 3 * ntris (0, 1, 2, ...) or NULL, rgb: 3 * ntris
+ * packed colours (hash of the vertex index) or NULL — DEVICE pointers on the current CUDA device; enqueued on
+ * cuda_stream.  Needs no spraygpu_device. */
+SPRAYGPU_API int spraygpu_gen_soup(uint32_t key, size_t ntris, const float lo[3], const float hi[3], float h, float* xyz,
+                                   uint32_t* idx, uint32_t* rgb, void* cuda_stream);
+
 /* Per-vertex normals WITHOUT any allocation.  No counterpart in the reference (Embree and the reference allocate
  * freely on the host); it exists for hosts that cannot let a plug-in call cudaMalloc — typically the simulation an
  * in-situ renderer lives in, which has given all of HBM to its own memory pool (a cudaMalloc would fail or eat into

@@ -107,6 +107,8 @@ def lib():
     L.orc_hit_attributes.argtypes = [vp, u64p, f32p, C.c_size_t, u32p, f32p]
     L.orc_render_tile.argtypes = [vp, C.POINTER(Camera), C.POINTER(Shade), Tile, f32p, C.POINTER(Stats)]
     L.orc_num_threads.restype = C.c_int
+    L.orc_philox4x32_10.argtypes = [u32p, u32p, u32p]
+    L.orc_gen_soup.argtypes = [C.c_uint32, C.c_size_t, f32p, f32p, C.c_float, f32p, u32p, u32p]
     _lib = L
     return L
 
@@ -294,3 +296,26 @@ def key_fields(keys):
     dom = ((keys >> np.uint64(23)) & np.uint64(0x1FF)).astype(np.int32)
     prim = (keys & np.uint64(0x7FFFFF)).astype(np.int32)
     return t, dom, prim
+
+
+def philox4x32_10(ctr, key):
+    c = np.asarray(ctr, np.uint32); k = np.asarray(key, np.uint32); out = np.zeros(4, np.uint32)
+    lib().orc_philox4x32_10(_p(c, C.c_uint32), _p(k, C.c_uint32), _p(out, C.c_uint32))
+    return out
+
+
+def soup_h(ntris, lo, hi):
+    """Mean triangle spacing of a soup cell, the float both generators are handed: extent / ntris^(1/3)."""
+    ext = np.asarray(hi, np.float32) - np.asarray(lo, np.float32)
+    return np.float32(float(ext.max()) / float(ntris) ** (1.0 / 3.0))
+
+
+def gen_soup(key, ntris, lo, hi, h=None):
+    """orc_gen_soup: (verts f32[3n,3], faces u32[n,3], rgb u32[3n]) of the counter-based soup domain."""
+    lo = np.ascontiguousarray(lo, np.float32); hi = np.ascontiguousarray(hi, np.float32)
+    if h is None:
+        h = soup_h(ntris, lo, hi)
+    xyz = np.zeros((3 * ntris, 3), np.float32); idx = np.zeros((ntris, 3), np.uint32); rgb = np.zeros(3 * ntris, np.uint32)
+    lib().orc_gen_soup(int(key) & 0xFFFFFFFF, ntris, _p(lo, C.c_float), _p(hi, C.c_float), float(h), _p(xyz, C.c_float),
+                       _p(idx, C.c_uint32), _p(rgb, C.c_uint32))
+    return xyz, idx, rgb

@@ -1176,3 +1176,68 @@ int orc_num_threads(void) {
   return 1;
 #endif
 }
+
+/* ---- counter-based triangle soup (bench configs C3 / C4) -------------------------------------------------
+ * CPU restatement of the device generator (spray_b200/csrc/build.cu, soup_kernel): Philox-4x32-10 (Salmon, Moraes,
+ * Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11; constants and round function as published, known
+ * answers in tests/test_oracle_kat.py), key (key, 0), counter (primID, block, 0, 0).  IEEE-exact float operations only
+ * (this file is built with -ffp-contract=off), so the two sides produce the same bits. */
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  uint32_t x0 = ctr[0], x1 = ctr[1], x2 = ctr[2], x3 = ctr[3], ka = key[0], kb = key[1];
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * x0, p1 = (uint64_t)0xCD9E8D57u * x2;
+    const uint32_t y0 = (uint32_t)(p1 >> 32) ^ x1 ^ ka, y2 = (uint32_t)(p0 >> 32) ^ x3 ^ kb;
+    x0 = y0; x1 = (uint32_t)p1; x2 = y2; x3 = (uint32_t)p0;
+    ka += 0x9E3779B9u; kb += 0xBB67AE85u;
+  }
+  out[0] = x0; out[1] = x1; out[2] = x2; out[3] = x3;
+}
+static inline float soup_u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-08f; }
+static void soup_edge(uint32_t key, uint32_t prim, uint32_t block0, float len, float e[3]) {
+  float dx = 1.0f, dy = 0.0f, dz = 0.0f;
+  const uint32_t k2[2] = {key, 0u};
+  for (uint32_t k = 0; k < 16u; ++k) {
+    const uint32_t c[4] = {prim, block0 + k, 0u, 0u};
+    uint32_t r[4];
+    orc_philox4x32_10(c, k2, r);
+    const float x = 2.0f * soup_u01(r[0]) - 1.0f, y = 2.0f * soup_u01(r[1]) - 1.0f, z = 2.0f * soup_u01(r[2]) - 1.0f;
+    const float q = x * x + y * y + z * z;
+    if (q > 1.0e-4f && q <= 1.0f) {
+      const float inv = 1.0f / sqrtf(q);
+      dx = x * inv; dy = y * inv; dz = z * inv;
+      break;
+    }
+  }
+  e[0] = dx * len; e[1] = dy * len; e[2] = dz * len;
+}
+void orc_gen_soup(uint32_t key, size_t ntris, const float lo[3], const float hi[3], float h, float* xyz, uint32_t* idx,
+                  uint32_t* rgb) {
+  const uint32_t k2[2] = {key, 0u};
+#pragma omp parallel for schedule(static)
+  for (int64_t pp = 0; pp < (int64_t)ntris; ++pp) {
+    const uint32_t p = (uint32_t)pp;
+    const uint32_t c0[4] = {p, 0u, 0u, 0u}, c1[4] = {p, 1u, 0u, 0u};
+    uint32_t r0[4], r1[4];
+    orc_philox4x32_10(c0, k2, r0);
+    orc_philox4x32_10(c1, k2, r1);
+    float c[3], e1[3], e2[3];
+    for (int a = 0; a < 3; ++a) c[a] = lo[a] + soup_u01(r0[a]) * (hi[a] - lo[a]);
+    const float len1 = (0.5f + 1.5f * soup_u01(r0[3])) * h, len2 = (0.5f + 1.5f * soup_u01(r1[0])) * h;
+    soup_edge(key, p, 2u, len1, e1);
+    soup_edge(key, p, 18u, len2, e2);
+    float* v = xyz + 9 * (size_t)p;
+    for (int a = 0; a < 3; ++a) {
+      v[a] = fminf(fmaxf(c[a], lo[a]), hi[a]);
+      v[3 + a] = fminf(fmaxf(c[a] + e1[a], lo[a]), hi[a]);
+      v[6 + a] = fminf(fmaxf(c[a] + e2[a], lo[a]), hi[a]);
+    }
+    for (uint32_t k = 0; k < 3u; ++k) {
+      const uint32_t i = 3u * p + k;
+      if (idx) idx[i] = i;
+      if (rgb) {
+        const uint32_t hsh = (i * 2654435761u) ^ (i >> 13);
+        rgb[i] = ((64u + (hsh & 0x7Fu)) << 16) | ((64u + ((hsh >> 8) & 0x7Fu)) << 8) | (64u + ((hsh >> 16) & 0x7Fu));
+      }
+    }
+  }
+}

@@ -138,6 +138,10 @@ void orc_gen_eye_rays_seed(const OrcCamera* cam, OrcTile tile, int spp, int eye_
 void orc_render_tile(const OrcScene*, const OrcCamera*, const OrcShade*, OrcTile tile, float* fb_rgba,
                      OrcStats* stats);
 int orc_num_threads(void);
+/* counter-based triangle soup of bench configs C3 / C4 (restates the device generator bit for bit) */
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+void orc_gen_soup(uint32_t key, size_t ntris, const float lo[3], const float hi[3], float h, float* xyz, uint32_t* idx,
+                  uint32_t* rgb);
 
 #ifdef __cplusplus
 }

@@ -98,6 +98,7 @@ _PROTOS = {
     "spraygpu_scene_get_normals": (C.c_int, [_vp, _vp]),
     "spraygpu_scene_get_vertices": (C.c_int, [_vp, _vp]),
     "spraygpu_compute_normals_static": (C.c_int, [_vp, C.c_size_t, _vp, C.c_size_t, _vp, _vp]),
+    "spraygpu_gen_soup": (C.c_int, [C.c_uint32, C.c_size_t, _vp, _vp, C.c_float, _vp, _vp, _vp, _vp]),
     "spraygpu_intersect": (C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp, _vp]),
     "spraygpu_occluded": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
     "spraygpu_domains_set": (C.c_int, [_vp, C.c_int, _vp, _vp]),
@@ -206,6 +207,14 @@ def _ptr(a):
         assert a.is_contiguous()
         return a.data_ptr()
     return a
+
+
+def gen_soup(key, ntris, lo, hi, h, xyz, idx=None, rgb=None, cuda_stream=None):
+    """spraygpu_gen_soup: the counter-based triangle soup of configs C3 / C4 written into CUDA tensors (xyz f32[9n],
+    idx i32[3n] or None, rgb i32[3n] or None) on the current device."""
+    lo = np.ascontiguousarray(lo, np.float32); hi = np.ascontiguousarray(hi, np.float32)
+    _check(lib().spraygpu_gen_soup(int(key) & 0xFFFFFFFF, int(ntris), lo.ctypes.data, hi.ctypes.data, float(np.float32(h)),
+                                   _ptr(xyz), _ptr(idx), _ptr(rgb), _vp(cuda_stream) if cuda_stream else None))
 
 
 STATIC_MAX_VERTS = 1 << 17

@@ -1054,6 +1054,78 @@ static int ns_device_pointer(const void* p, int device, const char* what) {
   return SPRAYGPU_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Counter-based triangle soup (the synthetic C3 / C4 domains of the benchmark): every triangle is a pure
+// function of (key, primID), so the bench scene is generated on the device in milliseconds AND can be handed to the
+// CPU checker, which restates this function in C, bit for bit.  Philox-4x32-10 (Salmon et al., SC'11), key = (key, 0),
+// counter = (primID, block, 0, 0).  Only IEEE-exact float operations are used (add, mul, div, sqrt, min, max; this file
+// is built with -fmad=false), and the direction of an edge comes from rejection sampling in the cube — no sin / cos /
+// log, whose device and libm versions differ in the last place.
+//   block 0      : centre x, y, z (uniform in the cell), length factor of edge 1
+//   block 1      : length factor of edge 2
+//   block 2 + k  : k-th candidate direction of edge 1, k < 16 (accepted when 1e-4 < |d|^2 <= 1), then (1, 0, 0)
+//   block 18 + k : the same for edge 2
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t k0) {
+  uint32_t x0 = c0, x1 = c1, x2 = 0u, x3 = 0u, ka = k0, kb = 0u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t h0 = __umulhi(0xD2511F53u, x0), l0 = 0xD2511F53u * x0;
+    const uint32_t h1 = __umulhi(0xCD9E8D57u, x2), l1 = 0xCD9E8D57u * x2;
+    const uint32_t y0 = h1 ^ x1 ^ ka, y2 = h0 ^ x3 ^ kb;
+    x0 = y0; x1 = l1; x2 = y2; x3 = l0;
+    ka += 0x9E3779B9u; kb += 0xBB67AE85u;
+  }
+  return make_uint4(x0, x1, x2, x3);
+}
+__device__ __forceinline__ float soup_u01(uint32_t x) { return mul_rn((float)(x >> 8), 5.9604644775390625e-08f); }   // [0, 1), exact
+__device__ __forceinline__ void soup_edge(uint32_t key, uint32_t prim, uint32_t block0, float len, float* ex, float* ey, float* ez) {
+  float dx = 1.0f, dy = 0.0f, dz = 0.0f;
+  for (uint32_t k = 0; k < 16u; ++k) {
+    const uint4 r = philox4x32_10(prim, block0 + k, key);
+    const float x = sub_rn(mul_rn(2.0f, soup_u01(r.x)), 1.0f), y = sub_rn(mul_rn(2.0f, soup_u01(r.y)), 1.0f),
+                z = sub_rn(mul_rn(2.0f, soup_u01(r.z)), 1.0f);
+    const float q = add_rn(add_rn(mul_rn(x, x), mul_rn(y, y)), mul_rn(z, z));
+    if (q > 1.0e-4f && q <= 1.0f) {
+      const float inv = div_rn(1.0f, sqrt_rn(q));
+      dx = mul_rn(x, inv); dy = mul_rn(y, inv); dz = mul_rn(z, inv);
+      break;
+    }
+  }
+  *ex = mul_rn(dx, len); *ey = mul_rn(dy, len); *ez = mul_rn(dz, len);
+}
+struct SoupArgs { uint32_t key; uint32_t n; float lo[3], hi[3], h; };
+__global__ void __launch_bounds__(256) soup_kernel(SoupArgs A, float* __restrict__ xyz, uint32_t* __restrict__ idx, uint32_t* __restrict__ rgb) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= A.n) return;
+  const uint4 r0 = philox4x32_10(p, 0u, A.key), r1 = philox4x32_10(p, 1u, A.key);
+  float c[3], e1[3], e2[3];
+  c[0] = add_rn(A.lo[0], mul_rn(soup_u01(r0.x), sub_rn(A.hi[0], A.lo[0])));
+  c[1] = add_rn(A.lo[1], mul_rn(soup_u01(r0.y), sub_rn(A.hi[1], A.lo[1])));
+  c[2] = add_rn(A.lo[2], mul_rn(soup_u01(r0.z), sub_rn(A.hi[2], A.lo[2])));
+  const float len1 = mul_rn(add_rn(0.5f, mul_rn(1.5f, soup_u01(r0.w))), A.h);
+  const float len2 = mul_rn(add_rn(0.5f, mul_rn(1.5f, soup_u01(r1.x))), A.h);
+  soup_edge(A.key, p, 2u, len1, &e1[0], &e1[1], &e1[2]);
+  soup_edge(A.key, p, 18u, len2, &e2[0], &e2[1], &e2[2]);
+  float* v = xyz + 9 * (size_t)p;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    v[a] = fminf(fmaxf(c[a], A.lo[a]), A.hi[a]);
+    v[3 + a] = fminf(fmaxf(add_rn(c[a], e1[a]), A.lo[a]), A.hi[a]);
+    v[6 + a] = fminf(fmaxf(add_rn(c[a], e2[a]), A.lo[a]), A.hi[a]);
+  }
+#pragma unroll
+  for (uint32_t k = 0; k < 3u; ++k) {
+    const uint32_t i = 3u * p + k;
+    if (idx) idx[i] = i;
+    if (rgb) {
+      const uint32_t hsh = (i * 2654435761u) ^ (i >> 13);
+      rgb[i] = ((64u + (hsh & 0x7Fu)) << 16) | ((64u + ((hsh >> 8) & 0x7Fu)) << 8) | (64u + ((hsh >> 16) & 0x7Fu));
+    }
+  }
+}
+
 }  // namespace spraygpu
 
 using namespace spraygpu;
@@ -1098,6 +1170,17 @@ extern "C" int spraygpu_compute_normals_static(const float* xyz, size_t nv, cons
   normals_light_kernel<<<grid_for(nv, T), T, 0, st>>>(xyz, idx, vlist, vstart, vcnt, normals, nv, heavy, ctr + 1);
   normals_heavy_kernel<<<std::min(sms * 4, npairs / (NRM_LIGHT_MAX + 1) + 1), 256, 0, st>>>(xyz, idx, vlist, vstart, vcnt, normals,
                                                                                           heavy, ctr + 1);
+  SG_CUDA(cudaGetLastError());
+  return SPRAYGPU_OK;
+}
+
+extern "C" int spraygpu_gen_soup(uint32_t key, size_t ntris, const float lo[3], const float hi[3], float h, float* xyz, uint32_t* idx,
+                                 uint32_t* rgb, void* cuda_stream) {
+  SG_CHECK(lo && hi && xyz && ntris >= 1 && ntris <= SPRAYGPU_MAX_PRIMS, SPRAYGPU_ERR_ARG, "gen_soup: bad argument (ntris=%zu)", ntris);
+  SoupArgs A;
+  A.key = key; A.n = (uint32_t)ntris; A.h = h;
+  for (int a = 0; a < 3; ++a) { A.lo[a] = lo[a]; A.hi[a] = hi[a]; }
+  soup_kernel<<<grid_for(ntris, 256), 256, 0, (cudaStream_t)cuda_stream>>>(A, xyz, idx, rgb);
   SG_CUDA(cudaGetLastError());
   return SPRAYGPU_OK;
 }

@@ -133,34 +133,27 @@ def soup_scene(grid=(4, 4, 4), tris_per_domain=1 << 14, cell=20.0, mtl=(MTL_DIFF
     return dict(domains=doms, lights=[(LIGHT_POINT, (0.0, 500.0, 1000.0), (1.0, 1.0, 1.0))])
 
 
+def soup_h(ntris, cell_lo, cell_hi):
+    """Mean triangle spacing of a soup cell: extent / ntris^(1/3), as the float both generators are handed."""
+    ext = np.asarray(cell_hi, np.float32) - np.asarray(cell_lo, np.float32)
+    return np.float32(float(ext.max()) / float(ntris) ** (1.0 / 3.0))
+
+
 def soup_domain_device(seed, ntris, cell_lo, cell_hi, device="cuda"):
-    """soup_domain's distribution generated ON THE GPU (torch's Philox generator keyed by 0x5EED0000 + seed): C3 / C4
-    build 64 x 2^20 ... 64 x 2^23 triangles per GPU in seconds and never touch the host ("generated on
-    device").  Returns CUDA tensors (verts f32[3n,3], faces i32[n,3] holding u32 values, rgb i32[3n]); the random STREAM
-    differs from the numpy generator's, the distribution does not.  Parity tests use the numpy form (the oracle needs
-    host arrays); this one feeds bench.py."""
+    """The soup domain of configs C3 / C4 generated ON THE GPU by the library's counter-based generator
+    (spraygpu_gen_soup: Philox-4x32-10, key 0x5EED0000 + seed, counter = primID — SURVEY 8d): 64 x 2^20 ... 64 x 2^23
+    triangles per GPU appear in milliseconds and never touch the host, and the CPU checker regenerates the SAME triangles
+    from the same function (bit-identical, tests/test_gpu_sizes.py), so the benched scene can be handed to it.
+    Returns CUDA tensors (verts f32[3n,3], faces i32[n,3] holding u32 values, rgb i32[3n])."""
     import torch
-    g = torch.Generator(device=device)
-    g.manual_seed(0x5EED0000 + int(seed))
-    lo = torch.tensor(cell_lo, dtype=torch.float32, device=device)
-    hi = torch.tensor(cell_hi, dtype=torch.float32, device=device)
-    ext = hi - lo
-    h = float(ext.max()) / float(ntris) ** (1.0 / 3.0)
-    c = lo + torch.rand((ntris, 3), generator=g, device=device) * ext
-
-    def edge():
-        d = torch.randn((ntris, 3), generator=g, device=device)
-        d = d / (d.norm(dim=1, keepdim=True) + 1e-20)
-        return d * (0.5 + 1.5 * torch.rand((ntris, 1), generator=g, device=device)) * h
-
-    e1, e2 = edge(), edge()
-    v = torch.stack([c, c + e1, c + e2], dim=1).reshape(-1, 3)
-    v = torch.minimum(torch.maximum(v, lo), hi).contiguous()
-    faces = torch.arange(3 * ntris, dtype=torch.int32, device=device).reshape(ntris, 3).contiguous()
-    idx = torch.arange(3 * ntris, dtype=torch.int64, device=device)
-    hsh = ((idx * 2654435761) & 0xFFFFFFFF) ^ (idx >> 13)
-    rgb = ((64 + (hsh & 0x7F)) << 16) | ((64 + ((hsh >> 8) & 0x7F)) << 8) | (64 + ((hsh >> 16) & 0x7F))
-    return v, faces, rgb.to(torch.int32).contiguous()
+    from . import capi
+    v = torch.empty((3 * ntris, 3), dtype=torch.float32, device=device)
+    faces = torch.empty((ntris, 3), dtype=torch.int32, device=device)
+    rgb = torch.empty(3 * ntris, dtype=torch.int32, device=device)
+    with torch.cuda.device(v.device):
+        capi.gen_soup(0x5EED0000 + int(seed), ntris, cell_lo, cell_hi, soup_h(ntris, cell_lo, cell_hi), v, faces, rgb,
+                      torch.cuda.current_stream().cuda_stream)
+    return v, faces, rgb
 
 
 def soup_scene_device(grid=(4, 4, 4), tris_per_domain=1 << 20, cell=20.0, mtl=(MTL_DIFFUSE, (1.0, 1.0, 1.0)), seed0=0,

@@ -314,3 +314,36 @@ def test_tri_test_conventions(oracle):
     o = np.array([0.6, 0.6, 2], np.float32)
     L.orc_tri_test(fp(o), fp(d), fp(v0), fp(v1), fp(v2), f32(1e-3), C.byref(hit), C.byref(t), C.byref(u), C.byref(v))
     assert hit.value == 0
+
+
+def test_philox4x32_10_known_answers(oracle):
+    """Philox-4x32-10 (Salmon et al., SC'11) as the soup generator of bench configs C3 / C4 uses it: the three known-answer
+    vectors published with Random123 (kat_vectors: counter / key all zero, all ones, digits of pi)."""
+    kat = [([0, 0, 0, 0], [0, 0], [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]),
+           ([0xffffffff] * 4, [0xffffffff] * 2, [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]),
+           ([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0], [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1])]
+    for ctr, key, want in kat:
+        assert [int(x) for x in oracle.philox4x32_10(ctr, key)] == want
+
+
+def test_soup_generator_properties(oracle):
+    """orc_gen_soup: deterministic, a function of (key, primID) only (a prefix of a larger soup with the same h is the
+    smaller soup), inside its cell, edge lengths in [0.5, 2] h before clipping, directions spread over the sphere."""
+    lo = np.array([20, 0, 40], np.float32); hi = lo + np.float32(20)
+    n = 1 << 14
+    h = oracle.soup_h(n, lo, hi)
+    v, f, c = oracle.gen_soup(0x5EED0003, n, lo, hi, h)
+    v2, _, _ = oracle.gen_soup(0x5EED0003, n, lo, hi, h)
+    assert np.array_equal(v, v2) and np.array_equal(f.reshape(-1), np.arange(3 * n, dtype=np.uint32))
+    vp, _, _ = oracle.gen_soup(0x5EED0003, n // 4, lo, hi, h)
+    assert np.array_equal(vp, v[:3 * (n // 4)])
+    vo, _, _ = oracle.gen_soup(0x5EED0004, n, lo, hi, h)
+    assert not np.array_equal(vo, v)
+    assert (v >= lo).all() and (v <= hi).all() and v.min(0).max() - lo.max() < 1 and (c >> 24 == 0).all()
+    t = v.reshape(n, 3, 3)
+    inner = ((t > lo + 2.5 * h) & (t < hi - 2.5 * h)).all(axis=(1, 2))              # triangles no clipping touched
+    e1 = t[inner, 1] - t[inner, 0]
+    ln = np.linalg.norm(e1, axis=1)
+    assert inner.sum() > n // 3 and ln.min() >= 0.4999 * h and ln.max() <= 2.0001 * h
+    d = e1 / ln[:, None]
+    assert np.abs(d.mean(0)).max() < 0.03 and np.abs((d * d).mean(0) - 1 / 3).max() < 0.02
